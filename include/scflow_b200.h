@@ -1,0 +1,136 @@
+/*
+ * scflow_b200 -- C ABI of the B200-native SCFlow refinement hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types.  Every entry point
+ * replaces the native work that one reference function reaches through PyTorch (cited as
+ * file:line relative to GiaKhangLuu/SCFlow).  The reference binds nothing natively itself (it
+ * is pure Python); the binding a maintainer adds is the ctypes stub shown in INTEGRATION.md.
+ *
+ * Conventions
+ *  - All tensor arguments are DEVICE pointers to contiguous fp32 data unless stated otherwise.
+ *  - Launchers are asynchronous: they only enqueue on `stream` (a cudaStream_t passed as
+ *    void*), never synchronise, never allocate or free device memory and keep no references.
+ *  - Return 0 on success, a negative SCFLOW_E_* otherwise (scflow_strerror() names it).
+ *    Unsupported configurations are rejected, never routed to another implementation.
+ *  - Re-entrant: no global mutable state besides one-time function-attribute setup.
+ */
+#ifndef SCFLOW_B200_H_
+#define SCFLOW_B200_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SCFLOW_ABI_VERSION 1
+
+enum {
+  SCFLOW_OK = 0,
+  SCFLOW_E_BAD_SHAPE = -1,      /* dimension not supported by the kernel                  */
+  SCFLOW_E_UNSUPPORTED = -2,    /* flag / mode the kernels do not implement               */
+  SCFLOW_E_MISALIGNED = -3,     /* pointer not 16-byte aligned                            */
+  SCFLOW_E_NULL = -4,           /* required pointer is NULL                               */
+  SCFLOW_E_LAUNCH = -5,         /* cudaGetLastError() after the launch was not success    */
+  SCFLOW_E_WORKSPACE = -6,      /* workspace too small                                    */
+  SCFLOW_E_DRIVER = -7,         /* driver entry point (cuTensorMapEncodeTiled) missing    */
+  SCFLOW_E_UNIMPLEMENTED = -8
+};
+
+/* correlation arithmetic */
+#define SCFLOW_PREC_FP32 0      /* CUDA-core fp32 FMA (exact-mode parity anchor)          */
+#define SCFLOW_PREC_TF32 1      /* tcgen05 kind::tf32, fp32 accumulate in TMEM (default)  */
+
+/* how `x * 2. / max(W-1, 1)` (models/utils/corr_lookup.py:64-65) is evaluated */
+#define SCFLOW_DIV_IEEE 0       /* true fp32 division: what ATen does on the CPU          */
+#define SCFLOW_DIV_RCP 1        /* x*2 * (1/(W-1)): ATen's CUDA div-by-scalar fast path   */
+
+int scflow_abi_version(void);
+const char* scflow_strerror(int rc);
+/* last cudaError_t seen by a failing launcher on this thread (0 if none) */
+int scflow_last_cuda_error(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * a1  CorrelationPyramid.forward   models/decoder/raft_decoder.py:35-58
+ *     replaces torch.matmul (:48-50), the /sqrt(C) pass (:51-52) and 3x nn.AvgPool2d (:54-56).
+ * feat1, feat2: (n, c, h, w).  levels[l]: (n*h*w, 1, h>>l, w>>l), l < num_levels (host array of
+ * device pointers).  corr[n*P+q][t] = sum_c feat1[n,c,q] feat2[n,c,t] / sqrt(c).
+ * TF32 path needs c % 32 == 0, h % 8 == 0, w % 32 == 0, (h*w) % 128 == 0, num_levels <= 4.
+ * ------------------------------------------------------------------------------------------- */
+size_t scflow_corr_pyramid_workspace_bytes(int n, int c, int h, int w, int precision);
+int scflow_corr_pyramid_fwd(const float* feat1, const float* feat2, float* const* levels,
+                            int num_levels, int n, int c, int h, int w, int precision,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a2  CorrLookup.forward           models/utils/corr_lookup.py:102-136 (+ bilinear_sample :31-67)
+ *     replaces 4x F.grid_sample and ~25 glue launches per iteration.
+ * levels as produced above; flow: (n, 2, h, w) in 1/8-resolution pixels;
+ * out: (n, num_levels*(2r+1)^2, h, w), channel = (2r+1)^2*l + (2r+1)*a + b, a = x offset.
+ * windows (optional, may be NULL): int16 (n*h*w, num_levels, 2, 2r+1) = floor of the
+ * un-normalised sample coordinate per x tap / per y tap -- the window selection, exported so
+ * tests can check it bit-exactly.  Only radius == 4, bilinear, zeros, align_corners=True.
+ * ------------------------------------------------------------------------------------------- */
+int scflow_corr_lookup_fwd(const float* const* levels, int num_levels, const float* flow,
+                           float* out, short* windows, int n, int h, int w, int radius,
+                           int div_mode, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a3  ConvGRU.forward (SeqConv)    models/decoder/raft_decoder.py:235-253
+ *     replaces 6 cuDNN convs + 6 activation kernels + 4 cat + 8 elementwise per iteration.
+ * Channels-last activations: h_in/h_out (n, hgt, wid, ch) , x (n, hgt, wid, cx); fp32.
+ * wpack: weights re-laid by scflow_convgru_pack_weights (device, size from _packed_floats).
+ * One call = one pass (pass 0: (1,5) taps along x, pass 1: (5,1) taps along y).
+ * ------------------------------------------------------------------------------------------- */
+size_t scflow_convgru_packed_floats(int ch, int cx);
+int scflow_convgru_pack_weights(const float* wz, const float* wr, const float* wq,
+                                const float* bz, const float* br, const float* bq,
+                                float* wpack, int ch, int cx, int pass, void* stream);
+int scflow_convgru_pass_fwd(const float* h_in, const float* x, const float* wpack, float* h_out,
+                            int n, int hgt, int wid, int ch, int cx, int pass, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a4  cal_3d_2d_corr / lift_2d_to_3d    models/utils/pose.py:26-64
+ *     replaces per crop: nonzero (host sync), 2x inverse, 2x mm, stack.
+ * depth (n,H,W); K,R0 (n,3,3); t0 (n,3) -> points3d (n,3,H,W) object-frame (0 on background),
+ * mask (n,H,W) uint8 (may be NULL).  Dense form of the ragged lists; no host sync.
+ * ------------------------------------------------------------------------------------------- */
+int scflow_lift_points(const float* depth, const float* K, const float* R0, const float* t0,
+                       float* points3d, unsigned char* mask, int n, int H, int W, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a6 + a5 + a7(i)  one launch per refinement iteration:
+ *   get_pose_from_delta_pose             models/utils/pose.py:124-169  (ortho6d, 'exp' depth)
+ *   get_flow_from_delta_pose_and_points  models/utils/pose.py:66-88
+ *   1/scale * F.interpolate(flow, 1/scale, bilinear, align_corners=True)
+ *                                        models/decoder/scflow_decoder.py:197-198
+ * dR6 (n,6), dt (n,3) may both be NULL: then (R_prev,t_prev) is used as the pose directly.
+ * Object points come from `points3d`+`mask` if points3d != NULL, else are recomputed from
+ * depth/K/R0/t0 (4 B/pixel instead of 13).  Outputs (each may be NULL to skip):
+ *   R_out (n,3,3), t_out (n,3), flow_full (n,2,H,W), flow_lr (n,2,H/scale,W/scale)
+ * flow_lr is the NEXT iteration's low-resolution flow, already multiplied by 1/scale.
+ * ------------------------------------------------------------------------------------------- */
+int scflow_pose_flow_fwd(const float* dR6, const float* dt, const float* R_prev,
+                         const float* t_prev, const float* K, const float* R0, const float* t0,
+                         const float* depth, const float* points3d, const unsigned char* mask,
+                         float* R_out, float* t_out, float* flow_full, float* flow_lr,
+                         int n, int H, int W, int scale, float invalid_num, float weight,
+                         void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a7(ii,iii)  scale * F.interpolate(x [+ y], scale, bilinear, align_corners=True)
+ *             models/decoder/scflow_decoder.py:223-228
+ * in, add (may be NULL): (n, c, h, w) -> out (n, c, h*scale, w*scale), out = mul * up(in + add)
+ * ------------------------------------------------------------------------------------------- */
+int scflow_upsample_fwd(const float* in, const float* add, float* out, int n, int c, int h,
+                        int w, int scale, float mul, void* stream);
+
+/* align_corners=True bilinear down-sampling by an integer factor, out = mul * down(in):
+ * the stand-alone form of a7(i) for callers that hold a full-resolution flow already. */
+int scflow_downsample_fwd(const float* in, float* out, int n, int c, int H, int W, int scale,
+                          float mul, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SCFLOW_B200_H_ */

@@ -1,0 +1,31 @@
+"""ConvGRU forward dispatch (a3, models/decoder/raft_decoder.py:235-253).
+
+`backend` is a build-stage switch, not a runtime fallback: "tcgen05" calls the fused sm_100a
+implicit-GEMM pass kernel and raises if it is unavailable; "cudnn" is the library baseline the
+kernel is measured against (what the reference itself runs on a GPU)."""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+BACKEND = "cudnn"
+
+
+def _cudnn_forward(mod, h, x):
+    for cz, cr, cq in zip(mod.conv_z, mod.conv_r, mod.conv_q):
+        hx = torch.cat([h, x], dim=1)
+        z = cz(hx)
+        r = cr(hx)
+        q = cq(torch.cat([r * h, x], dim=1))
+        h = (1 - z) * h + z * q
+    return h
+
+
+def conv_gru_forward(mod, h, x):
+    if BACKEND == "tcgen05":
+        from . import gru_tc
+        return gru_tc.forward(mod, h, x)
+    if not h.is_cuda:
+        from ._lib import ScflowError
+        raise ScflowError("ConvGRU: expected CUDA tensors (scflow_b200 has no CPU path)")
+    return _cudnn_forward(mod, h, x)

@@ -1,0 +1,167 @@
+"""mmflow-style module surface of the hot path (same names, constructor arguments, forward
+signatures and state_dict keys as the reference), backed by the sm_100a kernels.
+
+  CorrelationPyramid  models/decoder/raft_decoder.py:19-58
+  CorrLookup          models/utils/corr_lookup.py:71-136
+  ConvGRU             models/decoder/raft_decoder.py:168-253
+  MotionEncoder       models/decoder/raft_decoder.py:61-166   (cuDNN; ranked "next")
+  XHead               models/decoder/raft_decoder.py:256-294  (cuDNN; "next")
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops
+
+
+def _no_grad_only(*tensors):
+    if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors):
+        raise NotImplementedError(
+            "scflow_b200 kernels are forward-only in this round; wrap the call in torch.no_grad()")
+
+
+_ACT = {"ReLU": lambda: nn.ReLU(inplace=True), "Sigmoid": nn.Sigmoid, "Tanh": nn.Tanh}
+
+
+def _norm(cfg, ch):
+    cfg = dict(cfg)
+    t = cfg.pop("type")
+    cfg.pop("requires_grad", None)
+    if t == "GN":
+        return "gn", nn.GroupNorm(num_channels=ch, **cfg)
+    if t == "BN":
+        return "bn", nn.BatchNorm2d(ch, **cfg)
+    if t == "IN":
+        return "in", nn.InstanceNorm2d(ch, **cfg)
+    raise KeyError(f"norm type {t}")
+
+
+class ConvModule(nn.Module):
+    """conv -> [norm] -> [activation] with mmcv.cnn.ConvModule's attribute names (``conv``,
+    ``gn``/``bn``/``in``, ``activate``) so checkpoints load with strict=True."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0,
+                 conv_cfg=None, norm_cfg=None, act_cfg=dict(type="ReLU")):
+        super().__init__()
+        if conv_cfg is not None and conv_cfg.get("type", "Conv2d") not in ("Conv2d", "Conv"):
+            raise NotImplementedError(f"conv_cfg {conv_cfg}")
+        self.with_norm = norm_cfg is not None
+        self.with_activation = act_cfg is not None
+        self.conv = nn.Conv2d(in_channels, out_channels, kernel_size, stride=stride,
+                              padding=padding, bias=not self.with_norm)
+        self.norm_name = None
+        if self.with_norm:
+            self.norm_name, norm = _norm(norm_cfg, out_channels)
+            self.add_module(self.norm_name, norm)
+        if self.with_activation:
+            self.activate = _ACT[act_cfg["type"]]()
+
+    def forward(self, x):
+        x = self.conv(x)
+        if self.with_norm:
+            x = getattr(self, self.norm_name)(x)
+        if self.with_activation:
+            x = self.activate(x)
+        return x
+
+
+class CorrelationPyramid(nn.Module):
+    """All-pairs correlation + avg-pool pyramid in one tcgen05 kernel (a1)."""
+
+    def __init__(self, num_levels: int = 4, precision: str = "tf32") -> None:
+        super().__init__()
+        self.num_levels = num_levels
+        self.precision = {"fp32": ops.PREC_FP32, "tf32": ops.PREC_TF32}[precision]
+
+    def forward(self, feat1: torch.Tensor, feat2: torch.Tensor) -> Sequence[torch.Tensor]:
+        _no_grad_only(feat1, feat2)
+        return ops.corr_pyramid(feat1, feat2, self.num_levels, self.precision)
+
+
+class CorrLookup(nn.Module):
+    """Radius-r bilinear window lookup (a2).  Only the configuration every shipped config uses
+    is implemented (bilinear / zeros / align_corners=True / radius 4); others are rejected."""
+
+    def __init__(self, radius: int = 4, mode: str = "bilinear", padding_mode: str = "zeros",
+                 align_corners: bool = True, div_mode: str = "ieee") -> None:
+        super().__init__()
+        if mode != "bilinear" or padding_mode != "zeros" or not align_corners:
+            raise NotImplementedError(
+                f"CorrLookup(mode={mode}, padding_mode={padding_mode}, align_corners={align_corners})")
+        self.r = radius
+        self.mode, self.padding_mode, self.align_corners = mode, padding_mode, align_corners
+        self.div_mode = {"ieee": ops.DIV_IEEE, "rcp": ops.DIV_RCP}[div_mode]
+
+    def forward(self, corr_pyramid: Sequence[torch.Tensor], flow: torch.Tensor) -> torch.Tensor:
+        _no_grad_only(flow, *corr_pyramid)
+        return ops.corr_lookup(corr_pyramid, flow, self.r, self.div_mode)
+
+
+class ConvGRU(nn.Module):
+    """SeqConv GRU (a3).  Parameters keep the reference names conv_{z,r,q}.{0,1}.conv.*"""
+    _kernel = {"Conv": 3, "SeqConv": ((1, 5), (5, 1))}
+    _padding = {"Conv": 1, "SeqConv": ((0, 2), (2, 0))}
+
+    def __init__(self, h_channels: int, x_channels: int, net_type: str = "SeqConv") -> None:
+        super().__init__()
+        if net_type != "SeqConv":
+            raise NotImplementedError("gru_type='Conv' is not implemented (no config uses it)")
+        self.h_channels, self.x_channels = h_channels, x_channels
+        mk = lambda k, p, act: ConvModule(h_channels + x_channels, h_channels, k, padding=p,
+                                          act_cfg=dict(type=act))
+        ks, ps = self._kernel[net_type], self._padding[net_type]
+        self.conv_z = nn.ModuleList([mk(k, p, "Sigmoid") for k, p in zip(ks, ps)])
+        self.conv_r = nn.ModuleList([mk(k, p, "Sigmoid") for k, p in zip(ks, ps)])
+        self.conv_q = nn.ModuleList([mk(k, p, "Tanh") for k, p in zip(ks, ps)])
+
+    def init_weights(self) -> None:
+        for m in self.modules():
+            if isinstance(m, nn.Conv2d):
+                nn.init.orthogonal_(m.weight)
+
+    def forward(self, h: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+        from . import gru
+        return gru.conv_gru_forward(self, h, x)
+
+
+class MotionEncoder(nn.Module):
+    def __init__(self, num_levels: int = 4, radius: int = 4, net_type: str = "Basic",
+                 conv_cfg=None, norm_cfg=None, act_cfg=None) -> None:
+        super().__init__()
+        if net_type != "Basic":
+            raise NotImplementedError("net_type != 'Basic'")
+        kw = dict(conv_cfg=conv_cfg, norm_cfg=norm_cfg, act_cfg=act_cfg)
+        cin = num_levels * (2 * radius + 1) ** 2
+        self.corr_net = nn.Sequential(ConvModule(cin, 256, 1, padding=0, **kw),
+                                      ConvModule(256, 192, 3, padding=1, **kw))
+        self.flow_net = nn.Sequential(ConvModule(2, 128, 7, padding=3, **kw),
+                                      ConvModule(128, 64, 3, padding=1, **kw))
+        self.out_channels = [126]
+        self.out_net = nn.Sequential(ConvModule(192 + 64, 126, 3, padding=1, **kw))
+
+    def forward(self, corr: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
+        out = self.out_net(torch.cat([self.corr_net(corr), self.flow_net(flow)], dim=1))
+        return torch.cat([out, flow], dim=1)
+
+
+class XHead(nn.Module):
+    def __init__(self, in_channels: int, feat_channels: Sequence[int], x_channels: int, x: str) -> None:
+        super().__init__()
+        layers = []
+        for ch in feat_channels:
+            layers.append(ConvModule(in_channels, ch, 3, padding=1))
+            in_channels = ch
+        self.layers = nn.Sequential(*layers)
+        if x in ("flow", "tradeoff"):
+            self.predict_layer = nn.Conv2d(feat_channels[-1], x_channels, kernel_size=3, padding=1)
+        elif x == "mask":
+            self.predict_layer = nn.Conv2d(feat_channels[-1], x_channels, kernel_size=1, padding=0)
+        else:
+            raise ValueError(f"x must be 'flow' or 'mask', but got {x}")
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self.predict_layer(self.layers(x))

@@ -1,0 +1,137 @@
+"""Torch-tensor front ends of the C-ABI launchers (device pointers + current stream).
+
+Each function allocates its outputs with torch (the library never allocates), checks
+device/dtype/contiguity, and raises on any non-zero return code.  CPU tensors are rejected:
+there is no fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+
+PREC_FP32, PREC_TF32 = 0, 1
+DIV_IEEE, DIV_RCP = 0, 1
+
+
+def _chk(t: torch.Tensor, name: str, dtype=torch.float32) -> torch.Tensor:
+    if not t.is_cuda:
+        raise _lib.ScflowError(f"{name}: expected a CUDA tensor (scflow_b200 has no CPU path)")
+    if t.dtype != dtype:
+        raise _lib.ScflowError(f"{name}: expected {dtype}, got {t.dtype}")
+    return t.contiguous()
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def corr_pyramid(feat1: torch.Tensor, feat2: torch.Tensor, num_levels: int = 4,
+                 precision: int = PREC_TF32) -> List[torch.Tensor]:
+    """CorrelationPyramid.forward (raft_decoder.py:35-58): list of (N*H*W, 1, H>>l, W>>l)."""
+    lib = _lib.load()
+    f1, f2 = _chk(feat1, "feat1"), _chk(feat2, "feat2")
+    n, c, h, w = f1.shape
+    assert f2.shape == f1.shape
+    levels = [torch.empty((n * h * w, 1, h >> l, w >> l), device=f1.device, dtype=torch.float32)
+              for l in range(num_levels)]
+    arr = (ctypes.c_void_p * num_levels)(*[l.data_ptr() for l in levels])
+    rc = lib.scflow_corr_pyramid_fwd(_ptr(f1), _ptr(f2), arr, num_levels, n, c, h, w, precision,
+                                     None, 0, _stream())
+    _lib.check(rc, "scflow_corr_pyramid_fwd")
+    return levels
+
+
+def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int = 4,
+                div_mode: int = DIV_IEEE, return_windows: bool = False):
+    """CorrLookup.forward (corr_lookup.py:102-136): (N, L*(2r+1)^2, H, W)."""
+    lib = _lib.load()
+    fl = _chk(flow, "flow")
+    n, two, h, w = fl.shape
+    assert two == 2
+    lv = [_chk(p, f"pyramid[{i}]") for i, p in enumerate(pyramid)]
+    for l, p in enumerate(lv):
+        if p.shape != (n * h * w, 1, h >> l, w >> l):
+            raise _lib.ScflowError(f"pyramid[{l}] has shape {tuple(p.shape)}")
+    L = len(lv)
+    d = 2 * radius + 1
+    out = torch.empty((n, L * d * d, h, w), device=fl.device, dtype=torch.float32)
+    win = torch.empty((n * h * w, L, 2, d), device=fl.device, dtype=torch.int16) if return_windows else None
+    arr = (ctypes.c_void_p * L)(*[p.data_ptr() for p in lv])
+    rc = lib.scflow_corr_lookup_fwd(arr, L, _ptr(fl), _ptr(out), _ptr(win), n, h, w, radius, div_mode, _stream())
+    _lib.check(rc, "scflow_corr_lookup_fwd")
+    return (out, win) if return_windows else out
+
+
+def lift_points(depth, K, R0, t0):
+    """Dense cal_3d_2d_corr (pose.py:44-64): points3d (N,3,H,W), mask (N,H,W) uint8."""
+    lib = _lib.load()
+    depth, K, R0, t0 = _chk(depth, "depth"), _chk(K, "K"), _chk(R0, "R0"), _chk(t0, "t0")
+    n, H, W = depth.shape
+    pts = torch.empty((n, 3, H, W), device=depth.device, dtype=torch.float32)
+    mask = torch.empty((n, H, W), device=depth.device, dtype=torch.uint8)
+    rc = lib.scflow_lift_points(_ptr(depth), _ptr(K), _ptr(R0), _ptr(t0), _ptr(pts), _ptr(mask), n, H, W, _stream())
+    _lib.check(rc, "scflow_lift_points")
+    return pts, mask
+
+
+def pose_flow(R_prev, t_prev, K, *, dR6=None, dt=None, depth=None, R0=None, t0=None,
+              points3d=None, mask=None, H: int = 0, W: int = 0, scale: int = 8,
+              invalid_num: float = 0.0, weight: float = 10.0, want_full: bool = True,
+              want_lr: bool = True):
+    """Fused pose-compose + pose-induced flow + 1/scale down-sample (see scflow_pose_flow_fwd).
+    Returns (R, t, flow_full or None, flow_lr or None)."""
+    lib = _lib.load()
+    R_prev, t_prev, K = _chk(R_prev, "R_prev"), _chk(t_prev, "t_prev"), _chk(K, "K")
+    n = R_prev.shape[0]
+    dev = R_prev.device
+    if dR6 is not None:
+        dR6, dt = _chk(dR6, "dR6"), _chk(dt, "dt")
+    if points3d is not None:
+        points3d, mask = _chk(points3d, "points3d"), _chk(mask, "mask", torch.uint8)
+        H, W = points3d.shape[-2:]
+    else:
+        depth, R0, t0 = _chk(depth, "depth"), _chk(R0, "R0"), _chk(t0, "t0")
+        H, W = depth.shape[-2:]
+    R = torch.empty((n, 3, 3), device=dev, dtype=torch.float32)
+    t = torch.empty((n, 3), device=dev, dtype=torch.float32)
+    full = torch.empty((n, 2, H, W), device=dev, dtype=torch.float32) if want_full else None
+    lr = torch.empty((n, 2, H // scale, W // scale), device=dev, dtype=torch.float32) if want_lr else None
+    rc = lib.scflow_pose_flow_fwd(_ptr(dR6), _ptr(dt), _ptr(R_prev), _ptr(t_prev), _ptr(K), _ptr(R0),
+                                  _ptr(t0), _ptr(depth), _ptr(points3d), _ptr(mask), _ptr(R), _ptr(t),
+                                  _ptr(full), _ptr(lr), n, H, W, scale, float(invalid_num),
+                                  float(weight), _stream())
+    _lib.check(rc, "scflow_pose_flow_fwd")
+    return R, t, full, lr
+
+
+def upsample(x, add=None, scale: int = 8, mul: float = 1.0):
+    """mul * F.interpolate(x [+ add], scale_factor=scale, bilinear, align_corners=True)."""
+    lib = _lib.load()
+    x = _chk(x, "x")
+    if add is not None:
+        add = _chk(add, "add")
+        assert add.shape == x.shape
+    n, c, h, w = x.shape
+    out = torch.empty((n, c, h * scale, w * scale), device=x.device, dtype=torch.float32)
+    rc = lib.scflow_upsample_fwd(_ptr(x), _ptr(add), _ptr(out), n, c, h, w, scale, float(mul), _stream())
+    _lib.check(rc, "scflow_upsample_fwd")
+    return out
+
+
+def downsample(x, scale: int = 8, mul: float = 1.0):
+    """mul * F.interpolate(x, scale_factor=1/scale, bilinear, align_corners=True)."""
+    lib = _lib.load()
+    x = _chk(x, "x")
+    n, c, H, W = x.shape
+    out = torch.empty((n, c, H // scale, W // scale), device=x.device, dtype=torch.float32)
+    rc = lib.scflow_downsample_fwd(_ptr(x), _ptr(out), n, c, H, W, scale, float(mul), _stream())
+    _lib.check(rc, "scflow_downsample_fwd")
+    return out

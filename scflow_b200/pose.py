@@ -1,0 +1,62 @@
+"""Functional mirror of models/utils/pose.py for the hot path (same names and argument meaning).
+
+The reference keeps ragged per-crop point lists built with ``nonzero`` (a host sync per crop).
+Here ``cal_3d_2d_corr`` accepts a whole batch and returns a dense ``PointSet``; the two
+``*_list`` arguments of ``get_flow_from_delta_pose_and_points`` accept that PointSet."""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+
+from . import ops
+
+
+@dataclass
+class PointSet:
+    """Dense stand-in for (points_2d_list, points_3d_list): object-frame points (N,3,H,W), zero
+    on background, and the foreground mask (N,H,W) uint8.  points_2d is implicit (pixel grid)."""
+    points3d: torch.Tensor
+    mask: torch.Tensor
+
+    def __len__(self):
+        return self.points3d.shape[0]
+
+
+def cal_3d_2d_corr(depth, internel_k, rotation, translation, occlusion=None):
+    """pose.py:44-64.  depth (N,H,W) or (H,W); K (N,3,3); R (N,3,3); t (N,3)."""
+    if occlusion is not None:
+        raise NotImplementedError("occlusion mask is not used on the SCFlow path")
+    if depth.dim() == 2:
+        depth, internel_k = depth[None], internel_k[None]
+        rotation, translation = rotation[None], translation[None]
+    pts, mask = ops.lift_points(depth, internel_k, rotation, translation)
+    ps = PointSet(pts, mask)
+    return ps, ps
+
+
+def get_flow_from_delta_pose_and_points(rotation_dst, translation_dst, k, points_2d_list,
+                                        points_3d_list, height, width, invalid_num=400.):
+    """pose.py:66-88 -> (n, 2, height, width)."""
+    ps = points_3d_list
+    if not isinstance(ps, PointSet):
+        raise TypeError("pass the PointSet returned by scflow_b200.pose.cal_3d_2d_corr")
+    _, _, full, _ = ops.pose_flow(rotation_dst, translation_dst, k, points3d=ps.points3d,
+                                  mask=ps.mask, invalid_num=invalid_num, want_lr=False)
+    return full
+
+
+def get_pose_from_delta_pose(rotation_delta, translation_delta, rotation_src, translation_src,
+                             weight=10., depth_transform='exp', detach_depth_for_xy=False):
+    """pose.py:124-149 (ortho6d + 'exp' only).  K is not needed: only the 3x3 algebra runs."""
+    if rotation_delta.size(1) != 6:
+        raise NotImplementedError("quaternion deltas (kornia path) are not implemented")
+    if depth_transform != 'exp':
+        raise NotImplementedError("depth_transform != 'exp'")
+    n = rotation_src.shape[0]
+    eye = torch.eye(3, device=rotation_src.device).expand(n, 3, 3).contiguous()
+    R, t, _, _ = ops.pose_flow(rotation_src, translation_src, eye, dR6=rotation_delta,
+                               dt=translation_delta, depth=torch.zeros(n, 4, 4, device=eye.device),
+                               R0=eye, t0=translation_src, weight=weight, want_full=False,
+                               want_lr=False)
+    return R, t

@@ -1,0 +1,61 @@
+"""MultiClassPoseHead (models/head/pose_head.py:111-211) -- on the loop, stays PyTorch/cuDNN in
+this round.  Same parameter names/shapes; zero-initialised output layers."""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from .modules import ConvModule
+from .registry import register
+
+
+@register
+class MultiClassPoseHead(nn.Module):
+    _feat_size = {"Basic": (32, 32), "Large": (64, 64)}
+
+    def __init__(self, num_class: int, in_channels: int, net_type: str, norm_cfg: dict,
+                 act_cfg: dict, feat_size: tuple = None, rotation_mode: str = "quaternion",
+                 init_cfg=None):
+        super().__init__()
+        if rotation_mode != "ortho6d":
+            raise NotImplementedError("only rotation_mode='ortho6d' (what every config ships)")
+        assert net_type in ("Basic", "Large")
+        self.num_class = num_class
+        if feat_size is None:
+            feat_size = self._feat_size[net_type]
+        size = feat_size[0] * feat_size[1]
+        convs = []
+        for ch in (128, 128, 128):
+            convs.append(ConvModule(in_channels, ch, 3, stride=2, padding=1, norm_cfg=norm_cfg, act_cfg=act_cfg))
+            in_channels = ch
+            size = int(size / 4)
+        self.conv_layers = nn.Sequential(*convs)
+        fc_in = 128 * size
+        fcs = []
+        for ch in (1024, 256):
+            fcs.append(nn.Sequential(nn.Linear(fc_in, ch), nn.ReLU()))
+            fc_in = ch
+        self.flatten_op = nn.Flatten(1, -1)
+        self.fc_layers = nn.Sequential(*fcs)
+        self.rotation_mode = rotation_mode
+        self.rotation_out_channels = 6
+        self.rotation_pred = nn.Linear(fc_in, 6 * num_class)
+        self.translation_pred = nn.Linear(fc_in, 3 * num_class)
+        self.init_weights()
+
+    def init_weights(self):
+        nn.init.zeros_(self.translation_pred.weight)
+        nn.init.zeros_(self.translation_pred.bias)
+        nn.init.zeros_(self.rotation_pred.weight)
+        with torch.no_grad():
+            self.rotation_pred.bias.copy_(torch.tensor([1., 0., 0., 0., 1., 0.] * self.num_class))
+
+    def forward(self, x: torch.Tensor, label: torch.Tensor):
+        x = self.fc_layers(self.flatten_op(self.conv_layers(x)))
+        dt = self.translation_pred(x).view(-1, self.num_class, 3)
+        dr = self.rotation_pred(x).view(-1, self.num_class, self.rotation_out_channels)
+        # pose_head.py:209-210 -- index_select(dim=1, index=label)[:, 0, :]: every crop reads the
+        # class of label[0].  Reproduced as is (results must equal the reference's).
+        dt = torch.index_select(dt, dim=1, index=label)[:, 0, :]
+        dr = torch.index_select(dr, dim=1, index=label)[:, 0, :]
+        return dr, dt

@@ -1,0 +1,115 @@
+"""Inference-side host logic around the decoder: the feature extraction and `get_pose` of
+SCFlowRefiner (models/refiner/scflow_refiner.py:84-138) and batch-sharded multi-GPU refinement
+with one all-gather of the refined poses.  Renderer, data formatting, losses and
+the mmengine Runner are out of scope and stay in the reference."""
+from __future__ import annotations
+
+from typing import Dict, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from .decoder import SCFlowDecoder
+from .encoder import RAFTEncoder
+
+DECODER_CFG = dict(
+    net_type="Basic", num_levels=4, radius=4, iters=8,
+    detach_flow=True, detach_mask=True, detach_pose=True, detach_depth_for_xy=True,
+    mask_flow=False, mask_corr=False,
+    pose_head_cfg=dict(type="MultiClassPoseHead", num_class=21, in_channels=224, net_type="Basic",
+                       rotation_mode="ortho6d", norm_cfg=dict(type="GN", num_groups=32, requires_grad=True),
+                       act_cfg=dict(type="ReLU")),
+    corr_lookup_cfg=dict(align_corners=True), gru_type="SeqConv", act_cfg=dict(type="ReLU"))
+
+
+def decoder_cfg(feat_size=None, **over) -> dict:
+    import copy
+    cfg = copy.deepcopy(DECODER_CFG)
+    if feat_size is not None:
+        cfg["pose_head_cfg"]["feat_size"] = tuple(feat_size)
+    cfg.update(over)
+    return cfg
+
+
+class SCFlowRefinerCore(nn.Module):
+    """encoder (shared IN), context encoder (BN), decoder -- the part of SCFlowRefiner that
+    `get_pose` touches (scflow_ycbv_real.py:172-230)."""
+
+    def __init__(self, image_size: int = 256, h_channels: int = 128, cxt_channels: int = 128,
+                 decoder: Optional[dict] = None):
+        super().__init__()
+        self.encoder = RAFTEncoder(3, 256, net_type="Basic", norm_cfg=dict(type="IN"))
+        self.context = RAFTEncoder(3, 256, net_type="Basic", norm_cfg=dict(type="BN"))
+        hs = image_size // 8
+        self.decoder = SCFlowDecoder(**(decoder or decoder_cfg(feat_size=(hs, hs))))
+        self.h_channels, self.cxt_channels = h_channels, cxt_channels
+        assert self.h_channels == self.decoder.h_channels
+        assert self.cxt_channels == self.decoder.cxt_channels
+
+    def extract_feat(self, render_images, real_images):
+        real_feat = self.encoder(real_images)
+        render_feat = self.encoder(render_images)
+        cxt = self.context(render_images)
+        h_feat, cxt_feat = torch.split(cxt, [self.h_channels, self.cxt_channels], dim=1)
+        return render_feat, real_feat, torch.tanh(h_feat), torch.relu(cxt_feat)
+
+    @torch.no_grad()
+    def get_pose(self, render_images, real_images, ref_rotation, ref_translation, depth,
+                 internel_k, label, init_flow=None):
+        feat_render, feat_real, h_feat, cxt_feat = self.extract_feat(render_images, real_images)
+        if init_flow is None:
+            N, _, H, W = real_images.shape
+            init_flow = feat_render.new_zeros((N, 2, H, W), dtype=torch.float32)
+        return self.decoder(feat_render, feat_real, h_feat, cxt_feat, ref_rotation, ref_translation,
+                            depth, internel_k, init_flow=init_flow, label=label, invalid_flow_num=0.)
+
+    @torch.no_grad()
+    def refine(self, batch: Dict[str, torch.Tensor]) -> torch.Tensor:
+        """(N,12) packed [R row-major | t] after `decoder.iters` iterations."""
+        out = self.get_pose(batch["rendered_images"], batch["real_images"], batch["R0"], batch["t0"],
+                            batch["depth"], batch["K"], batch["labels"])
+        return pack_pose(out[2][-1], out[3][-1])
+
+
+def pack_pose(R: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
+    return torch.cat([R.reshape(-1, 9), t.reshape(-1, 3)], dim=1).contiguous()
+
+
+def unpack_pose(p: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    return p[:, :9].reshape(-1, 3, 3), p[:, 9:12]
+
+
+def shard_range(total: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous batch split: rank k takes crops [lo, hi); remainders go to the first ranks."""
+    base, rem = divmod(total, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def gather_poses(local: torch.Tensor, total: int) -> torch.Tensor:
+    """All-gather of the (n_local, 12) refined poses in rank order (= original crop order).
+    The only collective on the path: 48 B per crop, enqueued on the current stream.
+    Uneven shards are padded to the largest shard."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return local
+    world = dist.get_world_size()
+    sizes = [shard_range(total, r, world) for r in range(world)]
+    mx = max(hi - lo for lo, hi in sizes)
+    buf = local.new_zeros((mx, local.shape[1]))
+    buf[: local.shape[0]] = local
+    out = local.new_empty((world * mx, local.shape[1]))
+    dist.all_gather_into_tensor(out, buf)
+    return torch.cat([out[r * mx: r * mx + (hi - lo)] for r, (lo, hi) in enumerate(sizes)], dim=0)
+
+
+@torch.no_grad()
+def refine_sharded(core: SCFlowRefinerCore, batch: Dict[str, torch.Tensor], micro_batch: int = 64):
+    """Refine this rank's shard of `batch` (already sliced by the caller with shard_range) in
+    micro-batches and return this rank's (n_local, 12) poses."""
+    n = batch["depth"].shape[0]
+    outs = []
+    for lo in range(0, n, micro_batch):
+        mb = {k: v[lo: lo + micro_batch] for k, v in batch.items()}
+        outs.append(core.refine(mb))
+    return torch.cat(outs, dim=0) if outs else batch["depth"].new_zeros((0, 12))
