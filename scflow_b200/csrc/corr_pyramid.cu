@@ -3,7 +3,7 @@
 //
 // TF32 path (default): persistent warp-specialised tcgen05 GEMM.  Both operands are MN-major in
 // the reference's NCHW layout (the contraction dim C is the slow axis), so TMA loads fp32 boxes
-// straight from the feature maps into the UMMA MN-major SWIZZLE_128B layout -- no transpose or
+// straight from the feature maps into the UMMA MN-major SWIZZLE_128B_BASE32B layout -- no transpose or
 // cast pre-pass -- and tcgen05.mma kind::tf32 accumulates 128 queries x 256 targets in TMEM.  A
 // tile's 256 target columns are an 8-row x 32-column PATCH of the target plane, so the scale and
 // all four pyramid levels are produced thread-locally in the epilogue (each thread owns one
@@ -230,9 +230,12 @@ corr_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           const uint32_t b_addr = a_addr + A_BYTES;
 #pragma unroll
           for (int kk = 0; kk < BK / UK; ++kk) {
-            // MN-major SWIZZLE_128B atoms: 8 k-rows x 128 B = 1024 B; 32-element MN groups 4096 B apart
-            const uint64_t da = tc::make_smem_desc(a_addr + kk * 1024, 4096, 1024, tc::kLayoutSw128);
-            const uint64_t db = tc::make_smem_desc(b_addr + kk * 1024, 4096, 1024, tc::kLayoutSw128);
+            // MN-major 32-bit operands: SWIZZLE_128B_BASE32B is the only layout tcgen05 accepts.
+            // Atom = 4 k-rows x 128 B (SBO = 512 B between atoms along K); 32-element MN groups
+            // are 4096 B apart (LBO); one MMA (K = 8) spans two atoms = 1024 B.  Pinned on
+            // hardware with tools/umma_probe.cu.
+            const uint64_t da = tc::make_smem_desc(a_addr + kk * 1024, 4096, 512, tc::kLayoutSw128Base32);
+            const uint64_t db = tc::make_smem_desc(b_addr + kk * 1024, 4096, 512, tc::kLayoutSw128Base32);
             tc::mma_tf32_ss(d_tmem, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
           }
           tc::tc_commit(&empty[stage]);            // frees the smem slot when these MMAs retire
@@ -366,13 +369,13 @@ static int corr_tf32(const float* f1, const float* f2, float* const* levels, int
     const uint64_t dims[4] = {32, (uint64_t)c, (uint64_t)(P / 32), (uint64_t)n};
     const uint64_t strides[3] = {(uint64_t)P * 4, 128, (uint64_t)c * P * 4};
     const uint32_t box[4] = {32, BK, BM / 32, 1};
-    if (!tc::encode_f32_map(&mapA, f1, 4, dims, strides, box, true)) return SCFLOW_E_DRIVER;
+    if (!tc::encode_f32_map(&mapA, f1, 4, dims, strides, box, tc::kTmaSw128Atom32)) return SCFLOW_E_DRIVER;
   }
   {
     const uint64_t dims[4] = {(uint64_t)w, (uint64_t)c, (uint64_t)h, (uint64_t)n};
     const uint64_t strides[3] = {(uint64_t)P * 4, (uint64_t)w * 4, (uint64_t)c * P * 4};
     const uint32_t box[4] = {32, BK, 8, 1};
-    if (!tc::encode_f32_map(&mapB, f2, 4, dims, strides, box, true)) return SCFLOW_E_DRIVER;
+    if (!tc::encode_f32_map(&mapB, f2, 4, dims, strides, box, tc::kTmaSw128Atom32)) return SCFLOW_E_DRIVER;
   }
   Params p;
   for (int l = 0; l < 4; ++l) p.lvl[l] = l < num_levels ? levels[l] : nullptr;

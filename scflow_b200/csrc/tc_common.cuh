@@ -147,6 +147,7 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
 }
 constexpr uint32_t kLayoutSw128 = 2;
 constexpr uint32_t kLayoutNone = 0;
+constexpr uint32_t kLayoutSw128Base32 = 1;   // SWIZZLE_128B_BASE32B: 32-byte chunks XOR (row & 3)
 
 // Instruction descriptor for kind::tf32, fp32 accumulate (cute::UMMA::InstrDescriptor):
 //  [4,6) c_format=1 (F32)  [7,10) a_format=2 (TF32)  [10,13) b_format=2  [15] a_major  [16] b_major
@@ -177,9 +178,13 @@ inline EncodeTiledFn get_encode_tiled() {
   return fn;
 }
 
+// TMA swizzle modes (match the UMMA layout types: kLayoutSw128 <-> kTmaSw128, kLayoutSw128Base32 <->
+// kTmaSw128Atom32; the latter is the only layout tcgen05 accepts for MN-major 32-bit operands).
+constexpr int kTmaNone = 0, kTmaSw128 = 1, kTmaSw128Atom32 = 2;
+
 // fp32 tensor map of rank `rank`; dims/box innermost first; strides in BYTES for dims 1..rank-1.
 inline bool encode_f32_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
-                           const uint64_t* strides_bytes, const uint32_t* box, bool swizzle128) {
+                           const uint64_t* strides_bytes, const uint32_t* box, int swizzle) {
   EncodeTiledFn fn = get_encode_tiled();
   if (!fn) return false;
   cuuint64_t gdim[5], gstr[4];
@@ -192,7 +197,9 @@ inline bool encode_f32_map(CUtensorMap* map, const void* base, int rank, const u
   for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(base),
                   gdim, gstr, bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                  swizzle == kTmaSw128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                  : swizzle == kTmaSw128Atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                                               : CU_TENSOR_MAP_SWIZZLE_NONE,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;
 }

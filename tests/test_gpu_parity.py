@@ -1,0 +1,259 @@
+"""GPU tier: every CUDA kernel, called through the C ABI, against the CPU oracle on the same
+seeded inputs, against the committed golden fixtures (outputs of the unmodified reference), and
+-- at full BASELINE sizes -- through size-independent properties."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import scflow_oracle as O
+from oracle.gen_golden import lookup_flow
+from scflow_b200 import ops, synthetic as syn
+import scflow_b200 as sb
+from scflow_b200.refiner import SCFlowRefinerCore, decoder_cfg
+
+DEV = "cuda"
+
+
+def rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+@pytest.fixture(autouse=True, scope="module")
+def _strict_fp32():
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+# ------------------------------------------------------------------ a1 correlation pyramid
+@pytest.mark.parametrize("prec,tol", [(ops.PREC_FP32, 2e-6), (ops.PREC_TF32, 1e-3)])
+@pytest.mark.parametrize("n,c,h,w", [(2, 64, 8, 32), (1, 256, 32, 32), (1, 32, 16, 64)])
+def test_corr_pyramid_vs_oracle(prec, tol, n, c, h, w):
+    ft = syn.make_features(n, h, w, seed=3, c=c, hc=4)
+    want = O.correlation_pyramid(ft["feat_render"], ft["feat_real"], 4)
+    got = ops.corr_pyramid(ft["feat_render"].to(DEV), ft["feat_real"].to(DEV), 4, prec)
+    torch.cuda.synchronize()
+    for l in range(4):
+        assert got[l].shape == want[l].shape
+        # tolerance relative to the level-0 scale: pooled levels average noise away
+        err = float((got[l].cpu().double() - want[l].double()).abs().max() / want[0].abs().max())
+        assert err < tol, (l, err)
+
+
+def test_corr_pyramid_tf32_vs_tf32_rounded_oracle():
+    """Tight check of the tcgen05 path: with inputs pre-rounded to TF32 the only difference left
+    is fp32 accumulation order."""
+    ft = syn.make_features(1, 32, 32, seed=5, c=256, hc=4)
+    rnd = lambda t: (t.view(torch.int32) & ~0x1FFF).view(torch.float32)
+    f1, f2 = rnd(ft["feat_render"].clone()), rnd(ft["feat_real"].clone())
+    want = O.correlation_pyramid(f1, f2, 4)
+    got = ops.corr_pyramid(f1.to(DEV), f2.to(DEV), 4, ops.PREC_TF32)
+    for l in range(4):
+        assert rel(got[l], want[l]) < 2e-5, l
+
+
+def test_corr_pyramid_properties_full_size():
+    """cfg2 size (N=64, 256 ch, 32x32): level l+1 is the exact 2x2 mean of level l, and the
+    fp32 and tf32 kernels agree to TF32 precision."""
+    g = torch.Generator(device=DEV).manual_seed(0)
+    f1 = torch.randn(64, 256, 32, 32, device=DEV, generator=g)
+    f2 = torch.randn(64, 256, 32, 32, device=DEV, generator=g)
+    tf = ops.corr_pyramid(f1, f2, 4, ops.PREC_TF32)
+    for l in range(3):
+        pooled = torch.nn.functional.avg_pool2d(tf[l], 2, 2)
+        assert float((pooled - tf[l + 1]).abs().max()) < 1e-5
+    fp = ops.corr_pyramid(f1[:8], f2[:8], 4, ops.PREC_FP32)
+    assert rel(tf[0][: 8 * 1024], fp[0]) < 1e-3
+    ref = torch.matmul(f1[63].reshape(256, -1).t().double(), f2[63].reshape(256, -1).double()) / 16.0
+    assert rel(tf[0][63 * 1024:].reshape(1024, 1024), ref) < 1e-3
+
+
+# ------------------------------------------------------------------ a2 lookup
+@pytest.mark.parametrize("div_mode", [ops.DIV_IEEE, ops.DIV_RCP])
+@pytest.mark.parametrize("n,h,w", [(2, 8, 16), (1, 32, 32), (1, 16, 64)])
+def test_lookup_vs_oracle_bit_exact_windows(div_mode, n, h, w):
+    ft = syn.make_features(n, h, w, seed=11, c=16, hc=4)
+    pyr = O.correlation_pyramid(ft["feat_render"], ft["feat_real"], 4)
+    flow = lookup_flow(n, h, w, 12)
+    want, wwin = O.corr_lookup(pyr, flow, 4, div_mode, return_windows=True)
+    got, gwin = ops.corr_lookup([p.to(DEV) for p in pyr], flow.to(DEV), 4, div_mode, return_windows=True)
+    # window selection: integer corner indices, bit-exact (kernel clamps far-outside windows to
+    # [-32, size+32], where every tap is zero padding anyway)
+    for l in range(4):
+        for ax, size in ((0, w >> l), (1, h >> l)):
+            a = wwin[:, l, ax].clamp(-32, size + 32).to(torch.int16)
+            assert torch.equal(gwin[:, l, ax].cpu(), a), (l, ax)
+    assert rel(got, want) < 2e-6
+
+
+def test_lookup_golden_fixture(golden_dir):
+    g = np.load(os.path.join(golden_dir, "lookup_small.npz"))
+    pyr = [torch.from_numpy(g[f"pyr{i}"]).to(DEV) for i in range(4)]
+    got = ops.corr_lookup(pyr, torch.from_numpy(g["flow"]).to(DEV), 4, ops.DIV_IEEE)
+    assert rel(got, torch.from_numpy(g["out"])) < 2e-6
+
+
+def test_lookup_impulse_and_zero_flow():
+    h = w = 32
+    qy, qx = 5, 6
+    lvl0 = torch.zeros(h * w, 1, h, w, device=DEV)
+    lvl0[qy * w + qx, 0, qy + 1, qx + 3] = 1.0
+    pyr = [lvl0] + [torch.zeros(h * w, 1, h >> i, w >> i, device=DEV) for i in (1, 2, 3)]
+    out = ops.corr_lookup(pyr, torch.zeros(1, 2, h, w, device=DEV), 4)
+    ch = out[0, :81, qy, qx]
+    assert int(ch.argmax()) == 68 and abs(float(ch[68]) - 1.0) < 1e-6     # 9*a + b, a = x offset
+    # zero flow: centre tap (a=b=4 -> channel 40) returns corr[q][q] up to the round-trip noise
+    lvl = torch.randn(h * w, 1, h, w, device=DEV)
+    pyr = [lvl] + pyr[1:]
+    out = ops.corr_lookup(pyr, torch.zeros(1, 2, h, w, device=DEV), 4)
+    diag = lvl.reshape(h * w, h * w).diagonal().reshape(h, w)
+    assert float((out[0, 40] - diag).abs().max()) < 1e-4
+
+
+# ------------------------------------------------------------------ a4-a7 pose / flow / resize
+def _cuda(d):
+    return {k: v.to(DEV) for k, v in d.items()}
+
+
+def test_lift_and_pose_flow_vs_oracle_and_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "pose_small.npz"))
+    cr = syn.make_crops(3, 32, seed=31)
+    c = _cuda(cr)
+    pts, mask = ops.lift_points(c["depth"], c["K"], c["R0"], c["t0"])
+    wpts, wmask = O.lift_points_dense(cr["depth"], cr["K"], cr["R0"], cr["t0"])
+    assert torch.equal(mask.cpu().bool(), wmask)
+    assert rel(pts, wpts) < 1e-5 and rel(pts, torch.from_numpy(g["points3d"])) < 1e-5
+    dR6, dt = torch.from_numpy(g["dR6"]), torch.from_numpy(g["dt"])
+    wR, wt = O.pose_compose(dR6, dt, cr["R0"], cr["t0"])
+    for inv, key in ((0.0, "flow"), (400.0, "flow400")):
+        R, t, full, lr = ops.pose_flow(c["R0"], c["t0"], c["K"], dR6=dR6.to(DEV), dt=dt.to(DEV),
+                                       depth=c["depth"], R0=c["R0"], t0=c["t0"], scale=8, invalid_num=inv)
+        assert float((R.cpu() - torch.from_numpy(g["R"])).abs().max()) < 1e-6
+        assert rel(t, torch.from_numpy(g["t"])) < 1e-6
+        assert rel(R, wR) < 1e-6 and rel(t, wt) < 1e-6
+        wfull = O.pose_flow_dense(wR, wt, cr["K"], wpts, wmask, inv)
+        assert rel(full, wfull) < 1e-3                       # north_star: flow within 1e-3 relative
+        assert rel(full, torch.from_numpy(g[key])) < 1e-3
+        wlr = (1.0 / 8) * O.resize_bilinear_ac(wfull, 4, 4)
+        assert rel(lr, wlr) < 1e-3
+    # the stored-points variant (drop-in for get_flow_from_delta_pose_and_points) agrees
+    ps, _ = sb.cal_3d_2d_corr(c["depth"], c["K"], c["R0"], c["t0"])
+    f2 = sb.get_flow_from_delta_pose_and_points(R, t, c["K"], ps, ps, 32, 32, invalid_num=400.)
+    assert rel(f2, full) < 1e-5
+    R3, t3 = sb.get_pose_from_delta_pose(dR6.to(DEV), dt.to(DEV), c["R0"], c["t0"], detach_depth_for_xy=True)
+    assert torch.equal(R3, R) and torch.equal(t3, t)
+
+
+def test_identity_delta_pose_keeps_pose_and_zero_flow():
+    """KAT from the zero-initialised pose head (pose_head.py:187-198): dR6 = [1,0,0,0,1,0], dt = 0
+    => R_k = R_0, t_k = t_0 and the pose-induced flow vanishes on the foreground."""
+    cr = _cuda(syn.make_crops(4, 256, seed=5))
+    dR6 = torch.tensor([1., 0, 0, 0, 1., 0], device=DEV).repeat(4, 1)
+    dt = torch.zeros(4, 3, device=DEV)
+    R, t, full, lr = ops.pose_flow(cr["R0"], cr["t0"], cr["K"], dR6=dR6, dt=dt, depth=cr["depth"],
+                                   R0=cr["R0"], t0=cr["t0"])
+    assert float((R - cr["R0"]).abs().max()) < 1e-6 and float((t - cr["t0"]).abs().max()) < 1e-4
+    assert float(full.abs().max()) < 2e-2      # fp32 cancellation of ~1e3 mm coordinates
+    assert float(lr.abs().max()) < 1e-2
+
+
+def test_resize_vs_oracle():
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(2, 2, 8, 8, generator=g)
+    y = torch.randn(2, 2, 8, 8, generator=g)
+    up = ops.upsample(x.to(DEV), y.to(DEV), 8, 8.0)
+    assert rel(up, 8.0 * O.resize_bilinear_ac(x + y, 64, 64)) < 1e-6
+    big = torch.randn(2, 2, 64, 64, generator=g)
+    dn = ops.downsample(big.to(DEV), 8, 0.125)
+    assert rel(dn, 0.125 * O.resize_bilinear_ac(big, 8, 8)) < 1e-6
+
+
+# ------------------------------------------------------------------ a8 whole decoder / refiner
+def _build_decoder(s, seed, golden_dir, **over):
+    hh = s // 8
+    dec = sb.SCFlowDecoder(**decoder_cfg(feat_size=(hh, hh), **over)).eval()
+    shp = {k: tuple(v.shape) for k, v in dec.state_dict().items()}
+    sd = syn.fill_state_dict(shp, seed=seed)
+    dec.load_state_dict(sd, strict=True)
+    return dec.to(DEV), sd
+
+
+@pytest.mark.parametrize("tag,n,s,seed", [("s64", 2, 64, 41), ("cfg1", 1, 256, 51)])
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_decoder_vs_oracle_and_golden(golden_dir, tag, n, s, seed, prec):
+    if prec == "tf32" and s == 64:
+        pytest.skip("tcgen05 correlation needs w % 32 == 0")
+    dec, sd = _build_decoder(s, seed, golden_dir, corr_precision=prec)
+    cr = syn.make_crops(n, s, seed=seed + 1)
+    ft = syn.make_features(n, s // 8, s // 8, seed=seed + 2)
+    c, f = _cuda(cr), _cuda(ft)
+    with torch.no_grad():
+        out = dec(f["feat_render"], f["feat_real"], f["h_feat"], f["cxt_feat"], c["R0"], c["t0"],
+                  c["depth"], c["K"], c["labels"], torch.zeros(n, 2, s, s, device=DEV), 0.)
+    assert len(out) == 7 and all(len(o) == 8 for o in out)
+    g = np.load(os.path.join(golden_dir, f"decoder_{tag}.npz"))
+    Rg, tg = torch.from_numpy(g["rotations"]), torch.from_numpy(g["translations"])
+    assert float(O.rotation_geodesic(Rg[-1], cr["R0"]).max()) > 1e-2       # the pose really moved
+    R8, t8 = out[2][-1].cpu(), out[3][-1].cpu()
+    # north_star: final 6D pose within 1e-4 rad / 1e-4 m (= 0.1 mm) after 8 iterations
+    assert float(O.rotation_geodesic(R8, Rg[-1]).max()) < 1e-4
+    assert float((t8 - tg[-1]).abs().max()) < 0.1
+    names = ["flow_from_pose", "flow_from_pred", None, None, "masks"]
+    for i in (0, 1, 4):
+        st = torch.stack(out[i])[[0, -1]][..., ::4, ::4].cpu()
+        assert rel(st, torch.from_numpy(g[names[i]])) < 1e-3, names[i]
+
+
+def test_zero_init_pose_head_is_identity(golden_dir):
+    """As shipped the pose head outputs the identity delta: every iteration returns (R0, t0)."""
+    dec = sb.SCFlowDecoder(**decoder_cfg()).eval().to(DEV)
+    cr = _cuda(syn.make_crops(2, 256, seed=9))
+    ft = _cuda(syn.make_features(2, 32, 32, seed=10))
+    with torch.no_grad():
+        out = dec(ft["feat_render"], ft["feat_real"], ft["h_feat"], ft["cxt_feat"], cr["R0"], cr["t0"],
+                  cr["depth"], cr["K"], cr["labels"], torch.zeros(2, 2, 256, 256, device=DEV), 0.)
+    for R, t in zip(out[2], out[3]):
+        assert float((R - cr["R0"]).abs().max()) < 1e-5
+        assert float((t - cr["t0"]).abs().max()) < 1e-3
+
+
+def test_refiner_cfg1_vs_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "refiner_cfg1.npz"))
+    es = json.load(open(os.path.join(golden_dir, "encoder_state_shapes.json")))
+    core = SCFlowRefinerCore(256).eval()
+    core.encoder.load_state_dict(syn.fill_state_dict(es["IN"], seed=61, gain=1.7))
+    core.context.load_state_dict(syn.fill_state_dict(es["BN"], seed=62, gain=1.7))
+    shp = {k: tuple(v.shape) for k, v in core.decoder.state_dict().items()}
+    core.decoder.load_state_dict(syn.fill_state_dict(shp, seed=64))
+    core.to(DEV)
+    cr = _cuda(syn.make_crops(1, 256, seed=63))
+    out = core.get_pose(cr["rendered_images"], cr["real_images"], cr["R0"], cr["t0"], cr["depth"],
+                        cr["K"], cr["labels"])
+    Rg, tg = torch.from_numpy(g["rotations"]), torch.from_numpy(g["translations"])
+    assert float(O.rotation_geodesic(out[2][-1].cpu(), Rg[-1]).max()) < 1e-4
+    assert float((out[3][-1].cpu() - tg[-1]).abs().max()) < 0.1
+
+
+def test_batch64_matches_per_crop_runs():
+    """Crops are independent: refining 64 crops at once equals refining them 8 at a time."""
+    dec, _ = _build_decoder(256, 77, None)
+    cr = _cuda(syn.make_crops(16, 256, seed=78))
+    ft = _cuda(syn.make_features(16, 32, 32, seed=79))
+    cr["labels"][:] = cr["labels"][0]     # pose_head.py:209 reads label[0] for the whole batch
+    def run(sl):
+        with torch.no_grad():
+            o = dec(ft["feat_render"][sl], ft["feat_real"][sl], ft["h_feat"][sl], ft["cxt_feat"][sl],
+                    cr["R0"][sl], cr["t0"][sl], cr["depth"][sl], cr["K"][sl], cr["labels"][sl],
+                    torch.zeros(cr["R0"][sl].shape[0], 2, 256, 256, device=DEV), 0.)
+        return o[2][-1], o[3][-1]
+    Ra, ta = run(slice(0, 16))
+    Rb = torch.cat([run(slice(i, i + 8))[0] for i in (0, 8)])
+    assert float(O.rotation_geodesic(Ra.cpu(), Rb.cpu()).max()) < 1e-4
