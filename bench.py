@@ -1,0 +1,294 @@
+#!/usr/bin/env python
+"""bench.py -- object-crops/sec of the SCFlow refiner forward (3 encoder passes + 8-iteration
+decoder) on synthetic YCB-V-shaped 256x256 crops.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
+
+One "step" = one refinement of a batch of B=64 crops per GPU (BASELINE.json configs[1]; with
+N GPUs every rank refines its own 64 crops and the (B,12) poses are all-gathered: weak scaling,
+N=8 is configs[2]'s 512 crops).  Rank 0 prints ONE JSON line (contract in the task statement).
+`--impl reference` times the CPU oracle port of the reference path on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch
+import torch.distributed as dist
+
+METRIC = "object-crops/sec (8-iter refine)"
+UNIT = "crops/s"
+WORKLOAD = "SCFlow refiner inference, batch 64 YCB-V-shaped 256x256 crops per GPU, 8 iters"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=float(d["hbm_gbs"]), bf16=float(d["bf16_tflops"]),
+                    bf16_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), src="measured")
+    return dict(hbm=6650.0, bf16=1590.0, bf16_sustained=1400.0, src="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_ev = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_ev.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            self._stop_ev.wait(0.2)
+
+    def stop(self):
+        self._stop_ev.set()
+        self.join(timeout=6)
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i] == "Active"})
+        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=reasons, samples=len(self.rows))
+
+
+def make_batch(n, seed):
+    from scflow_b200 import synthetic as syn
+    cr = syn.make_crops(n, 256, seed=seed)
+    cr["labels"][:] = cr["labels"][0]
+    return {k: cr[k] for k in ("rendered_images", "real_images", "depth", "K", "R0", "t0", "labels")}
+
+
+def tile_batch(small, n):
+    """Cheaply build an n-crop batch by tiling a few distinct synthetic crops with a per-crop
+    perturbation of the images, so every crop is a distinct input without minutes of host
+    ray-casting."""
+    k = small["depth"].shape[0]
+    rep = (n + k - 1) // k
+    out = {}
+    for key, v in small.items():
+        out[key] = v.repeat((rep,) + (1,) * (v.dim() - 1))[:n].clone()
+    g = torch.Generator().manual_seed(1)
+    out["real_images"] = (out["real_images"] + 0.01 * torch.randn(out["real_images"].shape, generator=g)).clamp_(0, 1)
+    return out
+
+
+def seeded_weights(core):
+    from scflow_b200 import synthetic as syn
+    for mod, seed, gain in ((core.encoder, 61, 1.7), (core.context, 62, 1.7), (core.decoder, 64, 1.0)):
+        shp = {k: tuple(v.shape) for k, v in mod.state_dict().items()}
+        mod.load_state_dict(syn.fill_state_dict(shp, seed=seed, gain=gain))
+    return core
+
+
+# --------------------------------------------------------------------------- CPU / reference arm
+def cpu_refiner_state():
+    from scflow_b200 import synthetic as syn
+    gd = os.path.join(ROOT, "tests", "golden")
+    es = json.load(open(os.path.join(gd, "encoder_state_shapes.json")))
+    ds = {k: tuple(v) for k, v in json.load(open(os.path.join(gd, "decoder_state_shapes.json"))).items()}
+    return (syn.fill_state_dict(es["IN"], seed=61, gain=1.7), syn.fill_state_dict(es["BN"], seed=62, gain=1.7),
+            syn.fill_state_dict(ds, seed=64))
+
+
+def cpu_run(batch, state, reps, warm):
+    """Reference path on the host cores (oracle port of the reference's PyTorch CPU code)."""
+    from oracle import scflow_oracle as O
+    se, sc, sd = state
+    n = batch["depth"].shape[0]
+    def once():
+        with torch.no_grad():
+            O.refiner_forward(se, sc, sd, batch["rendered_images"], batch["real_images"], batch["R0"], batch["t0"],
+                              batch["depth"], batch["K"], batch["labels"])
+    for _ in range(warm):
+        once()
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        once()
+        ts.append(time.perf_counter() - t0)
+    return n, ts
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sample_n = 8
+    batch = tile_batch(make_batch(2, 1234), sample_n)
+    n, ts = cpu_run(batch, cpu_refiner_state(), max(1, args.steps), max(1, min(args.warmup, 2)))
+    ms = 1e3 * sum(ts) / len(ts)
+    val = n / (ms / 1e3)
+    sample = f"{n} of the 64 crops of one step per timed step (same refiner, weights and input generator)"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": len(ts), "warmup": max(1, min(args.warmup, 2)), "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": sample, "threads": torch.get_num_threads()},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# --------------------------------------------------------------------------- our arm
+def algorithmic_bytes(name, B, S=256, C=256):
+    """Per-launch algorithmic HBM bytes (DESIGN.md 'Kernels')."""
+    P = (S // 8) ** 2
+    if name == "scflow_corr_pyramid_fwd":
+        return B * (2 * P * C * 4 + (85 * P * P * 4) // 64)
+    if name == "scflow_corr_lookup_fwd":
+        return B * (P * 324 * 4 + P * 4 * 100 * 4 + 8 * P)
+    if name == "scflow_pose_flow_fwd":
+        return B * (4 * S * S + 8 * S * S + 8 * P)      # depth in, full-res flow + 1/8 flow out
+    if name == "scflow_upsample_fwd":
+        return None                                     # two shapes share the launcher; reported in ms only
+    return None
+
+
+def ours(args):
+    from scflow_b200 import ops
+    from scflow_b200.refiner import SCFlowRefinerCore, gather_poses
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B = args.batch
+    torch.backends.cudnn.allow_tf32 = True      # cuDNN parts at the reference's own GPU default
+    torch.backends.cudnn.benchmark = True
+    core = seeded_weights(SCFlowRefinerCore(256)).eval().to(dev)
+    if os.environ.get("SCFLOW_CHANNELS_LAST", "0") == "1":
+        core = core.to(memory_format=torch.channels_last)
+    # two distinct input sets, alternated, so no step re-reads the previous step's inputs from L2;
+    # a step's working set (118 MB inputs, 340 MB pyramid, activations) is several times the L2
+    host = [tile_batch(make_batch(4, 1234 + 10 * rank + s), B) for s in range(2)]
+    pinned = [{k: v.pin_memory() for k, v in h.items()} for h in host]
+    resident = [{k: v.to(dev) for k, v in h.items()} for h in host]
+    h2d = sum(v.numel() * v.element_size() for v in host[0].values())
+    d2h = B * 12 * 4
+
+    def step_resident(i):
+        return gather_poses(core.refine(resident[i % 2]), B * world)
+
+    def step_e2e(i):
+        b = {k: v.to(dev, non_blocking=True) for k, v in pinned[i % 2].items()}
+        poses = gather_poses(core.refine(b), B * world)
+        return poses.cpu()                                    # D2H read of the step's result
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, timing_events):
+        ops.STATS.reset(timing=timing_events)
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(steps):
+            fn(i)
+        b.record()
+        barrier()
+        ms = torch.tensor([a.elapsed_time(b)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    W = max(args.warmup, 3)
+    for i in range(W):
+        step_resident(i)
+    for i in range(2):
+        step_e2e(i)
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    if os.environ.get("SCFLOW_PROFILE") == "1":      # ncu --profile-from-start off
+        torch.cuda.profiler.start()
+    ms_total = timed(step_resident, args.steps, True)
+    if os.environ.get("SCFLOW_PROFILE") == "1":
+        torch.cuda.profiler.stop()
+    launches = ops.STATS.count
+    per_kernel = ops.STATS.summary()
+    ms_e2e = timed(step_e2e, args.steps, False)
+    clocks = sampler.stop() if sampler else None
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    ms_step = ms_total / args.steps
+    value = B * world / (ms_step / 1e3)
+    e2e_val = B * world / (ms_e2e / args.steps / 1e3)
+    pk = peaks()
+    kern = {}
+    for name, (calls, tot) in per_kernel.items():
+        ab = algorithmic_bytes(name, B)
+        avg_ms = tot / calls
+        kern[name] = {"calls_per_step": calls / args.steps, "avg_ms": avg_ms, "share_of_step": tot / ms_total,
+                      "gbs": (ab / (avg_ms * 1e-3) / 1e9) if ab else None}
+    cand = {k: v for k, v in kern.items() if v["gbs"] is not None}
+    top = max(cand, key=lambda k: cand[k]["avg_ms"] * cand[k]["calls_per_step"])
+    roof = {"kernel": top, "bound": "hbm", "achieved": cand[top]["gbs"], "peak": pk["hbm"], "unit": "GB/s",
+            "frac": cand[top]["gbs"] / pk["hbm"], "traffic": None, "peak_source": pk["src"],
+            "algorithmic_bytes_per_launch": algorithmic_bytes(top, B)}
+    # bounded CPU baseline on this box's host cores (rank 0, N=1 only)
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        n, ts = cpu_run(tile_batch(make_batch(2, 1234), 8), cpu_refiner_state(), 2, 1)
+        cpu = {"value": n / (sum(ts) / len(ts)), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+               "sample": f"{n} crops per run, 1 warm-up + 2 timed runs of the oracle port (reference CPU path)"}
+    print(json.dumps({
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "tf32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "crops_per_gpu_per_step": B, "image": 256, "iters": 8,
+                   "parallelism": f"batch-shard x{world} + pose all-gather",
+                   "l2": "two alternating input sets; per-step working set (>450 MB) exceeds the 126 MB L2",
+                   "gru_backend": __import__("scflow_b200.gru", fromlist=["BACKEND"]).BACKEND},
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches, "roofline": roof, "kernels": kern, "cpu_baseline": cpu, "clocks": clocks,
+    }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -17,6 +17,49 @@ PREC_FP32, PREC_TF32 = 0, 1
 DIV_IEEE, DIV_RCP = 0, 1
 
 
+class LaunchStats:
+    """Counts launches of OUR kernels; with `timing` on, brackets each launcher call with CUDA
+    events on the launching (current) stream so bench.py can attribute device time per kernel."""
+
+    def __init__(self):
+        self.count = 0
+        self.timing = False
+        self.events = []          # (name, kernels_in_call, start, end)
+
+    def reset(self, timing: bool = False):
+        self.count, self.timing, self.events = 0, timing, []
+
+    def summary(self):
+        """{name: (calls, total_ms)} -- call after a synchronize."""
+        out = {}
+        for name, _, a, b in self.events:
+            c, t = out.get(name, (0, 0.0))
+            out[name] = (c + 1, t + a.elapsed_time(b))
+        return out
+
+
+STATS = LaunchStats()
+
+
+class _timed:
+    def __init__(self, name, kernels=1):
+        self.name, self.kernels = name, kernels
+
+    def __enter__(self):
+        STATS.count += self.kernels
+        if STATS.timing:
+            self.a = torch.cuda.Event(enable_timing=True)
+            self.b = torch.cuda.Event(enable_timing=True)
+            self.a.record()
+        return self
+
+    def __exit__(self, *exc):
+        if STATS.timing:
+            self.b.record()
+            STATS.events.append((self.name, self.kernels, self.a, self.b))
+        return False
+
+
 def _chk(t: torch.Tensor, name: str, dtype=torch.float32) -> torch.Tensor:
     if not t.is_cuda:
         raise _lib.ScflowError(f"{name}: expected a CUDA tensor (scflow_b200 has no CPU path)")
@@ -43,8 +86,9 @@ def corr_pyramid(feat1: torch.Tensor, feat2: torch.Tensor, num_levels: int = 4,
     levels = [torch.empty((n * h * w, 1, h >> l, w >> l), device=f1.device, dtype=torch.float32)
               for l in range(num_levels)]
     arr = (ctypes.c_void_p * num_levels)(*[l.data_ptr() for l in levels])
-    rc = lib.scflow_corr_pyramid_fwd(_ptr(f1), _ptr(f2), arr, num_levels, n, c, h, w, precision,
-                                     None, 0, _stream())
+    with _timed("scflow_corr_pyramid_fwd", 1 if precision == PREC_TF32 else 2):
+        rc = lib.scflow_corr_pyramid_fwd(_ptr(f1), _ptr(f2), arr, num_levels, n, c, h, w, precision,
+                                         None, 0, _stream())
     _lib.check(rc, "scflow_corr_pyramid_fwd")
     return levels
 
@@ -65,7 +109,8 @@ def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int
     out = torch.empty((n, L * d * d, h, w), device=fl.device, dtype=torch.float32)
     win = torch.empty((n * h * w, L, 2, d), device=fl.device, dtype=torch.int16) if return_windows else None
     arr = (ctypes.c_void_p * L)(*[p.data_ptr() for p in lv])
-    rc = lib.scflow_corr_lookup_fwd(arr, L, _ptr(fl), _ptr(out), _ptr(win), n, h, w, radius, div_mode, _stream())
+    with _timed("scflow_corr_lookup_fwd", 1):
+        rc = lib.scflow_corr_lookup_fwd(arr, L, _ptr(fl), _ptr(out), _ptr(win), n, h, w, radius, div_mode, _stream())
     _lib.check(rc, "scflow_corr_lookup_fwd")
     return (out, win) if return_windows else out
 
@@ -77,7 +122,8 @@ def lift_points(depth, K, R0, t0):
     n, H, W = depth.shape
     pts = torch.empty((n, 3, H, W), device=depth.device, dtype=torch.float32)
     mask = torch.empty((n, H, W), device=depth.device, dtype=torch.uint8)
-    rc = lib.scflow_lift_points(_ptr(depth), _ptr(K), _ptr(R0), _ptr(t0), _ptr(pts), _ptr(mask), n, H, W, _stream())
+    with _timed("scflow_lift_points", 1):
+        rc = lib.scflow_lift_points(_ptr(depth), _ptr(K), _ptr(R0), _ptr(t0), _ptr(pts), _ptr(mask), n, H, W, _stream())
     _lib.check(rc, "scflow_lift_points")
     return pts, mask
 
@@ -104,10 +150,11 @@ def pose_flow(R_prev, t_prev, K, *, dR6=None, dt=None, depth=None, R0=None, t0=N
     t = torch.empty((n, 3), device=dev, dtype=torch.float32)
     full = torch.empty((n, 2, H, W), device=dev, dtype=torch.float32) if want_full else None
     lr = torch.empty((n, 2, H // scale, W // scale), device=dev, dtype=torch.float32) if want_lr else None
-    rc = lib.scflow_pose_flow_fwd(_ptr(dR6), _ptr(dt), _ptr(R_prev), _ptr(t_prev), _ptr(K), _ptr(R0),
-                                  _ptr(t0), _ptr(depth), _ptr(points3d), _ptr(mask), _ptr(R), _ptr(t),
-                                  _ptr(full), _ptr(lr), n, H, W, scale, float(invalid_num),
-                                  float(weight), _stream())
+    with _timed("scflow_pose_flow_fwd", 1):
+        rc = lib.scflow_pose_flow_fwd(_ptr(dR6), _ptr(dt), _ptr(R_prev), _ptr(t_prev), _ptr(K), _ptr(R0),
+                                      _ptr(t0), _ptr(depth), _ptr(points3d), _ptr(mask), _ptr(R), _ptr(t),
+                                      _ptr(full), _ptr(lr), n, H, W, scale, float(invalid_num),
+                                      float(weight), _stream())
     _lib.check(rc, "scflow_pose_flow_fwd")
     return R, t, full, lr
 
@@ -121,7 +168,8 @@ def upsample(x, add=None, scale: int = 8, mul: float = 1.0):
         assert add.shape == x.shape
     n, c, h, w = x.shape
     out = torch.empty((n, c, h * scale, w * scale), device=x.device, dtype=torch.float32)
-    rc = lib.scflow_upsample_fwd(_ptr(x), _ptr(add), _ptr(out), n, c, h, w, scale, float(mul), _stream())
+    with _timed("scflow_upsample_fwd", 1):
+        rc = lib.scflow_upsample_fwd(_ptr(x), _ptr(add), _ptr(out), n, c, h, w, scale, float(mul), _stream())
     _lib.check(rc, "scflow_upsample_fwd")
     return out
 
@@ -132,6 +180,7 @@ def downsample(x, scale: int = 8, mul: float = 1.0):
     x = _chk(x, "x")
     n, c, H, W = x.shape
     out = torch.empty((n, c, H // scale, W // scale), device=x.device, dtype=torch.float32)
-    rc = lib.scflow_downsample_fwd(_ptr(x), _ptr(out), n, c, H, W, scale, float(mul), _stream())
+    with _timed("scflow_downsample_fwd", 1):
+        rc = lib.scflow_downsample_fwd(_ptr(x), _ptr(out), n, c, H, W, scale, float(mul), _stream())
     _lib.check(rc, "scflow_downsample_fwd")
     return out
