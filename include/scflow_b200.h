@@ -80,14 +80,17 @@ int scflow_corr_lookup_fwd(const float* const* levels, int num_levels, const flo
  *     replaces 6 cuDNN convs + 6 activation kernels + 4 cat + 8 elementwise per iteration.
  * Channels-last activations: h_in/h_out (n, hgt, wid, ch) , x (n, hgt, wid, cx); fp32.
  * wpack: weights re-laid by scflow_convgru_pack_weights (device, size from _packed_floats).
- * One call = one pass (pass 0: (1,5) taps along x, pass 1: (5,1) taps along y).
+ * rh_scratch: caller-owned (n, hgt, wid, ch) fp32 buffer for r*h (written and re-read by the
+ * same CTA through L2).  h_out may alias h_in.  ch = 128, cx = 256, wid | 128 (pass 0) or
+ * hgt | 128 (pass 1).  One call = one pass (pass 0: (1,5) taps along x, pass 1: (5,1) along y).
  * ------------------------------------------------------------------------------------------- */
 size_t scflow_convgru_packed_floats(int ch, int cx);
 int scflow_convgru_pack_weights(const float* wz, const float* wr, const float* wq,
                                 const float* bz, const float* br, const float* bq,
                                 float* wpack, int ch, int cx, int pass, void* stream);
 int scflow_convgru_pass_fwd(const float* h_in, const float* x, const float* wpack, float* h_out,
-                            int n, int hgt, int wid, int ch, int cx, int pass, void* stream);
+                            float* rh_scratch, int n, int hgt, int wid, int ch, int cx, int pass,
+                            void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * a4  cal_3d_2d_corr / lift_2d_to_3d    models/utils/pose.py:26-64

@@ -25,7 +25,7 @@ SIGNATURES = {
     "scflow_corr_lookup_fwd": (c_int, [_P, c_int, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_convgru_packed_floats": (c_size_t, [c_int, c_int]),
     "scflow_convgru_pack_weights": (c_int, [_P] * 7 + [c_int, c_int, c_int, _P]),
-    "scflow_convgru_pass_fwd": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
+    "scflow_convgru_pass_fwd": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_lift_points": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P]),
     "scflow_pose_flow_fwd": (c_int, [_P] * 14 + [c_int, c_int, c_int, c_int, c_float, c_float, _P]),
     "scflow_upsample_fwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_float, _P]),

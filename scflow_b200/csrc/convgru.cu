@@ -1,17 +1,351 @@
-// ConvGRU (SeqConv) pass as a fused tcgen05 implicit GEMM -- placeholder entry points until the
-// kernel lands: they reject the call (no fallback), the Python ConvGRU module then uses cuDNN.
+// ConvGRU (SeqConv) pass as ONE fused tcgen05 implicit-GEMM kernel.
+// Replaces models/decoder/raft_decoder.py:245-252 for one (1,5) or (5,1) pass: 3 cuDNN convs,
+// 3 activation kernels, 2 cat and 5 elementwise kernels of the reference.
+//
+//   hx = cat[h, x];  z = sigmoid(Wz*hx + bz);  r = sigmoid(Wr*hx + br)
+//   q  = tanh(Wq*cat[r.h, x] + bq);            h' = (1 - z).h + z.q
+//
+// Data layout: channels-last fp32 activations (n, H, W, C): a pixel's channels are contiguous, so
+// an activation tile is a K-major GEMM operand that TMA loads as 128 pixels x 32 channels with
+// SWIZZLE_128B.  Weights are pre-packed to [tap][k-block][384 rows = z|r|q][32] (K-major too).
+//
+// A tile is 128 pixels that span the WHOLE convolution axis (pass 0: 128/W full rows; pass 1:
+// 128/H full columns).  The 5 taps are 5 shifted TMA loads of the same tile, the zero padding is
+// TMA's out-of-bounds fill, and -- because no tap ever leaves the tile's lines -- r.h of the
+// tile is all the second convolution needs, so both convolutions and all gating fuse:
+//
+//   stage 1  D[:,   0:256] = sum_{tap,kb<12} hx_tap . [Wz|Wr]^T       (N = 256)
+//            D[:, 256:384] = sum_{tap,kb>=4}  x_tap . Wq[:, x part]^T  (N = 128)
+//   epi 1    r = sigmoid(D[:,128:256] + br);  r.h -> scratch (64 KB per tile, stays in L2)
+//   stage 2  D[:, 256:384] += sum_{tap,kb<4} (r.h)_tap . Wq[:, h part]^T
+//   epi 2    z = sigmoid(D[:,0:128] + bz); q = tanh(D[:,256:384] + bq); h' = (1-z)h + zq
+//
+// Accumulators live in TMEM (384 of 512 columns); tcgen05.mma kind::tf32 reads the fp32 smem
+// tiles directly.  Warp roles: warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 epilogue.
+// Tensor-bound: 3 convs x 2*pixels*128*1920 FLOP per pass (96.6 GFLOP for 64 crops at 32x32).
 #include "common.cuh"
+#include "tc_common.cuh"
+
+namespace scflow {
+namespace gru {
+
+constexpr int CH = 128;                 // hidden channels
+constexpr int CX = 256;                 // x channels (context 128 + motion 126 + flow 2)
+constexpr int TAPS = 5;
+constexpr int BM = 128;                 // pixels per tile
+constexpr int BK = 32;                  // channels per k-block (128-byte swizzle row)
+constexpr int KB_H = CH / BK;           // 4 k-blocks from h (or r.h)
+constexpr int KB_ALL = (CH + CX) / BK;  // 12 k-blocks of hx
+constexpr int ROWS = 3 * CH;            // 384 packed weight rows per (tap, k-block): z | r | q
+constexpr int STAGES = 3;
+constexpr int A_BYTES = BM * BK * 4;    // 16 KB
+constexpr int B_BYTES = ROWS * BK * 4;  // 48 KB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int THREADS = 192;
+constexpr int TMEM_COLS = 512;
+constexpr int S1_ITERS = TAPS * KB_ALL;   // 60
+constexpr int S2_ITERS = TAPS * KB_H;     // 20
+constexpr size_t WPACK_FLOATS = (size_t)TAPS * KB_ALL * ROWS * BK + ROWS;
+constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + ROWS * 4 + 256;
+
+// wz/wr/wq: (CH, CH+CX, 1, 5) or (CH, CH+CX, 5, 1) -- both are [o][ci][tap] in memory.
+__global__ void pack_weights_kernel(const float* __restrict__ wz, const float* __restrict__ wr,
+                                    const float* __restrict__ wq, const float* __restrict__ bz,
+                                    const float* __restrict__ br, const float* __restrict__ bq,
+                                    float* __restrict__ out) {
+  const int cin = CH + CX;
+  const size_t total = (size_t)TAPS * KB_ALL * ROWS * BK;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total + ROWS;
+       i += (size_t)gridDim.x * blockDim.x) {
+    if (i >= total) {
+      const int r = (int)(i - total);
+      out[i] = r < CH ? bz[r] : r < 2 * CH ? br[r - CH] : bq[r - 2 * CH];
+      continue;
+    }
+    const int c = (int)(i % BK);
+    const int row = (int)((i / BK) % ROWS);
+    const int kb = (int)((i / ((size_t)BK * ROWS)) % KB_ALL);
+    const int t = (int)(i / ((size_t)BK * ROWS * KB_ALL));
+    const float* w = row < CH ? wz : row < 2 * CH ? wr : wq;
+    const int o = row % CH, ci = kb * BK + c;
+    // round-to-nearest TF32 here (free): tcgen05 would otherwise truncate the low 13 mantissa bits
+    float v = w[((size_t)o * cin + ci) * TAPS + t];
+    uint32_t u;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+    out[i] = __uint_as_float(u);
+  }
+}
+
+struct Params {
+  const float* h_in;
+  const float* bias;     // [384] z | r | q (tail of wpack)
+  float* h_out;
+  float* rh;
+  int n, H, W, pass;
+  int tiles_per_img, total_tiles, G;   // G = lines per tile (128 / conv-axis length)
+};
+
+__device__ __forceinline__ float sigmoidf_(float v) { return 1.0f / (1.0f + expf(-v)); }
+
+__global__ void __launch_bounds__(THREADS, 1)
+convgru_pass_kernel(const __grid_constant__ CUtensorMap map_h, const __grid_constant__ CUtensorMap map_x,
+                    const __grid_constant__ CUtensorMap map_rh, const __grid_constant__ CUtensorMap map_w,
+                    const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  float* sbias = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + ROWS * 4);
+  uint64_t* full = bars;                    // [STAGES]
+  uint64_t* empty = bars + STAGES;          // [STAGES]
+  uint64_t* s1_done = bars + 2 * STAGES;    // stage-1 accumulators complete
+  uint64_t* s2_done = s1_done + 1;          // stage-2 accumulation complete
+  uint64_t* rh_ready = s1_done + 2;         // r.h tile written (4 epilogue warps)
+  uint64_t* tmem_free = s1_done + 3;        // epilogue finished reading TMEM (4 warps)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s1_done + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tc::tma_prefetch_desc(&map_h); tc::tma_prefetch_desc(&map_x);
+    tc::tma_prefetch_desc(&map_rh); tc::tma_prefetch_desc(&map_w);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < STAGES; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
+      tc::mbar_init(s1_done, 1); tc::mbar_init(s2_done, 1);
+      tc::mbar_init(rh_ready, 4); tc::mbar_init(tmem_free, 4);
+      tc::fence_barrier_init();
+    }
+    __syncwarp();
+    tc::tmem_alloc(tmem_slot, TMEM_COLS);
+  }
+  for (int i = threadIdx.x; i < ROWS; i += THREADS) sbias[i] = p.bias[i];
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ---------------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0; uint32_t it_tile = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it_tile) {
+        const int n = tile / p.tiles_per_img, tl = tile % p.tiles_per_img;
+        for (int it = 0; it < S1_ITERS + S2_ITERS; ++it) {
+          const bool s2 = it >= S1_ITERS;
+          if (it == S1_ITERS) tc::mbar_wait(rh_ready, it_tile & 1);   // r.h of this tile is in L2
+          const int j = s2 ? it - S1_ITERS : it;
+          const int t = s2 ? j / KB_H : j / KB_ALL;
+          const int kb = s2 ? j % KB_H : j % KB_ALL;
+          tc::mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* a_s = smem + stage * STAGE_BYTES;
+          uint8_t* b_s = a_s + A_BYTES;
+          const int nb = s2 ? 1 : (kb < KB_H ? 2 : 3);                // 128-row weight boxes
+          tc::mbar_expect_tx(&full[stage], A_BYTES + nb * (CH * BK * 4));
+          const CUtensorMap* am = s2 ? &map_rh : (kb < KB_H ? &map_h : &map_x);
+          const int c0 = (s2 || kb < KB_H) ? kb * BK : (kb - KB_H) * BK;
+          // tile origin (x, y) shifted by the tap along the convolution axis; TMA zero-fills
+          // everything outside [0,W) x [0,H): that is the conv's zero padding
+          const int cx = p.pass == 0 ? (t - 2) : tl * p.G;
+          const int cy = p.pass == 0 ? tl * p.G : (t - 2);
+          tc::tma_load_4d(am, &full[stage], a_s, c0, cx, cy, n);
+          const int wrow = (t * KB_ALL + kb) * ROWS;
+          if (s2) {
+            tc::tma_load_2d(&map_w, &full[stage], b_s, 0, wrow + 2 * CH);
+          } else {
+            for (int b = 0; b < nb; ++b)
+              tc::tma_load_2d(&map_w, &full[stage], b_s + b * (CH * BK * 4), 0, wrow + b * CH);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t id256 = tc::make_idesc_tf32(BM, 256, 0, 0);   // K-major A and B
+      constexpr uint32_t id128 = tc::make_idesc_tf32(BM, 128, 0, 0);
+      int stage = 0; uint32_t phase = 0; uint32_t it_tile = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it_tile) {
+        tc::mbar_wait(tmem_free, (it_tile & 1) ^ 1);
+        tc::tc_fence_after();
+        for (int it = 0; it < S1_ITERS + S2_ITERS; ++it) {
+          const bool s2 = it >= S1_ITERS;
+          const int kb = s2 ? 0 : it % KB_ALL;
+          tc::mbar_wait(&full[stage], phase);
+          tc::tc_fence_after();
+          const uint32_t a_addr = tc::smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t b_addr = a_addr + A_BYTES;
+#pragma unroll
+          for (int ks = 0; ks < BK / 8; ++ks) {
+            // K-major SWIZZLE_128B: 8-row groups 1024 B apart; a k-step (8 tf32) is +32 B
+            const uint64_t da = tc::make_smem_desc(a_addr + ks * 32, 16, 1024, tc::kLayoutSw128);
+            if (s2) {
+              const uint64_t dq = tc::make_smem_desc(b_addr + ks * 32, 16, 1024, tc::kLayoutSw128);
+              tc::mma_tf32_ss(tmem_base + 2 * CH, da, dq, id128, 1u);
+            } else {
+              const uint64_t dzr = tc::make_smem_desc(b_addr + ks * 32, 16, 1024, tc::kLayoutSw128);
+              tc::mma_tf32_ss(tmem_base, da, dzr, id256, (it | ks) != 0 ? 1u : 0u);
+              if (kb >= KB_H) {
+                const uint64_t dq = tc::make_smem_desc(b_addr + 2 * CH * BK * 4 + ks * 32, 16, 1024, tc::kLayoutSw128);
+                tc::mma_tf32_ss(tmem_base + 2 * CH, da, dq, id128, (it != KB_H || ks != 0) ? 1u : 0u);
+              }
+            }
+          }
+          tc::tc_commit(&empty[stage]);
+          if (it == S1_ITERS - 1) tc::tc_commit(s1_done);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        tc::tc_commit(s2_done);
+      }
+    }
+  } else {
+    // ---------------------------------------------------------------- epilogue (4 warps)
+    const int quarter = warp & 3;
+    const int m = quarter * 32 + lane;                     // TMEM lane = pixel of the tile
+    uint32_t it_tile = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it_tile) {
+      const int n = tile / p.tiles_per_img, tl = tile % p.tiles_per_img;
+      long long pix;
+      if (p.pass == 0) {
+        pix = (long long)n * p.H * p.W + (long long)tl * BM + m;                 // G full rows
+      } else {
+        const int y = m / p.G, x = tl * p.G + (m % p.G);                          // G full columns
+        pix = ((long long)n * p.H + y) * p.W + x;
+      }
+      const float* hp = p.h_in + pix * CH;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+
+      // ---- epilogue 1: r = sigmoid(r_pre + br); r.h -> scratch
+      tc::mbar_wait(s1_done, it_tile & 1);
+      tc::tc_fence_after();
+      float* rhp = p.rh + pix * CH;
+#pragma unroll 1
+      for (int c = 0; c < CH / 32; ++c) {
+        float v[32];
+        tc::tmem_ld_32x32(taddr + CH + c * 32, v);
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float4 hv = *reinterpret_cast<const float4*>(hp + c * 32 + 4 * k);
+          float4 o;
+          o.x = sigmoidf_(v[4 * k + 0] + sbias[CH + c * 32 + 4 * k + 0]) * hv.x;
+          o.y = sigmoidf_(v[4 * k + 1] + sbias[CH + c * 32 + 4 * k + 1]) * hv.y;
+          o.z = sigmoidf_(v[4 * k + 2] + sbias[CH + c * 32 + 4 * k + 2]) * hv.z;
+          o.w = sigmoidf_(v[4 * k + 3] + sbias[CH + c * 32 + 4 * k + 3]) * hv.w;
+          *reinterpret_cast<float4*>(rhp + c * 32 + 4 * k) = o;
+        }
+      }
+      __threadfence();                       // r.h visible device-wide (L2) ...
+      tc::fence_proxy_async_all();           // ... and ordered before the async-proxy (TMA) reads
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(rh_ready);
+
+      // ---- epilogue 2: z, q, gate
+      tc::mbar_wait(s2_done, it_tile & 1);
+      tc::tc_fence_after();
+      float* op = p.h_out + pix * CH;
+#pragma unroll 1
+      for (int c = 0; c < CH / 32; ++c) {
+        float zv[32], qv[32];
+        tc::tmem_ld_32x32(taddr + c * 32, zv);
+        tc::tmem_ld_32x32(taddr + 2 * CH + c * 32, qv);
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float4 hv = *reinterpret_cast<const float4*>(hp + c * 32 + 4 * k);
+          const float hh[4] = {hv.x, hv.y, hv.z, hv.w};
+          float o[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int ch = c * 32 + 4 * k + e;
+            const float z = sigmoidf_(zv[4 * k + e] + sbias[ch]);
+            const float q = tanhf(qv[4 * k + e] + sbias[2 * CH + ch]);
+            o[e] = (1.0f - z) * hh[e] + z * q;
+          }
+          *reinterpret_cast<float4*>(op + c * 32 + 4 * k) = make_float4(o[0], o[1], o[2], o[3]);
+        }
+      }
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(tmem_free);
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc::tc_fence_after();
+    tc::tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+}  // namespace gru
+}  // namespace scflow
 
 extern "C" size_t scflow_convgru_packed_floats(int ch, int cx) {
-  return (size_t)3 * ch * (ch + cx) * 5 + 3 * (size_t)ch;
+  if (ch != scflow::gru::CH || cx != scflow::gru::CX) return 0;
+  return scflow::gru::WPACK_FLOATS;
 }
 
-extern "C" int scflow_convgru_pack_weights(const float*, const float*, const float*, const float*,
-                                           const float*, const float*, float*, int, int, int, void*) {
-  return SCFLOW_E_UNIMPLEMENTED;
+extern "C" int scflow_convgru_pack_weights(const float* wz, const float* wr, const float* wq,
+                                           const float* bz, const float* br, const float* bq,
+                                           float* wpack, int ch, int cx, int pass, void* stream) {
+  using namespace scflow;
+  if (!wz || !wr || !wq || !bz || !br || !bq || !wpack) return SCFLOW_E_NULL;
+  if (ch != gru::CH || cx != gru::CX) return SCFLOW_E_BAD_SHAPE;
+  if (pass != 0 && pass != 1) return SCFLOW_E_UNSUPPORTED;
+  gru::pack_weights_kernel<<<148 * 4, 256, 0, (cudaStream_t)stream>>>(wz, wr, wq, bz, br, bq, wpack);
+  return check_launch();
 }
 
-extern "C" int scflow_convgru_pass_fwd(const float*, const float*, const float*, float*, int, int,
-                                       int, int, int, int, void*) {
-  return SCFLOW_E_UNIMPLEMENTED;
+extern "C" int scflow_convgru_pass_fwd(const float* h_in, const float* x, const float* wpack,
+                                       float* h_out, float* rh_scratch, int n, int hgt, int wid,
+                                       int ch, int cx, int pass, void* stream) {
+  using namespace scflow;
+  using namespace scflow::gru;
+  if (!h_in || !x || !wpack || !h_out || !rh_scratch) return SCFLOW_E_NULL;
+  if (ch != CH || cx != CX) return SCFLOW_E_BAD_SHAPE;
+  if (pass != 0 && pass != 1) return SCFLOW_E_UNSUPPORTED;
+  const int axis = pass == 0 ? wid : hgt;           // convolution axis length
+  if (n <= 0 || hgt <= 0 || wid <= 0 || axis > BM || (BM % axis) != 0) return SCFLOW_E_BAD_SHAPE;
+  const int G = BM / axis;
+  const int lines = pass == 0 ? hgt : wid;
+  if ((lines % G) != 0) return SCFLOW_E_BAD_SHAPE;
+  if (!aligned16(h_in) || !aligned16(x) || !aligned16(wpack) || !aligned16(h_out) || !aligned16(rh_scratch))
+    return SCFLOW_E_MISALIGNED;
+
+  // activation maps: dims (c, x, y, n); box = 32 channels x the tile's pixel rectangle
+  auto act_map = [&](CUtensorMap* mp, const float* base, int c) {
+    const uint64_t dims[4] = {(uint64_t)c, (uint64_t)wid, (uint64_t)hgt, (uint64_t)n};
+    const uint64_t strides[3] = {(uint64_t)c * 4, (uint64_t)wid * c * 4, (uint64_t)hgt * wid * c * 4};
+    const uint32_t box[4] = {BK, (uint32_t)(pass == 0 ? wid : G), (uint32_t)(pass == 0 ? G : hgt), 1};
+    return tc::encode_f32_map(mp, base, 4, dims, strides, box, tc::kTmaSw128);
+  };
+  CUtensorMap map_h, map_x, map_rh, map_w;
+  if (!act_map(&map_h, h_in, CH) || !act_map(&map_x, x, CX) || !act_map(&map_rh, rh_scratch, CH))
+    return SCFLOW_E_DRIVER;
+  {
+    const uint64_t dims[2] = {BK, (uint64_t)TAPS * KB_ALL * ROWS};
+    const uint64_t strides[1] = {BK * 4};
+    const uint32_t box[2] = {BK, CH};
+    if (!tc::encode_f32_map(&map_w, wpack, 2, dims, strides, box, tc::kTmaSw128)) return SCFLOW_E_DRIVER;
+  }
+  Params p;
+  p.h_in = h_in; p.bias = wpack + (size_t)TAPS * KB_ALL * ROWS * BK; p.h_out = h_out; p.rh = rh_scratch;
+  p.n = n; p.H = hgt; p.W = wid; p.pass = pass; p.G = G;
+  p.tiles_per_img = lines / G;
+  p.total_tiles = n * p.tiles_per_img;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(convgru_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+    attr_set = true;
+  }
+  int sms = 0, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (sms <= 0) sms = 148;
+  const int grid = p.total_tiles < sms ? p.total_tiles : sms;
+  convgru_pass_kernel<<<grid, THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(map_h, map_x, map_rh, map_w, p);
+  return check_launch();
 }

@@ -8,7 +8,9 @@ from __future__ import annotations
 import torch
 import torch.nn.functional as F
 
-BACKEND = "cudnn"
+import os
+
+BACKEND = os.environ.get("SCFLOW_GRU_BACKEND", "tcgen05")
 
 
 def _cudnn_forward(mod, h, x):

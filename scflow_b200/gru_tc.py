@@ -1,0 +1,70 @@
+"""ConvGRU through the fused tcgen05 pass kernel (scflow_convgru_pass_fwd).
+
+Weights stay fp32 nn.Parameters under the reference names; the packed [tap][k-block][z|r|q][32]
+copy is a derived cache keyed on the parameters' version counters and storage, rebuilt after
+load_state_dict / optimizer steps / .to(device) and never saved."""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _lib
+from .ops import _chk, _ptr, _stream, _timed
+
+
+def _pack_key(mod, p):
+    ps = [getattr(mod, f"conv_{g}")[p].conv for g in "zrq"]
+    return tuple((t.data_ptr(), t._version) for c in ps for t in (c.weight, c.bias))
+
+
+def packed_weights(mod, p: int) -> torch.Tensor:
+    cache = mod.__dict__.setdefault("_scflow_wpack", {})
+    key = _pack_key(mod, p)
+    hit = cache.get(p)
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    lib = _lib.load()
+    cz, cr, cq = (getattr(mod, f"conv_{g}")[p].conv for g in "zrq")
+    ch, cx = mod.h_channels, mod.x_channels
+    nfl = lib.scflow_convgru_packed_floats(ch, cx)
+    if nfl == 0:
+        raise _lib.ScflowError(f"ConvGRU({ch},{cx}) is not supported by the tcgen05 kernel (128/256 only)")
+    ws = [_chk(c.weight.detach(), "gru weight") for c in (cz, cr, cq)]
+    bs = [_chk(c.bias.detach(), "gru bias") for c in (cz, cr, cq)]
+    out = torch.empty(nfl, device=ws[0].device, dtype=torch.float32)
+    with _timed("scflow_convgru_pack_weights"):
+        rc = lib.scflow_convgru_pack_weights(_ptr(ws[0]), _ptr(ws[1]), _ptr(ws[2]), _ptr(bs[0]), _ptr(bs[1]),
+                                             _ptr(bs[2]), _ptr(out), ch, cx, p, _stream())
+    _lib.check(rc, "scflow_convgru_pack_weights")
+    cache[p] = (key, out)
+    return out
+
+
+def forward_nhwc(mod, h: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """h (N,H,W,128), x (N,H,W,256) channels-last contiguous -> new h (N,H,W,128)."""
+    lib = _lib.load()
+    h, x = _chk(h, "h"), _chk(x, "x")
+    n, H, W, ch = h.shape
+    cx = x.shape[-1]
+    out = torch.empty_like(h)
+    rh = torch.empty_like(h)
+    src = h
+    for p in (0, 1):
+        wp = packed_weights(mod, p)
+        with _timed("scflow_convgru_pass_fwd"):
+            rc = lib.scflow_convgru_pass_fwd(_ptr(src), _ptr(x), _ptr(wp), _ptr(out), _ptr(rh), n, H, W, ch, cx,
+                                             p, _stream())
+        _lib.check(rc, "scflow_convgru_pass_fwd")
+        src = out          # second pass updates in place (a tile only reads its own pixels)
+    return out
+
+
+def forward(mod, h: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """NCHW-shaped in / out (reference signature); tensors already in channels_last memory format
+    pass through without a copy."""
+    if torch.is_grad_enabled() and (h.requires_grad or x.requires_grad):
+        raise NotImplementedError("ConvGRU tcgen05 kernel is forward-only in this round")
+    hn = h.permute(0, 2, 3, 1).contiguous()
+    xn = x.permute(0, 2, 3, 1).contiguous()
+    return forward_nhwc(mod, hn, xn).permute(0, 3, 1, 2)

@@ -257,3 +257,72 @@ def test_batch64_matches_per_crop_runs():
     Ra, ta = run(slice(0, 16))
     Rb = torch.cat([run(slice(i, i + 8))[0] for i in (0, 8)])
     assert float(O.rotation_geodesic(Ra.cpu(), Rb.cpu()).max()) < 1e-4
+
+
+# ------------------------------------------------------------------ a3 ConvGRU (tcgen05)
+def _gru_sd(seed):
+    shapes = {}
+    for nm in "zrq":
+        for p, k in ((0, (1, 5)), (1, (5, 1))):
+            shapes[f"conv_{nm}.{p}.conv.weight"] = (128, 384) + k
+            shapes[f"conv_{nm}.{p}.conv.bias"] = (128,)
+    return syn.fill_state_dict(shapes, seed=seed, gain=2.0)
+
+
+@pytest.mark.parametrize("n,h,w", [(2, 32, 32), (1, 64, 64), (3, 8, 32)])
+def test_convgru_tcgen05_vs_oracle(n, h, w):
+    from scflow_b200 import gru_tc
+    sd = _gru_sd(21)
+    mod = sb.ConvGRU(128, 256)
+    mod.load_state_dict(sd)
+    mod.to(DEV)
+    rs = np.random.RandomState(22)
+    hh = torch.from_numpy(np.tanh(rs.standard_normal((n, 128, h, w))).astype(np.float32))
+    xx = torch.from_numpy(rs.standard_normal((n, 256, h, w)).astype(np.float32))
+    want = O.conv_gru(hh, xx, sd)
+    got = gru_tc.forward(mod, hh.to(DEV), xx.to(DEV))
+    assert got.shape == want.shape
+    err = rel(got, want)
+    assert err < 3e-3, err                      # TF32 operands, fp32 accumulate
+    # against cuDNN at the same (TF32) operand precision the agreement is tighter
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = True
+    try:
+        from scflow_b200 import gru as g
+        ref = g._cudnn_forward(mod, hh.to(DEV), xx.to(DEV))
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    assert rel(got, ref) < 3e-3
+
+
+def test_convgru_weight_cache_tracks_parameter_updates():
+    from scflow_b200 import gru_tc
+    mod = sb.ConvGRU(128, 256).to(DEV)
+    a = gru_tc.packed_weights(mod, 0)
+    assert gru_tc.packed_weights(mod, 0) is a
+    with torch.no_grad():
+        mod.conv_z[0].conv.weight.mul_(2.0)
+    b = gru_tc.packed_weights(mod, 0)
+    assert b is not a and not torch.equal(a, b)
+
+
+def test_decoder_with_tcgen05_gru(golden_dir):
+    from scflow_b200 import gru as g
+    old = g.BACKEND
+    g.BACKEND = "tcgen05"
+    try:
+        dec, sd = _build_decoder(256, 51, golden_dir, corr_precision="tf32")
+        cr = syn.make_crops(1, 256, seed=52)
+        ft = syn.make_features(1, 32, 32, seed=53)
+        c, f = _cuda(cr), _cuda(ft)
+        with torch.no_grad():
+            out = dec(f["feat_render"], f["feat_real"], f["h_feat"], f["cxt_feat"], c["R0"], c["t0"],
+                      c["depth"], c["K"], c["labels"], torch.zeros(1, 2, 256, 256, device=DEV), 0.)
+    finally:
+        g.BACKEND = old
+    gd = np.load(os.path.join(golden_dir, "decoder_cfg1.npz"))
+    Rg, tg = torch.from_numpy(gd["rotations"]), torch.from_numpy(gd["translations"])
+    er = float(O.rotation_geodesic(out[2][-1].cpu(), Rg[-1]).max())
+    et = float((out[3][-1].cpu() - tg[-1]).abs().max())
+    print(f"tcgen05 GRU + TF32 corr: pose err {er:.3e} rad, {et:.3e} mm")
+    assert er < 1e-4 and et < 0.1
