@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define SCFLOW_ABI_VERSION 1
+#define SCFLOW_ABI_VERSION 2
 
 enum {
   SCFLOW_OK = 0,
@@ -70,10 +70,15 @@ int scflow_corr_pyramid_fwd(const float* feat1, const float* feat2, float* const
  * windows (optional, may be NULL): int16 (n*h*w, num_levels, 2, 2r+1) = floor of the
  * un-normalised sample coordinate per x tap / per y tap -- the window selection, exported so
  * tests can check it bit-exactly.  Only radius == 4, bilinear, zeros, align_corners=True.
+ * out_layout: SCFLOW_LAYOUT_NCHW writes (n, 324, h, w) as the reference does; SCFLOW_LAYOUT_NHWC
+ * writes (n, h, w, 324) -- same values, channels-last memory, the layout the downstream 1x1
+ * convolution and the ConvGRU kernel consume (one warp per query, TMA-staged windows).
  * ------------------------------------------------------------------------------------------- */
+#define SCFLOW_LAYOUT_NCHW 0
+#define SCFLOW_LAYOUT_NHWC 1
 int scflow_corr_lookup_fwd(const float* const* levels, int num_levels, const float* flow,
                            float* out, short* windows, int n, int h, int w, int radius,
-                           int div_mode, void* stream);
+                           int div_mode, int out_layout, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * a3  ConvGRU.forward (SeqConv)    models/decoder/raft_decoder.py:235-253
@@ -81,16 +86,30 @@ int scflow_corr_lookup_fwd(const float* const* levels, int num_levels, const flo
  * Channels-last activations: h_in/h_out (n, hgt, wid, ch) , x (n, hgt, wid, cx); fp32.
  * wpack: weights re-laid by scflow_convgru_pack_weights (device, size from _packed_floats).
  * rh_scratch: caller-owned (n, hgt, wid, ch) fp32 buffer for r*h (written and re-read by the
- * same CTA through L2).  h_out may alias h_in.  ch = 128, cx = 256, wid | 128 (pass 0) or
+ * same CTA through L2).  h_out may alias h_in.  h_in_tf32 (optional): copy of h_in rounded to
+ * nearest TF32, read by the tensor core instead of h_in (which tcgen05 would truncate); the
+ * gating still uses the exact h_in.  h_out_tf32 (optional): receives that copy of h_out; may
+ * alias h_in_tf32.  x is read by the tensor core as is (see scflow_pack_nhwc).  ch = 128, cx = 256, wid | 128 (pass 0) or
  * hgt | 128 (pass 1).  One call = one pass (pass 0: (1,5) taps along x, pass 1: (5,1) along y).
  * ------------------------------------------------------------------------------------------- */
 size_t scflow_convgru_packed_floats(int ch, int cx);
 int scflow_convgru_pack_weights(const float* wz, const float* wr, const float* wq,
                                 const float* bz, const float* br, const float* bq,
                                 float* wpack, int ch, int cx, int pass, void* stream);
-int scflow_convgru_pass_fwd(const float* h_in, const float* x, const float* wpack, float* h_out,
-                            float* rh_scratch, int n, int hgt, int wid, int ch, int cx, int pass,
-                            void* stream);
+int scflow_convgru_pass_fwd(const float* h_in, const float* h_in_tf32, const float* x,
+                            const float* wpack, float* h_out, float* h_out_tf32, float* rh_scratch,
+                            int n, int hgt, int wid, int ch, int cx, int pass, void* stream);
+
+/* Channels-last packing of the GRU input x = cat[cxt, motion, flow] (raft_decoder.py:166 and
+ * scflow_decoder.py:208) with round-to-nearest TF32, replacing two torch.cat and a layout pass.
+ * dst: (npix, cdst) channels-last; channels [dst_off, dst_off + ca + cb + cf) are written from
+ *   a: (npix, ca) channels-last (may be NULL with ca = 0), b: (npix, cb) channels-last (ditto),
+ *   f: (n, cf, P) planar, P = pixels per image (may be NULL with cf = 0).
+ * round_tf32 != 0 rounds every value to the nearest TF32 (what tcgen05 kind::tf32 would otherwise
+ * truncate). */
+int scflow_pack_nhwc(const float* a, int ca, const float* b, int cb, const float* f, int cf,
+                     float* dst, int cdst, int dst_off, long long npix, int P, int round_tf32,
+                     void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * a4  cal_3d_2d_corr / lift_2d_to_3d    models/utils/pose.py:26-64

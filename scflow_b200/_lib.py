@@ -14,6 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libscflow_b200.so")
 
 _P = c_void_p
+ABI_VERSION = 2
 # name -> (restype, argtypes); mirrors include/scflow_b200.h one to one
 SIGNATURES = {
     "scflow_abi_version": (c_int, []),
@@ -22,10 +23,12 @@ SIGNATURES = {
     "scflow_corr_pyramid_workspace_bytes": (c_size_t, [c_int] * 5),
     "scflow_corr_pyramid_fwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                                         _P, c_size_t, _P]),
-    "scflow_corr_lookup_fwd": (c_int, [_P, c_int, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
+    "scflow_corr_lookup_fwd": (c_int, [_P, c_int, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_convgru_packed_floats": (c_size_t, [c_int, c_int]),
     "scflow_convgru_pack_weights": (c_int, [_P] * 7 + [c_int, c_int, c_int, _P]),
-    "scflow_convgru_pass_fwd": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
+    "scflow_convgru_pass_fwd": (c_int, [_P] * 7 + [c_int, c_int, c_int, c_int, c_int, c_int, _P]),
+    "scflow_pack_nhwc": (c_int, [_P, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, ctypes.c_longlong, c_int,
+                                 c_int, _P]),
     "scflow_lift_points": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P]),
     "scflow_pose_flow_fwd": (c_int, [_P] * 14 + [c_int, c_int, c_int, c_int, c_float, c_float, _P]),
     "scflow_upsample_fwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_float, _P]),
@@ -53,7 +56,7 @@ def load() -> ctypes.CDLL:
         fn = getattr(lib, name)      # AttributeError if the .so does not export it
         fn.restype = res
         fn.argtypes = args
-    if lib.scflow_abi_version() != 1:
+    if lib.scflow_abi_version() != ABI_VERSION:
         raise ScflowError("libscflow_b200.so ABI version mismatch; rebuild")
     _lib = lib
     return lib

@@ -80,12 +80,22 @@ struct Params {
   const float* h_in;
   const float* bias;     // [384] z | r | q (tail of wpack)
   float* h_out;
+  float* h_out_tf32;     // optional copy of h_out rounded to nearest TF32: the next pass's MMA operand
   float* rh;
   int n, H, W, pass;
   int tiles_per_img, total_tiles, G;   // G = lines per tile (128 / conv-axis length)
+  int ni;                              // images per tile (>1 only when H*W < 128: whole-image tiles)
+  long long total_pix;
 };
 
 __device__ __forceinline__ float sigmoidf_(float v) { return 1.0f / (1.0f + expf(-v)); }
+// tcgen05 kind::tf32 ignores the low 13 mantissa bits (truncation, a biased error that adds up
+// coherently over K = 1920); operands we produce ourselves are rounded to nearest instead
+__device__ __forceinline__ float rn_tf32(float v) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+  return __uint_as_float(u);
+}
 
 __global__ void __launch_bounds__(THREADS, 1)
 convgru_pass_kernel(const __grid_constant__ CUtensorMap map_h, const __grid_constant__ CUtensorMap map_x,
@@ -130,7 +140,7 @@ convgru_pass_kernel(const __grid_constant__ CUtensorMap map_h, const __grid_cons
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0; uint32_t it_tile = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it_tile) {
-        const int n = tile / p.tiles_per_img, tl = tile % p.tiles_per_img;
+        const int n = (tile / p.tiles_per_img) * p.ni, tl = tile % p.tiles_per_img;
         for (int it = 0; it < S1_ITERS + S2_ITERS; ++it) {
           const bool s2 = it >= S1_ITERS;
           if (it == S1_ITERS) tc::mbar_wait(rh_ready, it_tile & 1);   // r.h of this tile is in L2
@@ -205,9 +215,9 @@ convgru_pass_kernel(const __grid_constant__ CUtensorMap map_h, const __grid_cons
     const int m = quarter * 32 + lane;                     // TMEM lane = pixel of the tile
     uint32_t it_tile = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it_tile) {
-      const int n = tile / p.tiles_per_img, tl = tile % p.tiles_per_img;
+      const int n = (tile / p.tiles_per_img) * p.ni, tl = tile % p.tiles_per_img;
       long long pix;
-      if (p.pass == 0) {
+      if (p.pass == 0 || p.ni > 1) {
         pix = (long long)n * p.H * p.W + (long long)tl * BM + m;                 // G full rows
       } else {
         const int y = m / p.G, x = tl * p.G + (m % p.G);                          // G full columns
@@ -220,19 +230,21 @@ convgru_pass_kernel(const __grid_constant__ CUtensorMap map_h, const __grid_cons
       tc::mbar_wait(s1_done, it_tile & 1);
       tc::tc_fence_after();
       float* rhp = p.rh + pix * CH;
+      const bool live = pix < p.total_pix;       // whole-image tiles may run past the last image
 #pragma unroll 1
       for (int c = 0; c < CH / 32; ++c) {
         float v[32];
         tc::tmem_ld_32x32(taddr + CH + c * 32, v);
         tc::tmem_ld_wait();
+        if (!live) continue;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const float4 hv = *reinterpret_cast<const float4*>(hp + c * 32 + 4 * k);
           float4 o;
-          o.x = sigmoidf_(v[4 * k + 0] + sbias[CH + c * 32 + 4 * k + 0]) * hv.x;
-          o.y = sigmoidf_(v[4 * k + 1] + sbias[CH + c * 32 + 4 * k + 1]) * hv.y;
-          o.z = sigmoidf_(v[4 * k + 2] + sbias[CH + c * 32 + 4 * k + 2]) * hv.z;
-          o.w = sigmoidf_(v[4 * k + 3] + sbias[CH + c * 32 + 4 * k + 3]) * hv.w;
+          o.x = rn_tf32(sigmoidf_(v[4 * k + 0] + sbias[CH + c * 32 + 4 * k + 0]) * hv.x);
+          o.y = rn_tf32(sigmoidf_(v[4 * k + 1] + sbias[CH + c * 32 + 4 * k + 1]) * hv.y);
+          o.z = rn_tf32(sigmoidf_(v[4 * k + 2] + sbias[CH + c * 32 + 4 * k + 2]) * hv.z);
+          o.w = rn_tf32(sigmoidf_(v[4 * k + 3] + sbias[CH + c * 32 + 4 * k + 3]) * hv.w);
           *reinterpret_cast<float4*>(rhp + c * 32 + 4 * k) = o;
         }
       }
@@ -245,12 +257,14 @@ convgru_pass_kernel(const __grid_constant__ CUtensorMap map_h, const __grid_cons
       tc::mbar_wait(s2_done, it_tile & 1);
       tc::tc_fence_after();
       float* op = p.h_out + pix * CH;
+      float* opr = p.h_out_tf32 ? p.h_out_tf32 + pix * CH : nullptr;
 #pragma unroll 1
       for (int c = 0; c < CH / 32; ++c) {
         float zv[32], qv[32];
         tc::tmem_ld_32x32(taddr + c * 32, zv);
         tc::tmem_ld_32x32(taddr + 2 * CH + c * 32, qv);
         tc::tmem_ld_wait();
+        if (!live) continue;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const float4 hv = *reinterpret_cast<const float4*>(hp + c * 32 + 4 * k);
@@ -264,6 +278,9 @@ convgru_pass_kernel(const __grid_constant__ CUtensorMap map_h, const __grid_cons
             o[e] = (1.0f - z) * hh[e] + z * q;
           }
           *reinterpret_cast<float4*>(op + c * 32 + 4 * k) = make_float4(o[0], o[1], o[2], o[3]);
+          if (opr)
+            *reinterpret_cast<float4*>(opr + c * 32 + 4 * k) =
+                make_float4(rn_tf32(o[0]), rn_tf32(o[1]), rn_tf32(o[2]), rn_tf32(o[3]));
         }
       }
       tc::tc_fence_before();
@@ -299,9 +316,10 @@ extern "C" int scflow_convgru_pack_weights(const float* wz, const float* wr, con
   return check_launch();
 }
 
-extern "C" int scflow_convgru_pass_fwd(const float* h_in, const float* x, const float* wpack,
-                                       float* h_out, float* rh_scratch, int n, int hgt, int wid,
-                                       int ch, int cx, int pass, void* stream) {
+extern "C" int scflow_convgru_pass_fwd(const float* h_in, const float* h_in_tf32, const float* x,
+                                       const float* wpack, float* h_out, float* h_out_tf32,
+                                       float* rh_scratch, int n, int hgt, int wid, int ch, int cx,
+                                       int pass, void* stream) {
   using namespace scflow;
   using namespace scflow::gru;
   if (!h_in || !x || !wpack || !h_out || !rh_scratch) return SCFLOW_E_NULL;
@@ -309,21 +327,30 @@ extern "C" int scflow_convgru_pass_fwd(const float* h_in, const float* x, const 
   if (pass != 0 && pass != 1) return SCFLOW_E_UNSUPPORTED;
   const int axis = pass == 0 ? wid : hgt;           // convolution axis length
   if (n <= 0 || hgt <= 0 || wid <= 0 || axis > BM || (BM % axis) != 0) return SCFLOW_E_BAD_SHAPE;
-  const int G = BM / axis;
+  int G = BM / axis;
   const int lines = pass == 0 ? hgt : wid;
-  if ((lines % G) != 0) return SCFLOW_E_BAD_SHAPE;
-  if (!aligned16(h_in) || !aligned16(x) || !aligned16(wpack) || !aligned16(h_out) || !aligned16(rh_scratch))
+  int ni = 1;
+  if (hgt * wid < BM) {                             // small maps: a tile is BM/(H*W) whole images
+    if (BM % (hgt * wid) != 0) return SCFLOW_E_BAD_SHAPE;
+    ni = BM / (hgt * wid);
+    G = lines;
+  } else if ((lines % G) != 0) {
+    return SCFLOW_E_BAD_SHAPE;
+  }
+  if (!aligned16(h_in) || !aligned16(x) || !aligned16(wpack) || !aligned16(h_out) || !aligned16(rh_scratch) ||
+      !aligned16(h_in_tf32) || !aligned16(h_out_tf32))
     return SCFLOW_E_MISALIGNED;
+  const float* h_mma = h_in_tf32 ? h_in_tf32 : h_in;    // what the tensor core reads
 
   // activation maps: dims (c, x, y, n); box = 32 channels x the tile's pixel rectangle
   auto act_map = [&](CUtensorMap* mp, const float* base, int c) {
     const uint64_t dims[4] = {(uint64_t)c, (uint64_t)wid, (uint64_t)hgt, (uint64_t)n};
     const uint64_t strides[3] = {(uint64_t)c * 4, (uint64_t)wid * c * 4, (uint64_t)hgt * wid * c * 4};
-    const uint32_t box[4] = {BK, (uint32_t)(pass == 0 ? wid : G), (uint32_t)(pass == 0 ? G : hgt), 1};
+    const uint32_t box[4] = {BK, (uint32_t)(pass == 0 ? wid : G), (uint32_t)(pass == 0 ? G : hgt), (uint32_t)ni};
     return tc::encode_f32_map(mp, base, 4, dims, strides, box, tc::kTmaSw128);
   };
   CUtensorMap map_h, map_x, map_rh, map_w;
-  if (!act_map(&map_h, h_in, CH) || !act_map(&map_x, x, CX) || !act_map(&map_rh, rh_scratch, CH))
+  if (!act_map(&map_h, h_mma, CH) || !act_map(&map_x, x, CX) || !act_map(&map_rh, rh_scratch, CH))
     return SCFLOW_E_DRIVER;
   {
     const uint64_t dims[2] = {BK, (uint64_t)TAPS * KB_ALL * ROWS};
@@ -332,10 +359,12 @@ extern "C" int scflow_convgru_pass_fwd(const float* h_in, const float* x, const 
     if (!tc::encode_f32_map(&map_w, wpack, 2, dims, strides, box, tc::kTmaSw128)) return SCFLOW_E_DRIVER;
   }
   Params p;
-  p.h_in = h_in; p.bias = wpack + (size_t)TAPS * KB_ALL * ROWS * BK; p.h_out = h_out; p.rh = rh_scratch;
+  p.h_in = h_in; p.bias = wpack + (size_t)TAPS * KB_ALL * ROWS * BK; p.h_out = h_out; p.h_out_tf32 = h_out_tf32; p.rh = rh_scratch;
   p.n = n; p.H = hgt; p.W = wid; p.pass = pass; p.G = G;
+  p.ni = ni;
+  p.total_pix = (long long)n * hgt * wid;
   p.tiles_per_img = lines / G;
-  p.total_tiles = n * p.tiles_per_img;
+  p.total_tiles = ((n + ni - 1) / ni) * p.tiles_per_img;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(convgru_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
@@ -347,5 +376,47 @@ extern "C" int scflow_convgru_pass_fwd(const float* h_in, const float* x, const 
   if (sms <= 0) sms = 148;
   const int grid = p.total_tiles < sms ? p.total_tiles : sms;
   convgru_pass_kernel<<<grid, THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(map_h, map_x, map_rh, map_w, p);
+  return check_launch();
+}
+
+namespace scflow {
+namespace gru {
+__global__ void pack_nhwc_kernel(const float* __restrict__ a, int ca, const float* __restrict__ b, int cb,
+                                 const float* __restrict__ f, int cf, float* __restrict__ dst, int cdst,
+                                 int dst_off, long long npix, int P, int round_tf32) {
+  const int ctot = ca + cb + cf;
+  const long long total = npix * ctot;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long pix = i / ctot;
+    const int c = (int)(i - pix * ctot);
+    float v;
+    if (c < ca) {
+      v = a[pix * ca + c];
+    } else if (c < ca + cb) {
+      v = b[pix * cb + (c - ca)];
+    } else {
+      const long long n = pix / P;
+      v = f[(n * cf + (c - ca - cb)) * P + (pix - n * P)];
+    }
+    dst[pix * cdst + dst_off + c] = round_tf32 ? rn_tf32(v) : v;
+  }
+}
+}  // namespace gru
+}  // namespace scflow
+
+extern "C" int scflow_pack_nhwc(const float* a, int ca, const float* b, int cb, const float* f, int cf,
+                                float* dst, int cdst, int dst_off, long long npix, int P,
+                                int round_tf32, void* stream) {
+  using namespace scflow;
+  if (!dst || (ca > 0 && !a) || (cb > 0 && !b) || (cf > 0 && !f)) return SCFLOW_E_NULL;
+  if (ca < 0 || cb < 0 || cf < 0 || npix <= 0 || P <= 0 || dst_off < 0 || dst_off + ca + cb + cf > cdst)
+    return SCFLOW_E_BAD_SHAPE;
+  const long long total = npix * (ca + cb + cf);
+  if (total == 0) return SCFLOW_OK;
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  gru::pack_nhwc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a, ca, b, cb, f, cf, dst, cdst,
+                                                                          dst_off, npix, P, round_tf32);
   return check_launch();
 }

@@ -161,13 +161,26 @@ corr_lookup_kernel(const LookupParams p) {
 
 }  // namespace scflow
 
+namespace scflow {
+int launch_corr_lookup_nhwc(const float* const* levels, const float* flow, float* out, short* windows,
+                            int n, int h, int w, int div_mode, cudaStream_t stream);
+}
+
 extern "C" int scflow_corr_lookup_fwd(const float* const* levels, int num_levels,
                                       const float* flow, float* out, short* windows, int n,
-                                      int h, int w, int radius, int div_mode, void* stream) {
+                                      int h, int w, int radius, int div_mode, int out_layout,
+                                      void* stream) {
   using namespace scflow;
   if (!levels || !flow || !out) return SCFLOW_E_NULL;
   if (radius != kR || num_levels != kLevels) return SCFLOW_E_UNSUPPORTED;
   if (div_mode != SCFLOW_DIV_IEEE && div_mode != SCFLOW_DIV_RCP) return SCFLOW_E_UNSUPPORTED;
+  if (out_layout != SCFLOW_LAYOUT_NCHW && out_layout != SCFLOW_LAYOUT_NHWC) return SCFLOW_E_UNSUPPORTED;
+  if (out_layout == SCFLOW_LAYOUT_NHWC) {
+    if (n <= 0 || h < 8 || w < 8) return SCFLOW_E_BAD_SHAPE;
+    for (int l = 0; l < kLevels; ++l)
+      if (!levels[l]) return SCFLOW_E_NULL;
+    return launch_corr_lookup_nhwc(levels, flow, out, windows, n, h, w, div_mode, (cudaStream_t)stream);
+  }
   if (n <= 0 || h < 8 || w < 8 || ((h * w) % kQB) != 0) return SCFLOW_E_BAD_SHAPE;
   LookupParams p;
   for (int l = 0; l < kLevels; ++l) {

@@ -68,6 +68,14 @@ __device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, uint64_t* ba
       "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0,
+                                            int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0,
                                             int c1) {
   asm volatile(
@@ -187,8 +195,10 @@ inline EncodeTiledFn get_encode_tiled() {
 constexpr int kTmaNone = 0, kTmaSw128 = 1, kTmaSw128Atom32 = 2;
 
 // fp32 tensor map of rank `rank`; dims/box innermost first; strides in BYTES for dims 1..rank-1.
+// l2_promote: widen L2 fills to 256 B (streaming tiles) or leave them at sector size (gathers).
 inline bool encode_f32_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
-                           const uint64_t* strides_bytes, const uint32_t* box, int swizzle) {
+                           const uint64_t* strides_bytes, const uint32_t* box, int swizzle,
+                           bool l2_promote = true) {
   EncodeTiledFn fn = get_encode_tiled();
   if (!fn) return false;
   cuuint64_t gdim[5], gstr[4];
@@ -204,7 +214,8 @@ inline bool encode_f32_map(CUtensorMap* map, const void* base, int rank, const u
                   swizzle == kTmaSw128 ? CU_TENSOR_MAP_SWIZZLE_128B
                   : swizzle == kTmaSw128Atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
                                                : CU_TENSOR_MAP_SWIZZLE_NONE,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  l2_promote ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;
 }
 

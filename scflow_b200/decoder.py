@@ -20,7 +20,7 @@ from typing import Optional, Sequence, Union
 import torch
 import torch.nn as nn
 
-from . import ops
+from . import gru, gru_tc, ops
 from .modules import (ConvGRU, ConvModule, CorrelationPyramid, CorrLookup, MotionEncoder, XHead,
                       _no_grad_only)
 from .registry import MODELS, register
@@ -76,6 +76,15 @@ class SCFlowDecoder(nn.Module):
         self.mask_encoder = nn.Sequential(ConvModule(1, 64, 3, padding=1, **kw),
                                           ConvModule(64, 32, 3, padding=1, **kw))
 
+    def _convs_channels_last(self) -> None:
+        """cuDNN-side convolutions of the loop take channels-last activations (what the lookup
+        and GRU kernels produce); their filters are re-laid once, values unchanged."""
+        mods = (self.encoder, self.flow_pred, self.mask_pred, self.delta_flow_encoder, self.mask_encoder,
+                self.pose_pred)
+        for m in (c for top in mods for c in top.modules()):
+            if isinstance(m, nn.Conv2d) and not m.weight.is_contiguous(memory_format=torch.channels_last):
+                m.weight.data = m.weight.data.contiguous(memory_format=torch.channels_last)
+
     def forward(self, feat_render: torch.Tensor, feat_real: torch.Tensor, h_feat: torch.Tensor,
                 cxt_feat: torch.Tensor, ref_rotation: torch.Tensor, ref_translation: torch.Tensor,
                 depth: torch.Tensor, internel_k: torch.Tensor, label: torch.Tensor,
@@ -94,11 +103,30 @@ class SCFlowDecoder(nn.Module):
         flow_from_pose, flow_from_pred, mask_preds = [], [], []
         # scflow_decoder.py:197-198 on the caller-supplied init flow (zeros from the refiner)
         flow = ops.downsample(init_flow.float(), scale, 1.0 / scale)
+        fused_gru = gru.BACKEND == "tcgen05"
+        if fused_gru:
+            # Channels-last state for the whole loop.  x = cat[cxt | motion | flow] lives in one
+            # (N,h,w,256) buffer: the context half is packed once, the motion half every iteration
+            # (scflow_pack_nhwc, rounding to nearest TF32 for the tensor core); h is updated in
+            # place together with its TF32 copy.  Values equal the reference's NCHW tensors.
+            self._convs_channels_last()
+            n_, _, hh, ww = h_feat.shape
+            h_state = h_feat.float().permute(0, 2, 3, 1).contiguous()
+            h_round = gru_tc.round_tf32(h_state)
+            rh = torch.empty_like(h_state)
+            x_buf = torch.empty((n_, hh, ww, self.gru.x_channels), device=h_state.device, dtype=torch.float32)
+            ops.pack_nhwc(x_buf, 0, a=cxt_feat.float().permute(0, 2, 3, 1).contiguous())
+            h_feat = h_state.permute(0, 3, 1, 2)
         for _ in range(self.iters):
             corr = self.corr_lookup(corr_pyramid, flow)
-            motion_feat = self.encoder(corr, flow)
-            x = torch.cat([cxt_feat, motion_feat], dim=1)
-            h_feat = self.gru(h_feat, x)
+            if fused_gru:
+                motion = self.encoder.features(corr, flow.contiguous(memory_format=torch.channels_last))
+                ops.pack_nhwc(x_buf, self.cxt_channels, a=motion.permute(0, 2, 3, 1), planar=flow)
+                gru_tc.update_inplace(self.gru, h_state, h_round, x_buf, rh)
+            else:
+                motion_feat = self.encoder(corr, flow)
+                x = torch.cat([cxt_feat, motion_feat], dim=1)
+                h_feat = self.gru(h_feat, x)
             delta_flow_pred = self.flow_pred(h_feat)
             mask = torch.sigmoid(self.mask_pred(h_feat))
             delta_flow_feat = self.delta_flow_encoder(delta_flow_pred)

@@ -2,14 +2,18 @@
 
 Weights stay fp32 nn.Parameters under the reference names; the packed [tap][k-block][z|r|q][32]
 copy is a derived cache keyed on the parameters' version counters and storage, rebuilt after
-load_state_dict / optimizer steps / .to(device) and never saved."""
-from __future__ import annotations
+load_state_dict / optimizer steps / .to(device) and never saved.
 
-import ctypes
+Operand rounding: tcgen05 kind::tf32 ignores the low 13 mantissa bits of its fp32 operands, a
+truncation whose bias adds up coherently over K = 1920.  Every tensor-core operand is therefore
+rounded to the NEAREST TF32 by its producer (weights when packed, x by scflow_pack_nhwc, r*h and
+the MMA copy of h by the kernel's own epilogues); the gating arithmetic keeps the exact fp32 h."""
+from __future__ import annotations
 
 import torch
 
 from . import _lib
+from . import ops
 from .ops import _chk, _ptr, _stream, _timed
 
 
@@ -41,22 +45,31 @@ def packed_weights(mod, p: int) -> torch.Tensor:
     return out
 
 
-def forward_nhwc(mod, h: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
-    """h (N,H,W,128), x (N,H,W,256) channels-last contiguous -> new h (N,H,W,128)."""
+def round_tf32(t: torch.Tensor) -> torch.Tensor:
+    """Nearest-TF32 copy of a channels-last (N,H,W,C) tensor (one launch)."""
+    return ops.pack_nhwc(torch.empty_like(t), 0, a=t, round_tf32=True)
+
+
+def update_inplace(mod, h: torch.Tensor, h_r: torch.Tensor, x_r: torch.Tensor, rh: torch.Tensor) -> None:
+    """Both passes of the SeqConv GRU, in place: h (N,H,W,128) exact state, h_r its nearest-TF32
+    copy (the tensor-core operand), x_r (N,H,W,256) already rounded, rh scratch like h.
+    In place is safe: a tile spans the whole convolution axis, so it reads only its own pixels."""
     lib = _lib.load()
-    h, x = _chk(h, "h"), _chk(x, "x")
     n, H, W, ch = h.shape
-    cx = x.shape[-1]
-    out = torch.empty_like(h)
-    rh = torch.empty_like(h)
-    src = h
+    cx = x_r.shape[-1]
     for p in (0, 1):
         wp = packed_weights(mod, p)
         with _timed("scflow_convgru_pass_fwd"):
-            rc = lib.scflow_convgru_pass_fwd(_ptr(src), _ptr(x), _ptr(wp), _ptr(out), _ptr(rh), n, H, W, ch, cx,
-                                             p, _stream())
+            rc = lib.scflow_convgru_pass_fwd(_ptr(h), _ptr(h_r), _ptr(x_r), _ptr(wp), _ptr(h), _ptr(h_r), _ptr(rh),
+                                             n, H, W, ch, cx, p, _stream())
         _lib.check(rc, "scflow_convgru_pass_fwd")
-        src = out          # second pass updates in place (a tile only reads its own pixels)
+
+
+def forward_nhwc(mod, h: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """h (N,H,W,128), x (N,H,W,256) channels-last contiguous -> new h (N,H,W,128)."""
+    h, x = _chk(h, "h"), _chk(x, "x")
+    out = h.clone()
+    update_inplace(mod, out, round_tf32(h), round_tf32(x), torch.empty_like(h))
     return out
 
 

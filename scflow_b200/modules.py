@@ -143,9 +143,12 @@ class MotionEncoder(nn.Module):
         self.out_channels = [126]
         self.out_net = nn.Sequential(ConvModule(192 + 64, 126, 3, padding=1, **kw))
 
+    def features(self, corr: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
+        """The 126 learned motion channels (raft_decoder.py:162-165), before `flow` is appended."""
+        return self.out_net(torch.cat([self.corr_net(corr), self.flow_net(flow)], dim=1))
+
     def forward(self, corr: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
-        out = self.out_net(torch.cat([self.corr_net(corr), self.flow_net(flow)], dim=1))
-        return torch.cat([out, flow], dim=1)
+        return torch.cat([self.features(corr, flow), flow], dim=1)
 
 
 class XHead(nn.Module):

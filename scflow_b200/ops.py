@@ -93,9 +93,16 @@ def corr_pyramid(feat1: torch.Tensor, feat2: torch.Tensor, num_levels: int = 4,
     return levels
 
 
+LAYOUT_NCHW, LAYOUT_NHWC = 0, 1
+
+
 def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int = 4,
-                div_mode: int = DIV_IEEE, return_windows: bool = False):
-    """CorrLookup.forward (corr_lookup.py:102-136): (N, L*(2r+1)^2, H, W)."""
+                div_mode: int = DIV_IEEE, return_windows: bool = False, channels_last: bool = True):
+    """CorrLookup.forward (corr_lookup.py:102-136): (N, L*(2r+1)^2, H, W).
+
+    With `channels_last` (default) the result has the reference's shape but channels-last
+    strides (memory (N, H, W, 324)): what the warp-per-query kernel writes and what the
+    downstream convolutions consume without a layout pass."""
     lib = _lib.load()
     fl = _chk(flow, "flow")
     n, two, h, w = fl.shape
@@ -106,13 +113,43 @@ def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int
             raise _lib.ScflowError(f"pyramid[{l}] has shape {tuple(p.shape)}")
     L = len(lv)
     d = 2 * radius + 1
-    out = torch.empty((n, L * d * d, h, w), device=fl.device, dtype=torch.float32)
+    if channels_last:
+        out = torch.empty((n, h, w, L * d * d), device=fl.device, dtype=torch.float32).permute(0, 3, 1, 2)
+    else:
+        out = torch.empty((n, L * d * d, h, w), device=fl.device, dtype=torch.float32)
     win = torch.empty((n * h * w, L, 2, d), device=fl.device, dtype=torch.int16) if return_windows else None
     arr = (ctypes.c_void_p * L)(*[p.data_ptr() for p in lv])
     with _timed("scflow_corr_lookup_fwd", 1):
-        rc = lib.scflow_corr_lookup_fwd(arr, L, _ptr(fl), _ptr(out), _ptr(win), n, h, w, radius, div_mode, _stream())
+        rc = lib.scflow_corr_lookup_fwd(arr, L, _ptr(fl), _ptr(out), _ptr(win), n, h, w, radius, div_mode,
+                                        LAYOUT_NHWC if channels_last else LAYOUT_NCHW, _stream())
     _lib.check(rc, "scflow_corr_lookup_fwd")
     return (out, win) if return_windows else out
+
+
+def pack_nhwc(dst: torch.Tensor, dst_off: int, a: Optional[torch.Tensor] = None,
+              b: Optional[torch.Tensor] = None, planar: Optional[torch.Tensor] = None,
+              round_tf32: bool = True) -> torch.Tensor:
+    """dst[..., dst_off:dst_off+ca+cb+cf] = cat[a, b, planar] per pixel, optionally rounded to the
+    nearest TF32.  dst (N,H,W,C) and a, b (N,H,W,c) are channels-last contiguous; planar is
+    (N,cf,H,W).  Replaces the torch.cat + layout pass that builds the ConvGRU input."""
+    lib = _lib.load()
+    dst = _chk(dst, "dst")
+    n, H, W, cd = dst.shape
+    ca = cb = cf = 0
+    if a is not None:
+        a = _chk(a, "a"); ca = a.shape[-1]
+        assert a.shape[:3] == dst.shape[:3]
+    if b is not None:
+        b = _chk(b, "b"); cb = b.shape[-1]
+        assert b.shape[:3] == dst.shape[:3]
+    if planar is not None:
+        planar = _chk(planar, "planar"); cf = planar.shape[1]
+        assert planar.shape[0] == n and planar.shape[2:] == (H, W)
+    with _timed("scflow_pack_nhwc", 1):
+        rc = lib.scflow_pack_nhwc(_ptr(a), ca, _ptr(b), cb, _ptr(planar), cf, _ptr(dst), cd, dst_off,
+                                  n * H * W, H * W, 1 if round_tf32 else 0, _stream())
+    _lib.check(rc, "scflow_pack_nhwc")
+    return dst
 
 
 def lift_points(depth, K, R0, t0):

@@ -77,14 +77,18 @@ def test_corr_pyramid_properties_full_size():
 
 
 # ------------------------------------------------------------------ a2 lookup
+@pytest.mark.parametrize("channels_last", [True, False])
 @pytest.mark.parametrize("div_mode", [ops.DIV_IEEE, ops.DIV_RCP])
-@pytest.mark.parametrize("n,h,w", [(2, 8, 16), (1, 32, 32), (1, 16, 64)])
-def test_lookup_vs_oracle_bit_exact_windows(div_mode, n, h, w):
+@pytest.mark.parametrize("n,h,w", [(2, 8, 16), (1, 32, 32), (1, 16, 64), (3, 8, 8), (1, 64, 64)])
+def test_lookup_vs_oracle_bit_exact_windows(div_mode, n, h, w, channels_last):
     ft = syn.make_features(n, h, w, seed=11, c=16, hc=4)
     pyr = O.correlation_pyramid(ft["feat_render"], ft["feat_real"], 4)
     flow = lookup_flow(n, h, w, 12)
     want, wwin = O.corr_lookup(pyr, flow, 4, div_mode, return_windows=True)
-    got, gwin = ops.corr_lookup([p.to(DEV) for p in pyr], flow.to(DEV), 4, div_mode, return_windows=True)
+    got, gwin = ops.corr_lookup([p.to(DEV) for p in pyr], flow.to(DEV), 4, div_mode, return_windows=True,
+                                channels_last=channels_last)
+    assert got.shape == want.shape
+    assert got.is_contiguous(memory_format=torch.channels_last if channels_last else torch.contiguous_format)
     # window selection: integer corner indices, bit-exact (kernel clamps far-outside windows to
     # [-32, size+32], where every tap is zero padding anyway)
     for l in range(4):
@@ -94,11 +98,38 @@ def test_lookup_vs_oracle_bit_exact_windows(div_mode, n, h, w):
     assert rel(got, want) < 2e-6
 
 
-def test_lookup_golden_fixture(golden_dir):
-    g = np.load(os.path.join(golden_dir, "lookup_small.npz"))
-    pyr = [torch.from_numpy(g[f"pyr{i}"]).to(DEV) for i in range(4)]
-    got = ops.corr_lookup(pyr, torch.from_numpy(g["flow"]).to(DEV), 4, ops.DIV_IEEE)
-    assert rel(got, torch.from_numpy(g["out"])) < 2e-6
+@pytest.mark.parametrize("channels_last", [True, False])
+@pytest.mark.parametrize("name", ["lookup_small", "lookup_sq32"])
+def test_lookup_golden_fixture(golden_dir, name, channels_last):
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    if name == "lookup_small":
+        pyr = [torch.from_numpy(g[f"pyr{i}"]) for i in range(4)]
+        sub = slice(None)
+    else:      # inputs come from the seed; the fixture holds every other output pixel
+        n, c, h, w = (int(v) for v in g["shape"])
+        ft = syn.make_features(n, h, w, seed=11, c=c, hc=4)
+        pyr = O.correlation_pyramid(ft["feat_render"], ft["feat_real"], 4)
+        sub = slice(None, None, 2)
+    got = ops.corr_lookup([p.to(DEV) for p in pyr], torch.from_numpy(g["flow"]).to(DEV), 4, ops.DIV_IEEE,
+                          channels_last=channels_last)
+    assert rel(got[:, :, sub, sub], torch.from_numpy(g["out"])) < 5e-6
+
+
+def test_lookup_layouts_agree_full_size():
+    """cfg2 size (N=64, 32x32): the warp-per-query NHWC kernel and the NCHW kernel replay the
+    same op sequence, so values and window selection are identical; large flows push windows
+    partly and wholly outside the levels (zero padding)."""
+    g = torch.Generator(device=DEV).manual_seed(2)
+    n, h, w = 64, 32, 32
+    pyr = [torch.randn(n * h * w, 1, h >> l, w >> l, device=DEV, generator=g) for l in range(4)]
+    flow = 9.0 * torch.randn(n, 2, h, w, device=DEV, generator=g)
+    flow[0] = 0.0                      # integer coordinates: the round-trip edge case
+    flow[1] = 500.0                    # everything out of range
+    a, wa = ops.corr_lookup(pyr, flow, 4, return_windows=True, channels_last=True)
+    b, wb = ops.corr_lookup(pyr, flow, 4, return_windows=True, channels_last=False)
+    assert torch.equal(wa, wb)
+    assert torch.equal(a.contiguous(), b)
+    assert float(a[1].abs().max()) == 0.0
 
 
 def test_lookup_impulse_and_zero_flow():
