@@ -128,7 +128,9 @@ def test_lookup_layouts_agree_full_size():
     a, wa = ops.corr_lookup(pyr, flow, 4, return_windows=True, channels_last=True)
     b, wb = ops.corr_lookup(pyr, flow, 4, return_windows=True, channels_last=False)
     assert torch.equal(wa, wb)
-    assert torch.equal(a.contiguous(), b)
+    # same windows and weights; the NHWC kernel sums the four corners row-wise (separable), the
+    # NCHW kernel in ATen's nw, ne, sw, se order: equal up to fp32 rounding order
+    assert float((a - b).abs().max()) < 4e-6 * float(b.abs().max())
     assert float(a[1].abs().max()) == 0.0
 
 

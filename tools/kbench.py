@@ -1,0 +1,69 @@
+"""Per-kernel micro-benchmark at cfg2 shapes (N=64, 256x256 crops -> 32x32 features).
+    python tools/kbench.py [lookup] [gru] [corr] [pose] [--n 64] [--s 256]
+Each kernel is timed with CUDA events over `reps` launches on rotating buffers larger than L2."""
+import os, sys, argparse
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from scflow_b200 import ops, gru_tc, modules
+
+ap = argparse.ArgumentParser()
+ap.add_argument("which", nargs="*", default=["lookup", "gru", "corr", "pose"])
+ap.add_argument("--n", type=int, default=64)
+ap.add_argument("--s", type=int, default=256)
+ap.add_argument("--reps", type=int, default=20)
+a = ap.parse_args()
+dev = "cuda"
+N, S = a.n, a.s
+h = w = S // 8
+P = h * w
+HBM = 6553.3
+
+
+def timeit(fn, reps=a.reps, warm=3):
+    for i in range(warm):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(reps):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps * 1e3   # us
+
+
+g = torch.Generator(device=dev).manual_seed(0)
+if "corr" in a.which:
+    f1 = [torch.randn(N, 256, h, w, device=dev, generator=g) for _ in range(2)]
+    f2 = [torch.randn(N, 256, h, w, device=dev, generator=g) for _ in range(2)]
+    us = timeit(lambda i: ops.corr_pyramid(f1[i % 2], f2[i % 2], 4, ops.PREC_TF32))
+    by = N * (2 * P * 256 * 4 + 85 * P * P * 4 // 64)
+    fl = N * 2.0 * P * P * 256
+    print(f"corr_pyramid tf32   {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)  {fl/us/1e6:6.1f} TFLOP/s")
+if "lookup" in a.which:
+    sets = 2 if N * P * P * 4 * 85 // 64 > 100e6 else 4
+    pyrs = [[torch.randn(N * P, 1, h >> l, w >> l, device=dev, generator=g) for l in range(4)] for _ in range(sets)]
+    flow = [2.0 * torch.randn(N, 2, h, w, device=dev, generator=g) for _ in range(sets)]
+    by = N * (P * 324 * 4 + P * 4 * 100 * 4 + 8 * P)
+    for cl in (True, False):
+        us = timeit(lambda i: ops.corr_lookup(pyrs[i % sets], flow[i % sets], 4, channels_last=cl))
+        print(f"corr_lookup {'nhwc' if cl else 'nchw'}    {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)")
+if "gru" in a.which:
+    mod = modules.ConvGRU(128, 256).to(dev)
+    hs = [torch.randn(N, h, w, 128, device=dev, generator=g) for _ in range(3)]
+    xs = [gru_tc.round_tf32(torch.randn(N, h, w, 256, device=dev, generator=g)) for _ in range(3)]
+    hr = [gru_tc.round_tf32(t) for t in hs]
+    rh = torch.empty_like(hs[0])
+    us = timeit(lambda i: gru_tc.update_inplace(mod, hs[i % 3], hr[i % 3], xs[i % 3], rh)) / 2
+    fl = 3 * 2.0 * N * P * 128 * 1920
+    print(f"convgru pass        {us:8.1f} us  {fl/us/1e6:6.1f} TFLOP/s tf32")
+if "pose" in a.which:
+    from scflow_b200 import synthetic as syn
+    cr = {k: v.to(dev) for k, v in syn.make_crops(4, S, seed=1).items()}
+    rep = lambda t: t.repeat((N // 4,) + (1,) * (t.dim() - 1)).contiguous()
+    c = {k: rep(v) for k, v in cr.items()}
+    dR6 = torch.tensor([1., 0, 0, 0, 1., 0], device=dev).repeat(N, 1) + 0.01 * torch.randn(N, 6, device=dev)
+    dt = 0.01 * torch.randn(N, 3, device=dev)
+    us = timeit(lambda i: ops.pose_flow(c["R0"], c["t0"], c["K"], dR6=dR6, dt=dt, depth=c["depth"], R0=c["R0"], t0=c["t0"]))
+    by = N * (4 * S * S + 8 * S * S + 8 * P)
+    print(f"pose_flow           {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)  (includes 4 output allocations)")
