@@ -152,6 +152,29 @@ int scflow_upsample_fwd(const float* in, const float* add, float* out, int n, in
 int scflow_downsample_fwd(const float* in, float* out, int n, int c, int H, int W, int scale,
                           float mul, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * f3 (glue)  InstanceNorm2d / eval BatchNorm2d + ReLU + residual add of the RAFT encoders
+ *            models/encoder/raft_encoder.py:286-314, BasicBlock models/backbone/resnet.py:12-92
+ *            replaces per layer: conv-bias add_, native_batch_norm (2 kernels), relu_, add, relu_.
+ * Channels-last activations (n, P, C) fp32, C % 4 == 0.
+ * scflow_chan_stats_nhwc: sums[n][C][2] (fp64) = per image and channel (sum, sum of squares).
+ * scflow_norm_act_nhwc:   out = act( N(x) [+ N_r(res)] ), act = ReLU if relu != 0, where each side
+ *   is normalised by its statistics (sums != NULL: (v - mean) * rsqrt(var_biased + eps), the
+ *   affine=False InstanceNorm2d of the encoder), or mapped by a per-channel affine (scale/shift
+ *   != NULL: eval BatchNorm2d folded with the convolution bias), or passed through (both NULL).
+ *   res may be NULL.  out may alias x or res.
+ * ------------------------------------------------------------------------------------------- */
+int scflow_chan_stats_nhwc(const float* x, double* sums, int n, int P, int C, void* stream);
+int scflow_norm_act_nhwc(const float* x, const double* sums, const float* scale, const float* shift,
+                         const float* res, const double* res_sums, const float* res_scale,
+                         const float* res_shift, float* out, int n, int P, int C, float eps,
+                         int relu, void* stream);
+
+/* (n, P, C) channels-last -> (n, C, P) planar, with optional round-to-nearest TF32: the hand-over
+ * of channels-last encoder features to scflow_corr_pyramid_fwd (planar operands), replacing a
+ * torch .contiguous() pass.  in != out. */
+int scflow_nhwc_to_nchw(const float* in, float* out, int n, int P, int C, int round_tf32, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,196 @@
+// Channels-last normalisation glue of the RAFT encoders (models/encoder/raft_encoder.py:286-314,
+// BasicBlock in models/backbone/resnet.py:12-92): InstanceNorm2d / eval BatchNorm2d + ReLU +
+// residual add as TWO HBM-bound launches per layer instead of the reference's
+// bias add_ + batch_norm(collect, transform) + relu_ + add + relu_ chain (each a full pass).
+//
+//   chan_stats_kernel   per (image, channel) sum and sum of squares over the pixels, fp32 partials
+//                       folded into fp64 atomics: [n][C][2] doubles
+//   norm_act_kernel     out = act( x*sc + sh  [+ res*rsc + rsh] ) with (sc, sh) either derived from
+//                       the fp64 sums (instance norm: rstd, -mean*rstd), or a per-channel affine
+//                       (eval batch norm folded with the convolution bias), or identity
+//
+// Layout (n, P, C) fp32, C % 4 == 0: a thread owns one float4 channel group and strides over the
+// pixels of its chunk, so every warp access is a run of full 128-byte lines.
+#include "common.cuh"
+
+namespace scflow {
+namespace na {
+
+constexpr int kThreads = 256;
+constexpr int kChunk = 512;      // pixels per CTA
+
+__global__ void __launch_bounds__(kThreads)
+chan_stats_kernel(const float* __restrict__ x, double* __restrict__ sums, int P, int C) {
+  const int groups = C >> 2;                 // float4 channel groups
+  const int lanes = kThreads / groups;       // pixel lanes
+  const int cg = threadIdx.x % groups, pl = threadIdx.x / groups;
+  const int n = blockIdx.y;
+  const int p0 = blockIdx.x * kChunk, p1 = min(p0 + kChunk, P);
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = s;
+  if (pl < lanes) {
+    const float4* src = reinterpret_cast<const float4*>(x + ((size_t)n * P) * C) + cg;
+    for (int p = p0 + pl; p < p1; p += lanes) {
+      const float4 v = __ldg(src + (size_t)p * groups);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      q.x = fmaf(v.x, v.x, q.x); q.y = fmaf(v.y, v.y, q.y);
+      q.z = fmaf(v.z, v.z, q.z); q.w = fmaf(v.w, v.w, q.w);
+    }
+  }
+  // fold the pixel lanes of a channel group in fp64 through shared memory
+  __shared__ double red[kThreads][8];
+  double* mine = red[threadIdx.x];
+  mine[0] = s.x; mine[1] = s.y; mine[2] = s.z; mine[3] = s.w;
+  mine[4] = q.x; mine[5] = q.y; mine[6] = q.z; mine[7] = q.w;
+  __syncthreads();
+  for (int t = threadIdx.x; t < groups * 8; t += kThreads) {
+    const int g = t >> 3, e = t & 7;
+    double acc = 0.0;
+    for (int l = 0; l < lanes; ++l) acc += red[l * groups + g][e];
+    const int c = 4 * g + (e & 3);
+    atomicAdd(&sums[((size_t)n * C + c) * 2 + (e >> 2)], acc);
+  }
+}
+
+struct Side {
+  const float* x;          // (n, P, C) or nullptr (side absent)
+  const double* sums;      // instance-norm statistics [n][C][2], or nullptr
+  const float* scale;      // per-channel affine [C] (with shift), or nullptr
+  const float* shift;
+};
+
+__device__ __forceinline__ void side_coeffs(const Side& s, int n, int C, int c, int P, float eps,
+                                            float* sc, float* sh) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (s.sums) {
+      const double su = s.sums[((size_t)n * C + c + j) * 2], sq = s.sums[((size_t)n * C + c + j) * 2 + 1];
+      const double mean = su / P;
+      const double var = fmax(sq / P - mean * mean, 0.0);       // biased, as F.instance_norm
+      const float rstd = 1.0f / sqrtf((float)var + eps);
+      sc[j] = rstd;
+      sh[j] = -(float)mean * rstd;
+    } else if (s.scale) {
+      sc[j] = s.scale[c + j];
+      sh[j] = s.shift[c + j];
+    } else {
+      sc[j] = 1.0f;
+      sh[j] = 0.0f;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+norm_act_kernel(const Side a, const Side r, float* __restrict__ out, int P, int C, float eps, int relu) {
+  const int groups = C >> 2;
+  const int lanes = kThreads / groups;
+  const int cg = threadIdx.x % groups, pl = threadIdx.x / groups;
+  if (pl >= lanes) return;
+  const int n = blockIdx.y;
+  const int p0 = blockIdx.x * kChunk, p1 = min(p0 + kChunk, P);
+  float sc[4], sh[4], rsc[4], rsh[4];
+  side_coeffs(a, n, C, 4 * cg, P, eps, sc, sh);
+  if (r.x) side_coeffs(r, n, C, 4 * cg, P, eps, rsc, rsh);
+  const size_t base = ((size_t)n * P) * groups + cg;
+  const float4* xa = reinterpret_cast<const float4*>(a.x) + base;
+  const float4* xr = r.x ? reinterpret_cast<const float4*>(r.x) + base : nullptr;
+  float4* o = reinterpret_cast<float4*>(out) + base;
+  for (int p = p0 + pl; p < p1; p += lanes) {
+    const float4 v = xa[(size_t)p * groups];
+    float4 y;
+    y.x = fmaf(v.x, sc[0], sh[0]); y.y = fmaf(v.y, sc[1], sh[1]);
+    y.z = fmaf(v.z, sc[2], sh[2]); y.w = fmaf(v.w, sc[3], sh[3]);
+    if (xr) {
+      const float4 w = xr[(size_t)p * groups];
+      y.x += fmaf(w.x, rsc[0], rsh[0]); y.y += fmaf(w.y, rsc[1], rsh[1]);
+      y.z += fmaf(w.z, rsc[2], rsh[2]); y.w += fmaf(w.w, rsc[3], rsh[3]);
+    }
+    if (relu) {
+      y.x = fmaxf(y.x, 0.f); y.y = fmaxf(y.y, 0.f); y.z = fmaxf(y.z, 0.f); y.w = fmaxf(y.w, 0.f);
+    }
+    o[(size_t)p * groups] = y;
+  }
+}
+
+}  // namespace na
+}  // namespace scflow
+
+static int check_shape(int n, int P, int C) {
+  if (n <= 0 || P <= 0 || C < 4 || (C & 3) != 0 || C > 4 * scflow::na::kThreads || n > 65535)
+    return SCFLOW_E_BAD_SHAPE;
+  return SCFLOW_OK;
+}
+
+extern "C" int scflow_chan_stats_nhwc(const float* x, double* sums, int n, int P, int C, void* stream) {
+  using namespace scflow;
+  if (!x || !sums) return SCFLOW_E_NULL;
+  if (int rc = check_shape(n, P, C)) return rc;
+  if (!aligned16(x)) return SCFLOW_E_MISALIGNED;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cudaMemsetAsync(sums, 0, (size_t)n * C * 2 * sizeof(double), st) != cudaSuccess) return check_launch();
+  dim3 grid((P + na::kChunk - 1) / na::kChunk, n);
+  na::chan_stats_kernel<<<grid, na::kThreads, 0, st>>>(x, sums, P, C);
+  return check_launch();
+}
+
+extern "C" int scflow_norm_act_nhwc(const float* x, const double* sums, const float* scale,
+                                    const float* shift, const float* res, const double* res_sums,
+                                    const float* res_scale, const float* res_shift, float* out,
+                                    int n, int P, int C, float eps, int relu, void* stream) {
+  using namespace scflow;
+  if (!x || !out) return SCFLOW_E_NULL;
+  if ((scale == nullptr) != (shift == nullptr) || (res_scale == nullptr) != (res_shift == nullptr))
+    return SCFLOW_E_NULL;
+  if (int rc = check_shape(n, P, C)) return rc;
+  if (!aligned16(x) || !aligned16(out) || !aligned16(res)) return SCFLOW_E_MISALIGNED;
+  na::Side a{x, sums, scale, shift};
+  na::Side r{res, res_sums, res_scale, res_shift};
+  dim3 grid((P + na::kChunk - 1) / na::kChunk, n);
+  na::norm_act_kernel<<<grid, na::kThreads, 0, (cudaStream_t)stream>>>(a, r, out, P, C, eps, relu);
+  return check_launch();
+}
+
+// ---------------------------------------------------------------------------------------------
+// (n, P, C) channels-last -> (n, C, P) planar, optionally rounding to the nearest TF32: hands the
+// channels-last encoder features to the correlation GEMM (whose operands are MN-major = planar)
+// already rounded, instead of letting tcgen05 truncate them (a biased error that the 8 refinement
+// iterations amplify: 6.4e-5 rad on the cfg1 fixture against 6e-6 rounded).
+namespace scflow {
+namespace na {
+__global__ void __launch_bounds__(256)
+nhwc_to_nchw_kernel(const float* __restrict__ in, float* __restrict__ out, int P, int C, int round_tf32) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z, p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const float* src = in + (size_t)n * P * C;
+  float* dst = out + (size_t)n * C * P;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int p = p0 + ty + 8 * j, c = c0 + tx;
+    float v = 0.0f;
+    if (p < P && c < C) v = __ldg(src + (size_t)p * C + c);
+    if (round_tf32) {
+      uint32_t u;
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+      v = __uint_as_float(u);
+    }
+    tile[ty + 8 * j][tx] = v;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = c0 + ty + 8 * j, p = p0 + tx;
+    if (p < P && c < C) dst[(size_t)c * P + p] = tile[tx][ty + 8 * j];
+  }
+}
+}  // namespace na
+}  // namespace scflow
+
+extern "C" int scflow_nhwc_to_nchw(const float* in, float* out, int n, int P, int C, int round_tf32,
+                                   void* stream) {
+  using namespace scflow;
+  if (!in || !out) return SCFLOW_E_NULL;
+  if (n <= 0 || P <= 0 || C <= 0 || n > 65535 || (C + 31) / 32 > 65535) return SCFLOW_E_BAD_SHAPE;
+  dim3 grid((P + 31) / 32, (C + 31) / 32, n);
+  na::nhwc_to_nchw_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(in, out, P, C, round_tf32);
+  return check_launch();
+}

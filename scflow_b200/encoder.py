@@ -6,8 +6,56 @@ from __future__ import annotations
 
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
+from . import ops
 from .registry import register
+
+
+# ------------------------------------------------------------------ fused inference path
+# Convolutions stay on cuDNN (SURVEY 8f-3 "next") but run channels-last end to end, and every
+# norm + ReLU (+ residual add) is two launches of our HBM-bound kernels (csrc/norm_act.cu)
+# instead of the reference's bias add_ / batch_norm / relu_ / add / relu_ chain.
+def _conv_cl(conv: nn.Conv2d, x: torch.Tensor, with_bias: bool = False) -> torch.Tensor:
+    """cuDNN convolution on a channels-last (N,C,H,W)-shaped tensor; the filter is re-laid once."""
+    w = conv.weight
+    if not w.is_contiguous(memory_format=torch.channels_last):
+        conv.weight.data = w.data.contiguous(memory_format=torch.channels_last)
+        w = conv.weight
+    y = F.conv2d(x, w, conv.bias if with_bias else None, conv.stride, conv.padding)
+    return y.contiguous(memory_format=torch.channels_last)      # no-op when cuDNN kept the layout
+
+
+def _nhwc(x: torch.Tensor) -> torch.Tensor:
+    return x.permute(0, 2, 3, 1)
+
+
+def _bn_affine(bn: nn.BatchNorm2d, bias):
+    """Eval BatchNorm2d folded with the preceding convolution bias: y = conv*scale + shift."""
+    key = tuple((t.data_ptr(), t._version) for t in (bn.weight, bn.bias, bn.running_mean, bn.running_var, bias)
+                if t is not None)
+    hit = bn.__dict__.get("_scflow_affine")
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    with torch.no_grad():
+        scale = bn.weight.float() * torch.rsqrt(bn.running_var.float() + bn.eps)
+        b = bias.float() if bias is not None else 0.0
+        shift = bn.bias.float() + (b - bn.running_mean.float()) * scale
+        val = (scale.contiguous(), shift.contiguous())
+    bn.__dict__["_scflow_affine"] = (key, val)
+    return val
+
+
+def _side(norm: nn.Module, y: torch.Tensor, bias):
+    """Normalisation coefficients of conv output y (channels-last view): kwargs for ops.norm_act."""
+    if isinstance(norm, nn.InstanceNorm2d):
+        # the convolution bias cancels in (v - mean): it is never added
+        if norm.affine or norm.track_running_stats:
+            raise NotImplementedError("InstanceNorm2d(affine/track_running_stats) on the fused path")
+        return dict(sums=ops.chan_stats(y)), norm.eps
+    if isinstance(norm, nn.BatchNorm2d):
+        return dict(affine=_bn_affine(norm, bias)), norm.eps
+    raise NotImplementedError(type(norm))
 
 
 def _norm(kind: str, ch: int, postfix):
@@ -37,6 +85,23 @@ class BasicBlock(nn.Module):
         if self.downsample is not None:
             identity = self.downsample(x)
         return self.relu(out + identity)
+
+    def forward_fused(self, x: torch.Tensor) -> torch.Tensor:
+        """x, result: channels-last (N,C,H,W)-shaped tensors."""
+        n1, n2 = getattr(self, self.norm1_name), getattr(self, self.norm2_name)
+        o = _conv_cl(self.conv1, x)
+        kw, eps = _side(n1, _nhwc(o), self.conv1.bias)
+        ops.norm_act(_nhwc(o), relu=True, eps=eps, **kw)
+        o2 = _conv_cl(self.conv2, o)
+        kw, eps = _side(n2, _nhwc(o2), self.conv2.bias)
+        if self.downsample is not None:
+            d = _conv_cl(self.downsample[0], x)
+            kr, _ = _side(self.downsample[1], _nhwc(d), self.downsample[0].bias)
+            kw.update({"res_" + k: v for k, v in kr.items()})
+            ops.norm_act(_nhwc(o2), res=_nhwc(d), relu=True, eps=eps, **kw)
+        else:
+            ops.norm_act(_nhwc(o2), res=_nhwc(x), relu=True, eps=eps, **kw)
+        return o2
 
 
 def _res_layer(inplanes, planes, stride, norm):
@@ -71,8 +136,28 @@ class RAFTEncoder(nn.Module):
             inpl = planes
         self.conv2 = nn.Conv2d(128, out_channels, 1)
 
+    def _fused_ok(self, x: torch.Tensor) -> bool:
+        n1 = getattr(self, self.norm1_name)
+        if torch.is_grad_enabled() or not x.is_cuda or x.dtype != torch.float32:
+            return False
+        return isinstance(n1, nn.InstanceNorm2d) or not self.training
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self._fused_ok(x):
+            return self.forward_fused(x)
         x = self.relu(getattr(self, self.norm1_name)(self.conv1(x)))
         for name in self.res_layers:
             x = getattr(self, name)(x)
         return self.conv2(x)
+
+    def forward_fused(self, x: torch.Tensor) -> torch.Tensor:
+        """Inference path: same values as forward() (the IN-cancelled conv bias aside, a rounding-
+        level difference), channels-last activations, norms through csrc/norm_act.cu."""
+        x = x.contiguous(memory_format=torch.channels_last)
+        y = _conv_cl(self.conv1, x)
+        kw, eps = _side(getattr(self, self.norm1_name), _nhwc(y), self.conv1.bias)
+        ops.norm_act(_nhwc(y), relu=True, eps=eps, **kw)
+        for name in self.res_layers:
+            for block in getattr(self, name):
+                y = block.forward_fused(y)
+        return _conv_cl(self.conv2, y, with_bias=True)

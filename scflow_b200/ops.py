@@ -76,11 +76,37 @@ def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def _planar_tf32(t: torch.Tensor, name: str) -> torch.Tensor:
+    """NCHW-contiguous copy of a feature map rounded to the nearest TF32 (one launch); takes
+    channels-last tensors (the fused encoder's output) without a separate layout pass."""
+    lib = _lib.load()
+    if not t.is_cuda or t.dtype != torch.float32:
+        _chk(t, name)
+    n, c, h, w = t.shape
+    out = torch.empty((n, c, h, w), device=t.device, dtype=torch.float32)
+    if t.is_contiguous(memory_format=torch.channels_last) and not t.is_contiguous():
+        with _timed("scflow_nhwc_to_nchw", 1):
+            rc = lib.scflow_nhwc_to_nchw(_ptr(t), _ptr(out), n, h * w, c, 1, _stream())
+        _lib.check(rc, "scflow_nhwc_to_nchw")
+        return out
+    t = t.contiguous()
+    if t.numel() % 4:
+        raise _lib.ScflowError(f"{name}: element count must be a multiple of 4")
+    with _timed("scflow_pack_nhwc", 1):
+        rc = lib.scflow_pack_nhwc(_ptr(t), 4, None, 0, None, 0, _ptr(out), 4, 0, t.numel() // 4, 1, 1, _stream())
+    _lib.check(rc, "scflow_pack_nhwc")
+    return out
+
+
 def corr_pyramid(feat1: torch.Tensor, feat2: torch.Tensor, num_levels: int = 4,
                  precision: int = PREC_TF32) -> List[torch.Tensor]:
     """CorrelationPyramid.forward (raft_decoder.py:35-58): list of (N*H*W, 1, H>>l, W>>l)."""
     lib = _lib.load()
-    f1, f2 = _chk(feat1, "feat1"), _chk(feat2, "feat2")
+    if precision == PREC_TF32:
+        # tcgen05 kind::tf32 truncates its operands; hand it features rounded to nearest instead
+        f1, f2 = _planar_tf32(feat1, "feat1"), _planar_tf32(feat2, "feat2")
+    else:
+        f1, f2 = _chk(feat1, "feat1"), _chk(feat2, "feat2")
     n, c, h, w = f1.shape
     assert f2.shape == f1.shape
     levels = [torch.empty((n * h * w, 1, h >> l, w >> l), device=f1.device, dtype=torch.float32)
@@ -150,6 +176,44 @@ def pack_nhwc(dst: torch.Tensor, dst_off: int, a: Optional[torch.Tensor] = None,
                                   n * H * W, H * W, 1 if round_tf32 else 0, _stream())
     _lib.check(rc, "scflow_pack_nhwc")
     return dst
+
+
+def chan_stats(x: torch.Tensor) -> torch.Tensor:
+    """(N,H,W,C) channels-last -> (N,C,2) fp64 per-image, per-channel (sum, sum of squares)."""
+    lib = _lib.load()
+    x = _chk(x, "x")
+    n, H, W, C = x.shape
+    sums = torch.empty((n, C, 2), device=x.device, dtype=torch.float64)
+    with _timed("scflow_chan_stats_nhwc", 1):
+        rc = lib.scflow_chan_stats_nhwc(_ptr(x), _ptr(sums), n, H * W, C, _stream())
+    _lib.check(rc, "scflow_chan_stats_nhwc")
+    return sums
+
+
+def norm_act(x: torch.Tensor, sums=None, affine=None, res=None, res_sums=None, res_affine=None,
+             relu: bool = True, eps: float = 1e-5, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out = act(N(x) [+ N_r(res)]) on channels-last (N,H,W,C) tensors; see scflow_norm_act_nhwc.
+    `affine` / `res_affine` are (scale, shift) per-channel fp32 tensors."""
+    lib = _lib.load()
+    x = _chk(x, "x")
+    n, H, W, C = x.shape
+    if res is not None:
+        res = _chk(res, "res")
+        assert res.shape == x.shape
+    if out is None:
+        out = x
+    sc, sh = affine if affine is not None else (None, None)
+    rsc, rsh = res_affine if res_affine is not None else (None, None)
+    if sums is not None:
+        sums = _chk(sums, "sums", torch.float64)
+    if res_sums is not None:
+        res_sums = _chk(res_sums, "res_sums", torch.float64)
+    with _timed("scflow_norm_act_nhwc", 1):
+        rc = lib.scflow_norm_act_nhwc(_ptr(x), _ptr(sums), _ptr(sc), _ptr(sh), _ptr(res), _ptr(res_sums),
+                                      _ptr(rsc), _ptr(rsh), _ptr(out), n, H * W, C, float(eps),
+                                      1 if relu else 0, _stream())
+    _lib.check(rc, "scflow_norm_act_nhwc")
+    return out
 
 
 def lift_points(depth, K, R0, t0):

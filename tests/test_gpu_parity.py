@@ -359,3 +359,45 @@ def test_decoder_with_tcgen05_gru(golden_dir):
     et = float((out[3][-1].cpu() - tg[-1]).abs().max())
     print(f"tcgen05 GRU + TF32 corr: pose err {er:.3e} rad, {et:.3e} mm")
     assert er < 1e-4 and et < 0.1
+
+
+# ------------------------------------------------------------------ f3 glue: norm + act kernels
+@pytest.mark.parametrize("n,h,w,c", [(2, 16, 24, 64), (3, 8, 8, 96), (1, 32, 32, 128), (2, 5, 7, 256)])
+def test_instance_norm_relu_residual_vs_torch(n, h, w, c):
+    g = torch.Generator().manual_seed(c)
+    x = (torch.randn(n, c, h, w, generator=g) * 3 + 1.5)
+    r = torch.randn(n, c, h, w, generator=g)
+    want = torch.relu(torch.nn.functional.instance_norm(x.double()) + torch.nn.functional.instance_norm(r.double()))
+    xn = x.to(DEV).permute(0, 2, 3, 1).contiguous()
+    rn = r.to(DEV).permute(0, 2, 3, 1).contiguous()
+    sums = ops.chan_stats(xn)
+    ref_s = torch.stack([x.double().sum((2, 3)), (x.double() ** 2).sum((2, 3))], dim=-1)
+    assert float((sums.cpu() - ref_s).abs().max() / ref_s.abs().max()) < 1e-6
+    out = ops.norm_act(xn.clone(), sums=sums, res=rn, res_sums=ops.chan_stats(rn), relu=True)
+    assert rel(out.permute(0, 3, 1, 2), want) < 2e-6
+    # plain norm + relu in place, and identity residual
+    y = xn.clone()
+    ops.norm_act(y, sums=sums, res=rn, relu=False)
+    want2 = torch.nn.functional.instance_norm(x.double()) + r.double()
+    assert rel(y.permute(0, 3, 1, 2), want2) < 2e-6
+
+
+@pytest.mark.parametrize("norm", ["IN", "BN"])
+def test_encoder_fused_path_matches_module_path(norm):
+    """The channels-last fused inference path of RAFTEncoder equals the plain nn.Module path
+    (cuDNN fp32 in both; the strict-fp32 fixture disables TF32)."""
+    from scflow_b200.encoder import RAFTEncoder
+    torch.manual_seed(3)
+    enc = RAFTEncoder(3, 256, net_type="Basic", norm_cfg=dict(type=norm)).to(DEV).eval()
+    if norm == "BN":
+        for m in enc.modules():
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.running_mean.normal_(0, 0.3); m.running_var.uniform_(0.5, 2.0)
+                m.weight.data.uniform_(0.5, 1.5); m.bias.data.normal_(0, 0.2)
+    x = torch.rand(2, 3, 64, 64, device=DEV)
+    with torch.no_grad():
+        got = enc(x)
+        with torch.enable_grad():            # grad mode on -> the module path
+            want = enc(x.clone().requires_grad_(False)).detach()
+    assert got.shape == want.shape
+    assert rel(got, want) < 2e-5
