@@ -30,6 +30,15 @@ UNIT = "crops/s"
 WORKLOAD = "SCFlow refiner inference, batch 64 YCB-V-shaped 256x256 crops per GPU, 8 iters"
 
 
+def workload(S=256):
+    return WORKLOAD if S == 256 else WORKLOAD.replace("256x256", f"{S}x{S}")
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full`
+# captures (profiles/): kernel -> bytes.  null where no capture exists for the current kernel.
+NCU_TRAFFIC = {}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -37,6 +46,28 @@ def peaks():
         return dict(hbm=float(d["hbm_gbs"]), bf16=float(d["bf16_tflops"]),
                     bf16_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), src="measured")
     return dict(hbm=6650.0, bf16=1590.0, bf16_sustained=1400.0, src="fallback")
+
+
+def measure_tf32_peak(dev, reps=8):
+    """cuBLAS TF32 GEMM 8192^3 (fp32 operands, allow_tf32), the same way MEASURED_PEAKS.json's bf16
+    figure was taken; back-to-back reps = the sustained figure a kernel inside a long step sees."""
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        n = 8192
+        a = torch.randn(n, n, device=dev); b = torch.randn(n, n, device=dev)
+        for _ in range(2):
+            a @ b
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            a @ b
+        e1.record()
+        torch.cuda.synchronize()
+        return 2.0 * n ** 3 * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
 
 
 class ClockSampler(threading.Thread):
@@ -69,9 +100,9 @@ class ClockSampler(threading.Thread):
                     reasons=reasons, samples=len(self.rows))
 
 
-def make_batch(n, seed):
+def make_batch(n, seed, S=256):
     from scflow_b200 import synthetic as syn
-    cr = syn.make_crops(n, 256, seed=seed)
+    cr = syn.make_crops(n, S, seed=seed)
     cr["labels"][:] = cr["labels"][0]
     return {k: cr[k] for k in ("rendered_images", "real_images", "depth", "K", "R0", "t0", "labels")}
 
@@ -151,8 +182,19 @@ def reference_arm(args):
 
 
 # --------------------------------------------------------------------------- our arm
+def algorithmic_flops(name, B, S=256):
+    P = (S // 8) ** 2
+    if name == "scflow_convgru_pass_fwd":
+        return B * 3 * 2.0 * P * 128 * 1920            # three gate convolutions of one pass
+    if name == "scflow_corr_pyramid_fwd":
+        return B * 2.0 * P * P * 256
+    return None
+
+
 def algorithmic_bytes(name, B, S=256, C=256):
-    """Per-launch algorithmic HBM bytes (DESIGN.md 'Kernels')."""
+    """Per-launch algorithmic HBM bytes (DESIGN.md 'Kernels').  Launchers that serve
+    several tensor shapes (norm/act, stats, pack, resize) are attributed from their measured
+    arguments instead: see ops.STATS bytes."""
     P = (S // 8) ** 2
     if name == "scflow_corr_pyramid_fwd":
         return B * (2 * P * C * 4 + (85 * P * P * 4) // 64)
@@ -167,7 +209,7 @@ def algorithmic_bytes(name, B, S=256, C=256):
 
 def ours(args):
     from scflow_b200 import ops
-    from scflow_b200.refiner import SCFlowRefinerCore, gather_poses
+    from scflow_b200.refiner import GraphedRefiner, SCFlowRefinerCore, gather_poses
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -175,27 +217,41 @@ def ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    B = args.batch
+    B, S = args.batch, args.image
     torch.backends.cudnn.allow_tf32 = True      # cuDNN parts at the reference's own GPU default
     torch.backends.cudnn.benchmark = True
-    core = seeded_weights(SCFlowRefinerCore(256)).eval().to(dev)
-    if os.environ.get("SCFLOW_CHANNELS_LAST", "0") == "1":
-        core = core.to(memory_format=torch.channels_last)
+    core = seeded_weights(SCFlowRefinerCore(S)).eval().to(dev)
     # two distinct input sets, alternated, so no step re-reads the previous step's inputs from L2;
     # a step's working set (118 MB inputs, 340 MB pyramid, activations) is several times the L2
-    host = [tile_batch(make_batch(4, 1234 + 10 * rank + s), B) for s in range(2)]
+    host = [tile_batch(make_batch(4, 1234 + 10 * rank + s, S), B) for s in range(2)]
     pinned = [{k: v.pin_memory() for k, v in h.items()} for h in host]
     resident = [{k: v.to(dev) for k, v in h.items()} for h in host]
     h2d = sum(v.numel() * v.element_size() for v in host[0].values())
     d2h = B * 12 * 4
+    W = max(args.warmup, 3)
+    for i in range(W):                          # eager warm-up: cuDNN autotune, weight packs, folded BN
+        core.refine(resident[i % 2])
+    torch.cuda.synchronize()
+    if args.no_graph:
+        graphs = g_e2e = None
+    else:
+        # the public call a deployment makes: one CUDA graph per input signature
+        graphs = [GraphedRefiner(core, resident[i], warmup=1, own_inputs=False) for i in range(2)]
+        g_e2e = GraphedRefiner(core, resident[0], warmup=1, own_inputs=True)
 
     def step_resident(i):
-        return gather_poses(core.refine(resident[i % 2]), B * world)
+        poses = graphs[i % 2]() if graphs else core.refine(resident[i % 2])
+        return gather_poses(poses, B * world)
 
     def step_e2e(i):
-        b = {k: v.to(dev, non_blocking=True) for k, v in pinned[i % 2].items()}
-        poses = gather_poses(core.refine(b), B * world)
-        return poses.cpu()                                    # D2H read of the step's result
+        if g_e2e:
+            poses = g_e2e(pinned[i % 2])                      # H2D into the graph's inputs, replay
+        else:
+            poses = core.refine({k: v.to(dev, non_blocking=True) for k, v in pinned[i % 2].items()})
+        return gather_poses(poses, B * world).cpu()           # D2H read of the step's result
+
+    def step_eager(i):
+        return gather_poses(core.refine(resident[i % 2]), B * world)
 
     def barrier():
         if world > 1:
@@ -216,7 +272,6 @@ def ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
-    W = max(args.warmup, 3)
     for i in range(W):
         step_resident(i)
     for i in range(2):
@@ -226,13 +281,16 @@ def ours(args):
         sampler.start()
     if os.environ.get("SCFLOW_PROFILE") == "1":      # ncu --profile-from-start off
         torch.cuda.profiler.start()
-    ms_total = timed(step_resident, args.steps, True)
+    ms_total = timed(step_resident, args.steps, False)
     if os.environ.get("SCFLOW_PROFILE") == "1":
         torch.cuda.profiler.stop()
     launches = ops.STATS.count
-    per_kernel = ops.STATS.summary()
     ms_e2e = timed(step_e2e, args.steps, False)
+    # per-kernel attribution: the same steps run eagerly with CUDA events around every launcher
+    ms_eager = timed(step_eager, args.steps, True)
+    per_kernel = ops.STATS.summary()
     clocks = sampler.stop() if sampler else None
+    tf32_peak = measure_tf32_peak(dev) if rank == 0 else None
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -242,34 +300,47 @@ def ours(args):
     e2e_val = B * world / (ms_e2e / args.steps / 1e3)
     pk = peaks()
     kern = {}
-    for name, (calls, tot) in per_kernel.items():
-        ab = algorithmic_bytes(name, B)
+    for name, (calls, tot, nbytes) in per_kernel.items():
         avg_ms = tot / calls
-        kern[name] = {"calls_per_step": calls / args.steps, "avg_ms": avg_ms, "share_of_step": tot / ms_total,
-                      "gbs": (ab / (avg_ms * 1e-3) / 1e9) if ab else None}
-    cand = {k: v for k, v in kern.items() if v["gbs"] is not None}
-    top = max(cand, key=lambda k: cand[k]["avg_ms"] * cand[k]["calls_per_step"])
-    roof = {"kernel": top, "bound": "hbm", "achieved": cand[top]["gbs"], "peak": pk["hbm"], "unit": "GB/s",
-            "frac": cand[top]["gbs"] / pk["hbm"], "traffic": None, "peak_source": pk["src"],
-            "algorithmic_bytes_per_launch": algorithmic_bytes(top, B)}
+        ab = algorithmic_bytes(name, B, S) or (nbytes / calls if nbytes else None)
+        fl = algorithmic_flops(name, B, S)
+        kern[name] = {"calls_per_step": calls / args.steps, "avg_ms": avg_ms, "share_of_eager_step": tot / ms_eager,
+                      "gbs": (ab / (avg_ms * 1e-3) / 1e9) if ab else None,
+                      "hbm_frac": (ab / (avg_ms * 1e-3) / 1e9 / pk["hbm"]) if ab else None,
+                      "tflops": (fl / (avg_ms * 1e-3) / 1e12) if fl else None}
+    # roofline object: the kernel of ours with the largest share of the step
+    top = max(kern, key=lambda k: kern[k]["avg_ms"] * kern[k]["calls_per_step"])
+    traffic = NCU_TRAFFIC.get(top)
+    if kern[top]["tflops"] is not None and top == "scflow_convgru_pass_fwd":
+        roof = {"kernel": top, "bound": "tensor", "achieved": kern[top]["tflops"], "peak": tf32_peak,
+                "unit": "TFLOP/s", "frac": kern[top]["tflops"] / tf32_peak, "traffic": traffic,
+                "peak_source": "cuBLAS TF32 8192^3 sustained, measured in this run (bf16 figure of "
+                               "MEASURED_PEAKS.json: %.0f sustained)" % pk["bf16_sustained"],
+                "algorithmic_flops_per_launch": algorithmic_flops(top, B, S)}
+    else:
+        roof = {"kernel": top, "bound": "hbm", "achieved": kern[top]["gbs"], "peak": pk["hbm"], "unit": "GB/s",
+                "frac": kern[top]["hbm_frac"], "traffic": traffic, "peak_source": pk["src"],
+                "algorithmic_bytes_per_launch": algorithmic_bytes(top, B, S)}
     # bounded CPU baseline on this box's host cores (rank 0, N=1 only)
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
-        n, ts = cpu_run(tile_batch(make_batch(2, 1234), 8), cpu_refiner_state(), 2, 1)
+        n, ts = cpu_run(tile_batch(make_batch(2, 1234, S), 8), cpu_refiner_state(), 2, 1)
         cpu = {"value": n / (sum(ts) / len(ts)), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                "sample": f"{n} crops per run, 1 warm-up + 2 timed runs of the oracle port (reference CPU path)"}
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "tf32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "crops_per_gpu_per_step": B, "image": 256, "iters": 8,
+        "config": {"workload": workload(S), "crops_per_gpu_per_step": B, "image": S, "iters": 8,
                    "parallelism": f"batch-shard x{world} + pose all-gather",
                    "l2": "two alternating input sets; per-step working set (>450 MB) exceeds the 126 MB L2",
+                   "execution": "eager launches" if args.no_graph else "CUDA graph replay per step",
                    "gru_backend": __import__("scflow_b200.gru", fromlist=["BACKEND"]).BACKEND},
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": launches, "roofline": roof, "kernels": kern, "cpu_baseline": cpu, "clocks": clocks,
+        "gpu_launches": launches, "roofline": roof, "tf32_peak_tflops": tf32_peak,
+        "eager_ms_per_step": ms_eager / args.steps, "kernels": kern, "cpu_baseline": cpu, "clocks": clocks,
     }))
     if world > 1:
         dist.destroy_process_group()
@@ -283,6 +354,8 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
+    ap.add_argument("--image", type=int, default=256, help="crop side (256 = configs[1]; 512 = configs[3])")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)

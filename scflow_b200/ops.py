@@ -24,17 +24,17 @@ class LaunchStats:
     def __init__(self):
         self.count = 0
         self.timing = False
-        self.events = []          # (name, kernels_in_call, start, end)
+        self.events = []          # (name, kernels_in_call, start, end, algorithmic bytes or None)
 
     def reset(self, timing: bool = False):
         self.count, self.timing, self.events = 0, timing, []
 
     def summary(self):
-        """{name: (calls, total_ms)} -- call after a synchronize."""
+        """{name: (calls, total_ms, total algorithmic bytes or None)} -- call after a synchronize."""
         out = {}
-        for name, _, a, b in self.events:
-            c, t = out.get(name, (0, 0.0))
-            out[name] = (c + 1, t + a.elapsed_time(b))
+        for name, _, a, b, nb in self.events:
+            c, t, by = out.get(name, (0, 0.0, 0))
+            out[name] = (c + 1, t + a.elapsed_time(b), None if (nb is None or by is None) else by + nb)
         return out
 
 
@@ -42,8 +42,8 @@ STATS = LaunchStats()
 
 
 class _timed:
-    def __init__(self, name, kernels=1):
-        self.name, self.kernels = name, kernels
+    def __init__(self, name, kernels=1, nbytes=None):
+        self.name, self.kernels, self.nbytes = name, kernels, nbytes
 
     def __enter__(self):
         STATS.count += self.kernels
@@ -56,7 +56,7 @@ class _timed:
     def __exit__(self, *exc):
         if STATS.timing:
             self.b.record()
-            STATS.events.append((self.name, self.kernels, self.a, self.b))
+            STATS.events.append((self.name, self.kernels, self.a, self.b, self.nbytes))
         return False
 
 
@@ -85,7 +85,7 @@ def _planar_tf32(t: torch.Tensor, name: str) -> torch.Tensor:
     n, c, h, w = t.shape
     out = torch.empty((n, c, h, w), device=t.device, dtype=torch.float32)
     if t.is_contiguous(memory_format=torch.channels_last) and not t.is_contiguous():
-        with _timed("scflow_nhwc_to_nchw", 1):
+        with _timed("scflow_nhwc_to_nchw", 1, 8 * t.numel()):
             rc = lib.scflow_nhwc_to_nchw(_ptr(t), _ptr(out), n, h * w, c, 1, _stream())
         _lib.check(rc, "scflow_nhwc_to_nchw")
         return out
@@ -171,7 +171,7 @@ def pack_nhwc(dst: torch.Tensor, dst_off: int, a: Optional[torch.Tensor] = None,
     if planar is not None:
         planar = _chk(planar, "planar"); cf = planar.shape[1]
         assert planar.shape[0] == n and planar.shape[2:] == (H, W)
-    with _timed("scflow_pack_nhwc", 1):
+    with _timed("scflow_pack_nhwc", 1, 8 * n * H * W * (ca + cb + cf)):
         rc = lib.scflow_pack_nhwc(_ptr(a), ca, _ptr(b), cb, _ptr(planar), cf, _ptr(dst), cd, dst_off,
                                   n * H * W, H * W, 1 if round_tf32 else 0, _stream())
     _lib.check(rc, "scflow_pack_nhwc")
@@ -184,7 +184,7 @@ def chan_stats(x: torch.Tensor) -> torch.Tensor:
     x = _chk(x, "x")
     n, H, W, C = x.shape
     sums = torch.empty((n, C, 2), device=x.device, dtype=torch.float64)
-    with _timed("scflow_chan_stats_nhwc", 1):
+    with _timed("scflow_chan_stats_nhwc", 1, 4 * x.numel()):
         rc = lib.scflow_chan_stats_nhwc(_ptr(x), _ptr(sums), n, H * W, C, _stream())
     _lib.check(rc, "scflow_chan_stats_nhwc")
     return sums
@@ -208,7 +208,7 @@ def norm_act(x: torch.Tensor, sums=None, affine=None, res=None, res_sums=None, r
         sums = _chk(sums, "sums", torch.float64)
     if res_sums is not None:
         res_sums = _chk(res_sums, "res_sums", torch.float64)
-    with _timed("scflow_norm_act_nhwc", 1):
+    with _timed("scflow_norm_act_nhwc", 1, 4 * x.numel() * (3 if res is not None else 2)):
         rc = lib.scflow_norm_act_nhwc(_ptr(x), _ptr(sums), _ptr(sc), _ptr(sh), _ptr(res), _ptr(res_sums),
                                       _ptr(rsc), _ptr(rsh), _ptr(out), n, H * W, C, float(eps),
                                       1 if relu else 0, _stream())
@@ -269,7 +269,7 @@ def upsample(x, add=None, scale: int = 8, mul: float = 1.0):
         assert add.shape == x.shape
     n, c, h, w = x.shape
     out = torch.empty((n, c, h * scale, w * scale), device=x.device, dtype=torch.float32)
-    with _timed("scflow_upsample_fwd", 1):
+    with _timed("scflow_upsample_fwd", 1, 4 * (x.numel() * (2 if add is not None else 1) + out.numel())):
         rc = lib.scflow_upsample_fwd(_ptr(x), _ptr(add), _ptr(out), n, c, h, w, scale, float(mul), _stream())
     _lib.check(rc, "scflow_upsample_fwd")
     return out
@@ -281,7 +281,7 @@ def downsample(x, scale: int = 8, mul: float = 1.0):
     x = _chk(x, "x")
     n, c, H, W = x.shape
     out = torch.empty((n, c, H // scale, W // scale), device=x.device, dtype=torch.float32)
-    with _timed("scflow_downsample_fwd", 1):
+    with _timed("scflow_downsample_fwd", 1, 4 * (x.numel() + out.numel())):
         rc = lib.scflow_downsample_fwd(_ptr(x), _ptr(out), n, c, H, W, scale, float(mul), _stream())
     _lib.check(rc, "scflow_downsample_fwd")
     return out

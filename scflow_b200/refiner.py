@@ -72,6 +72,49 @@ class SCFlowRefinerCore(nn.Module):
         return pack_pose(out[2][-1], out[3][-1])
 
 
+class GraphedRefiner:
+    """`core.refine` for one fixed batch signature, captured once into a CUDA graph and replayed.
+
+    The refinement step is ~700 small launches (cuDNN convolutions plus our kernels); replaying a
+    graph removes the per-launch CPU cost, which otherwise bounds the step once the kernels are
+    fast.  Everything on the path is capture-safe: no host synchronisation, static shapes, all
+    buffers from the graph's private pool (TMA descriptors stay valid across replays), weight
+    packs / folded BN / cuDNN algorithm choices cached by the warm-up runs.  The pose all-gather
+    stays outside the graph.  Re-capture (build a new object) after changing weights' storage."""
+
+    def __init__(self, core: "SCFlowRefinerCore", example: Dict[str, torch.Tensor], warmup: int = 3,
+                 own_inputs: bool = True):
+        from . import ops
+        if ops.STATS.timing:
+            raise RuntimeError("turn ops.STATS timing off before capturing a graph")
+        self.core = core
+        dev = next(core.parameters()).device
+        self.inputs = {k: (v.to(dev).clone() if own_inputs else v) for k, v in example.items()}
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                core.refine(self.inputs)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        launches_before = ops.STATS.count
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.poses = core.refine(self.inputs)
+        self.launches_per_replay = ops.STATS.count - launches_before    # OUR kernels in the graph
+
+    @torch.no_grad()
+    def __call__(self, batch: Optional[Dict[str, torch.Tensor]] = None) -> torch.Tensor:
+        """Refine `batch` (device or pinned-host tensors, same shapes as the example); returns the
+        (N,12) packed poses (a static buffer: clone it to keep it across calls)."""
+        if batch is not None:
+            for k, v in batch.items():
+                self.inputs[k].copy_(v, non_blocking=True)
+        self.graph.replay()
+        from . import ops
+        ops.STATS.count += self.launches_per_replay
+        return self.poses
+
+
 def pack_pose(R: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
     return torch.cat([R.reshape(-1, 9), t.reshape(-1, 3)], dim=1).contiguous()
 
