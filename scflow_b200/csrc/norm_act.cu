@@ -29,12 +29,20 @@ chan_stats_kernel(const float* __restrict__ x, double* __restrict__ sums, int P,
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = s;
   if (pl < lanes) {
     const float4* src = reinterpret_cast<const float4*>(x + ((size_t)n * P) * C) + cg;
-    for (int p = p0 + pl; p < p1; p += lanes) {
-      const float4 v = __ldg(src + (size_t)p * groups);
+    auto acc = [&](const float4 v) {
       s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
       q.x = fmaf(v.x, v.x, q.x); q.y = fmaf(v.y, v.y, q.y);
       q.z = fmaf(v.z, v.z, q.z); q.w = fmaf(v.w, v.w, q.w);
+    };
+    int p = p0 + pl;
+    for (; p + 3 * lanes < p1; p += 4 * lanes) {      // 4 independent loads in flight
+      float4 v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = __ldg(src + (size_t)(p + j * lanes) * groups);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc(v[j]);
     }
+    for (; p < p1; p += lanes) acc(__ldg(src + (size_t)p * groups));
   }
   // fold the pixel lanes of a channel group in fp64 through shared memory
   __shared__ double red[kThreads][8];
@@ -94,21 +102,33 @@ norm_act_kernel(const Side a, const Side r, float* __restrict__ out, int P, int 
   const float4* xa = reinterpret_cast<const float4*>(a.x) + base;
   const float4* xr = r.x ? reinterpret_cast<const float4*>(r.x) + base : nullptr;
   float4* o = reinterpret_cast<float4*>(out) + base;
-  for (int p = p0 + pl; p < p1; p += lanes) {
-    const float4 v = xa[(size_t)p * groups];
+  auto apply = [&](const float4 v, const float4 w) {
     float4 y;
     y.x = fmaf(v.x, sc[0], sh[0]); y.y = fmaf(v.y, sc[1], sh[1]);
     y.z = fmaf(v.z, sc[2], sh[2]); y.w = fmaf(v.w, sc[3], sh[3]);
     if (xr) {
-      const float4 w = xr[(size_t)p * groups];
       y.x += fmaf(w.x, rsc[0], rsh[0]); y.y += fmaf(w.y, rsc[1], rsh[1]);
       y.z += fmaf(w.z, rsc[2], rsh[2]); y.w += fmaf(w.w, rsc[3], rsh[3]);
     }
     if (relu) {
       y.x = fmaxf(y.x, 0.f); y.y = fmaxf(y.y, 0.f); y.z = fmaxf(y.z, 0.f); y.w = fmaxf(y.w, 0.f);
     }
-    o[(size_t)p * groups] = y;
+    return y;
+  };
+  // four pixels per trip: 4 (8 with a residual) independent 16-byte loads in flight per thread
+  int p = p0 + pl;
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (; p + 3 * lanes < p1; p += 4 * lanes) {
+    float4 v[4], w[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = xa[(size_t)(p + j * lanes) * groups];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) w[j] = xr ? xr[(size_t)(p + j * lanes) * groups] : zero;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[(size_t)(p + j * lanes) * groups] = apply(v[j], w[j]);
   }
+  for (; p < p1; p += lanes)
+    o[(size_t)p * groups] = apply(xa[(size_t)p * groups], xr ? xr[(size_t)p * groups] : zero);
 }
 
 }  // namespace na
