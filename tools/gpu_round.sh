@@ -1,20 +1,28 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, bench, then ncu captures of the hand-written kernels.
-# usage: tools/gpu_round.sh <tag> [skip_tests]
+# One gpurun call: GPU parity tests, smoke, bench (both arms), then the ncu launch list of the same
+# bench command and ncu --set full captures of the hand-written kernels (exported to CSV here so the
+# bulky .ncu-rep files stay on the box).  usage: tools/gpu_round.sh <tag>
 set -u
 TAG=${1:-x}
 mkdir -p gpurun_out
-if [ "${2:-}" != "skip_tests" ]; then
-  timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest.log 2>&1
-  echo "pytest rc=$?" ; tail -3 gpurun_out/${TAG}_pytest.log
-fi
+timeout 900 python -m pytest tests -m gpu -q > gpurun_out/${TAG}_pytest.log 2>&1
+echo "pytest rc=$?"; tail -2 gpurun_out/${TAG}_pytest.log
+timeout 300 python __graft_entry__.py --smoke > gpurun_out/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 gpurun_out/${TAG}_smoke.log
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err
+echo "bench reference rc=$?"
 timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err
-echo "bench rc=$?"; cat gpurun_out/${TAG}_bench.json
-SCFLOW_PROFILE=1 timeout 600 python bench.py --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_plain.log 2>&1 &&
-SCFLOW_PROFILE=1 timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off \
-  -k regex:'corr_lookup_kernel|corr_tf32_kernel|convgru_pass_kernel|pose_flow_kernel' -c 33 \
-  -o gpurun_out/${TAG}_prof -f python bench.py --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu.log 2>&1
-echo "ncu full rc=$?"
+echo "bench rc=$?"; cut -c1-300 gpurun_out/${TAG}_bench.json
+CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-graph"
+SCFLOW_PROFILE=1 timeout 600 $CMD > gpurun_out/${TAG}_plain.log 2>&1 &&
 SCFLOW_PROFILE=1 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off \
-  --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu2.log 2>&1
+  --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
+for K in corr_lookup_nhwc_kernel:2:2 convgru_pass_kernel:2:2 corr_tf32_kernel:1:0 norm_act_kernel:3:10 chan_stats_kernel:2:4 pose_flow_kernel:1:2; do
+  RE=${K%%:*}; R=${K#*:}; CNT=${R%%:*}; SKIP=${R#*:}
+  SCFLOW_PROFILE=1 timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off \
+    -k regex:"$RE" -s $SKIP -c $CNT -o /tmp/${TAG}_${RE} -f $CMD > gpurun_out/${TAG}_ncu_${RE}.log 2>&1
+  echo "ncu $RE rc=$?"
+  ncu -i /tmp/${TAG}_${RE}.ncu-rep --page raw --csv > gpurun_out/${TAG}_${RE}_raw.csv 2>/dev/null
+  ncu -i /tmp/${TAG}_${RE}.ncu-rep --page source --csv > gpurun_out/${TAG}_${RE}_source.csv 2>/dev/null
+done
+ls -la gpurun_out | tail -30
