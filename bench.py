@@ -173,7 +173,7 @@ def reference_arm(args):
     ms = 1e3 * sum(ts) / len(ts)
     val = n / (ms / 1e3)
     sample = f"{n} of the 64 crops of one step per timed step (same refiner, weights and input generator)"
-    print(json.dumps({
+    _emit(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": len(ts), "warmup": max(1, min(args.warmup, 2)), "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -362,7 +362,7 @@ def ours(args):
         n, ts = cpu_run(tile_batch(make_batch(2, 1234, S), 8), cpu_refiner_state(), 2, 1)
         cpu = {"value": n / (sum(ts) / len(ts)), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                "sample": f"{n} crops per run, 1 warm-up + 2 timed runs of the oracle port (reference CPU path)"}
-    print(json.dumps({
+    _emit(json.dumps({
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "tf32", "data": "synthetic",
@@ -379,6 +379,15 @@ def ours(args):
         dist.destroy_process_group()
 
 
+_OUT = None
+
+
+def _emit(line):
+    out = _OUT or sys.stdout
+    out.write(line + "\n")
+    out.flush()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -390,6 +399,12 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--image", type=int, default=256, help="crop side (256 = configs[1]; 512 = configs[3])")
     args = ap.parse_args()
+    # libraries (NCCL's version banner, cuDNN warnings) write to fd 1: keep the real stdout for the
+    # one JSON line and send everything else to stderr
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         reference_arm(args)
     else:
