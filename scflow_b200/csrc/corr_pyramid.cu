@@ -13,6 +13,7 @@
 // kernel (reference default is fp32 SGEMM, torch.backends.cuda.matmul.allow_tf32 = False).
 #include "common.cuh"
 #include "tc_common.cuh"
+#include <cstdlib>
 
 namespace scflow {
 
@@ -136,11 +137,13 @@ constexpr int STAGES = 3;
 constexpr int A_BYTES = BM * BK * 4;             // 16 KB: [4 groups][32 k][32 q]
 constexpr int B_BYTES = BN * BK * 4;             // 32 KB: [8 rows ][32 k][32 x]
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int EPI_STRIDE = 36;                   // floats; 144-byte rows keep float4 aligned
-constexpr int EPI_WARP_BYTES = 32 * EPI_STRIDE * 4;
-constexpr int THREADS = 192;                     // warp0 TMA, warp1 MMA + TMEM alloc, warps2-5 epilogue
+constexpr int EPI_GROUPS = 2;                    // one 4-warp epilogue group per accumulator stage
+constexpr int EPI_BUF_BYTES = 32 * 128;          // 32 queries x one 32-float target row (swizzled)
+constexpr int EPI_WARP_BYTES = 2 * EPI_BUF_BYTES;
+constexpr int EPI_BYTES = EPI_GROUPS * 4 * EPI_WARP_BYTES;
+constexpr int THREADS = 64 + EPI_GROUPS * 128;   // warp0 TMA, warp1 MMA + TMEM alloc, 8 epilogue warps
 constexpr int TMEM_COLS = 512;                   // two 256-column accumulator stages
-constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + 4 * EPI_WARP_BYTES + 256;
+constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + EPI_BYTES + 256;
 
 struct Params {
   float* lvl[4];
@@ -148,22 +151,28 @@ struct Params {
   int tiles_m, tiles_y, tiles_x;
   float scale, inv_scale;
   int scale_is_pow2;
+  int dbg;              // SCFLOW_CORR_DBG bits (profiling only): 1 no L0 stores, 2 no L1-3 stores, 4 no loads, 8 no MMA
 };
 
-__device__ __forceinline__ void store_row_chunks(float* stg, const float* v, int lane) {
-#pragma unroll
-  for (int k = 0; k < 8; ++k)
-    *reinterpret_cast<float4*>(stg + lane * EPI_STRIDE + 4 * k) =
-        make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+__device__ __forceinline__ void decode_tile(const Params& p, int tile, int tiles_per_m, int& pj, int& mt, int& n) {
+  if (p.dbg & 16) {       // query tile fastest: CTAs running side by side share the TARGET tile
+    mt = tile % p.tiles_m;
+    pj = (tile / p.tiles_m) % tiles_per_m;
+  } else {                // target tile fastest: neighbours share the QUERY tile
+    pj = tile % tiles_per_m;
+    mt = (tile / tiles_per_m) % p.tiles_m;
+  }
+  n = tile / (tiles_per_m * p.tiles_m);
 }
 
+template <bool POW2>
 __global__ void __launch_bounds__(THREADS, 1)
 corr_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
-                 const Params p) {
+                 const __grid_constant__ CUtensorMap mapC, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  float* epi = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + 4 * EPI_WARP_BYTES);
+  uint8_t* epi = smem + STAGES * STAGE_BYTES;                 // 1024-byte aligned (swizzle phase)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + EPI_BYTES);
   uint64_t* full = bars;                 // [STAGES] TMA -> MMA
   uint64_t* empty = bars + STAGES;       // [STAGES] MMA -> TMA
   uint64_t* tfull = bars + 2 * STAGES;   // [2] MMA -> epilogue
@@ -179,6 +188,7 @@ corr_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   if (warp == 0 && lane == 0) {
     tc::tma_prefetch_desc(&mapA);
     tc::tma_prefetch_desc(&mapB);
+    tc::tma_prefetch_desc(&mapC);
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -199,16 +209,18 @@ corr_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int pj = tile % tiles_per_m;
-        const int mt = (tile / tiles_per_m) % p.tiles_m;
-        const int n = tile / (tiles_per_m * p.tiles_m);
+        int pj, mt, n;
+        decode_tile(p, tile, tiles_per_m, pj, mt, n);
         const int ty = pj / p.tiles_x, tx = pj % p.tiles_x;
         for (int kb = 0; kb < KB; ++kb) {
           tc::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* a_s = smem + stage * STAGE_BYTES;
+          if (p.dbg & 4) { tc::mbar_arrive(&full[stage]); }
+          else {
           tc::mbar_expect_tx(&full[stage], STAGE_BYTES);
           tc::tma_load_4d(&mapA, &full[stage], a_s, 0, kb * BK, mt * (BM / 32), n);
           tc::tma_load_4d(&mapB, &full[stage], a_s + A_BYTES, tx * 32, kb * BK, ty * 8, n);
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -228,6 +240,7 @@ corr_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           tc::tc_fence_after();
           const uint32_t a_addr = tc::smem_u32(smem + stage * STAGE_BYTES);
           const uint32_t b_addr = a_addr + A_BYTES;
+          if (!(p.dbg & 8))
 #pragma unroll
           for (int kk = 0; kk < BK / UK; ++kk) {
             // MN-major 32-bit operands: SWIZZLE_128B_BASE32B is the only layout tcgen05 accepts.
@@ -246,66 +259,66 @@ corr_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (4 warps)
+    // ------------------------------------------------------------------ epilogue (2 groups x 4 warps)
+    // Group g drains accumulator stage g (every other tile of this CTA), so one tile's epilogue may
+    // take two MMA periods.  A warp owns 32 queries (its TMEM lane quarter); a lane owns one query.
     const int quarter = warp & 3;                  // TMEM lane quarter this warp may access
-    float* stg = epi + quarter * (32 * EPI_STRIDE);
-    int acc = 0; uint32_t acc_phase = 0;
+    const int group = (warp - 2) >> 2;
+    uint8_t* stg = epi + ((group * 4 + quarter) * EPI_WARP_BYTES);
+    const uint32_t stg_lane = tc::smem_u32(stg) + lane * 128;
+    const int sw = lane & 7;                       // SWIZZLE_128B: 16-byte chunk index ^= row & 7
+    uint32_t acc_phase = 0;
     const int w1 = p.w / 2, w2 = p.w / 4, w3 = p.w / 8;
     const long long P1 = (long long)(p.h / 2) * w1, P2 = (long long)(p.h / 4) * w2,
                     P3 = (long long)(p.h / 8) * w3;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int pj = tile % tiles_per_m;
-      const int mt = (tile / tiles_per_m) % p.tiles_m;
-      const int n = tile / (tiles_per_m * p.tiles_m);
+    for (int tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += EPI_GROUPS * gridDim.x) {
+      int pj, mt, n;
+      decode_tile(p, tile, tiles_per_m, pj, mt, n);
       const int ty = pj / p.tiles_x, tx = pj % p.tiles_x;
       const long long qbase = (long long)n * P + mt * BM + quarter * 32;   // first query of this warp
-      tc::mbar_wait(&tfull[acc], acc_phase);
+      tc::mbar_wait(&tfull[group], acc_phase);
       tc::tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
-      float prev0[32], prev1[16], prev2[8];
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + group * BN;
+      float vb[2][32], prev0[32], prev1[16], prev2[8];
+      tc::tmem_ld_32x32(taddr, vb[0]);
 #pragma unroll
       for (int r = 0; r < 8; ++r) {
-        float v[32];
-        tc::tmem_ld_32x32(taddr + r * 32, v);
-        tc::tmem_ld_wait();
+        float* v = vb[r & 1];
+        tc::tmem_ld_wait_on(v);
+        if (r < 7) tc::tmem_ld_32x32(taddr + (r + 1) * 32, vb[(r + 1) & 1]);
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          v[j] = p.scale_is_pow2 ? v[j] * p.inv_scale : __fdiv_rn(v[j], p.scale);
-        // level 0: transpose the warp's 32x32 block through smem, store 4 rows x 128 B per step
-        store_row_chunks(stg, v, lane);
+        for (int j = 0; j < 32; ++j) v[j] = POW2 ? v[j] * p.inv_scale : __fdiv_rn(v[j], p.scale);
+        // level 0: the warp's 32 queries x 32 targets of row r go out as one TMA box; the store
+        // issued two rows ago must have drained this staging buffer
+        if (!(p.dbg & 1)) {
+        if (lane == 0) tc::bulk_wait_read<1>();
         __syncwarp();
         {
-          float* dst = p.lvl[0] + qbase * P + (long long)(ty * 8 + r) * p.w + tx * 32 + 4 * (lane & 7);
+          const uint32_t base = stg_lane + (r & 1) * EPI_BUF_BYTES;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int rr = i * 4 + (lane >> 3);
-            const float4 val = *reinterpret_cast<const float4*>(stg + rr * EPI_STRIDE + 4 * (lane & 7));
-            *reinterpret_cast<float4*>(dst + (long long)rr * P) = val;
-          }
+          for (int k = 0; k < 8; ++k)
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(base + ((k ^ sw) << 4)),
+                         "f"(v[4 * k]), "f"(v[4 * k + 1]), "f"(v[4 * k + 2]), "f"(v[4 * k + 3])
+                         : "memory");
         }
+        tc::fence_proxy_async();
         __syncwarp();
+        if (lane == 0) {
+          tc::tma_store_3d(&mapC, stg + (r & 1) * EPI_BUF_BYTES, tx * 32, ty * 8 + r, (int)qbase);
+          tc::bulk_commit();
+        }
+        }
         if ((r & 1) == 0) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) prev0[j] = v[j];
-        } else if (p.num_levels > 1) {
+        } else if (p.num_levels > 1 && !(p.dbg & 2)) {
           float l1[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) l1[j] = pool4(prev0[2 * j], prev0[2 * j + 1], v[2 * j], v[2 * j + 1]);
+          float* d1 = p.lvl[1] + (qbase + lane) * P1 + (long long)(ty * 4 + (r >> 1)) * w1 + tx * 16;
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            *reinterpret_cast<float4*>(stg + lane * EPI_STRIDE + 4 * k) =
-                make_float4(l1[4 * k], l1[4 * k + 1], l1[4 * k + 2], l1[4 * k + 3]);
-          __syncwarp();
-          {
-            float* dst = p.lvl[1] + qbase * P1 + (long long)(ty * 4 + (r >> 1)) * w1 + tx * 16 + 4 * (lane & 3);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int rr = i * 8 + (lane >> 2);
-              const float4 val = *reinterpret_cast<const float4*>(stg + rr * EPI_STRIDE + 4 * (lane & 3));
-              *reinterpret_cast<float4*>(dst + (long long)rr * P1) = val;
-            }
-          }
-          __syncwarp();
+            *reinterpret_cast<float4*>(d1 + 4 * k) = make_float4(l1[4 * k], l1[4 * k + 1], l1[4 * k + 2], l1[4 * k + 3]);
           if ((r & 3) == 1) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) prev1[j] = l1[j];
@@ -330,9 +343,10 @@ corr_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       }
       tc::tc_fence_before();
       __syncwarp();
-      if (lane == 0) tc::mbar_arrive(&tempty[acc]);
-      acc ^= 1; if (acc == 0) acc_phase ^= 1;
+      if (lane == 0) tc::mbar_arrive(&tempty[group]);
+      acc_phase ^= 1;
     }
+    if (lane == 0) tc::bulk_wait_all<0>();         // level-0 stores complete before the CTA exits
   }
 
   tc::tc_fence_before();
@@ -364,7 +378,8 @@ static int corr_tf32(const float* f1, const float* f2, float* const* levels, int
   if (!aligned16(f1) || !aligned16(f2)) return SCFLOW_E_MISALIGNED;
   for (int l = 0; l < num_levels; ++l)
     if (!aligned16(levels[l])) return SCFLOW_E_MISALIGNED;
-  CUtensorMap mapA, mapB;
+  CUtensorMap mapA, mapB, mapC;
+  if ((long long)n * P > 0x7fffffffLL) return SCFLOW_E_BAD_SHAPE;
   {
     const uint64_t dims[4] = {32, (uint64_t)c, (uint64_t)(P / 32), (uint64_t)n};
     const uint64_t strides[3] = {(uint64_t)P * 4, 128, (uint64_t)c * P * 4};
@@ -377,6 +392,13 @@ static int corr_tf32(const float* f1, const float* f2, float* const* levels, int
     const uint32_t box[4] = {32, BK, 8, 1};
     if (!tc::encode_f32_map(&mapB, f2, 4, dims, strides, box, tc::kTmaSw128Atom32)) return SCFLOW_E_DRIVER;
   }
+  {
+    // level 0 as (w, h, n*P) for the epilogue's stores: one box = 32 targets of one row x 32 queries
+    const uint64_t dims[3] = {(uint64_t)w, (uint64_t)h, (uint64_t)n * P};
+    const uint64_t strides[2] = {(uint64_t)w * 4, (uint64_t)P * 4};
+    const uint32_t box[3] = {32, 1, 32};
+    if (!tc::encode_f32_map(&mapC, levels[0], 3, dims, strides, box, tc::kTmaSw128)) return SCFLOW_E_DRIVER;
+  }
   Params p;
   for (int l = 0; l < 4; ++l) p.lvl[l] = l < num_levels ? levels[l] : nullptr;
   p.n = n; p.c = c; p.h = h; p.w = w; p.num_levels = num_levels;
@@ -385,14 +407,19 @@ static int corr_tf32(const float* f1, const float* f2, float* const* levels, int
   p.inv_scale = 1.0f / p.scale;
   int e; const float fr = frexpf(p.scale, &e);
   p.scale_is_pow2 = (fr == 0.5f) ? 1 : 0;
+  { const char* e = getenv("SCFLOW_CORR_DBG"); p.dbg = e ? atoi(e) : 0; }
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(corr_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+    cudaFuncSetAttribute(corr_tf32_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+    cudaFuncSetAttribute(corr_tf32_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
     attr_set = true;
   }
   const long long total = (long long)n * p.tiles_m * p.tiles_y * p.tiles_x;
   const int grid = (int)(total < device_sm_count() ? total : device_sm_count());
-  corr_tf32_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(mapA, mapB, p);
+  if (p.scale_is_pow2)
+    corr_tf32_kernel<true><<<grid, THREADS, SMEM_BYTES, st>>>(mapA, mapB, mapC, p);
+  else
+    corr_tf32_kernel<false><<<grid, THREADS, SMEM_BYTES, st>>>(mapA, mapB, mapC, p);
   return check_launch();
 }
 

