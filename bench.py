@@ -30,8 +30,8 @@ UNIT = "crops/s"
 WORKLOAD = "SCFlow refiner inference, batch 64 YCB-V-shaped 256x256 crops per GPU, 8 iters"
 
 
-def workload(S=256):
-    return WORKLOAD if S == 256 else WORKLOAD.replace("256x256", f"{S}x{S}")
+def workload(S=256, B=64):
+    return WORKLOAD.replace("256x256", f"{S}x{S}").replace("batch 64", f"batch {B}")
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full`
@@ -366,7 +366,7 @@ def ours(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "tf32", "data": "synthetic",
-        "config": {"workload": workload(S), "crops_per_gpu_per_step": B, "image": S, "iters": 8,
+        "config": {"workload": workload(S, B), "crops_per_gpu_per_step": B, "image": S, "iters": 8,
                    "parallelism": f"batch-shard x{world} + pose all-gather",
                    "l2": "two alternating input sets; per-step working set (>450 MB) exceeds the 126 MB L2",
                    "execution": "eager launches" if args.no_graph else "CUDA graph replay per step",

@@ -10,6 +10,7 @@ that is cheaper than a seed), so they stay small.  TEST INFRASTRUCTURE.
 import copy
 import json
 import os
+import sys
 
 import numpy as np
 import torch
@@ -35,10 +36,42 @@ def shapes_of(m):
     return {k: tuple(v.shape) for k, v in m.state_dict().items()}
 
 
+def refiner_fixture(R, enc, cxt, s, tag, seed):
+    """Whole refiner forward of the unmodified reference on one seeded s x s crop."""
+    cr = syn.make_crops(1, s, seed=seed)
+    cfg = copy.deepcopy(S.DECODER_CFG)
+    cfg["pose_head_cfg"]["feat_size"] = (s // 8, s // 8)
+    dec = R.SCFlowDecoder(**cfg).eval()
+    dec.load_state_dict(syn.fill_state_dict(shapes_of(dec), seed=64))
+    with torch.no_grad():
+        fr = enc(cr["real_images"]); fn = enc(cr["rendered_images"]); cx = cxt(cr["rendered_images"])
+        hf, cf = torch.split(cx, [128, 128], 1)
+        o = dec(fn, fr, torch.tanh(hf), torch.relu(cf), cr["R0"], cr["t0"], cr["depth"], cr["K"],
+                cr["labels"], torch.zeros(1, 2, s, s), 0.)
+    st = 4 * s // 256
+    np.savez_compressed(os.path.join(OUT, f"refiner_{tag}.npz"),
+                        feat_real=fr[:, ::16, ::st, ::st].numpy(), feat_render=fn[:, ::16, ::st, ::st].numpy(),
+                        cxt=cx[:, ::16, ::st, ::st].numpy(),
+                        rotations=torch.stack(o[2]).numpy(), translations=torch.stack(o[3]).numpy())
+
+
+def encoders(R):
+    enc = R.RAFTEncoder(in_channels=3, out_channels=256, net_type="Basic", norm_cfg=dict(type="IN")).eval()
+    cxt = R.RAFTEncoder(in_channels=3, out_channels=256, net_type="Basic", norm_cfg=dict(type="BN")).eval()
+    se, sc = shapes_of(enc), shapes_of(cxt)
+    enc.load_state_dict(syn.fill_state_dict(se, seed=61, gain=1.7))
+    cxt.load_state_dict(syn.fill_state_dict(sc, seed=62, gain=1.7))
+    return enc, cxt, se, sc
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(8)
     R = S.load_reference()
+    if sys.argv[1:] == ["cfg4"]:          # only the 512^2 refiner fixture (the others stay as committed)
+        enc, cxt, _, _ = encoders(R)
+        refiner_fixture(R, enc, cxt, 512, "cfg4", 65)
+        return
 
     # ---- 1. pyramid + lookup, small non-square map (H=8 -> last level H=1: max(H-1,1) branch)
     for tag, (n, c, h, w) in {"small": (2, 8, 8, 16), "sq32": (1, 16, 32, 32)}.items():
@@ -114,27 +147,12 @@ def main():
         json.dump({k: list(v) for k, v in shp.items()}, f, indent=0, sort_keys=True)
 
     # ---- 5. RAFT encoders + whole refiner forward (cfg1: N=1, 256^2)
-    enc = R.RAFTEncoder(in_channels=3, out_channels=256, net_type="Basic", norm_cfg=dict(type="IN")).eval()
-    cxt = R.RAFTEncoder(in_channels=3, out_channels=256, net_type="Basic", norm_cfg=dict(type="BN")).eval()
-    se, sc = shapes_of(enc), shapes_of(cxt)
-    enc.load_state_dict(syn.fill_state_dict(se, seed=61, gain=1.7))
-    cxt.load_state_dict(syn.fill_state_dict(sc, seed=62, gain=1.7))
+    enc, cxt, se, sc = encoders(R)
     with open(os.path.join(OUT, "encoder_state_shapes.json"), "w") as f:
         json.dump({"IN": {k: list(v) for k, v in se.items()}, "BN": {k: list(v) for k, v in sc.items()}},
                   f, indent=0, sort_keys=True)
-    cr = syn.make_crops(1, 256, seed=63)
-    cfg = copy.deepcopy(S.DECODER_CFG)
-    dec = R.SCFlowDecoder(**cfg).eval()
-    dec.load_state_dict(syn.fill_state_dict(shapes_of(dec), seed=64))
-    with torch.no_grad():
-        fr = enc(cr["real_images"]); fn = enc(cr["rendered_images"]); cx = cxt(cr["rendered_images"])
-        hf, cf = torch.split(cx, [128, 128], 1)
-        o = dec(fn, fr, torch.tanh(hf), torch.relu(cf), cr["R0"], cr["t0"], cr["depth"], cr["K"],
-                cr["labels"], torch.zeros(1, 2, 256, 256), 0.)
-    np.savez_compressed(os.path.join(OUT, "refiner_cfg1.npz"),
-                        feat_real=fr[:, ::16, ::4, ::4].numpy(), feat_render=fn[:, ::16, ::4, ::4].numpy(),
-                        cxt=cx[:, ::16, ::4, ::4].numpy(),
-                        rotations=torch.stack(o[2]).numpy(), translations=torch.stack(o[3]).numpy())
+    refiner_fixture(R, enc, cxt, 256, "cfg1", 63)
+    refiner_fixture(R, enc, cxt, 512, "cfg4", 65)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

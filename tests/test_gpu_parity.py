@@ -258,21 +258,26 @@ def test_zero_init_pose_head_is_identity(golden_dir):
         assert float((t - cr["t0"]).abs().max()) < 1e-3
 
 
-def test_refiner_cfg1_vs_golden(golden_dir):
-    g = np.load(os.path.join(golden_dir, "refiner_cfg1.npz"))
+@pytest.mark.parametrize("tag,s,seed", [("cfg1", 256, 63), ("cfg4", 512, 65)])
+def test_refiner_vs_golden(golden_dir, tag, s, seed):
+    """Whole refiner (3 encoder passes + 8 iterations) against the unmodified reference's poses:
+    cfg1 = one 256x256 crop, cfg4 = one 512x512 crop (64x64 features, 4096^2 correlation)."""
+    g = np.load(os.path.join(golden_dir, f"refiner_{tag}.npz"))
     es = json.load(open(os.path.join(golden_dir, "encoder_state_shapes.json")))
-    core = SCFlowRefinerCore(256).eval()
+    core = SCFlowRefinerCore(s).eval()
     core.encoder.load_state_dict(syn.fill_state_dict(es["IN"], seed=61, gain=1.7))
     core.context.load_state_dict(syn.fill_state_dict(es["BN"], seed=62, gain=1.7))
     shp = {k: tuple(v.shape) for k, v in core.decoder.state_dict().items()}
     core.decoder.load_state_dict(syn.fill_state_dict(shp, seed=64))
     core.to(DEV)
-    cr = _cuda(syn.make_crops(1, 256, seed=63))
+    cr = _cuda(syn.make_crops(1, s, seed=seed))
     out = core.get_pose(cr["rendered_images"], cr["real_images"], cr["R0"], cr["t0"], cr["depth"],
                         cr["K"], cr["labels"])
     Rg, tg = torch.from_numpy(g["rotations"]), torch.from_numpy(g["translations"])
-    assert float(O.rotation_geodesic(out[2][-1].cpu(), Rg[-1]).max()) < 1e-4
-    assert float((out[3][-1].cpu() - tg[-1]).abs().max()) < 0.1
+    er = float(O.rotation_geodesic(out[2][-1].cpu(), Rg[-1]).max())
+    et = float((out[3][-1].cpu() - tg[-1]).abs().max())
+    print(f"refiner {tag}: pose err {er:.3e} rad, {et:.3e} mm")
+    assert er < 1e-4 and et < 0.1
 
 
 def test_batch64_matches_per_crop_runs():

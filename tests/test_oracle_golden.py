@@ -160,3 +160,23 @@ def test_refiner_cfg1(golden_dir):
     Rg, tg = _t(g["rotations"]), _t(g["translations"])
     assert float(O.rotation_geodesic(torch.stack(o["rotations"])[-1], Rg[-1]).max()) < 5e-5
     assert float((torch.stack(o["translations"])[-1] - tg[-1]).abs().max()) < 5e-2
+
+
+def test_refiner_cfg4_512(golden_dir):
+    """BASELINE.json configs[3]: 512x512 crop, 64x64 feature map, pose head fed 8x8 (FC in 8192)."""
+    g = _load(golden_dir, "refiner_cfg4.npz")
+    with open(os.path.join(golden_dir, "encoder_state_shapes.json")) as f:
+        es = json.load(f)
+    with open(os.path.join(golden_dir, "decoder_state_shapes.json")) as f:
+        ds = {k: tuple(v) for k, v in json.load(f).items()}
+    ds["pose_pred.fc_layers.0.0.weight"] = (1024, 8192)
+    se = syn.fill_state_dict(es["IN"], seed=61, gain=1.7)
+    sc = syn.fill_state_dict(es["BN"], seed=62, gain=1.7)
+    sd = syn.fill_state_dict(ds, seed=64)
+    cr = syn.make_crops(1, 512, seed=65)
+    o = O.refiner_forward(se, sc, sd, cr["rendered_images"], cr["real_images"], cr["R0"], cr["t0"],
+                          cr["depth"], cr["K"], cr["labels"])
+    Rg, tg = _t(g["rotations"]), _t(g["translations"])
+    assert float(O.rotation_geodesic(Rg[-1], cr["R0"]).max()) > 1e-2          # the pose moved
+    assert float(O.rotation_geodesic(torch.stack(o["rotations"])[-1], Rg[-1]).max()) < 5e-5
+    assert float((torch.stack(o["translations"])[-1] - tg[-1]).abs().max()) < 5e-2
