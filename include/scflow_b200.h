@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define SCFLOW_ABI_VERSION 2
+#define SCFLOW_ABI_VERSION 3
 
 enum {
   SCFLOW_OK = 0,
@@ -174,6 +174,39 @@ int scflow_norm_act_nhwc(const float* x, const double* sums, const float* scale,
  * of channels-last encoder features to scflow_corr_pyramid_fwd (planar operands), replacing a
  * torch .contiguous() pass.  in != out. */
 int scflow_nhwc_to_nchw(const float* in, float* out, int n, int P, int C, int round_tf32, void* stream);
+
+/* ------------------------------------------------------------------ backward (training, cfg5)
+ * The reference gets these from autograd through ATen (grid_sampler_2d_backward,
+ * avg_pool2d_backward, bmm backward, upsample_bilinear2d_backward and the elementwise chain of
+ * models/utils/pose.py:66-88).  The host wraps each forward/backward pair in a
+ * torch.autograd.Function (scflow_b200/autograd.py). */
+
+/* Gradient of scflow_corr_lookup_fwd wrt the pyramid (corr_lookup.py:67, grid_sample `input`).
+ * grad_out: (n, 324, h, w) in `grad_layout` (SCFLOW_LAYOUT_*); flow as in the forward;
+ * grad_levels[l]: (n*h*w, 1, h>>l, w>>l), fully OVERWRITTEN (no memset needed).  The flow carries
+ * no gradient on the SCFlow path (detach_flow=True, scflow_decoder.py:193-194). */
+int scflow_corr_lookup_bwd(const float* grad_out, int grad_layout, const float* flow,
+                           float* const* grad_levels, int num_levels, int n, int h, int w, int radius,
+                           int div_mode, void* stream);
+
+/* First half of the backward of scflow_corr_pyramid_fwd (raft_decoder.py:48-56): folds the level
+ * gradients (NULL entries = no gradient) into grad_corr (n*h*w, h, w) = d loss / d (f1^T f2), i.e.
+ * including the 1/sqrt(c) scale and the 2x2-mean adjoints.  The caller finishes with two plain
+ * batched GEMMs: d f1 = f2 . grad_corr^T, d f2 = f1 . grad_corr (per crop). */
+int scflow_corr_fold_bwd(const float* const* grad_levels, int num_levels, float* grad_corr, int n,
+                         int c, int h, int w, void* stream);
+
+/* Adjoint of scflow_upsample_fwd: grad_in (n, c, h, w) = mul * resize^T(grad_out (n, c, h*scale,
+ * w*scale)); the gradient is the same for `in` and `add`. */
+int scflow_upsample_bwd(const float* grad_out, float* grad_in, int n, int c, int h, int w, int scale,
+                        float mul, void* stream);
+
+/* Gradient of the pose-induced flow (scflow_pose_flow_fwd's flow_full, depth path) wrt the pose it
+ * was rendered with: grad_pose (n, 12) = [dL/dR row-major | dL/dt], overwritten.  R, t are the
+ * (n,3,3)/(n,3) pose of the forward call; depth/K/R0/t0 as in the forward. */
+int scflow_pose_flow_bwd(const float* grad_full, const float* depth, const float* K, const float* R0,
+                         const float* t0, const float* R, const float* t, float* grad_pose, int n, int H,
+                         int W, void* stream);
 
 #ifdef __cplusplus
 }

@@ -55,6 +55,39 @@ def refiner_fixture(R, enc, cxt, s, tag, seed):
                         rotations=torch.stack(o[2]).numpy(), translations=torch.stack(o[3]).numpy())
 
 
+GRAD_KEYS = ("gru.conv_z.0.conv.bias", "gru.conv_q.1.conv.bias", "flow_pred.predict_layer.weight",
+             "encoder.corr_net.0.conv.bias", "pose_pred.rotation_pred.weight")
+
+
+def decoder_grad_fixture(R, n=2, s=64, seed=41):
+    """Gradients of scflow_b200.synthetic.synthetic_loss through the unmodified reference decoder
+    (shipped detach flags) wrt its four feature inputs and its parameters."""
+    cfg = copy.deepcopy(S.DECODER_CFG)
+    hh = s // 8
+    cfg["pose_head_cfg"]["feat_size"] = (hh, hh)
+    dec = R.SCFlowDecoder(**cfg).train()
+    dec.load_state_dict(syn.fill_state_dict(shapes_of(dec), seed=seed))
+    cr = syn.make_crops(n, s, seed=seed + 1)
+    ft = syn.make_features(n, hh, hh, seed=seed + 2)
+    ins = [ft[k].clone().requires_grad_(True) for k in ("feat_render", "feat_real", "h_feat", "cxt_feat")]
+    o = dec(ins[0], ins[1], ins[2], ins[3], cr["R0"], cr["t0"], cr["depth"], cr["K"], cr["labels"],
+            torch.zeros(n, 2, s, s), 0.)
+    loss = syn.synthetic_loss(o)
+    loss.backward()
+    d = {"loss": np.float64(loss.item())}
+    for k, t in zip(("feat_render", "feat_real", "h_feat", "cxt_feat"), ins):
+        d["g_" + k] = t.grad[:, ::4].numpy()
+    names, norms = [], []
+    for k, p in dec.named_parameters():
+        names.append(k)
+        norms.append(0.0 if p.grad is None else float(p.grad.double().norm()))
+        if k in GRAD_KEYS:
+            d["p_" + k] = p.grad.numpy()
+    d["param_names"] = np.array(names)
+    d["param_grad_norms"] = np.array(norms)
+    np.savez_compressed(os.path.join(OUT, "decoder_s64_grads.npz"), **d)
+
+
 def encoders(R):
     enc = R.RAFTEncoder(in_channels=3, out_channels=256, net_type="Basic", norm_cfg=dict(type="IN")).eval()
     cxt = R.RAFTEncoder(in_channels=3, out_channels=256, net_type="Basic", norm_cfg=dict(type="BN")).eval()
@@ -68,6 +101,9 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(8)
     R = S.load_reference()
+    if sys.argv[1:] == ["grads"]:         # only the training-gradient fixture
+        decoder_grad_fixture(R)
+        return
     if sys.argv[1:] == ["cfg4"]:          # only the 512^2 refiner fixture (the others stay as committed)
         enc, cxt, _, _ = encoders(R)
         refiner_fixture(R, enc, cxt, 512, "cfg4", 65)
@@ -153,6 +189,7 @@ def main():
                   f, indent=0, sort_keys=True)
     refiner_fixture(R, enc, cxt, 256, "cfg1", 63)
     refiner_fixture(R, enc, cxt, 512, "cfg4", 65)
+    decoder_grad_fixture(R)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

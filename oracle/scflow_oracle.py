@@ -240,13 +240,15 @@ def rotation_from_ortho6d(o: Tensor) -> Tensor:
     return torch.stack([x, y, z], dim=2)  # columns
 
 
-def pose_compose(dR6: Tensor, dt: Tensor, R: Tensor, t: Tensor, weight: float = 10.0):
+def pose_compose(dR6: Tensor, dt: Tensor, R: Tensor, t: Tensor, weight: float = 10.0,
+                 detach_depth_for_xy: bool = False):
     """R' = dR R;  tz' = tz / exp(dtz);  tx' = tz' (dtx/weight + tx/tz);  ty' likewise
-    (depth_transform='exp'; detach_depth_for_xy only affects gradients)."""
+    (depth_transform='exp'; detach_depth_for_xy only affects gradients, pose.py:142-144)."""
     Rn = torch.bmm(rotation_from_ortho6d(dR6), R)
     vz = t[:, 2] / torch.exp(dt[:, 2])
-    vx = vz * (dt[:, 0] / weight + t[:, 0] / t[:, 2])
-    vy = vz * (dt[:, 1] / weight + t[:, 1] / t[:, 2])
+    vz_xy = vz.detach() if detach_depth_for_xy else vz
+    vx = vz_xy * (dt[:, 0] / weight + t[:, 0] / t[:, 2])
+    vy = vz_xy * (dt[:, 1] / weight + t[:, 1] / t[:, 2])
     return Rn, torch.stack([vx, vy, vz], -1)
 
 
@@ -296,7 +298,10 @@ def pose_head(x: Tensor, label: Tensor, sd, p="pose_pred.", num_class=21, groups
 def decoder_forward(sd: Dict[str, Tensor], feat_render, feat_real, h_feat, cxt_feat,
                     ref_rotation, ref_translation, depth, K, label, init_flow,
                     invalid_flow_num: float = 0.0, iters: int = 8, num_levels: int = 4,
-                    radius: int = 4, div_mode: int = DIV_IEEE):
+                    radius: int = 4, div_mode: int = DIV_IEEE, train_detach: bool = False):
+    """`train_detach` reproduces the shipped config's gradient cuts (scflow_ycbv_real.py:213-216:
+    detach_flow / detach_pose / detach_depth_for_xy = True; scflow_decoder.py:193-194,231-232) --
+    it changes no forward value."""
     pyr = correlation_pyramid(feat_render, feat_real, num_levels)
     scale = 2 ** (num_levels - 1)
     N, H, W = depth.shape
@@ -307,6 +312,8 @@ def decoder_forward(sd: Dict[str, Tensor], feat_render, feat_real, h_feat, cxt_f
                 masks=[], delta_rotations=[], delta_translations=[])
     h = h_feat
     for _ in range(iters):
+        if train_detach:
+            flow, R, t = flow.detach(), R.detach(), t.detach()
         flow_lr = (1.0 / scale) * resize_bilinear_ac(flow, H // scale, W // scale)
         corr = corr_lookup(pyr, flow_lr, radius, div_mode)
         motion = motion_encoder(corr, flow_lr, sd)
@@ -320,7 +327,7 @@ def decoder_forward(sd: Dict[str, Tensor], feat_render, feat_real, h_feat, cxt_f
         dR6, dt = pose_head(torch.cat([h, df, mf], 1), label, sd)
         flow_pred = scale * resize_bilinear_ac(flow_lr + dflow, H, W)
         mask_up = resize_bilinear_ac(m, H, W)
-        R, t = pose_compose(dR6, dt, R, t)
+        R, t = pose_compose(dR6, dt, R, t, detach_depth_for_xy=train_detach)
         flow = pose_flow_dense(R, t, K, pts, mask, invalid_flow_num)
         outs["flow_from_pose"].append(flow)
         outs["flow_from_pred"].append(flow_pred)

@@ -1,0 +1,395 @@
+// Backward kernels of the hot path (BASELINE.json configs[4]: training step forward+backward).
+//
+//   corr_lookup_bwd     adjoint of the radius-4 bilinear window gather wrt the pyramid
+//                       (grid_sampler_2d_backward of corr_lookup.py:67 for the `input` argument)
+//   corr_fold_bwd       folds the four pyramid-level gradients into one gradient of the scaled
+//                       correlation volume (adjoint of 3x avg_pool2d + the 1/sqrt(C) scale,
+//                       raft_decoder.py:48-56); the two remaining contractions are plain GEMMs
+//   resize_bwd          adjoint of the align_corners=True bilinear up-sampling (scflow_decoder.py
+//                       :223-228): gradient wrt the low-resolution flow / mask
+//   pose_flow_bwd       gradient of the pose-induced flow (pose.py:66-88) wrt R_k and t_k
+//
+// All HBM-bound.  Every query / crop owns its output exclusively, so no kernel here needs global
+// atomics except the 12-value-per-crop reduction of pose_flow_bwd.
+#include "common.cuh"
+
+namespace scflow {
+namespace bw {
+
+constexpr int kR = 4, kD = 9, kTaps = 81, kLevels = 4;
+
+// Same separately rounded fp32 op sequence as the forward (corr_lookup.cu: unnorm_coord), so the
+// backward scatters into exactly the cells the forward read.
+__device__ __forceinline__ float unnorm_coord(float centre_lvl, int off, float denom, float rcp,
+                                              float sizem1, int div_mode) {
+  float c = __fadd_rn(centre_lvl, (float)off);
+  float g = __fmul_rn(c, 2.0f);
+  g = (div_mode == SCFLOW_DIV_IEEE) ? __fdiv_rn(g, denom) : __fmul_rn(g, rcp);
+  g = __fsub_rn(g, 1.0f);
+  float u = __fadd_rn(g, 1.0f);
+  u = __fmul_rn(u, 0.5f);
+  return __fmul_rn(u, sizem1);
+}
+
+__device__ __forceinline__ int floor_clamped(float v, int lo, int hi) {
+  float f = floorf(v);
+  f = fminf(fmaxf(f, (float)lo), (float)hi);  // NaN -> lo
+  return (int)f;
+}
+
+struct LookupBwdParams {
+  const float* grad_out;      // (n, 324, h, w) with strides gs_q (query) / gs_c (channel)
+  const float* flow;          // (n, 2, h, w)
+  float* grad_lvl[kLevels];   // (n*h*w, 1, h>>l, w>>l), overwritten
+  long long gs_q, gs_c;
+  int n, h, w, div_mode;
+  int plane_off[kLevels + 1];  // float offsets of the level planes inside a warp's staging area
+};
+
+constexpr int kLBWarps = 4;
+
+// One warp per query: the four gradient planes of the query are assembled in shared memory (zero
+// + 4 x 81 x 4 weighted corner adds) and streamed out whole, so the pyramid gradient is written
+// exactly once with full-line stores and needs no memset.
+__global__ void __launch_bounds__(kLBWarps * 32)
+corr_lookup_bwd_kernel(const LookupBwdParams p) {
+  extern __shared__ float smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int plane_floats = p.plane_off[kLevels];
+  float* pl = smem + (size_t)warp * plane_floats;
+  const int P = p.h * p.w;
+  const long long total_q = (long long)p.n * P;
+  for (long long q = (long long)blockIdx.x * kLBWarps + warp; q < total_q; q += (long long)gridDim.x * kLBWarps) {
+    for (int i = lane; i < plane_floats; i += 32) pl[i] = 0.0f;
+    __syncwarp();
+    const int n = (int)(q / P), qin = (int)(q - (long long)n * P);
+    const int y = qin / p.w, x = qin - y * p.w;
+    const float fx = __ldg(p.flow + ((long long)n * 2 + 0) * P + qin);
+    const float fy = __ldg(p.flow + ((long long)n * 2 + 1) * P + qin);
+    const float* g = p.grad_out + (long long)n * (kLevels * kTaps) * P + (long long)qin * p.gs_q;
+#pragma unroll
+    for (int l = 0; l < kLevels; ++l) {
+      const float sc = 1.0f / (float)(1 << l);
+      const float cx = __fmul_rn(__fadd_rn((float)x, fx), sc);
+      const float cy = __fmul_rn(__fadd_rn((float)y, fy), sc);
+      const int wl = p.w >> l, hl = p.h >> l;
+      const float dx = (float)max(wl - 1, 1), dy = (float)max(hl - 1, 1);
+      const float rx = __fdiv_rn(1.0f, dx), ry = __fdiv_rn(1.0f, dy);
+      float* plane = pl + p.plane_off[l];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const int t = lane + 32 * k;
+        if (t < kTaps) {
+          const int a = t / kD, b = t - a * kD;       // channel 81*l + 9*a + b: a offsets x, b offsets y
+          const float gv = __ldg(g + (long long)(l * kTaps + t) * p.gs_c);
+          const float ix = unnorm_coord(cx, a - kR, dx, rx, (float)(wl - 1), p.div_mode);
+          const float iy = unnorm_coord(cy, b - kR, dy, ry, (float)(hl - 1), p.div_mode);
+          const float x0f = floorf(ix), y0f = floorf(iy);
+          const int x0 = floor_clamped(ix, -32, wl + 32), y0 = floor_clamped(iy, -32, hl + 32);
+          const float wx1 = __fsub_rn(ix, x0f), wx0 = __fsub_rn(__fadd_rn(x0f, 1.0f), ix);
+          const float wy1 = __fsub_rn(iy, y0f), wy0 = __fsub_rn(__fadd_rn(y0f, 1.0f), iy);
+          const bool xin0 = x0 >= 0 && x0 < wl, xin1 = x0 + 1 >= 0 && x0 + 1 < wl;
+          const bool yin0 = y0 >= 0 && y0 < hl, yin1 = y0 + 1 >= 0 && y0 + 1 < hl;
+          if (yin0 && xin0) atomicAdd(plane + y0 * wl + x0, gv * (wx0 * wy0));
+          if (yin0 && xin1) atomicAdd(plane + y0 * wl + x0 + 1, gv * (wx1 * wy0));
+          if (yin1 && xin0) atomicAdd(plane + (y0 + 1) * wl + x0, gv * (wx0 * wy1));
+          if (yin1 && xin1) atomicAdd(plane + (y0 + 1) * wl + x0 + 1, gv * (wx1 * wy1));
+        }
+      }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int l = 0; l < kLevels; ++l) {
+      const int cnt = (p.h >> l) * (p.w >> l);
+      const float* src = pl + p.plane_off[l];
+      float* dst = p.grad_lvl[l] + q * cnt;
+      if ((cnt & 3) == 0) {
+        for (int i = lane; i < cnt / 4; i += 32)
+          reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(src)[i];
+      } else {
+        for (int i = lane; i < cnt; i += 32) dst[i] = src[i];
+      }
+    }
+    __syncwarp();
+  }
+}
+
+}  // namespace bw
+}  // namespace scflow
+
+extern "C" int scflow_corr_lookup_bwd(const float* grad_out, int grad_layout, const float* flow,
+                                      float* const* grad_levels, int num_levels, int n, int h, int w,
+                                      int radius, int div_mode, void* stream) {
+  using namespace scflow;
+  if (!grad_out || !flow || !grad_levels) return SCFLOW_E_NULL;
+  if (radius != bw::kR || num_levels != bw::kLevels) return SCFLOW_E_UNSUPPORTED;
+  if (div_mode != SCFLOW_DIV_IEEE && div_mode != SCFLOW_DIV_RCP) return SCFLOW_E_UNSUPPORTED;
+  if (grad_layout != SCFLOW_LAYOUT_NCHW && grad_layout != SCFLOW_LAYOUT_NHWC) return SCFLOW_E_UNSUPPORTED;
+  if (n <= 0 || h < 8 || w < 8) return SCFLOW_E_BAD_SHAPE;
+  bw::LookupBwdParams p;
+  p.grad_out = grad_out; p.flow = flow;
+  p.n = n; p.h = h; p.w = w; p.div_mode = div_mode;
+  const long long P = (long long)h * w;
+  p.gs_q = grad_layout == SCFLOW_LAYOUT_NHWC ? bw::kLevels * bw::kTaps : 1;
+  p.gs_c = grad_layout == SCFLOW_LAYOUT_NHWC ? 1 : P;
+  int off = 0;
+  for (int l = 0; l < bw::kLevels; ++l) {
+    if (!grad_levels[l]) return SCFLOW_E_NULL;
+    if (!aligned16(grad_levels[l])) return SCFLOW_E_MISALIGNED;
+    p.grad_lvl[l] = grad_levels[l];
+    p.plane_off[l] = off;
+    off += (((h >> l) * (w >> l)) + 3) & ~3;      // 16-byte aligned planes in the staging area
+  }
+  p.plane_off[bw::kLevels] = off;
+  const size_t smem = (size_t)bw::kLBWarps * off * sizeof(float);
+  if (smem > 200 * 1024) return SCFLOW_E_BAD_SHAPE;
+  static size_t attr_smem = 0;
+  if (smem > attr_smem) {
+    cudaFuncSetAttribute(bw::corr_lookup_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    attr_smem = smem;
+  }
+  const long long total_q = (long long)n * P;
+  long long blocks = (total_q + bw::kLBWarps - 1) / bw::kLBWarps;
+  const long long cap = 148LL * (smem > 64 * 1024 ? 2 : 8);
+  if (blocks > cap) blocks = cap;
+  bw::corr_lookup_bwd_kernel<<<(unsigned)blocks, bw::kLBWarps * 32, smem, (cudaStream_t)stream>>>(p);
+  return check_launch();
+}
+
+// ---------------------------------------------------------------------------------------------
+// corr_fold_bwd: G[q, y, x] = (g0[q,y,x] + g1[q,y/2,x/2]/4 + g2[q,y/4,x/4]/16 + g3[q,y/8,x/8]/64) / sqrt(C)
+// One thread = 4 consecutive x of one row (w % 4 == 0); absent levels are skipped.
+namespace scflow {
+namespace bw {
+
+struct FoldParams {
+  const float* g[kLevels];
+  float* out;
+  long long rows;          // n*P*h rows of w floats
+  int h, w, num_levels;
+  float inv_scale;
+};
+
+__global__ void __launch_bounds__(256)
+corr_fold_bwd_kernel(const FoldParams p) {
+  const int qw = p.w >> 2;
+  const long long total = p.rows * qw;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / qw;
+    const int x4 = (int)(i - row * qw) * 4;
+    const long long q = row / p.h;
+    const int y = (int)(row - q * p.h);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.g[0]) v = __ldg(reinterpret_cast<const float4*>(p.g[0] + row * p.w + x4));
+    if (p.num_levels > 1 && p.g[1]) {
+      const int w1 = p.w >> 1, h1 = p.h >> 1;
+      const float* s = p.g[1] + (q * h1 + (y >> 1)) * w1 + (x4 >> 1);
+      const float a = 0.25f * __ldg(s), b = 0.25f * __ldg(s + 1);
+      v.x += a; v.y += a; v.z += b; v.w += b;
+    }
+    if (p.num_levels > 2 && p.g[2]) {
+      const int w2 = p.w >> 2, h2 = p.h >> 2;
+      const float a = 0.0625f * __ldg(p.g[2] + (q * h2 + (y >> 2)) * w2 + (x4 >> 2));
+      v.x += a; v.y += a; v.z += a; v.w += a;
+    }
+    if (p.num_levels > 3 && p.g[3]) {
+      const int w3 = p.w >> 3, h3 = p.h >> 3;
+      const float a = 0.015625f * __ldg(p.g[3] + (q * h3 + (y >> 3)) * w3 + (x4 >> 3));
+      v.x += a; v.y += a; v.z += a; v.w += a;
+    }
+    v.x *= p.inv_scale; v.y *= p.inv_scale; v.z *= p.inv_scale; v.w *= p.inv_scale;
+    *reinterpret_cast<float4*>(p.out + row * p.w + x4) = v;
+  }
+}
+
+}  // namespace bw
+}  // namespace scflow
+
+extern "C" int scflow_corr_fold_bwd(const float* const* grad_levels, int num_levels, float* grad_corr,
+                                    int n, int c, int h, int w, void* stream) {
+  using namespace scflow;
+  if (!grad_levels || !grad_corr) return SCFLOW_E_NULL;
+  if (num_levels < 1 || num_levels > bw::kLevels) return SCFLOW_E_UNSUPPORTED;
+  if (n <= 0 || c <= 0 || h <= 0 || w <= 0 || (w & 3) != 0 || (h % (1 << (num_levels - 1))) != 0 ||
+      (w % (1 << (num_levels - 1))) != 0)
+    return SCFLOW_E_BAD_SHAPE;
+  if (!aligned16(grad_corr)) return SCFLOW_E_MISALIGNED;
+  bw::FoldParams p;
+  for (int l = 0; l < bw::kLevels; ++l) p.g[l] = l < num_levels ? grad_levels[l] : nullptr;
+  if (p.g[0] && !aligned16(p.g[0])) return SCFLOW_E_MISALIGNED;
+  p.out = grad_corr;
+  p.rows = (long long)n * h * w * h;
+  p.h = h; p.w = w; p.num_levels = num_levels;
+  p.inv_scale = 1.0f / sqrtf((float)c);
+  long long blocks = (p.rows * (w >> 2) + 255) / 256;
+  if (blocks > 148LL * 16) blocks = 148LL * 16;
+  bw::corr_fold_bwd_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(p);
+  return check_launch();
+}
+
+// ---------------------------------------------------------------------------------------------
+// resize_bwd: adjoint of out = mul * bilinear_align_corners(in [+ add]) for an integer up-scale.
+// One CTA per (plane, low-res row): the <= 2*scale+2 contributing high-res rows are first reduced
+// along y into a shared row (coalesced reads), then along x.  Weights are recomputed with the
+// forward's expressions (pose_flow.cu: resize_kernel), so the pair is an exact adjoint.
+namespace scflow {
+namespace bw {
+
+__global__ void __launch_bounds__(256)
+resize_bwd_kernel(const float* __restrict__ grad_out, float* __restrict__ grad_in, int ih, int iw,
+                  int oh, int ow, float mul) {
+  extern __shared__ float col[];                    // [ow]
+  const int y = blockIdx.x, pl = blockIdx.y;
+  const float sy = oh > 1 ? (float)(ih - 1) / (float)(oh - 1) : 0.0f;
+  const float sx = ow > 1 ? (float)(iw - 1) / (float)(ow - 1) : 0.0f;
+  const float* g = grad_out + (size_t)pl * oh * ow;
+  // candidate high-res rows: src = sy*Y lies in (y-1, y+1)
+  int Ylo = 0, Yhi = oh - 1;
+  if (sy > 0.0f) {
+    Ylo = max(0, (int)floorf((float)(y - 1) / sy) - 1);
+    Yhi = min(oh - 1, (int)ceilf((float)(y + 1) / sy) + 1);
+  }
+  for (int X = threadIdx.x; X < ow; X += blockDim.x) {
+    float acc = 0.0f;
+    for (int Y = Ylo; Y <= Yhi; ++Y) {
+      const float srcy = sy * (float)Y;
+      const int y0 = (int)srcy;
+      const int y1 = y0 + (y0 < ih - 1 ? 1 : 0);
+      const float ly1 = srcy - (float)y0, ly0 = 1.0f - ly1;
+      float wgt = 0.0f;
+      if (y0 == y) wgt += ly0;
+      if (y1 == y) wgt += ly1;
+      if (wgt != 0.0f) acc = fmaf(wgt, __ldg(g + (size_t)Y * ow + X), acc);
+    }
+    col[X] = acc;
+  }
+  __syncthreads();
+  for (int x = threadIdx.x; x < iw; x += blockDim.x) {
+    int Xlo = 0, Xhi = ow - 1;
+    if (sx > 0.0f) {
+      Xlo = max(0, (int)floorf((float)(x - 1) / sx) - 1);
+      Xhi = min(ow - 1, (int)ceilf((float)(x + 1) / sx) + 1);
+    }
+    float acc = 0.0f;
+    for (int X = Xlo; X <= Xhi; ++X) {
+      const float srcx = sx * (float)X;
+      const int x0 = (int)srcx;
+      const int x1 = x0 + (x0 < iw - 1 ? 1 : 0);
+      const float lx1 = srcx - (float)x0, lx0 = 1.0f - lx1;
+      float wgt = 0.0f;
+      if (x0 == x) wgt += lx0;
+      if (x1 == x) wgt += lx1;
+      acc = fmaf(wgt, col[X], acc);
+    }
+    grad_in[((size_t)pl * ih + y) * iw + x] = mul * acc;
+  }
+}
+
+}  // namespace bw
+}  // namespace scflow
+
+extern "C" int scflow_upsample_bwd(const float* grad_out, float* grad_in, int n, int c, int h, int w,
+                                   int scale, float mul, void* stream) {
+  using namespace scflow;
+  if (!grad_out || !grad_in) return SCFLOW_E_NULL;
+  if (n <= 0 || c <= 0 || h <= 0 || w <= 0 || scale <= 0 || (long long)n * c > 65535 ||
+      (size_t)w * scale * sizeof(float) > 48 * 1024)
+    return SCFLOW_E_BAD_SHAPE;
+  dim3 grid(h, n * c);
+  bw::resize_bwd_kernel<<<grid, 256, (size_t)w * scale * sizeof(float), (cudaStream_t)stream>>>(
+      grad_out, grad_in, h, w, h * scale, w * scale, mul);
+  return check_launch();
+}
+
+// ---------------------------------------------------------------------------------------------
+// pose_flow_bwd: flow(x,y) = (K (R X + t)).xy / (.)z - (x,y) on foreground pixels (depth > 0),
+// X = R0^-1 (K^-1 [x,y,1] d - t0) recomputed as in the forward.  Per crop:
+//   dL/dt = sum_px K^T dL/du,   dL/dR = sum_px (K^T dL/du) X^T,
+//   dL/du = (gx/uz, gy/uz, -(gx ux + gy uy)/uz^2).
+namespace scflow {
+namespace bw {
+
+struct PoseBwdSmem { float R[9], t[3], K[9], Kinv[9], R0inv[9], t0[3]; float red[8][12]; };
+
+__device__ __forceinline__ void mv3(const float* M, float a, float b, float c, float& x, float& y, float& z) {
+  x = M[0] * a + M[1] * b + M[2] * c;
+  y = M[3] * a + M[4] * b + M[5] * c;
+  z = M[6] * a + M[7] * b + M[8] * c;
+}
+
+__global__ void __launch_bounds__(256)
+pose_flow_bwd_kernel(const float* __restrict__ grad_full, const float* __restrict__ depth,
+                     const float* __restrict__ K, const float* __restrict__ R0,
+                     const float* __restrict__ t0, const float* __restrict__ R, const float* __restrict__ t,
+                     float* __restrict__ grad_pose, int H, int W) {
+  __shared__ PoseBwdSmem s;
+  const int n = blockIdx.y;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 9; ++i) { s.R[i] = R[n * 9 + i]; s.K[i] = K[n * 9 + i]; }
+    for (int i = 0; i < 3; ++i) { s.t[i] = t[n * 3 + i]; s.t0[i] = t0[n * 3 + i]; }
+    inverse3x3(K + n * 9, s.Kinv);
+    inverse3x3(R0 + n * 9, s.R0inv);
+  }
+  __syncthreads();
+  const long long hw = (long long)H * W;
+  float acc[12];
+#pragma unroll
+  for (int i = 0; i < 12; ++i) acc[i] = 0.0f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hw; i += (long long)gridDim.x * blockDim.x) {
+    const float d = __ldg(depth + n * hw + i);
+    if (d > 0.0f) {
+      const int y = (int)(i / W), x = (int)(i - (long long)y * W);
+      const float gx = __ldg(grad_full + ((long long)n * 2 + 0) * hw + i);
+      const float gy = __ldg(grad_full + ((long long)n * 2 + 1) * hw + i);
+      float cx, cy, cz, ox, oy, oz, rx, ry, rz, ux, uy, uz;
+      mv3(s.Kinv, (float)x * d, (float)y * d, d, cx, cy, cz);
+      mv3(s.R0inv, cx - s.t0[0], cy - s.t0[1], cz - s.t0[2], ox, oy, oz);
+      mv3(s.R, ox, oy, oz, rx, ry, rz);
+      mv3(s.K, rx + s.t[0], ry + s.t[1], rz + s.t[2], ux, uy, uz);
+      const float iz = 1.0f / uz;
+      const float du0 = gx * iz, du1 = gy * iz, du2 = -(gx * ux + gy * uy) * iz * iz;
+      // dc = K^T du
+      const float dc0 = s.K[0] * du0 + s.K[3] * du1 + s.K[6] * du2;
+      const float dc1 = s.K[1] * du0 + s.K[4] * du1 + s.K[7] * du2;
+      const float dc2 = s.K[2] * du0 + s.K[5] * du1 + s.K[8] * du2;
+      acc[0] += dc0 * ox; acc[1] += dc0 * oy; acc[2] += dc0 * oz;
+      acc[3] += dc1 * ox; acc[4] += dc1 * oy; acc[5] += dc1 * oz;
+      acc[6] += dc2 * ox; acc[7] += dc2 * oy; acc[8] += dc2 * oz;
+      acc[9] += dc0; acc[10] += dc1; acc[11] += dc2;
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int i = 0; i < 12; ++i) {
+    float v = acc[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s.red[warp][i] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 12) {
+    float v = 0.0f;
+    for (int k = 0; k < 8; ++k) v += s.red[k][threadIdx.x];
+    atomicAdd(grad_pose + n * 12 + threadIdx.x, v);
+  }
+}
+
+}  // namespace bw
+}  // namespace scflow
+
+extern "C" int scflow_pose_flow_bwd(const float* grad_full, const float* depth, const float* K,
+                                    const float* R0, const float* t0, const float* R, const float* t,
+                                    float* grad_pose, int n, int H, int W, void* stream) {
+  using namespace scflow;
+  if (!grad_full || !depth || !K || !R0 || !t0 || !R || !t || !grad_pose) return SCFLOW_E_NULL;
+  if (n <= 0 || H <= 0 || W <= 0 || n > 65535) return SCFLOW_E_BAD_SHAPE;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cudaMemsetAsync(grad_pose, 0, (size_t)n * 12 * sizeof(float), st) != cudaSuccess) return check_launch();
+  long long hw = (long long)H * W;
+  int bx = (int)((hw + 256 * 8 - 1) / (256 * 8));
+  if (bx > 16) bx = 16;
+  if (bx < 1) bx = 1;
+  bw::pose_flow_bwd_kernel<<<dim3(bx, n), 256, 0, st>>>(grad_full, depth, K, R0, t0, R, t, grad_pose, H, W);
+  return check_launch();
+}

@@ -22,7 +22,7 @@ import torch.nn as nn
 
 from . import gru, gru_tc, ops
 from .modules import (ConvGRU, ConvModule, CorrelationPyramid, CorrLookup, MotionEncoder, XHead,
-                      _no_grad_only)
+                      _needs_grad)
 from .registry import MODELS, register
 
 
@@ -89,7 +89,10 @@ class SCFlowDecoder(nn.Module):
                 cxt_feat: torch.Tensor, ref_rotation: torch.Tensor, ref_translation: torch.Tensor,
                 depth: torch.Tensor, internel_k: torch.Tensor, label: torch.Tensor,
                 init_flow: torch.Tensor, invalid_flow_num: float) -> Sequence[torch.Tensor]:
-        _no_grad_only(feat_render, feat_real, h_feat, cxt_feat, *self.parameters())
+        if _needs_grad(feat_render, feat_real, h_feat, cxt_feat, *self.parameters()):
+            return self._forward_autograd(feat_render, feat_real, h_feat, cxt_feat, ref_rotation,
+                                          ref_translation, depth, internel_k, label, init_flow,
+                                          invalid_flow_num)
         scale = 2 ** (self.num_levels - 1)
         N, H, W = depth.size()
         corr_pyramid = self.corr_block(feat_render, feat_real)
@@ -140,6 +143,52 @@ class SCFlowDecoder(nn.Module):
                 update_rotation, update_translation, K, dR6=delta_rotation.float(),
                 dt=delta_translation.float(), depth=depth, R0=R0, t0=t0, scale=scale,
                 invalid_num=invalid_flow_num)
+            rotation_preds.append(update_rotation)
+            translation_preds.append(update_translation)
+            delta_rotation_preds.append(delta_rotation)
+            delta_translation_preds.append(delta_translation)
+            flow_from_pose.append(flow_full)
+            flow_from_pred.append(flow_pred)
+            mask_preds.append(upsample_mask_pred)
+        return (flow_from_pose, flow_from_pred, rotation_preds, translation_preds, mask_preds,
+                delta_rotation_preds, delta_translation_preds)
+
+    def _forward_autograd(self, feat_render, feat_real, h_feat, cxt_feat, ref_rotation, ref_translation,
+                          depth, internel_k, label, init_flow, invalid_flow_num):
+        """Training forward (scflow_decoder.py:151-252 under autograd).  Same loop; the hot-path
+        operators go through scflow_b200.autograd (one forward launch + hand-written adjoint each),
+        the pose compose is a dozen differentiable 3x3 torch ops, and every convolution (GRU gates
+        included) runs in cuDNN so that autograd supplies dgrad / wgrad."""
+        from . import autograd as ag
+        scale = 2 ** (self.num_levels - 1)
+        corr_pyramid = self.corr_block(feat_render, feat_real)
+        depth = depth.contiguous().float()
+        K = internel_k.contiguous().float()
+        R0 = ref_rotation.detach().contiguous().float()
+        t0 = ref_translation.detach().contiguous().float()
+        update_rotation, update_translation = R0, t0
+        rotation_preds, translation_preds = [], []
+        delta_rotation_preds, delta_translation_preds = [], []
+        flow_from_pose, flow_from_pred, mask_preds = [], [], []
+        flow = ops.downsample(init_flow.detach().float(), scale, 1.0 / scale)      # detach_flow=True
+        for _ in range(self.iters):
+            corr = self.corr_lookup(corr_pyramid, flow)
+            motion_feat = self.encoder(corr, flow)
+            x = torch.cat([cxt_feat, motion_feat], dim=1)
+            h_feat = self.gru(h_feat, x)
+            delta_flow_pred = self.flow_pred(h_feat)
+            mask = torch.sigmoid(self.mask_pred(h_feat))
+            delta_flow_feat = self.delta_flow_encoder(delta_flow_pred)
+            mask_feat = self.mask_encoder(mask)
+            delta_rotation, delta_translation = self.pose_pred(
+                torch.cat([h_feat, delta_flow_feat, mask_feat], axis=1), label)
+            flow_pred = ag.upsample(flow, delta_flow_pred.contiguous(), scale, float(scale))
+            upsample_mask_pred = ag.upsample(mask.contiguous(), None, scale, 1.0)
+            update_rotation, update_translation = ag.compose_pose(
+                delta_rotation.float(), delta_translation.float(), update_rotation.detach(),
+                update_translation.detach(), detach_depth_for_xy=self.detach_depth_for_xy)   # detach_pose=True
+            flow_full, flow = ag.pose_flow(update_rotation, update_translation, K, depth, R0, t0,
+                                           scale, invalid_flow_num)
             rotation_preds.append(update_rotation)
             translation_preds.append(update_translation)
             delta_rotation_preds.append(delta_rotation)

@@ -24,6 +24,14 @@ def _cudnn_forward(mod, h, x):
 
 
 def conv_gru_forward(mod, h, x):
+    if torch.is_grad_enabled() and (h.requires_grad or x.requires_grad
+                                    or any(p.requires_grad for p in mod.parameters())):
+        # training: the six gate convolutions and their dgrad/wgrad run in cuDNN under autograd
+        # (the tcgen05 pass kernel is inference-only; DESIGN.md "training path")
+        if not h.is_cuda:
+            from ._lib import ScflowError
+            raise ScflowError("ConvGRU: expected CUDA tensors (scflow_b200 has no CPU path)")
+        return _cudnn_forward(mod, h, x)
     if BACKEND == "tcgen05":
         from . import gru_tc
         return gru_tc.forward(mod, h, x)

@@ -18,10 +18,9 @@ import torch.nn.functional as F
 from . import ops
 
 
-def _no_grad_only(*tensors):
-    if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors):
-        raise NotImplementedError(
-            "scflow_b200 kernels are forward-only in this round; wrap the call in torch.no_grad()")
+def _needs_grad(*tensors) -> bool:
+    """True when autograd must record the call (training, BASELINE.json configs[4])."""
+    return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors)
 
 
 _ACT = {"ReLU": lambda: nn.ReLU(inplace=True), "Sigmoid": nn.Sigmoid, "Tanh": nn.Tanh}
@@ -98,7 +97,9 @@ class CorrelationPyramid(nn.Module):
         self.precision = {"fp32": ops.PREC_FP32, "tf32": ops.PREC_TF32}[precision]
 
     def forward(self, feat1: torch.Tensor, feat2: torch.Tensor) -> Sequence[torch.Tensor]:
-        _no_grad_only(feat1, feat2)
+        if _needs_grad(feat1, feat2):
+            from . import autograd
+            return autograd.corr_pyramid(feat1, feat2, self.num_levels, self.precision)
         return ops.corr_pyramid(feat1, feat2, self.num_levels, self.precision)
 
 
@@ -117,7 +118,13 @@ class CorrLookup(nn.Module):
         self.div_mode = {"ieee": ops.DIV_IEEE, "rcp": ops.DIV_RCP}[div_mode]
 
     def forward(self, corr_pyramid: Sequence[torch.Tensor], flow: torch.Tensor) -> torch.Tensor:
-        _no_grad_only(flow, *corr_pyramid)
+        if _needs_grad(flow):
+            # every shipped config detaches the flow before the lookup (scflow_decoder.py:193-194,
+            # detach_flow=True); the coordinate gradient of grid_sample is not implemented
+            raise NotImplementedError("CorrLookup: gradient wrt the flow is not implemented; detach it")
+        if _needs_grad(*corr_pyramid):
+            from . import autograd
+            return autograd.corr_lookup(corr_pyramid, flow, self.r, self.div_mode)
         return ops.corr_lookup(corr_pyramid, flow, self.r, self.div_mode)
 
 

@@ -41,6 +41,9 @@ def get_flow_from_delta_pose_and_points(rotation_dst, translation_dst, k, points
     ps = points_3d_list
     if not isinstance(ps, PointSet):
         raise TypeError("pass the PointSet returned by scflow_b200.pose.cal_3d_2d_corr")
+    if torch.is_grad_enabled() and (rotation_dst.requires_grad or translation_dst.requires_grad):
+        raise NotImplementedError("differentiable pose-induced flow: use scflow_b200.autograd.pose_flow "
+                                  "(depth path), as SCFlowDecoder does when training")
     _, _, full, _ = ops.pose_flow(rotation_dst, translation_dst, k, points3d=ps.points3d,
                                   mask=ps.mask, invalid_num=invalid_num, want_lr=False)
     return full
@@ -53,6 +56,11 @@ def get_pose_from_delta_pose(rotation_delta, translation_delta, rotation_src, tr
         raise NotImplementedError("quaternion deltas (kornia path) are not implemented")
     if depth_transform != 'exp':
         raise NotImplementedError("depth_transform != 'exp'")
+    if torch.is_grad_enabled() and any(t.requires_grad for t in (rotation_delta, translation_delta,
+                                                                 rotation_src, translation_src)):
+        from . import autograd
+        return autograd.compose_pose(rotation_delta, translation_delta, rotation_src, translation_src,
+                                     weight=weight, detach_depth_for_xy=detach_depth_for_xy)
     n = rotation_src.shape[0]
     eye = torch.eye(3, device=rotation_src.device).expand(n, 3, 3).contiguous()
     R, t, _, _ = ops.pose_flow(rotation_src, translation_src, eye, dR6=rotation_delta,

@@ -54,9 +54,10 @@ class SCFlowRefinerCore(nn.Module):
         h_feat, cxt_feat = torch.split(cxt, [self.h_channels, self.cxt_channels], dim=1)
         return render_feat, real_feat, torch.tanh(h_feat), torch.relu(cxt_feat)
 
-    @torch.no_grad()
     def get_pose(self, render_images, real_images, ref_rotation, ref_translation, depth,
                  internel_k, label, init_flow=None):
+        # scflow_refiner.py:129-138; called under torch.no_grad() by the test loop (inference kernels)
+        # and with autograd on by `loss` (training path: scflow_b200.autograd)
         feat_render, feat_real, h_feat, cxt_feat = self.extract_feat(render_images, real_images)
         if init_flow is None:
             N, _, H, W = real_images.shape

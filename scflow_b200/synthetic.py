@@ -144,3 +144,30 @@ def make_features(n: int, h: int, w: int, seed: int = 7, c: int = 256, hc: int =
     cf = np.maximum(rs.standard_normal((n, hc, h, w)), 0.0)
     f32 = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32))
     return dict(feat_render=f32(f1), feat_real=f32(f2), h_feat=f32(hf), cxt_feat=f32(cf))
+
+
+def synthetic_loss(outs, gamma: float = 0.8, seed: int = 7) -> torch.Tensor:
+    """Deterministic scalar over every differentiable output of the decoder (the 7 lists of
+    scflow_decoder.py:252, or the oracle's dict): a SequenceLoss-style gamma-weighted sum of fixed
+    random linear functionals of flow_from_pred, flow_from_pose, masks, rotations and translations.
+    Used by the gradient fixtures, the gradient parity tests and the training bench, so that all
+    three back-propagate through the same paths the reference's losses do
+    (scflow_refiner.py:196-232)."""
+    if isinstance(outs, dict):
+        outs = (outs["flow_from_pose"], outs["flow_from_pred"], outs["rotations"], outs["translations"],
+                outs["masks"])
+    fpose, fpred, Rs, ts, masks = outs[:5]
+    dev = fpred[0].device
+    S = fpred[0].shape[-1]
+    rs = np.random.RandomState(seed)
+    to = lambda a: torch.from_numpy(a.astype(np.float32)).to(dev)
+    Wf, Wp = to(rs.standard_normal((1, 2, S, S))), to(rs.standard_normal((1, 2, S, S)))
+    Wm = to(rs.standard_normal((1, 1, S, S)))
+    wr, wt = to(rs.standard_normal((1, 3, 3))), to(rs.standard_normal((1, 3)) * 1e-2)
+    n = len(fpred)
+    loss = fpred[0].new_zeros(())
+    for i in range(n):
+        g = gamma ** (n - 1 - i)
+        loss = loss + g * ((fpred[i] * Wf).mean() + 0.5 * (fpose[i] * Wp).mean() + (masks[i] * Wm).mean()
+                           + (Rs[i] * wr).sum(dim=(1, 2)).mean() + (ts[i] * wt).sum(dim=1).mean())
+    return loss

@@ -271,8 +271,9 @@ def test_refiner_vs_golden(golden_dir, tag, s, seed):
     core.decoder.load_state_dict(syn.fill_state_dict(shp, seed=64))
     core.to(DEV)
     cr = _cuda(syn.make_crops(1, s, seed=seed))
-    out = core.get_pose(cr["rendered_images"], cr["real_images"], cr["R0"], cr["t0"], cr["depth"],
-                        cr["K"], cr["labels"])
+    with torch.no_grad():
+        out = core.get_pose(cr["rendered_images"], cr["real_images"], cr["R0"], cr["t0"], cr["depth"],
+                            cr["K"], cr["labels"])
     Rg, tg = torch.from_numpy(g["rotations"]), torch.from_numpy(g["translations"])
     er = float(O.rotation_geodesic(out[2][-1].cpu(), Rg[-1]).max())
     et = float((out[3][-1].cpu() - tg[-1]).abs().max())

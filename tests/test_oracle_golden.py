@@ -180,3 +180,31 @@ def test_refiner_cfg4_512(golden_dir):
     assert float(O.rotation_geodesic(Rg[-1], cr["R0"]).max()) > 1e-2          # the pose moved
     assert float(O.rotation_geodesic(torch.stack(o["rotations"])[-1], Rg[-1]).max()) < 5e-5
     assert float((torch.stack(o["translations"])[-1] - tg[-1]).abs().max()) < 5e-2
+
+
+def test_decoder_gradients_s64(golden_dir):
+    """Oracle autograd (train_detach = the shipped detach flags) against gradients taken through the
+    unmodified reference decoder (oracle/gen_golden.py: decoder_grad_fixture)."""
+    g = _load(golden_dir, "decoder_s64_grads.npz")
+    with open(os.path.join(golden_dir, "decoder_state_shapes.json")) as f:
+        ds = {k: tuple(v) for k, v in json.load(f).items()}
+    ds["pose_pred.fc_layers.0.0.weight"] = (1024, 128)          # feat_size 8x8 -> 1x1 after 3 stride-2 convs
+    sd = {k: v.clone().requires_grad_(True) for k, v in syn.fill_state_dict(ds, seed=41).items()}
+    cr = syn.make_crops(2, 64, seed=42)
+    ft = syn.make_features(2, 8, 8, seed=43)
+    ins = {k: ft[k].clone().requires_grad_(True) for k in ("feat_render", "feat_real", "h_feat", "cxt_feat")}
+    o = O.decoder_forward(sd, ins["feat_render"], ins["feat_real"], ins["h_feat"], ins["cxt_feat"],
+                          cr["R0"], cr["t0"], cr["depth"], cr["K"], cr["labels"],
+                          torch.zeros(2, 2, 64, 64), train_detach=True)
+    loss = syn.synthetic_loss(o)
+    assert abs(loss.item() - float(g["loss"])) < 1e-4 * abs(float(g["loss"]))
+    loss.backward()
+    for k, t in ins.items():
+        assert rel_err(t.grad[:, ::4], g["g_" + k]) < 2e-3, k
+    for k in g.files:
+        if k.startswith("p_"):
+            assert rel_err(sd[k[2:]].grad, g[k]) < 2e-3, k
+    norms = dict(zip([str(x) for x in g["param_names"]], g["param_grad_norms"]))
+    for k, want in norms.items():
+        got = 0.0 if sd[k].grad is None else float(sd[k].grad.double().norm())
+        assert abs(got - want) <= 2e-3 * max(want, 1e-6), (k, got, want)

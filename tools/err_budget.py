@@ -24,7 +24,8 @@ for fused, prec, backend in itertools.product((False, True), ("fp32", "tf32"), (
     shp = {k: tuple(v.shape) for k, v in core.decoder.state_dict().items()}
     core.decoder.load_state_dict(syn.fill_state_dict(shp, seed=64))
     core.cuda()
-    out = core.get_pose(cr["rendered_images"], cr["real_images"], cr["R0"], cr["t0"], cr["depth"], cr["K"], cr["labels"])
+    with torch.no_grad():
+      out = core.get_pose(cr["rendered_images"], cr["real_images"], cr["R0"], cr["t0"], cr["depth"], cr["K"], cr["labels"])
     er = [float(O.rotation_geodesic(out[2][i].cpu(), Rg[i]).max()) for i in range(8)]
     et = float((out[3][-1].cpu() - tg[-1]).abs().max())
     print(f"fused_enc={fused!s:5} corr={prec} gru={backend:8s} rot err per iter: " + " ".join(f"{e:.1e}" for e in er) + f"  | t err {et:.2e} mm")
