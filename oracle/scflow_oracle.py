@@ -365,7 +365,7 @@ def raft_encoder(x: Tensor, sd: Dict[str, Tensor], norm: str, p: str = "") -> Te
 
 
 def refiner_forward(sd_enc, sd_cxt, sd_dec, render_images, real_images, R0, t0, depth, K, label,
-                    iters: int = 8, div_mode: int = DIV_IEEE):
+                    iters: int = 8, div_mode: int = DIV_IEEE, train_detach: bool = False):
     """SCFlowRefiner.get_pose (models/refiner/scflow_refiner.py:84-138): shared IN encoder on
     real and rendered images, BN context encoder on the rendered image, tanh/relu split,
     zero init flow, invalid_flow_num = 0."""
@@ -377,7 +377,7 @@ def refiner_forward(sd_enc, sd_cxt, sd_dec, render_images, real_images, R0, t0, 
     N, _, H, W = real_images.shape
     init_flow = torch.zeros(N, 2, H, W, dtype=torch.float32)
     return decoder_forward(sd_dec, feat_render, feat_real, h, c, R0, t0, depth, K, label,
-                           init_flow, 0.0, iters, div_mode=div_mode)
+                           init_flow, 0.0, iters, div_mode=div_mode, train_detach=train_detach)
 
 
 def rotation_geodesic(Ra: Tensor, Rb: Tensor) -> Tensor:
