@@ -175,6 +175,43 @@ int scflow_norm_act_nhwc(const float* x, const double* sums, const float* scale,
  * torch .contiguous() pass.  in != out. */
 int scflow_nhwc_to_nchw(const float* in, float* out, int n, int P, int C, int round_tf32, void* stream);
 
+/* GroupNorm with 4 channels per group (+ ReLU) on channels-last (n, P, C), one launch: the conv -> GN ->
+ * ReLU layers of MultiClassPoseHead (models/head/pose_head.py:128-137; norm_cfg GN num_groups=32 on 128
+ * channels).  gamma/beta: [C].  x == out allowed.  C/4 must divide 512. */
+int scflow_group_norm4_act_nhwc(const float* x, const float* gamma, const float* beta, float* out, int n,
+                                int P, int C, float eps, int relu, void* stream);
+
+/* Fully connected tail of MultiClassPoseHead (models/head/pose_head.py:139-147, 201-211): fc0 + ReLU, fc1 +
+ * ReLU, rotation_pred / translation_pred restricted to the class of label[0] (index_select(...)[:, 0, :],
+ * pose_head.py:209-210).  x: (M, K) row-major; w0: (n0, K), w1: (n1, n0), wr: (6*classes, n1), wt:
+ * (3*classes, n1) row-major (torch Linear layout); label: int64 [M] on the device; workspace:
+ * scflow_pose_fc_workspace_floats(M, n0, n1, splitk) floats; dr: (M, 6), dt: (M, 3).  Exact fp32, deterministic. */
+size_t scflow_pose_fc_workspace_floats(int M, int n0, int n1, int splitk);
+int scflow_pose_fc_fwd(const float* x, const float* w0, const float* b0, const float* w1, const float* b1,
+                       const float* wr, const float* br, const float* wt, const float* bt,
+                       const long long* label, float* workspace, float* dr, float* dt, int M, int K, int n0,
+                       int n1, int num_class, int splitk, void* stream);
+
+/* ------------------------------------------------------------------ degenerate convolutions (8f-f2)
+ * Convolutions of the decoder with 1-2 input or 1-2 output channels, which cuDNN serves with generic
+ * engines: MotionEncoder.flow_net[0] / delta_flow_encoder[0] (7x7, 2 -> 128), mask_encoder[0] (3x3,
+ * 1 -> 64) -- raft_decoder.py:152-160, scflow_decoder.py:96-106 -- and XHead.predict_layer (3x3
+ * 256 -> 2, 1x1 256 -> 1; raft_decoder.py:281-287).  Stride 1, zero padding k/2, exact fp32. */
+
+/* out (n, h, w, cout) channels-last = act(conv(in) + bias).  in: element (n, ci, y, x) at
+ * n*stride_n + ci*stride_c + (y*w + x)*stride_px floats (planar or channels-last callers);
+ * wpack: [cin][k][k][cout] (Conv2d weight (cout,cin,k,k) permuted 1,2,3,0); cin in {1,2},
+ * ksize in {3,7}, cout % 32 == 0, w % 8 == 0. */
+int scflow_conv_small_cin_fwd(const float* in, long long stride_n, long long stride_c, long long stride_px,
+                              const float* wpack, const float* bias, float* out, int n, int cin, int h,
+                              int w, int cout, int ksize, int relu, void* stream);
+
+/* out (n, cout, h, w) planar = conv(in) + bias.  in: (n, h, w, c) channels-last, c % 4 == 0;
+ * wpack: [c][k*k][cout] (Conv2d weight (cout,c,k,k) permuted 1,2,3,0); cout in {1,2}, ksize in {1,3},
+ * (4 + 2*(ksize/2)) * w <= 1024. */
+int scflow_conv_small_cout_fwd(const float* in, const float* wpack, const float* bias, float* out, int n,
+                               int c, int h, int w, int cout, int ksize, void* stream);
+
 /* ------------------------------------------------------------------ backward (training, cfg5)
  * The reference gets these from autograd through ATen (grid_sampler_2d_backward,
  * avg_pool2d_backward, bmm backward, upsample_bilinear2d_backward and the elementwise chain of

@@ -214,3 +214,83 @@ extern "C" int scflow_nhwc_to_nchw(const float* in, float* out, int n, int P, in
   na::nhwc_to_nchw_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(in, out, P, C, round_tf32);
   return check_launch();
 }
+
+// ---------------------------------------------------------------------------------------------
+// GroupNorm (4 channels per group) + ReLU on a channels-last (n, P, C) tensor, one CTA per sample:
+// the pose head's conv -> GN -> ReLU layers (models/head/pose_head.py:128-137) work on 16x16 ... 4x4
+// maps, where torch's three-kernel native_group_norm + clamp_min_ chain costs 30-55 us per layer
+// against a 128 KB tensor.  A thread owns one group (= one float4) of a pixel column; statistics are
+// folded in fp64 through shared memory; the second pass re-reads the sample from L1/L2.
+namespace scflow {
+namespace na {
+constexpr int kGNThreads = 512;
+
+__global__ void __launch_bounds__(kGNThreads)
+group_norm4_act_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                       const float* __restrict__ beta, float* __restrict__ out, int P, int C, float eps,
+                       int relu) {
+  __shared__ double red[kGNThreads][2];
+  __shared__ float stat[256][2];                     // per group: mean, rstd
+  const int G = C >> 2;                              // groups == float4 columns
+  const int lanes = kGNThreads / G;
+  const int g = threadIdx.x % G, pl = threadIdx.x / G;
+  const float4* src = reinterpret_cast<const float4*>(x + (size_t)blockIdx.x * P * C) + g;
+  float4* dst = reinterpret_cast<float4*>(out + (size_t)blockIdx.x * P * C) + g;
+  float s = 0.f, q = 0.f;
+  if (pl < lanes) {
+    int p = pl;
+    for (; p + 3 * lanes < P; p += 4 * lanes) {
+      float4 v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = __ldg(src + (size_t)(p + j * lanes) * G);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+        q = fmaf(v[j].x, v[j].x, q); q = fmaf(v[j].y, v[j].y, q);
+        q = fmaf(v[j].z, v[j].z, q); q = fmaf(v[j].w, v[j].w, q);
+      }
+    }
+    for (; p < P; p += lanes) {
+      const float4 v = __ldg(src + (size_t)p * G);
+      s += (v.x + v.y) + (v.z + v.w);
+      q = fmaf(v.x, v.x, q); q = fmaf(v.y, v.y, q); q = fmaf(v.z, v.z, q); q = fmaf(v.w, v.w, q);
+    }
+  }
+  red[threadIdx.x][0] = s; red[threadIdx.x][1] = q;
+  __syncthreads();
+  if (threadIdx.x < G) {
+    double su = 0.0, sq = 0.0;
+    for (int l = 0; l < lanes; ++l) { su += red[l * G + threadIdx.x][0]; sq += red[l * G + threadIdx.x][1]; }
+    const double cnt = 4.0 * P;
+    const double mean = su / cnt;
+    const double var = fmax(sq / cnt - mean * mean, 0.0);          // biased, as F.group_norm
+    stat[threadIdx.x][0] = (float)mean;
+    stat[threadIdx.x][1] = (float)(1.0 / sqrt(var + (double)eps));
+  }
+  __syncthreads();
+  if (pl >= lanes) return;
+  const float mean = stat[g][0], rstd = stat[g][1];
+  const float4 ga = __ldg(reinterpret_cast<const float4*>(gamma) + g);
+  const float4 be = __ldg(reinterpret_cast<const float4*>(beta) + g);
+  const float4 sc = make_float4(ga.x * rstd, ga.y * rstd, ga.z * rstd, ga.w * rstd);
+  const float4 sh = make_float4(be.x - mean * sc.x, be.y - mean * sc.y, be.z - mean * sc.z, be.w - mean * sc.w);
+  for (int p = pl; p < P; p += lanes) {
+    const float4 v = src[(size_t)p * G];
+    float4 y = make_float4(fmaf(v.x, sc.x, sh.x), fmaf(v.y, sc.y, sh.y), fmaf(v.z, sc.z, sh.z), fmaf(v.w, sc.w, sh.w));
+    if (relu) { y.x = fmaxf(y.x, 0.f); y.y = fmaxf(y.y, 0.f); y.z = fmaxf(y.z, 0.f); y.w = fmaxf(y.w, 0.f); }
+    dst[(size_t)p * G] = y;
+  }
+}
+}  // namespace na
+}  // namespace scflow
+
+extern "C" int scflow_group_norm4_act_nhwc(const float* x, const float* gamma, const float* beta, float* out,
+                                           int n, int P, int C, float eps, int relu, void* stream) {
+  using namespace scflow;
+  if (!x || !gamma || !beta || !out) return SCFLOW_E_NULL;
+  if (n <= 0 || P <= 0 || C < 4 || (C & 3) != 0 || (C >> 2) > 256 || na::kGNThreads % (C >> 2) != 0)
+    return SCFLOW_E_BAD_SHAPE;
+  if (!aligned16(x) || !aligned16(out) || !aligned16(gamma) || !aligned16(beta)) return SCFLOW_E_MISALIGNED;
+  na::group_norm4_act_kernel<<<n, na::kGNThreads, 0, (cudaStream_t)stream>>>(x, gamma, beta, out, P, C, eps, relu);
+  return check_launch();
+}

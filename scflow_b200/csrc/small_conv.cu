@@ -1,0 +1,285 @@
+// The decoder's degenerate convolutions (flow/mask heads, delta-flow and mask
+// encoders), which cuDNN serves with generic engines at 65-75 us per call:
+//
+//   conv_small_cin   Cin in {1,2}, k in {3,7}, Cout % 32 == 0, stride 1, + bias + ReLU
+//                    MotionEncoder.flow_net[0] / delta_flow_encoder[0] (7x7, 2 -> 128) and
+//                    mask_encoder[0] (3x3, 1 -> 64): raft_decoder.py:152-160, scflow_decoder.py:96-106.
+//                    FP32-FMA bound (98 MAC per output): lane = output channel, 8 pixels of a row in
+//                    registers, weights [ci][ky][kx][Cout] and the input patch in shared memory.
+//   conv_small_cout  Cout in {1,2}, k in {1,3}, channels-last input, + bias
+//                    XHead.predict_layer (raft_decoder.py:281-287): flow 3x3 256 -> 2, mask 1x1 256 -> 1.
+//                    HBM-bound (reads the (N,h,w,C) feature map once): a CTA owns a band of rows, stages
+//                    32-channel slabs through shared memory (coalesced), every thread reduces its own
+//                    pixel against all taps, then the taps are gathered from the neighbours.
+//
+// Exact fp32 accumulation (tighter than the TF32 cuDNN kernels they replace).
+#include "common.cuh"
+
+namespace scflow {
+namespace sc {
+
+constexpr int kSegPx = 8;          // pixels per warp task (one row segment)
+constexpr int kTileW = 32;         // pixels per CTA tile (one row segment of <= 32)
+
+struct CinParams {
+  const float* in;        // element (n, ci, y, x) at n*sn + ci*sc + (y*w + x)*sp
+  const float* wpack;     // [CIN][KS][KS][Cout]
+  const float* bias;      // [Cout] or nullptr
+  float* out;             // (n, h, w, Cout) channels-last
+  long long sn, sc, sp;
+  int n, h, w, cout, relu;
+};
+
+template <int CIN, int KS>
+__global__ void __launch_bounds__(256)
+conv_small_cin_kernel(const CinParams p) {
+  constexpr int PAD = KS / 2;
+  constexpr int ROWLEN = kTileW + 8;                 // >= kTileW + KS - 1, multiple of 4
+  constexpr int PATCH = CIN * KS * ROWLEN;
+  constexpr int PER_THREAD = (PATCH + 255) / 256;
+  extern __shared__ __align__(16) float smem[];
+  float* wsm = smem;                                 // CIN*KS*KS*cout
+  float* patch0 = smem + CIN * KS * KS * p.cout;     // 2 x [CIN][KS][ROWLEN]
+  __shared__ __align__(8) uint64_t wbar;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t wbytes = (uint32_t)(CIN * KS * KS * p.cout * sizeof(float));
+  if (threadIdx.x == 0) {
+    // the filter bank (up to 50 KB) arrives as ONE bulk async copy while the first patch is fetched
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&wbar);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(wbytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     (uint32_t)__cvta_generic_to_shared(wsm)),
+                 "l"(p.wpack), "r"(wbytes), "r"(bar)
+                 : "memory");
+  }
+  const int xblocks = (p.w + kTileW - 1) / kTileW;
+  const long long tiles = (long long)p.n * p.h * xblocks;
+  const int groups = p.cout >> 5;
+  float pre[PER_THREAD];
+  auto fetch = [&](long long tile) {                 // this thread's share of a tile's input patch
+    const int xb = (int)(tile % xblocks);
+    const int y = (int)((tile / xblocks) % p.h);
+    const int n = (int)(tile / ((long long)xblocks * p.h));
+#pragma unroll
+    for (int k = 0; k < PER_THREAD; ++k) {
+      const int i = threadIdx.x + 256 * k;
+      const int col = i % ROWLEN, ky = (i / ROWLEN) % KS, ci = i / (ROWLEN * KS);
+      const int yy = y + ky - PAD, xx = xb * kTileW + col - PAD;
+      float v = 0.0f;
+      if (i < PATCH && col < kTileW + KS - 1 && yy >= 0 && yy < p.h && xx >= 0 && xx < p.w)
+        v = __ldg(p.in + n * p.sn + ci * p.sc + ((long long)yy * p.w + xx) * p.sp);
+      pre[k] = v;
+    }
+  };
+  auto stash = [&](float* dst) {
+#pragma unroll
+    for (int k = 0; k < PER_THREAD; ++k)
+      if (threadIdx.x + 256 * k < PATCH) dst[threadIdx.x + 256 * k] = pre[k];
+  };
+  int buf = 0;
+  if (blockIdx.x < tiles) { fetch(blockIdx.x); stash(patch0); }
+  __syncthreads();                                   // barrier initialised, first patch in place
+  {
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&wbar);
+    uint32_t done;
+    do {
+      asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], 0;\n\t"
+                   "selp.b32 %0, 1, 0, P1;\n\t}" : "=r"(done) : "r"(bar) : "memory");
+    } while (!done);
+  }
+  for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const int xb = (int)(tile % xblocks);
+    const int y = (int)((tile / xblocks) % p.h);
+    const int n = (int)(tile / ((long long)xblocks * p.h));
+    const int x0 = xb * kTileW;
+    const float* patch = patch0 + buf * PATCH;
+    const bool more = tile + gridDim.x < tiles;
+    if (more) fetch(tile + gridDim.x);               // next tile's loads fly under this tile's FMAs
+    const int segs = min(kTileW, p.w - x0) / kSegPx;
+    for (int task = warp; task < segs * groups; task += 8) {
+      const int seg = task % segs, grp = task / segs;
+      const int c = grp * 32 + lane;
+      float acc[kSegPx];
+      const float b = p.bias ? __ldg(p.bias + c) : 0.0f;
+#pragma unroll
+      for (int i = 0; i < kSegPx; ++i) acc[i] = b;
+#pragma unroll
+      for (int ci = 0; ci < CIN; ++ci) {
+#pragma unroll
+        for (int ky = 0; ky < KS; ++ky) {
+          float xr[kSegPx + 8];
+          const float4* src = reinterpret_cast<const float4*>(patch + (ci * KS + ky) * ROWLEN + seg * kSegPx);
+#pragma unroll
+          for (int j = 0; j < (kSegPx + KS - 1 + 3) / 4; ++j) {
+            const float4 v = src[j];                 // same address in every lane: broadcast
+            xr[4 * j] = v.x; xr[4 * j + 1] = v.y; xr[4 * j + 2] = v.z; xr[4 * j + 3] = v.w;
+          }
+          const float* wrow = wsm + ((ci * KS + ky) * KS) * p.cout + c;
+#pragma unroll
+          for (int kx = 0; kx < KS; ++kx) {
+            const float wv = wrow[kx * p.cout];
+#pragma unroll
+            for (int i = 0; i < kSegPx; ++i) acc[i] = fmaf(xr[kx + i], wv, acc[i]);
+          }
+        }
+      }
+      float* o = p.out + (((long long)n * p.h + y) * p.w + x0 + seg * kSegPx) * p.cout + c;
+#pragma unroll
+      for (int i = 0; i < kSegPx; ++i) o[(long long)i * p.cout] = p.relu ? fmaxf(acc[i], 0.0f) : acc[i];
+    }
+    if (more) stash(patch0 + (buf ^ 1) * PATCH);
+    __syncthreads();                                 // next patch visible; this one free for reuse
+    buf ^= 1;
+  }
+}
+
+template <int CIN, int KS>
+static int launch_cin(const CinParams& p, cudaStream_t st) {
+  const size_t smem = ((size_t)CIN * KS * KS * p.cout + 2 * (size_t)CIN * KS * (kTileW + 8)) * sizeof(float);
+  static size_t attr = 0;
+  if (smem > 48 * 1024 && smem > attr) {
+    cudaFuncSetAttribute(conv_small_cin_kernel<CIN, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    attr = smem;
+  }
+  const long long tiles = (long long)p.n * p.h * ((p.w + kTileW - 1) / kTileW);
+  const int per_sm = smem > 100 * 1024 ? 2 : smem > 56 * 1024 ? 3 : 4;
+  long long grid = tiles < 148LL * per_sm ? tiles : 148LL * per_sm;
+  conv_small_cin_kernel<CIN, KS><<<(unsigned)grid, 256, smem, st>>>(p);
+  return check_launch();
+}
+
+}  // namespace sc
+}  // namespace scflow
+
+extern "C" int scflow_conv_small_cin_fwd(const float* in, long long stride_n, long long stride_c,
+                                         long long stride_px, const float* wpack, const float* bias,
+                                         float* out, int n, int cin, int h, int w, int cout, int ksize,
+                                         int relu, void* stream) {
+  using namespace scflow;
+  if (!in || !wpack || !out) return SCFLOW_E_NULL;
+  if (n <= 0 || h <= 0 || w <= 0 || (w % sc::kSegPx) != 0 || cout <= 0 || (cout & 31) != 0 || cout > 256)
+    return SCFLOW_E_BAD_SHAPE;
+  sc::CinParams p{in, wpack, bias, out, stride_n, stride_c, stride_px, n, h, w, cout, relu};
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cin == 2 && ksize == 7) return sc::launch_cin<2, 7>(p, st);
+  if (cin == 1 && ksize == 3) return sc::launch_cin<1, 3>(p, st);
+  if (cin == 2 && ksize == 3) return sc::launch_cin<2, 3>(p, st);
+  if (cin == 1 && ksize == 7) return sc::launch_cin<1, 7>(p, st);
+  return SCFLOW_E_UNSUPPORTED;
+}
+
+// ---------------------------------------------------------------------------------------------
+namespace scflow {
+namespace sc {
+
+constexpr int kBandRows = 4;       // output rows per CTA
+constexpr int kSlab = 32;          // channels staged per step
+
+struct CoutParams {
+  const float* in;        // (n, h, w, C) channels-last
+  const float* wpack;     // [C][KS*KS*COUT]
+  const float* bias;      // [COUT] or nullptr
+  float* out;             // (n, COUT, h, w) planar
+  int n, h, w, c;
+};
+
+template <int KS, int COUT>
+__global__ void __launch_bounds__(1024)
+conv_small_cout_kernel(const CoutParams p) {
+  constexpr int PAD = KS / 2;
+  constexpr int NT = KS * KS * COUT;                 // partial sums per pixel
+  constexpr int NT4 = (NT + 3) & ~3;                 // padded so a channel's taps are float4 loads
+  extern __shared__ __align__(16) float smem[];
+  float* wsm = smem;                                 // [C][NT4]
+  float* T = wsm + p.c * NT4;                        // [pixels][NT]
+  const int bands = (p.h + kBandRows - 1) / kBandRows;
+  const int n = blockIdx.x / bands, band = blockIdx.x % bands;
+  const int y0 = band * kBandRows - PAD;             // first (halo) row of the band
+  const int tid = threadIdx.x;
+  for (int i = tid; i < p.c * NT4; i += blockDim.x) {
+    const int ch = i / NT4, j = i - ch * NT4;
+    wsm[i] = j < NT ? __ldg(p.wpack + ch * NT + j) : 0.0f;
+  }
+  __syncthreads();
+  const int r = tid / p.w, x = tid - r * p.w;
+  const int y = y0 + r;
+  float acc[NT4];
+#pragma unroll
+  for (int j = 0; j < NT4; ++j) acc[j] = 0.0f;
+  if (y >= 0 && y < p.h) {
+    // a thread walks its own pixel's channels (16 B per step; the 128-byte lines stay in L1 for the
+    // 8 steps that consume them), weights are broadcast float4 reads
+    const float4* src = reinterpret_cast<const float4*>(p.in + (((long long)n * p.h + y) * p.w + x) * p.c);
+#pragma unroll 2
+    for (int c4 = 0; c4 < p.c / 4; ++c4) {
+      const float4 v = __ldg(src + c4);
+      const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float4* wv = reinterpret_cast<const float4*>(wsm + (c4 * 4 + k) * NT4);
+#pragma unroll
+        for (int j = 0; j < NT4 / 4; ++j) {
+          const float4 w4 = wv[j];
+          acc[4 * j] = fmaf(vv[k], w4.x, acc[4 * j]);
+          acc[4 * j + 1] = fmaf(vv[k], w4.y, acc[4 * j + 1]);
+          acc[4 * j + 2] = fmaf(vv[k], w4.z, acc[4 * j + 2]);
+          acc[4 * j + 3] = fmaf(vv[k], w4.w, acc[4 * j + 3]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NT; ++j) T[tid * NT + j] = acc[j];
+  __syncthreads();
+  if (r >= PAD && r < PAD + kBandRows && y < p.h) {
+#pragma unroll
+    for (int co = 0; co < COUT; ++co) {
+      float s = p.bias ? __ldg(p.bias + co) : 0.0f;
+#pragma unroll
+      for (int ky = 0; ky < KS; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < KS; ++kx) {
+          const int xx = x + kx - PAD;
+          if (xx >= 0 && xx < p.w) s += T[((r + ky - PAD) * p.w + xx) * NT + (ky * KS + kx) * COUT + co];
+        }
+      p.out[(((long long)n * COUT + co) * p.h + y) * p.w + x] = s;
+    }
+  }
+}
+
+template <int KS, int COUT>
+static int launch_cout(const CoutParams& p, cudaStream_t st) {
+  constexpr int NT = KS * KS * COUT;
+  const int threads = (kBandRows + 2 * (KS / 2)) * p.w;
+  if (threads > 1024) return SCFLOW_E_BAD_SHAPE;
+  const size_t smem = ((size_t)p.c * ((NT + 3) & ~3) + (size_t)threads * NT) * sizeof(float);
+  if (smem > 200 * 1024) return SCFLOW_E_BAD_SHAPE;
+  static size_t attr = 0;
+  if (smem > 48 * 1024 && smem > attr) {
+    cudaFuncSetAttribute(conv_small_cout_kernel<KS, COUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    attr = smem;
+  }
+  const int bands = (p.h + kBandRows - 1) / kBandRows;
+  conv_small_cout_kernel<KS, COUT><<<(unsigned)(p.n * bands), threads, smem, st>>>(p);
+  return check_launch();
+}
+
+}  // namespace sc
+}  // namespace scflow
+
+extern "C" int scflow_conv_small_cout_fwd(const float* in, const float* wpack, const float* bias,
+                                          float* out, int n, int c, int h, int w, int cout, int ksize,
+                                          void* stream) {
+  using namespace scflow;
+  if (!in || !wpack || !out) return SCFLOW_E_NULL;
+  if (n <= 0 || h <= 0 || w <= 0 || c <= 0 || (c & 3) != 0) return SCFLOW_E_BAD_SHAPE;
+  sc::CoutParams p{in, wpack, bias, out, n, h, w, c};
+  cudaStream_t st = (cudaStream_t)stream;
+  if (ksize == 3 && cout == 2) return sc::launch_cout<3, 2>(p, st);
+  if (ksize == 3 && cout == 1) return sc::launch_cout<3, 1>(p, st);
+  if (ksize == 1 && cout == 1) return sc::launch_cout<1, 1>(p, st);
+  if (ksize == 1 && cout == 2) return sc::launch_cout<1, 2>(p, st);
+  return SCFLOW_E_UNSUPPORTED;
+}

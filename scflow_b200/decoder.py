@@ -123,7 +123,7 @@ class SCFlowDecoder(nn.Module):
         for _ in range(self.iters):
             corr = self.corr_lookup(corr_pyramid, flow)
             if fused_gru:
-                motion = self.encoder.features(corr, flow.contiguous(memory_format=torch.channels_last))
+                motion = self.encoder.features(corr, flow)
                 ops.pack_nhwc(x_buf, self.cxt_channels, a=motion.permute(0, 2, 3, 1), planar=flow)
                 gru_tc.update_inplace(self.gru, h_state, h_round, x_buf, rh)
             else:

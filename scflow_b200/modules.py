@@ -65,7 +65,36 @@ class ConvModule(nn.Module):
                 and (not self.with_activation or isinstance(self.activate, nn.ReLU))
                 and x.is_contiguous(memory_format=torch.channels_last))
 
+    def _small_cin_ok(self, x) -> bool:
+        c = self.conv
+        return (not torch.is_grad_enabled() and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4
+                and not self.with_norm and c.in_channels <= 2 and c.kernel_size in ((3, 3), (7, 7))
+                and c.stride == (1, 1) and c.padding == (c.kernel_size[0] // 2,) * 2 and c.dilation == (1, 1)
+                and c.groups == 1 and c.out_channels % 32 == 0 and c.out_channels <= 256
+                and x.shape[-1] % 8 == 0
+                and (not self.with_activation or isinstance(self.activate, nn.ReLU)))
+
+    def _gn_fused_ok(self, x) -> bool:
+        if not (self.with_norm and self.norm_name == "gn"):
+            return False
+        gn = self.gn
+        return (not torch.is_grad_enabled() and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4
+                and gn.affine and gn.num_channels == 4 * gn.num_groups and 512 % gn.num_groups == 0
+                and (not self.with_activation or isinstance(self.activate, nn.ReLU)))
+
     def forward(self, x):
+        if self._gn_fused_ok(x):
+            # conv (cuDNN, channels-last) -> GroupNorm + ReLU in ONE in-place launch
+            c = self.conv
+            if not c.weight.is_contiguous(memory_format=torch.channels_last):
+                c.weight.data = c.weight.data.contiguous(memory_format=torch.channels_last)
+            y = F.conv2d(x.contiguous(memory_format=torch.channels_last), c.weight, None, c.stride,
+                         c.padding).contiguous(memory_format=torch.channels_last)
+            ops.group_norm4_act(y.permute(0, 2, 3, 1), self.gn, relu=self.with_activation)
+            return y
+        if self._small_cin_ok(x):
+            # 1-2 input channels: FP32-FMA kernel with bias + ReLU fused (csrc/small_conv.cu)
+            return ops.conv_small_cin(x, self.conv, relu=self.with_activation)
         if self._fused_ok(x):
             # channels-last inference: cuDNN convolution without bias, then bias + ReLU in ONE
             # in-place pass of scflow_norm_act_nhwc (instead of add_ and clamp_min_)
@@ -194,4 +223,11 @@ class XHead(nn.Module):
             raise ValueError(f"x must be 'flow' or 'mask', but got {x}")
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return self.predict_layer(self.layers(x))
+        y = self.layers(x)
+        p = self.predict_layer
+        if (not torch.is_grad_enabled() and y.is_cuda and y.dtype == torch.float32
+                and y.is_contiguous(memory_format=torch.channels_last) and y.shape[1] % 32 == 0
+                and (4 + 2 * (p.kernel_size[0] // 2)) * y.shape[-1] <= 1024 and y.shape[-1] % 8 == 0):
+            # 1-2 output channels: one pass over the feature map (csrc/small_conv.cu)
+            return ops.conv_small_cout(y, p)
+        return p(y)

@@ -285,3 +285,89 @@ def downsample(x, scale: int = 8, mul: float = 1.0):
         rc = lib.scflow_downsample_fwd(_ptr(x), _ptr(out), n, c, H, W, scale, float(mul), _stream())
     _lib.check(rc, "scflow_downsample_fwd")
     return out
+
+
+def _packed_conv_weight(conv: torch.nn.Conv2d) -> torch.Tensor:
+    """Conv2d weight (cout, cin, k, k) as [cin][k][k][cout] fp32, cached on the module and rebuilt when
+    the parameter changes (version counter / storage), never saved."""
+    w = conv.weight
+    key = (w._version, w.data_ptr(), w.device)
+    hit = conv.__dict__.get("_scflow_wpack")
+    if hit is None or hit[0] != key:
+        hit = (key, w.detach().float().permute(1, 2, 3, 0).contiguous())
+        conv.__dict__["_scflow_wpack"] = hit
+    return hit[1]
+
+
+def conv_small_cin(x: torch.Tensor, conv: torch.nn.Conv2d, relu: bool) -> torch.Tensor:
+    """act(conv(x) + bias) for cin in {1,2}: returns an NCHW-shaped channels-last tensor.  x may be
+    planar or channels-last (strides are passed through)."""
+    lib = _lib.load()
+    if not x.is_cuda or x.dtype != torch.float32:
+        _chk(x, "x")
+    n, cin, h, w = x.shape
+    if x.is_contiguous():
+        sn, sc, sp = cin * h * w, h * w, 1
+    elif x.is_contiguous(memory_format=torch.channels_last):
+        sn, sc, sp = cin * h * w, 1, cin
+    else:
+        x = x.contiguous()
+        sn, sc, sp = cin * h * w, h * w, 1
+    cout, k = conv.out_channels, conv.kernel_size[0]
+    out = torch.empty((n, h, w, cout), device=x.device, dtype=torch.float32)
+    with _timed("scflow_conv_small_cin_fwd", 1, 4 * (x.numel() + out.numel())):
+        rc = lib.scflow_conv_small_cin_fwd(_ptr(x), sn, sc, sp, _ptr(_packed_conv_weight(conv)),
+                                           _ptr(conv.bias.detach() if conv.bias is not None else None),
+                                           _ptr(out), n, cin, h, w, cout, k, 1 if relu else 0, _stream())
+    _lib.check(rc, "scflow_conv_small_cin_fwd")
+    return out.permute(0, 3, 1, 2)
+
+
+def conv_small_cout(x: torch.Tensor, conv: torch.nn.Conv2d) -> torch.Tensor:
+    """conv(x) + bias for cout in {1,2} on a channels-last x: planar (n, cout, h, w)."""
+    lib = _lib.load()
+    n, c, h, w = x.shape
+    xn = _chk(x.permute(0, 2, 3, 1), "x")          # no copy for channels-last inputs
+    cout, k = conv.out_channels, conv.kernel_size[0]
+    out = torch.empty((n, cout, h, w), device=x.device, dtype=torch.float32)
+    with _timed("scflow_conv_small_cout_fwd", 1, 4 * (x.numel() + out.numel())):
+        rc = lib.scflow_conv_small_cout_fwd(_ptr(xn), _ptr(_packed_conv_weight(conv)),
+                                            _ptr(conv.bias.detach() if conv.bias is not None else None),
+                                            _ptr(out), n, c, h, w, cout, k, _stream())
+    _lib.check(rc, "scflow_conv_small_cout_fwd")
+    return out
+
+
+def group_norm4_act(x: torch.Tensor, gn: torch.nn.GroupNorm, relu: bool) -> torch.Tensor:
+    """In-place GroupNorm (4 channels per group) + ReLU on a channels-last (N,H,W,C) tensor."""
+    lib = _lib.load()
+    x = _chk(x, "x")
+    n, H, W, C = x.shape
+    with _timed("scflow_group_norm4_act_nhwc", 1, 8 * x.numel()):
+        rc = lib.scflow_group_norm4_act_nhwc(_ptr(x), _ptr(gn.weight.detach()), _ptr(gn.bias.detach()), _ptr(x),
+                                             n, H * W, C, float(gn.eps), 1 if relu else 0, _stream())
+    _lib.check(rc, "scflow_group_norm4_act_nhwc")
+    return x
+
+
+def pose_fc(x2d: torch.Tensor, w0: torch.Tensor, head, label: torch.Tensor, splitk: int = 4):
+    """FC tail of MultiClassPoseHead on x2d (M, K) with the (possibly column-permuted) fc0 weight w0:
+    returns (dr (M,6), dt (M,3)) of the class of label[0]."""
+    lib = _lib.load()
+    x2d = _chk(x2d, "x")
+    M, K = x2d.shape
+    fc0, fc1 = head.fc_layers[0][0], head.fc_layers[1][0]
+    n0, n1 = fc0.out_features, fc1.out_features
+    label = _chk(label, "label", torch.int64)
+    ws = torch.empty(lib.scflow_pose_fc_workspace_floats(M, n0, n1, splitk), device=x2d.device, dtype=torch.float32)
+    dr = torch.empty((M, 6), device=x2d.device, dtype=torch.float32)
+    dt = torch.empty((M, 3), device=x2d.device, dtype=torch.float32)
+    d = lambda t: _ptr(t.detach())
+    with _timed("scflow_pose_fc_fwd", 3, 4 * (w0.numel() + x2d.numel())):
+        rc = lib.scflow_pose_fc_fwd(_ptr(x2d), d(w0), d(fc0.bias), d(fc1.weight), d(fc1.bias),
+                                    d(head.rotation_pred.weight), d(head.rotation_pred.bias),
+                                    d(head.translation_pred.weight), d(head.translation_pred.bias),
+                                    _ptr(label), _ptr(ws), _ptr(dr), _ptr(dt), M, K, n0, n1, head.num_class,
+                                    splitk, _stream())
+    _lib.check(rc, "scflow_pose_fc_fwd")
+    return dr, dt

@@ -50,7 +50,27 @@ class MultiClassPoseHead(nn.Module):
         with torch.no_grad():
             self.rotation_pred.bias.copy_(torch.tensor([1., 0., 0., 0., 1., 0.] * self.num_class))
 
+    def _fc0_permuted(self, P: int) -> torch.Tensor:
+        """fc0 weight with its columns re-ordered from flatten(NCHW) = c*P + p to the channels-last memory
+        order p*C + c of the conv stack's output (so no flatten copy is needed); cached per version."""
+        w = self.fc_layers[0][0].weight
+        key = (w._version, w.data_ptr(), P)
+        hit = self.__dict__.get("_scflow_fc0")
+        if hit is None or hit[0] != key:
+            C = w.shape[1] // P
+            hit = (key, w.detach().view(w.shape[0], C, P).permute(0, 2, 1).reshape(w.shape[0], P * C).contiguous())
+            self.__dict__["_scflow_fc0"] = hit
+        return hit[1]
+
     def forward(self, x: torch.Tensor, label: torch.Tensor):
+        if (not torch.is_grad_enabled() and x.is_cuda and x.dtype == torch.float32
+                and self.fc_layers[1][0].out_features + self.fc_layers[0][0].out_features <= 12288):
+            # inference: conv -> GN+ReLU (fused) x3 in channels-last, then the whole FC tail in two launches
+            from . import ops
+            y = self.conv_layers(x)
+            n, c, hs, ws = y.shape
+            y2d = y.permute(0, 2, 3, 1).reshape(n, hs * ws * c)          # a view for channels-last y
+            return ops.pose_fc(y2d, self._fc0_permuted(hs * ws), self, label)
         x = self.fc_layers(self.flatten_op(self.conv_layers(x)))
         dt = self.translation_pred(x).view(-1, self.num_class, 3)
         dr = self.rotation_pred(x).view(-1, self.num_class, self.rotation_out_channels)

@@ -407,3 +407,79 @@ def test_encoder_fused_path_matches_module_path(norm):
             want = enc(x.clone().requires_grad_(False)).detach()
     assert got.shape == want.shape
     assert rel(got, want) < 2e-5
+
+
+# ------------------------------------------------------------------ f2: degenerate convolutions
+@pytest.mark.parametrize("cin,k,cout,n,h,w", [(2, 7, 128, 3, 32, 32), (1, 3, 64, 2, 32, 32), (2, 7, 128, 2, 8, 8),
+                                              (2, 7, 128, 1, 64, 64), (1, 3, 64, 2, 16, 40)])
+@pytest.mark.parametrize("channels_last", [False, True])
+def test_conv_small_cin_vs_torch(cin, k, cout, n, h, w, channels_last):
+    from scflow_b200.modules import ConvModule
+    g = torch.Generator().manual_seed(5)
+    m = ConvModule(cin, cout, k, padding=k // 2).to(DEV)
+    x = torch.randn(n, cin, h, w, generator=g).to(DEV)
+    if channels_last:
+        x = x.contiguous(memory_format=torch.channels_last)
+    want = torch.relu(torch.nn.functional.conv2d(x.double(), m.conv.weight.double(), m.conv.bias.double(), padding=k // 2))
+    ops.STATS.reset()
+    with torch.no_grad():
+        got = m(x)
+    assert ops.STATS.count == 1 and got.shape == want.shape
+    assert rel(got, want) < 1e-5
+
+
+@pytest.mark.parametrize("k,cout,n,h,w", [(3, 2, 3, 32, 32), (1, 1, 2, 32, 32), (3, 2, 2, 8, 8), (3, 2, 1, 64, 64),
+                                          (1, 1, 1, 64, 64), (3, 2, 1, 10, 16)])
+def test_conv_small_cout_vs_torch(k, cout, n, h, w):
+    from scflow_b200.modules import XHead
+    g = torch.Generator().manual_seed(6)
+    head = XHead(128, [256], cout, x="flow" if k == 3 else "mask").to(DEV)
+    y = torch.randn(n, 256, h, w, generator=g).to(DEV).contiguous(memory_format=torch.channels_last)
+    p = head.predict_layer
+    want = torch.nn.functional.conv2d(y.double(), p.weight.double(), p.bias.double(), padding=k // 2)
+    with torch.no_grad():
+        got = ops.conv_small_cout(y, p)
+    assert got.is_contiguous() and got.shape == want.shape
+    assert rel(got, want) < 1e-5
+    with torch.no_grad():                       # the module path picks the kernel up
+        ops.STATS.reset()
+        head(torch.randn(n, 128, h, w, generator=g).to(DEV).contiguous(memory_format=torch.channels_last))
+        assert ops.STATS.count >= 2
+
+
+def test_group_norm_relu_vs_torch():
+    from scflow_b200.modules import ConvModule
+    g = torch.Generator().manual_seed(8)
+    for (n, cin, h, w) in ((3, 224, 32, 32), (2, 128, 8, 8), (2, 128, 6, 10)):
+        m = ConvModule(cin, 128, 3, stride=2, padding=1, norm_cfg=dict(type="GN", num_groups=32), act_cfg=dict(type="ReLU")).to(DEV)
+        with torch.no_grad():
+            m.gn.weight.copy_(torch.randn(128, generator=g)); m.gn.bias.copy_(torch.randn(128, generator=g))
+        x = torch.randn(n, cin, h, w, generator=g).to(DEV)
+        y = torch.nn.functional.conv2d(x, m.conv.weight, None, stride=2, padding=1)
+        want = torch.relu(torch.nn.functional.group_norm(y.double(), 32, m.gn.weight.double(), m.gn.bias.double(), m.gn.eps))
+        ops.STATS.reset()
+        with torch.no_grad():
+            got = m(x.contiguous(memory_format=torch.channels_last))
+        assert ops.STATS.count == 1
+        assert rel(got, want) < 2e-5
+
+
+@pytest.mark.parametrize("n,feat", [(64, 32), (3, 32), (2, 64), (5, 8)])
+def test_pose_head_fused_vs_module_path(n, feat):
+    from scflow_b200.pose_head import MultiClassPoseHead
+    g = torch.Generator().manual_seed(9)
+    head = MultiClassPoseHead(21, 224, "Basic", dict(type="GN", num_groups=32), dict(type="ReLU"),
+                              feat_size=(feat, feat), rotation_mode="ortho6d").to(DEV)
+    with torch.no_grad():
+        for p_ in head.parameters():
+            p_.copy_(torch.randn(p_.shape, generator=g).to(DEV) * (0.05 if p_.dim() > 1 else 0.5))
+    x = torch.randn(n, 224, feat, feat, generator=g).to(DEV)
+    label = torch.randint(0, 21, (n,), generator=g).to(DEV)
+    with torch.enable_grad():                                  # module path (cuDNN / cuBLAS fp32)
+        dr_w, dt_w = head(x, label)
+    ops.STATS.reset()
+    with torch.no_grad():
+        dr, dt = head(x.contiguous(memory_format=torch.channels_last), label)
+    assert ops.STATS.count == 6                                # 3 GN launches + 3 FC launches
+    assert dr.shape == dr_w.shape and dt.shape == dt_w.shape
+    assert rel(dr, dr_w) < 1e-4 and rel(dt, dt_w) < 1e-4

@@ -7,7 +7,7 @@ import torch
 from scflow_b200 import ops, gru_tc, modules
 
 ap = argparse.ArgumentParser()
-ap.add_argument("which", nargs="*", default=["lookup", "gru", "corr", "pose"])
+ap.add_argument("which", nargs="*", default=["lookup", "gru", "corr", "pose", "small"])
 ap.add_argument("--n", type=int, default=64)
 ap.add_argument("--s", type=int, default=256)
 ap.add_argument("--reps", type=int, default=20)
@@ -78,3 +78,39 @@ if "pose" in a.which:
     us = timeit(lambda i: ops.pose_flow(c["R0"], c["t0"], c["K"], dR6=dR6, dt=dt, depth=c["depth"], R0=c["R0"], t0=c["t0"]))
     by = N * (4 * S * S + 8 * S * S + 8 * P)
     print(f"pose_flow           {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)  (includes 4 output allocations)")
+
+if "small" in a.which:
+    import torch.nn.functional as F
+    from scflow_b200.modules import ConvModule, XHead
+    torch.backends.cudnn.allow_tf32 = True
+    torch.backends.cudnn.benchmark = True
+    for cin, k, cout in ((2, 7, 128), (1, 3, 64)):
+        m = ConvModule(cin, cout, k, padding=k // 2).to(dev)
+        xs = [torch.randn(N, cin, h, w, device=dev, generator=g) for _ in range(4)]
+        with torch.no_grad():
+            us = timeit(lambda i: m(xs[i % 4]))
+            ref = timeit(lambda i: torch.relu_(F.conv2d(xs[i % 4].contiguous(memory_format=torch.channels_last), m.conv.weight, m.conv.bias, padding=k // 2)))
+        by = N * P * (cin + cout) * 4
+        print(f"conv_small_cin {cin}->{cout} {k}x{k}  {us:8.1f} us  {by/us/1e3:7.1f} GB/s  (cuDNN+relu {ref:.1f} us)")
+    for k, cout in ((3, 2), (1, 1)):
+        hd = XHead(128, [256], cout, x="flow" if k == 3 else "mask").to(dev)
+        ys = [torch.randn(N, 256, h, w, device=dev, generator=g).contiguous(memory_format=torch.channels_last) for _ in range(4)]
+        with torch.no_grad():
+            us = timeit(lambda i: ops.conv_small_cout(ys[i % 4], hd.predict_layer))
+            ref = timeit(lambda i: hd.predict_layer(ys[i % 4]))
+        by = N * P * (256 + cout) * 4
+        print(f"conv_small_cout 256->{cout} {k}x{k}  {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)  (cuDNN {ref:.1f} us)")
+if "posefc" in a.which:
+    from scflow_b200.pose_head import MultiClassPoseHead
+    head = MultiClassPoseHead(21, 224, "Basic", dict(type="GN", num_groups=32), dict(type="ReLU"),
+                              feat_size=(h, w), rotation_mode="ortho6d").to(dev)
+    fc_in = head.fc_layers[0][0].in_features
+    xs = [torch.randn(N, fc_in, device=dev, generator=g) for _ in range(4)]
+    lab = torch.zeros(N, dtype=torch.int64, device=dev)
+    w0 = head.fc_layers[0][0].weight.detach()
+    with torch.no_grad():
+        us = timeit(lambda i: ops.pose_fc(xs[i % 4], w0, head, lab))
+        def ref(i):
+            y = head.fc_layers(xs[i % 4]); return head.rotation_pred(y), head.translation_pred(y)
+        r = timeit(ref)
+    print(f"pose_fc (3 launches) {us:8.1f} us   (cuBLAS fp32 chain {r:.1f} us)")
