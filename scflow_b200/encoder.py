@@ -46,6 +46,22 @@ def _bn_affine(bn: nn.BatchNorm2d, bias):
     return val
 
 
+def _bn_folded(conv: nn.Conv2d, bn: nn.BatchNorm2d):
+    """Eval BatchNorm2d folded INTO the preceding convolution: (w * scale[cout], shift) as a
+    channels-last filter + bias, so cuDNN's fused conv+bias(+residual)+ReLU kernels produce the
+    block's output in one launch.  Cached on the conv, keyed on every tensor involved."""
+    key = tuple((t.data_ptr(), t._version) for t in (conv.weight, conv.bias, bn.weight, bn.bias,
+                                                     bn.running_mean, bn.running_var) if t is not None)
+    hit = conv.__dict__.get("_scflow_folded")
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    scale, shift = _bn_affine(bn, conv.bias)
+    with torch.no_grad():
+        w = (conv.weight.float() * scale.view(-1, 1, 1, 1)).contiguous(memory_format=torch.channels_last)
+    conv.__dict__["_scflow_folded"] = (key, (w, shift))
+    return w, shift
+
+
 def _side(norm: nn.Module, y: torch.Tensor, bias):
     """Normalisation coefficients of conv output y (channels-last view): kwargs for ops.norm_act."""
     if isinstance(norm, nn.InstanceNorm2d):
@@ -89,6 +105,18 @@ class BasicBlock(nn.Module):
     def forward_fused(self, x: torch.Tensor) -> torch.Tensor:
         """x, result: channels-last (N,C,H,W)-shaped tensors."""
         n1, n2 = getattr(self, self.norm1_name), getattr(self, self.norm2_name)
+        if isinstance(n1, nn.BatchNorm2d):
+            # eval BN folded into the filters: three cuDNN launches per block, no separate norm pass
+            w1, b1 = _bn_folded(self.conv1, n1)
+            w2, b2 = _bn_folded(self.conv2, n2)
+            o = torch.cudnn_convolution_relu(x, w1, b1, self.conv1.stride, self.conv1.padding, (1, 1), 1)
+            idt = x
+            if self.downsample is not None:
+                wd, bd = _bn_folded(self.downsample[0], self.downsample[1])
+                idt = F.conv2d(x, wd, bd, self.downsample[0].stride, self.downsample[0].padding)
+                idt = idt.contiguous(memory_format=torch.channels_last)
+            return torch.cudnn_convolution_add_relu(o, w2, idt, 1.0, b2, self.conv2.stride, self.conv2.padding,
+                                                    (1, 1), 1)
         o = _conv_cl(self.conv1, x)
         kw, eps = _side(n1, _nhwc(o), self.conv1.bias)
         ops.norm_act(_nhwc(o), relu=True, eps=eps, **kw)
@@ -154,9 +182,14 @@ class RAFTEncoder(nn.Module):
         """Inference path: same values as forward() (the IN-cancelled conv bias aside, a rounding-
         level difference), channels-last activations, norms through csrc/norm_act.cu."""
         x = x.contiguous(memory_format=torch.channels_last)
-        y = _conv_cl(self.conv1, x)
-        kw, eps = _side(getattr(self, self.norm1_name), _nhwc(y), self.conv1.bias)
-        ops.norm_act(_nhwc(y), relu=True, eps=eps, **kw)
+        n1 = getattr(self, self.norm1_name)
+        if isinstance(n1, nn.BatchNorm2d):
+            w1, b1 = _bn_folded(self.conv1, n1)
+            y = torch.cudnn_convolution_relu(x, w1, b1, self.conv1.stride, self.conv1.padding, (1, 1), 1)
+        else:
+            y = _conv_cl(self.conv1, x)
+            kw, eps = _side(n1, _nhwc(y), self.conv1.bias)
+            ops.norm_act(_nhwc(y), relu=True, eps=eps, **kw)
         for name in self.res_layers:
             for block in getattr(self, name):
                 y = block.forward_fused(y)

@@ -61,8 +61,8 @@ class ConvModule(nn.Module):
 
     def _fused_ok(self, x) -> bool:
         return (not torch.is_grad_enabled() and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4
-                and not self.with_norm and self.conv.bias is not None and self.conv.out_channels % 4 == 0
-                and (not self.with_activation or isinstance(self.activate, nn.ReLU))
+                and not self.with_norm and self.conv.bias is not None and self.conv.groups == 1
+                and self.with_activation and isinstance(self.activate, nn.ReLU)
                 and x.is_contiguous(memory_format=torch.channels_last))
 
     def _small_cin_ok(self, x) -> bool:
@@ -96,19 +96,12 @@ class ConvModule(nn.Module):
             # 1-2 input channels: FP32-FMA kernel with bias + ReLU fused (csrc/small_conv.cu)
             return ops.conv_small_cin(x, self.conv, relu=self.with_activation)
         if self._fused_ok(x):
-            # channels-last inference: cuDNN convolution without bias, then bias + ReLU in ONE
-            # in-place pass of scflow_norm_act_nhwc (instead of add_ and clamp_min_)
+            # channels-last inference: cuDNN's fused convolution + bias + ReLU (one launch, same bits as
+            # conv followed by a separate bias/ReLU pass, which it saves)
             c = self.conv
-            w = c.weight
-            if not w.is_contiguous(memory_format=torch.channels_last):
-                c.weight.data = w.data.contiguous(memory_format=torch.channels_last)
-            y = F.conv2d(x, c.weight, None, c.stride, c.padding).contiguous(memory_format=torch.channels_last)
-            ones = self.__dict__.get("_scflow_ones")
-            if ones is None or ones.device != y.device:
-                ones = torch.ones(c.out_channels, device=y.device, dtype=torch.float32)
-                self.__dict__["_scflow_ones"] = ones
-            ops.norm_act(y.permute(0, 2, 3, 1), affine=(ones, c.bias.detach()), relu=self.with_activation)
-            return y
+            if not c.weight.is_contiguous(memory_format=torch.channels_last):
+                c.weight.data = c.weight.data.contiguous(memory_format=torch.channels_last)
+            return torch.cudnn_convolution_relu(x, c.weight, c.bias, c.stride, c.padding, c.dilation, 1)
         x = self.conv(x)
         if self.with_norm:
             x = getattr(self, self.norm_name)(x)
