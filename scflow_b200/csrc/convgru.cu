@@ -631,6 +631,19 @@ __global__ void pack_nhwc_kernel(const float* __restrict__ a, int ca, const floa
     dst[pix * cdst + dst_off + c] = round_tf32 ? rn_tf32(v) : v;
   }
 }
+
+// one dense channels-last source whose channel counts / offsets are multiples of 4: a strided float4 copy
+__global__ void __launch_bounds__(256)
+pack4_nhwc_kernel(const float4* __restrict__ a, int ca4, float4* __restrict__ dst, int cdst4, int off4,
+                  unsigned total, int round_tf32) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const unsigned pix = i / (unsigned)ca4;
+    const unsigned c = i - pix * (unsigned)ca4;
+    float4 v = __ldg(a + i);
+    if (round_tf32) { v.x = rn_tf32(v.x); v.y = rn_tf32(v.y); v.z = rn_tf32(v.z); v.w = rn_tf32(v.w); }
+    dst[(size_t)pix * cdst4 + off4 + c] = v;
+  }
+}
 }  // namespace gru
 }  // namespace scflow
 
@@ -643,6 +656,15 @@ extern "C" int scflow_pack_nhwc(const float* a, int ca, const float* b, int cb, 
     return SCFLOW_E_BAD_SHAPE;
   const long long total = npix * (ca + cb + cf);
   if (total == 0) return SCFLOW_OK;
+  if (cb == 0 && cf == 0 && ((ca | cdst | dst_off) & 3) == 0 && total / 4 < (1ll << 32) && aligned16(a) &&
+      aligned16(dst)) {
+    long long b4 = (total / 4 + 255) / 256;
+    if (b4 > 148 * 16) b4 = 148 * 16;
+    gru::pack4_nhwc_kernel<<<(unsigned)b4, 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const float4*>(a), ca / 4, reinterpret_cast<float4*>(dst), cdst / 4, dst_off / 4,
+        (unsigned)(total / 4), round_tf32);
+    return check_launch();
+  }
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
   gru::pack_nhwc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a, ca, b, cb, f, cf, dst, cdst,

@@ -123,8 +123,14 @@ class SCFlowDecoder(nn.Module):
         for _ in range(self.iters):
             corr = self.corr_lookup(corr_pyramid, flow)
             if fused_gru:
-                motion = self.encoder.features(corr, flow)
-                ops.pack_nhwc(x_buf, self.cxt_channels, a=motion.permute(0, 2, 3, 1), planar=flow)
+                if self.encoder.out_channels[0] == 126 and self.cxt_channels == 128:
+                    # 128-channel motion tensor (2 zero channels) packed as float4s, then the flow pair
+                    motion = self.encoder.features_padded(corr, flow)
+                    ops.pack_nhwc(x_buf, self.cxt_channels, a=motion.permute(0, 2, 3, 1))
+                    ops.pack_nhwc(x_buf, self.cxt_channels + 126, planar=flow)
+                else:
+                    motion = self.encoder.features(corr, flow)
+                    ops.pack_nhwc(x_buf, self.cxt_channels, a=motion.permute(0, 2, 3, 1), planar=flow)
                 gru_tc.update_inplace(self.gru, h_state, h_round, x_buf, rh)
             else:
                 motion_feat = self.encoder(corr, flow)

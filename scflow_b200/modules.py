@@ -196,6 +196,23 @@ class MotionEncoder(nn.Module):
         """The 126 learned motion channels (raft_decoder.py:162-165), before `flow` is appended."""
         return self.out_net(torch.cat([self.corr_net(corr), self.flow_net(flow)], dim=1))
 
+    def features_padded(self, corr: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
+        """Inference only: the 126 motion channels as a 128-channel channels-last tensor whose last
+        two channels are exactly zero (two zero filters appended to out_net, cached): cuDNN's
+        128-channel kernel is 1.8x faster than its 126-channel one, and the consumer packs float4s."""
+        conv = self.out_net[0].conv
+        key = (conv.weight._version, conv.weight.data_ptr(), conv.bias._version)
+        hit = self.__dict__.get("_scflow_out128")
+        if hit is None or hit[0] != key:
+            pad = 128 - conv.out_channels
+            w = torch.cat([conv.weight.detach(), conv.weight.new_zeros((pad,) + tuple(conv.weight.shape[1:]))])
+            b = torch.cat([conv.bias.detach(), conv.bias.new_zeros(pad)])
+            hit = (key, (w.contiguous(memory_format=torch.channels_last), b))
+            self.__dict__["_scflow_out128"] = hit
+        w, b = hit[1]
+        x = torch.cat([self.corr_net(corr), self.flow_net(flow)], dim=1)
+        return torch.cudnn_convolution_relu(x, w, b, conv.stride, conv.padding, conv.dilation, 1)
+
     def forward(self, corr: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
         return torch.cat([self.features(corr, flow), flow], dim=1)
 
