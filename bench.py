@@ -147,10 +147,11 @@ def cpu_run(batch, state, reps, warm):
     from oracle import scflow_oracle as O
     se, sc, sd = state
     n = batch["depth"].shape[0]
+    last = {}
     def once():
         with torch.no_grad():
-            O.refiner_forward(se, sc, sd, batch["rendered_images"], batch["real_images"], batch["R0"], batch["t0"],
-                              batch["depth"], batch["K"], batch["labels"])
+            last["out"] = O.refiner_forward(se, sc, sd, batch["rendered_images"], batch["real_images"], batch["R0"],
+                                            batch["t0"], batch["depth"], batch["K"], batch["labels"])
     for _ in range(warm):
         once()
     ts = []
@@ -158,6 +159,7 @@ def cpu_run(batch, state, reps, warm):
         t0 = time.perf_counter()
         once()
         ts.append(time.perf_counter() - t0)
+    cpu_run.last_pose = (last["out"]["rotations"][-1], last["out"]["translations"][-1])
     return n, ts
 
 
@@ -221,7 +223,8 @@ def ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B, S = args.batch, args.image
-    torch.backends.cudnn.allow_tf32 = True      # cuDNN parts at the reference's own GPU default
+    # cuDNN parts at the reference's own GPU default (TF32 allowed) unless --strict-fp32
+    torch.backends.cudnn.allow_tf32 = not args.strict_fp32
     torch.backends.cudnn.benchmark = True
     core = seeded_weights(SCFlowRefinerCore(S)).eval().to(dev)
     # two distinct input sets, alternated, so no step re-reads the previous step's inputs from L2;
@@ -355,13 +358,36 @@ def ours(args):
                 "frac": kern[top]["hbm_frac"], "traffic": traffic, "peak_source": pk["src"],
                 "algorithmic_bytes_per_launch": algorithmic_bytes(top, B, S)}
     # bounded CPU baseline on this box's host cores (rank 0, N=1 only)
-    cpu = None
+    cpu = parity = strict = None
     if world == 1 and not args.no_cpu_baseline:
+        from oracle import scflow_oracle as O          # checker only: the CPU leg and the parity read-out
+        from scflow_b200.refiner import unpack_pose
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
-        n, ts = cpu_run(tile_batch(make_batch(2, 1234, S), 8), cpu_refiner_state(), 2, 1)
+        sample = tile_batch(make_batch(2, 1234, S), 8)
+        n, ts = cpu_run(sample, cpu_refiner_state(), 2, 1)
         cpu = {"value": n / (sum(ts) / len(ts)), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                "sample": f"{n} crops per run, 1 warm-up + 2 timed runs of the oracle port (reference CPU path)"}
+        # deviation of the TIMED configuration from the fp32 CPU oracle on the same 8 crops, and the same
+        # read-out + a short timing with cuDNN in plain fp32 (the mode tests/ pin to 1e-4 rad)
+        Rc, tc_ = cpu_run.last_pose
+        dsample = {k: v.to(dev) for k, v in sample.items()}
+
+        def deviation():
+            Rg, tg = unpack_pose(core.refine(dsample).cpu())
+            return {"rot_rad_max": float(O.rotation_geodesic(Rg, Rc).max()),
+                    "trans_mm_max": float((tg - tc_).abs().max())}
+        parity = dict(deviation(), crops=n, against="fp32 CPU oracle, same inputs and weights",
+                      cudnn_allow_tf32=torch.backends.cudnn.allow_tf32)
+        if not args.strict_fp32:
+            torch.backends.cudnn.allow_tf32 = False
+            for i in range(2):
+                core.refine(resident[i % 2])
+            torch.cuda.synchronize()
+            ms_s = timed(step_eager, 3, False) / 3
+            strict = dict(deviation(), value=B / (ms_s / 1e3), unit=UNIT, ms_per_step=ms_s, steps=3,
+                          execution="eager launches", cudnn_allow_tf32=False)
+            torch.backends.cudnn.allow_tf32 = True
     _emit(json.dumps({
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -370,10 +396,15 @@ def ours(args):
                    "parallelism": f"batch-shard x{world} + pose all-gather",
                    "l2": "two alternating input sets; per-step working set (>450 MB) exceeds the 126 MB L2",
                    "execution": "eager launches" if args.no_graph else "CUDA graph replay per step",
-                   "gru_backend": __import__("scflow_b200.gru", fromlist=["BACKEND"]).BACKEND},
+                   "gru_backend": __import__("scflow_b200.gru", fromlist=["BACKEND"]).BACKEND,
+                   "cudnn_allow_tf32": not args.strict_fp32},
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches, "roofline": roof, "roofline_lookup": roof_lookup, "tf32_peak_tflops": tf32_peak,
         "eager_ms_per_step": ms_eager / args.steps, "kernels": kern, "cpu_baseline": cpu, "clocks": clocks,
+        "precision": {"ours": "tcgen05 TF32 (correlation, ConvGRU; operands rounded to nearest), fp32 elsewhere",
+                      "cudnn": "fp32 (allow_tf32=False)" if args.strict_fp32 else
+                               "TF32 allowed (torch default = what the reference runs on a GPU)",
+                      "deviation_from_oracle": parity, "strict_fp32_cudnn": strict},
     }))
     if world > 1:
         dist.destroy_process_group()
@@ -554,6 +585,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--image", type=int, default=256, help="crop side (256 = configs[1]; 512 = configs[3])")
+    ap.add_argument("--strict-fp32", action="store_true",
+                    help="cuDNN convolutions in plain fp32 (torch.backends.cudnn.allow_tf32=False), the mode the parity tests pin")
     ap.add_argument("--train", action="store_true", help="configs[4]: forward+backward+optimizer step, batch 32/GPU")
     args = ap.parse_args()
     # libraries (NCCL's version banner, cuDNN warnings) write to fd 1: keep the real stdout for the
