@@ -10,7 +10,8 @@ root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 go, pr = os.path.join(root, "gpurun_out"), os.path.join(root, "profiles")
 os.makedirs(pr, exist_ok=True)
 for src, dst in ((f"{tag}_bench.json", f"{rnd}_bench.json"), (f"{tag}_bench_ref.json", f"{rnd}_bench_reference.json"),
-                 (f"{tag}_launches.csv", f"{rnd}_launches.csv")):
+                 (f"{tag}_launches.csv", f"{rnd}_launches.csv"), (f"{tag}_bench_cfg4.json", f"{rnd}_bench_cfg4_512.json"),
+                 (f"{tag}_bench_train.json", f"{rnd}_bench_train.json")):
     if os.path.exists(os.path.join(go, src)):
         shutil.copy(os.path.join(go, src), os.path.join(pr, dst))
 out = subprocess.run([sys.executable, os.path.join(root, "tools", "launch_summary.py"),
