@@ -38,7 +38,7 @@ def workload(S=256, B=64):
 # captures (profiles/): kernel -> bytes.  null where no capture exists for the current kernel.
 NCU_TRAFFIC = {            # profiles/r01_ncu_full_summary.txt (cfg2: 64 crops of 256x256)
     "scflow_convgru_pass_fwd": 189.6e6, "scflow_corr_lookup_fwd": 208.8e6,
-    "scflow_corr_pyramid_fwd": 436.7e6, "scflow_pose_flow_fwd": 16.8e6,
+    "scflow_corr_pyramid_fwd": 434.5e6, "scflow_pose_flow_fwd": 16.8e6,
 }
 
 
