@@ -322,9 +322,19 @@ corr_lookup_nhwc_kernel(const __grid_constant__ CUtensorMap map0, const __grid_c
 
 namespace scflow {
 
+int launch_corr_lookup_v2(const float* const* levels, const float* flow, float* out, short* windows,
+                          int n, int h, int w, int div_mode, cudaStream_t stream);
+
 int launch_corr_lookup_nhwc(const float* const* levels, const float* flow, float* out, short* windows,
                             int n, int h, int w, int div_mode, cudaStream_t stream) {
   using namespace lk;
+  // second-generation kernel (corr_lookup_v2.cu) wherever every level row is a 16-byte multiple;
+  // SCFLOW_LK=v1 keeps this file's kernel (cross-check and A/B timing)
+  const char* gen = getenv("SCFLOW_LK");
+  if (!(gen && strcmp(gen, "v1") == 0)) {
+    const int rc = launch_corr_lookup_v2(levels, flow, out, windows, n, h, w, div_mode, stream);
+    if (rc != SCFLOW_E_UNSUPPORTED) return rc;
+  }
   if (((h >> (kLevels - 1)) < 1) || ((w >> (kLevels - 1)) < 1)) return SCFLOW_E_BAD_SHAPE;
   const long long total_q = (long long)n * h * w;
   if (total_q >= (1ll << 31)) return SCFLOW_E_BAD_SHAPE;

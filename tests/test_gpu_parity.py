@@ -134,6 +134,31 @@ def test_lookup_layouts_agree_full_size():
     assert float(a[1].abs().max()) == 0.0
 
 
+def test_lookup_generations_identical(monkeypatch):
+    """The second-generation NHWC kernel (16x12 TMA box at every level, immediate-offset taps,
+    w0 = 1 - w1) replays the first generation's arithmetic: identical windows AND identical
+    values, on random, zero (round-trip edge case -> slow taps), far-out and mixed flows, for
+    every occupancy variant and both division modes; 512^2-crop shape included."""
+    g = torch.Generator(device=DEV).manual_seed(5)
+    for n, h, w in ((8, 32, 32), (2, 64, 64), (2, 24, 32)):
+        pyr = [torch.randn(n * h * w, 1, h >> l, w >> l, device=DEV, generator=g) for l in range(4)]
+        flow = 6.0 * torch.randn(n, 2, h, w, device=DEV, generator=g)
+        flow[0] = 0.0
+        flow[1, :, : h // 2] = 300.0
+        flow[1, :, h // 2:] = torch.round(flow[1, :, h // 2:])       # integer coordinates, non-zero
+        for div in (ops.DIV_IEEE, ops.DIV_RCP):
+            monkeypatch.setenv("SCFLOW_LK", "v1")
+            a, wa = ops.corr_lookup(pyr, flow, 4, div, return_windows=True)
+            a2 = ops.corr_lookup(pyr, flow, 4, div)
+            monkeypatch.setenv("SCFLOW_LK", "v2")
+            for cfg in ("0", "1", "2"):
+                monkeypatch.setenv("SCFLOW_LK2_CFG", cfg)
+                b, wb = ops.corr_lookup(pyr, flow, 4, div, return_windows=True)
+                b2 = ops.corr_lookup(pyr, flow, 4, div)
+                assert torch.equal(wa, wb), (n, h, w, div, cfg)
+                assert torch.equal(a, b) and torch.equal(a2, b2) and torch.equal(a, a2), (n, h, w, div, cfg)
+
+
 def test_lookup_impulse_and_zero_flow():
     h = w = 32
     qy, qx = 5, 6

@@ -56,9 +56,22 @@ if "lookup" in a.which:
     pyrs = [[torch.randn(N * P, 1, h >> l, w >> l, device=dev, generator=g) for l in range(4)] for _ in range(sets)]
     flow = [2.0 * torch.randn(N, 2, h, w, device=dev, generator=g) for _ in range(sets)]
     by = N * (P * 324 * 4 + P * 4 * 100 * 4 + 8 * P)
-    for cl in (True, False):
-        us = timeit(lambda i: ops.corr_lookup(pyrs[i % sets], flow[i % sets], 4, channels_last=cl))
-        print(f"corr_lookup {'nhwc' if cl else 'nchw'}    {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)")
+    for tag, env in (("v1", {"SCFLOW_LK": "v1"}), ("v2 8x3", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "0"}),
+                     ("v2 6x5", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "1"}),
+                     ("v2 7x4", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "2"}),
+                     ("v2 8x2", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "3"}),
+                     ("v2 6x3", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "4"}),
+                     ("v2 12x2", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "5"}),
+                     ("v2 4x6", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "6"})):
+        os.environ.update(env)
+        us = timeit(lambda i: ops.corr_lookup(pyrs[i % sets], flow[i % sets], 4, channels_last=True))
+        print(f"corr_lookup nhwc {tag:7s} {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)")
+    zero = torch.zeros_like(flow[0])
+    us = timeit(lambda i: ops.corr_lookup(pyrs[i % sets], zero, 4, channels_last=True))
+    print(f"corr_lookup nhwc zero flow (slow taps) {us:8.1f} us")
+    os.environ.pop("SCFLOW_LK2_CFG", None); os.environ.pop("SCFLOW_LK", None)
+    us = timeit(lambda i: ops.corr_lookup(pyrs[i % sets], flow[i % sets], 4, channels_last=False))
+    print(f"corr_lookup nchw    {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)")
 if "gru" in a.which:
     mod = modules.ConvGRU(128, 256).to(dev)
     hs = [torch.randn(N, h, w, 128, device=dev, generator=g) for _ in range(3)]
