@@ -191,6 +191,8 @@ def algorithmic_flops(name, B, S=256):
     P = (S // 8) ** 2
     if name == "scflow_convgru_pass_fwd":
         return B * 3 * 2.0 * P * 128 * 1920            # three gate convolutions of one pass
+    if name == "scflow_convgru_fwd":
+        return 2 * B * 3 * 2.0 * P * 128 * 1920        # both passes in one persistent launch
     if name == "scflow_corr_pyramid_fwd":
         return B * 2.0 * P * P * 256
     return None
@@ -347,7 +349,7 @@ def ours(args):
         "kernel": "scflow_corr_lookup_fwd", "bound": "hbm", "achieved": lk["gbs"], "peak": pk["hbm"], "unit": "GB/s",
         "frac": lk["hbm_frac"], "traffic": NCU_TRAFFIC.get("scflow_corr_lookup_fwd") if (B, S) == (64, 256) else None,
         "algorithmic_bytes_per_launch": algorithmic_bytes("scflow_corr_lookup_fwd", B, S)}
-    if kern[top]["tflops"] is not None and top == "scflow_convgru_pass_fwd":
+    if kern[top]["tflops"] is not None and top in ("scflow_convgru_pass_fwd", "scflow_convgru_fwd"):
         roof = {"kernel": top, "bound": "tensor", "achieved": kern[top]["tflops"], "peak": tf32_peak,
                 "unit": "TFLOP/s", "frac": kern[top]["tflops"] / tf32_peak, "traffic": traffic,
                 "peak_source": "cuBLAS TF32 8192^3 sustained, measured in this run (bf16 figure of "

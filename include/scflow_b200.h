@@ -99,6 +99,18 @@ int scflow_convgru_pack_weights(const float* wz, const float* wr, const float* w
 int scflow_convgru_pass_fwd(const float* h_in, const float* h_in_tf32, const float* x,
                             const float* wpack, float* h_out, float* h_out_tf32, float* rh_scratch,
                             int n, int hgt, int wid, int ch, int cx, int pass, void* stream);
+/* Both passes of ConvGRU.forward (raft_decoder.py:245-252) in ONE persistent launch, in place:
+ * h (exact fp32 state) and h_tf32 (its nearest-TF32 copy, optional) are read and overwritten.
+ * The (1,5) and (5,1) passes become one list of work items; a (5,1) item waits on a per-image
+ * counter (workspace) that the (1,5) items of the same image release, so the two passes fill
+ * the SMs as 7 waves instead of 2 x 4 at 64 crops.  workspace: scflow_convgru_workspace_bytes()
+ * bytes of device memory, 4-byte aligned, zeroed by the call itself (a memset node on `stream`).
+ * wpack0 / wpack1: packed weights of pass 0 / pass 1.  Results are bit-identical to two
+ * scflow_convgru_pass_fwd calls. */
+size_t scflow_convgru_workspace_bytes(int n, int hgt, int wid);
+int scflow_convgru_fwd(float* h, float* h_tf32, const float* x, const float* wpack0,
+                       const float* wpack1, float* rh_scratch, void* workspace,
+                       size_t workspace_bytes, int n, int hgt, int wid, int ch, int cx, void* stream);
 
 /* Channels-last packing of the GRU input x = cat[cxt, motion, flow] (raft_decoder.py:166 and
  * scflow_decoder.py:208) with round-to-nearest TF32, replacing two torch.cat and a layout pass.

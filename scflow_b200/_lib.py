@@ -27,6 +27,8 @@ SIGNATURES = {
     "scflow_convgru_packed_floats": (c_size_t, [c_int, c_int]),
     "scflow_convgru_pack_weights": (c_int, [_P] * 7 + [c_int, c_int, c_int, _P]),
     "scflow_convgru_pass_fwd": (c_int, [_P] * 7 + [c_int, c_int, c_int, c_int, c_int, c_int, _P]),
+    "scflow_convgru_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "scflow_convgru_fwd": (c_int, [_P] * 7 + [c_size_t, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_pack_nhwc": (c_int, [_P, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, ctypes.c_longlong, c_int,
                                  c_int, _P]),
     "scflow_chan_stats_nhwc": (c_int, [_P, _P, c_int, c_int, c_int, _P]),

@@ -10,6 +10,8 @@ rounded to the NEAREST TF32 by its producer (weights when packed, x by scflow_pa
 the MMA copy of h by the kernel's own epilogues); the gating arithmetic keeps the exact fp32 h."""
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import _lib
@@ -53,10 +55,24 @@ def round_tf32(t: torch.Tensor) -> torch.Tensor:
 def update_inplace(mod, h: torch.Tensor, h_r: torch.Tensor, x_r: torch.Tensor, rh: torch.Tensor) -> None:
     """Both passes of the SeqConv GRU, in place: h (N,H,W,128) exact state, h_r its nearest-TF32
     copy (the tensor-core operand), x_r (N,H,W,256) already rounded, rh scratch like h.
-    In place is safe: a tile spans the whole convolution axis, so it reads only its own pixels."""
+    In place is safe: a tile spans the whole convolution axis, so it reads only its own pixels.
+    One persistent launch for both passes (scflow_convgru_fwd); SCFLOW_GRU_FUSED=0 keeps the
+    launch-per-pass path (bit-identical results, used as the cross-check)."""
     lib = _lib.load()
     n, H, W, ch = h.shape
     cx = x_r.shape[-1]
+    if os.environ.get("SCFLOW_GRU_FUSED", "1") != "0" and "SCFLOW_GRU_2CTA" not in os.environ:
+        need = lib.scflow_convgru_workspace_bytes(n, H, W)
+        ws = mod.__dict__.get("_scflow_gru_ws")
+        if ws is None or ws.device != h.device or ws.numel() * 4 < need:
+            ws = torch.empty((need + 3) // 4, device=h.device, dtype=torch.int32)
+            mod.__dict__["_scflow_gru_ws"] = ws
+        w0, w1 = packed_weights(mod, 0), packed_weights(mod, 1)
+        with _timed("scflow_convgru_fwd"):
+            rc = lib.scflow_convgru_fwd(_ptr(h), _ptr(h_r), _ptr(x_r), _ptr(w0), _ptr(w1), _ptr(rh), _ptr(ws),
+                                        ws.numel() * 4, n, H, W, ch, cx, _stream())
+        _lib.check(rc, "scflow_convgru_fwd")
+        return
     for p in (0, 1):
         wp = packed_weights(mod, p)
         with _timed("scflow_convgru_pass_fwd"):

@@ -359,6 +359,33 @@ def test_convgru_tcgen05_vs_oracle(n, h, w):
     assert rel(got, ref) < 3e-3
 
 
+@pytest.mark.parametrize("n,h,w", [(64, 32, 32), (2, 32, 32), (1, 64, 64), (3, 8, 32), (5, 8, 8), (7, 16, 16)])
+def test_convgru_single_launch_equals_two_passes(n, h, w, monkeypatch):
+    """scflow_convgru_fwd (both passes as one persistent launch, pass-1 items released by
+    per-image counters) is bit-identical to two scflow_convgru_pass_fwd launches; repeated to
+    shake out ordering races between the passes."""
+    from scflow_b200 import gru_tc
+    mod = sb.ConvGRU(128, 256)
+    mod.load_state_dict(_gru_sd(23))
+    mod.to(DEV)
+    g = torch.Generator(device=DEV).manual_seed(24)
+    x = gru_tc.round_tf32(torch.randn(n, h, w, 256, device=DEV, generator=g))
+    h0 = torch.tanh(torch.randn(n, h, w, 128, device=DEV, generator=g))
+
+    def run(fused, reps):
+        monkeypatch.setenv("SCFLOW_GRU_FUSED", "1" if fused else "0")
+        hh, hr, rh = h0.clone(), gru_tc.round_tf32(h0), torch.empty_like(h0)
+        for _ in range(reps):
+            gru_tc.update_inplace(mod, hh, hr, x, rh)
+        return hh, hr
+
+    for reps in (1, 3):
+        a, ar = run(False, reps)
+        for _ in range(3):
+            b, br = run(True, reps)
+            assert torch.equal(a, b) and torch.equal(ar, br), (n, h, w, reps)
+
+
 def test_convgru_weight_cache_tracks_parameter_updates():
     from scflow_b200 import gru_tc
     mod = sb.ConvGRU(128, 256).to(DEV)

@@ -78,9 +78,12 @@ if "gru" in a.which:
     xs = [gru_tc.round_tf32(torch.randn(N, h, w, 256, device=dev, generator=g)) for _ in range(3)]
     hr = [gru_tc.round_tf32(t) for t in hs]
     rh = torch.empty_like(hs[0])
-    us = timeit(lambda i: gru_tc.update_inplace(mod, hs[i % 3], hr[i % 3], xs[i % 3], rh)) / 2
     fl = 3 * 2.0 * N * P * 128 * 1920
-    print(f"convgru pass        {us:8.1f} us  {fl/us/1e6:6.1f} TFLOP/s tf32")
+    for tag, env in (("two launches", "0"), ("one launch", "1")):
+        os.environ["SCFLOW_GRU_FUSED"] = env
+        us = timeit(lambda i: gru_tc.update_inplace(mod, hs[i % 3], hr[i % 3], xs[i % 3], rh)) / 2
+        print(f"convgru pass ({tag:12s}) {us:8.1f} us  {fl/us/1e6:6.1f} TFLOP/s tf32")
+    os.environ.pop("SCFLOW_GRU_FUSED", None)
 if "pose" in a.which:
     from scflow_b200 import synthetic as syn
     cr = {k: v.to(dev) for k, v in syn.make_crops(4, S, seed=1).items()}
