@@ -700,6 +700,9 @@ struct FParams {
   int pass[2];           // conv axis of each slot: 0 = along x, 1 = along y
   int G[2], tiles_per_img[2], tiles[2];
   int need;              // flag value that releases a slot-1 item: tiles_per_img[0] * EPI_WARPS
+  int dbg_max_boxes;     // timing experiments only (SCFLOW_GRU_DBG_BOXES): cap on weight boxes per k-block
+  long long* dbg_ts;     // timing experiments only (SCFLOW_GRU_DBG_TS): clock64 stamps of CTA 0, 8 per item
+  int dbg_mma;           // timing experiments only (SCFLOW_GRU_DBG_MMA): 1 = no stage-1 q MMAs, 2 = no MMAs at all
   long long total_pix;
 };
 
@@ -717,7 +720,7 @@ __device__ __forceinline__ void red_release_add(int* p, int v) {
 __device__ __forceinline__ void epilogue_item(const FParams& p, const float* sbias, uint32_t taddr, int off,
                                               bool live, int half, int lane, uint64_t* s1_done,
                                               uint64_t* s2_done, uint64_t* rh_ready, uint32_t parity,
-                                              const int* wait_flag, int* post_flag) {
+                                              const int* wait_flag, int* post_flag, long long* ts) {
   constexpr int HC = CH / 2;
   const int cbase = half * HC;
   if (wait_flag != nullptr) {
@@ -736,6 +739,7 @@ __device__ __forceinline__ void epilogue_item(const FParams& p, const float* sbi
   // ---- epilogue 1: r = sigmoid(r_pre + br); r.h (rounded to nearest TF32) -> scratch
   tc::mbar_wait(s1_done, parity);
   tc::tc_fence_after();
+  if (ts) ts[2] = clock64();
   float* rhp = p.rh + off + cbase;
 #pragma unroll
   for (int c = 0; c < HC / 32; ++c) {
@@ -758,10 +762,12 @@ __device__ __forceinline__ void epilogue_item(const FParams& p, const float* sbi
   tc::fence_proxy_async_all();           // ... and ordered before the async-proxy (TMA) reads
   __syncwarp();
   if (lane == 0) tc::mbar_arrive(rh_ready);
+  if (ts) ts[3] = clock64();
 
   // ---- epilogue 2: z, q, gate
   tc::mbar_wait(s2_done, parity);
   tc::tc_fence_after();
+  if (ts) ts[6] = clock64();
   float* op = p.h_out + off + cbase;
   float* opr = p.h_out_tf32 ? p.h_out_tf32 + off + cbase : nullptr;
 #pragma unroll
@@ -788,6 +794,7 @@ __device__ __forceinline__ void epilogue_item(const FParams& p, const float* sbi
       }
     }
   }
+  if (ts) ts[7] = clock64();
   if (post_flag != nullptr) {
     __threadfence();                     // h, h_tf32 of this warp's pixels visible device-wide ...
     tc::fence_proxy_async_all();         // ... also to the other SMs' TMA reads
@@ -796,7 +803,24 @@ __device__ __forceinline__ void epilogue_item(const FParams& p, const float* sbi
   }
 }
 
-constexpr size_t SMEMF_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + 2 * ROWS * 4 + 256;
+// Ring geometry per k-block width: 32 channels (128-byte rows, SWIZZLE_128B, 3 x 64 KB stages) or
+// 16 channels (64-byte rows, SWIZZLE_64B, 6 x 32 KB stages).  The ring is LATENCY-bound, not
+// bandwidth-bound (dropping every weight load changes nothing: 203.8 -> 201.6 us): a stage's
+// refill round trip is ~1.5 us whatever it carries, so twice the stages in the same 192 KB keep
+// the tensor core fed for longer.  Both read the same packed weights ([..][384][32] rows): the
+// narrow ring loads each row block as two 16-float column halves.
+template <int BKT>
+struct Ring {
+  static constexpr int kStages = BKT == 32 ? 3 : 6;
+  static constexpr int kABytes = BM * BKT * 4;
+  static constexpr int kBoxBytes = CH * BKT * 4;                 // one 128-row weight box
+  static constexpr int kStageBytes = kABytes + 3 * kBoxBytes;
+  static constexpr int kKbH = CH / BKT, kKbAll = (CH + CX) / BKT;
+  static constexpr int kS1 = TAPS * kKbAll, kS2 = TAPS * kKbH;
+  static constexpr uint32_t kLayout = BKT == 32 ? 2u : 4u;        // UMMA: SWIZZLE_128B / SWIZZLE_64B
+  static constexpr uint32_t kSbo = 8 * BKT * 4;                   // 8-row group pitch
+  static constexpr size_t kSmem = 1024 + (size_t)kStages * kStageBytes + 2 * ROWS * 4 + 256;
+};
 
 struct Item {
   int slot, tile, n, tl, grp;   // grp = image group = flag index
@@ -811,8 +835,13 @@ __device__ __forceinline__ Item decode_item(const FParams& p, int w) {
   return it;
 }
 
+template <int BKT>
 __global__ void __launch_bounds__(THREADS, 1)
 convgru_fused_kernel(const __grid_constant__ GruMaps maps, const __grid_constant__ FParams p) {
+  using R = Ring<BKT>;
+  constexpr int STAGES = R::kStages, STAGE_BYTES = R::kStageBytes, A_BYTES = R::kABytes;
+  constexpr int S1_ITERS = R::kS1, S2_ITERS = R::kS2, KB_H = R::kKbH, KB_ALL = R::kKbAll;
+  constexpr int BOX_BYTES = R::kBoxBytes;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   float* sbias = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES);          // [2][ROWS]
@@ -863,26 +892,32 @@ convgru_fused_kernel(const __grid_constant__ GruMaps maps, const __grid_constant
         }
         for (int it = 0; it < S1_ITERS + S2_ITERS; ++it) {
           const bool s2 = it >= S1_ITERS;
-          if (it == S1_ITERS) tc::mbar_wait(rh_ready, it_tile & 1);   // r.h of this tile is in L2
+          if (it == S1_ITERS) {
+            tc::mbar_wait(rh_ready, it_tile & 1);   // r.h of this tile is in L2
+            if (p.dbg_ts && blockIdx.x == 0 && it_tile < 4) p.dbg_ts[it_tile * 8 + 4] = clock64();
+          }
           const int j = s2 ? it - S1_ITERS : it;
           const int t = s2 ? j / KB_H : j / KB_ALL;
           const int kb = s2 ? j % KB_H : j % KB_ALL;
           tc::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* a_s = smem + stage * STAGE_BYTES;
           uint8_t* b_s = a_s + A_BYTES;
-          const int nb = s2 ? 1 : (kb < KB_H ? 2 : 3);                // 128-row weight boxes
-          tc::mbar_expect_tx(&full[stage], A_BYTES + nb * (CH * BK * 4));
+          int nb = s2 ? 1 : (kb < KB_H ? 2 : 3);                      // 128-row weight boxes
+          if (nb > p.dbg_max_boxes) nb = p.dbg_max_boxes;
+          tc::mbar_expect_tx(&full[stage], (p.dbg_mma == 4 ? 0 : A_BYTES) + nb * BOX_BYTES);
           const CUtensorMap* am = s2 ? &maps.rh[s] : (kb < KB_H ? &maps.h[s] : &maps.x[s]);
-          const int c0 = (s2 || kb < KB_H) ? kb * BK : (kb - KB_H) * BK;
+          const int c0 = (s2 || kb < KB_H) ? kb * BKT : (kb - KB_H) * BKT;
           const int cx = pass == 0 ? (t - 2) : item.tl * G;
           const int cy = pass == 0 ? item.tl * G : (t - 2);
-          tc::tma_load_4d(am, &full[stage], a_s, c0, cx, cy, item.n);
-          const int wrow = (t * KB_ALL + kb) * ROWS;
+          if (p.dbg_mma < 3) tc::tma_load_4d(am, &full[stage], a_s, c0, cx, cy, item.n);
+          else if (p.dbg_mma == 3) tc::tma_load_2d(&maps.w[s], &full[stage], a_s, 0, (it * 7 + item.tile) % 1000 * CH);
+          // packed weights are [tap][32-channel block][384 rows][32]: a narrower k-block is a column slice
+          const int wrow = (t * ((CH + CX) / BK) + (kb * BKT) / BK) * ROWS, wcol = (kb * BKT) % BK;
           if (s2) {
-            tc::tma_load_2d(&maps.w[s], &full[stage], b_s, 0, wrow + 2 * CH);
+            if (nb > 0) tc::tma_load_2d(&maps.w[s], &full[stage], b_s, wcol, wrow + 2 * CH);
           } else {
             for (int b = 0; b < nb; ++b)
-              tc::tma_load_2d(&maps.w[s], &full[stage], b_s + b * (CH * BK * 4), 0, wrow + b * CH);
+              tc::tma_load_2d(&maps.w[s], &full[stage], b_s + b * BOX_BYTES, wcol, wrow + b * CH);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -897,6 +932,8 @@ convgru_fused_kernel(const __grid_constant__ GruMaps maps, const __grid_constant
       for (int w = blockIdx.x; w < total_items; w += gridDim.x, ++it_tile) {
         tc::mbar_wait(tmem_free, (it_tile & 1) ^ 1);
         tc::tc_fence_after();
+        long long* ts = (p.dbg_ts && blockIdx.x == 0 && it_tile < 4) ? p.dbg_ts + it_tile * 8 : nullptr;
+        if (ts) ts[0] = clock64();
         for (int it = 0; it < S1_ITERS + S2_ITERS; ++it) {
           const bool s2 = it >= S1_ITERS;
           const int kb = s2 ? 0 : it % KB_ALL;
@@ -905,25 +942,27 @@ convgru_fused_kernel(const __grid_constant__ GruMaps maps, const __grid_constant
           const uint32_t a_addr = tc::smem_u32(smem + stage * STAGE_BYTES);
           const uint32_t b_addr = a_addr + A_BYTES;
 #pragma unroll
-          for (int ks = 0; ks < BK / 8; ++ks) {
-            const uint64_t da = tc::make_smem_desc(a_addr + ks * 32, 16, 1024, tc::kLayoutSw128);
+          for (int ks = 0; ks < BKT / 8; ++ks) {
+            // K-major swizzled rows: 8-row groups kSbo apart; a k-step (8 tf32) is +32 B
+            const uint64_t da = tc::make_smem_desc(a_addr + ks * 32, 16, R::kSbo, R::kLayout);
             if (s2) {
-              const uint64_t dq = tc::make_smem_desc(b_addr + ks * 32, 16, 1024, tc::kLayoutSw128);
+              const uint64_t dq = tc::make_smem_desc(b_addr + ks * 32, 16, R::kSbo, R::kLayout);
               tc::mma_tf32_ss(tmem_base + 2 * CH, da, dq, id128, 1u);
             } else {
-              const uint64_t dzr = tc::make_smem_desc(b_addr + ks * 32, 16, 1024, tc::kLayoutSw128);
-              tc::mma_tf32_ss(tmem_base, da, dzr, id256, (it | ks) != 0 ? 1u : 0u);
-              if (kb >= KB_H) {
-                const uint64_t dq = tc::make_smem_desc(b_addr + 2 * CH * BK * 4 + ks * 32, 16, 1024, tc::kLayoutSw128);
+              const uint64_t dzr = tc::make_smem_desc(b_addr + ks * 32, 16, R::kSbo, R::kLayout);
+              if (p.dbg_mma < 2) tc::mma_tf32_ss(tmem_base, da, dzr, id256, (it | ks) != 0 ? 1u : 0u);
+              if (kb >= KB_H && p.dbg_mma == 0) {
+                const uint64_t dq = tc::make_smem_desc(b_addr + 2 * BOX_BYTES + ks * 32, 16, R::kSbo, R::kLayout);
                 tc::mma_tf32_ss(tmem_base + 2 * CH, da, dq, id128, (it != KB_H || ks != 0) ? 1u : 0u);
               }
             }
           }
           tc::tc_commit(&empty[stage]);
-          if (it == S1_ITERS - 1) tc::tc_commit(s1_done);
+          if (it == S1_ITERS - 1) { tc::tc_commit(s1_done); if (ts) ts[1] = clock64(); }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         tc::tc_commit(s2_done);
+        if (ts) ts[5] = clock64();
       }
     }
   } else {
@@ -946,7 +985,8 @@ convgru_fused_kernel(const __grid_constant__ GruMaps maps, const __grid_constant
       const bool fused = p.npass == 2;
       epilogue_item(p, sbias + s * ROWS, taddr, (int)(pix * CH), live, (warp - 2) >> 2, lane, s1_done, s2_done,
                     rh_ready, it_tile & 1, fused && s == 1 ? p.flags + item.grp : nullptr,
-                    fused && s == 0 ? p.flags + item.grp : nullptr);
+                    fused && s == 0 ? p.flags + item.grp : nullptr,
+                    (p.dbg_ts && blockIdx.x == 0 && it_tile < 4 && warp == 2 && lane == 0) ? p.dbg_ts + it_tile * 8 : nullptr);
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(tmem_free);
@@ -995,6 +1035,10 @@ static int launch_fused(const float* h, const float* h_tf32, const float* x, con
   GruMaps maps;
   FParams p;
   const float* h_mma = h_tf32 ? h_tf32 : h;
+  // k-block width of the operand ring (see Ring<>): 16 = six 32 KB stages (default), 32 = three 64 KB
+  const char* ebk = getenv("SCFLOW_GRU_BK");
+  const int bk = (ebk && atoi(ebk) == 32) ? 32 : 16;
+  const int swz = bk == 32 ? tc::kTmaSw128 : tc::kTmaSw64;
   for (int s = 0; s < npass; ++s) {
     PassShape ps;
     const int rc = pass_shape(n, hgt, wid, passes[s], &ps);
@@ -1004,9 +1048,9 @@ static int launch_fused(const float* h, const float* h_tf32, const float* x, con
     auto act_map = [&](CUtensorMap* mp, const float* base, int c) {
       const uint64_t dims[4] = {(uint64_t)c, (uint64_t)wid, (uint64_t)hgt, (uint64_t)n};
       const uint64_t strides[3] = {(uint64_t)c * 4, (uint64_t)wid * c * 4, (uint64_t)hgt * wid * c * 4};
-      const uint32_t box[4] = {BK, (uint32_t)(passes[s] == 0 ? wid : ps.G), (uint32_t)(passes[s] == 0 ? ps.G : hgt),
-                               (uint32_t)ps.ni};
-      return tc::encode_f32_map(mp, base, 4, dims, strides, box, tc::kTmaSw128);
+      const uint32_t box[4] = {(uint32_t)bk, (uint32_t)(passes[s] == 0 ? wid : ps.G),
+                               (uint32_t)(passes[s] == 0 ? ps.G : hgt), (uint32_t)ps.ni};
+      return tc::encode_f32_map(mp, base, 4, dims, strides, box, swz);
     };
     // slot 1 reads the h that slot 0 wrote
     const float* hs = (s == 1 && h_out_tf32) ? h_out_tf32 : (s == 1 ? h_out : h_mma);
@@ -1014,8 +1058,8 @@ static int launch_fused(const float* h, const float* h_tf32, const float* x, con
       return SCFLOW_E_DRIVER;
     const uint64_t dims[2] = {BK, (uint64_t)TAPS * KB_ALL * ROWS};
     const uint64_t strides[1] = {BK * 4};
-    const uint32_t box[2] = {BK, (uint32_t)CH};
-    if (!tc::encode_f32_map(&maps.w[s], wpack[s], 2, dims, strides, box, tc::kTmaSw128)) return SCFLOW_E_DRIVER;
+    const uint32_t box[2] = {(uint32_t)bk, (uint32_t)CH};
+    if (!tc::encode_f32_map(&maps.w[s], wpack[s], 2, dims, strides, box, swz)) return SCFLOW_E_DRIVER;
     p.bias[s] = wpack[s] + (size_t)TAPS * KB_ALL * ROWS * BK;
   }
   if (npass == 1) {
@@ -1026,11 +1070,22 @@ static int launch_fused(const float* h, const float* h_tf32, const float* x, con
   p.h = h; p.h_out = h_out; p.h_out_tf32 = h_out_tf32; p.rh = rh; p.flags = flags;
   p.n = n; p.H = hgt; p.W = wid; p.npass = npass;
   p.need = p.tiles_per_img[0] * EPI_WARPS;
+  {
+    const char* e = getenv("SCFLOW_GRU_DBG_BOXES");
+    p.dbg_max_boxes = e ? atoi(e) : 3;
+    const char* m = getenv("SCFLOW_GRU_DBG_MMA");
+    p.dbg_mma = m ? atoi(m) : 0;
+    // stamps live in the 256 bytes after the flags (the workspace query reserves them)
+    p.dbg_ts = (getenv("SCFLOW_GRU_DBG_TS") && npass == 2)
+                   ? reinterpret_cast<long long*>(reinterpret_cast<char*>(flags) + (((size_t)n * 4 + 255) / 256) * 256)
+                   : nullptr;
+  }
   p.total_pix = (long long)n * hgt * wid;
   if (p.total_pix * CH >= (1ll << 31)) return SCFLOW_E_BAD_SHAPE;      // epilogue uses 32-bit offsets
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(convgru_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEMF_BYTES);
+    cudaFuncSetAttribute(convgru_fused_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Ring<32>::kSmem);
+    cudaFuncSetAttribute(convgru_fused_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Ring<16>::kSmem);
     attr_set = true;
   }
   int sms = 0, dev = 0;
@@ -1043,7 +1098,10 @@ static int launch_fused(const float* h, const float* h_tf32, const float* x, con
     if (cudaMemsetAsync(flags, 0, (size_t)groups * sizeof(int), stream) != cudaSuccess) return check_launch();
   }
   const int grid = items < sms ? items : sms;
-  convgru_fused_kernel<<<grid, THREADS, SMEMF_BYTES, stream>>>(maps, p);
+  if (bk == 32)
+    convgru_fused_kernel<32><<<grid, THREADS, Ring<32>::kSmem, stream>>>(maps, p);
+  else
+    convgru_fused_kernel<16><<<grid, THREADS, Ring<16>::kSmem, stream>>>(maps, p);
   return check_launch();
 }
 
@@ -1052,7 +1110,8 @@ static int launch_fused(const float* h, const float* h_tf32, const float* x, con
 
 extern "C" size_t scflow_convgru_workspace_bytes(int n, int hgt, int wid) {
   (void)hgt; (void)wid;
-  return n > 0 ? (size_t)n * sizeof(int) : 0;      // one dependency counter per image (group)
+  // one dependency counter per image (group) + 256 bytes of debug stamps
+  return n > 0 ? (((size_t)n * sizeof(int) + 255) / 256) * 256 + 256 : 0;
 }
 
 extern "C" int scflow_convgru_fwd(float* h, float* h_tf32, const float* x, const float* wpack0,

@@ -227,7 +227,7 @@ inline EncodeTiledFn get_encode_tiled() {
 
 // TMA swizzle modes (match the UMMA layout types: kLayoutSw128 <-> kTmaSw128, kLayoutSw128Base32 <->
 // kTmaSw128Atom32; the latter is the only layout tcgen05 accepts for MN-major 32-bit operands).
-constexpr int kTmaNone = 0, kTmaSw128 = 1, kTmaSw128Atom32 = 2;
+constexpr int kTmaNone = 0, kTmaSw128 = 1, kTmaSw128Atom32 = 2, kTmaSw64 = 3;
 
 // fp32 tensor map of rank `rank`; dims/box innermost first; strides in BYTES for dims 1..rank-1.
 // l2_promote: widen L2 fills to 256 B (streaming tiles) or leave them at sector size (gathers).
@@ -248,6 +248,7 @@ inline bool encode_f32_map(CUtensorMap* map, const void* base, int rank, const u
                   gdim, gstr, bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   swizzle == kTmaSw128 ? CU_TENSOR_MAP_SWIZZLE_128B
                   : swizzle == kTmaSw128Atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                  : swizzle == kTmaSw64 ? CU_TENSOR_MAP_SWIZZLE_64B
                                                : CU_TENSOR_MAP_SWIZZLE_NONE,
                   l2_promote ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_NONE,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

@@ -26,6 +26,44 @@ def _conv_cl(conv: nn.Conv2d, x: torch.Tensor, with_bias: bool = False) -> torch
     return y.contiguous(memory_format=torch.channels_last)      # no-op when cuDNN kept the layout
 
 
+def _s2d_enabled(conv: nn.Conv2d, x: torch.Tensor) -> bool:
+    """The 7x7 stride-2 stem on 3 channels is the one layer cuDNN has no tensor-core kernel for
+    (it runs a generic 3-channel implicit GEMM: 416 us per 64 crops, 7 % of the step).  Rewritten
+    as the equivalent 4x4 stride-1 convolution on the 2x2 space-to-depth input (12 -> 16 channels)
+    it takes cuDNN's regular TF32 path.  Only where TF32 convolutions are allowed (the mode the
+    reference itself runs in on a GPU): the strict-fp32 parity mode keeps the filter as shipped."""
+    import os
+    return (os.environ.get("SCFLOW_STEM_S2D", "1") != "0" and torch.backends.cudnn.allow_tf32
+            and conv.kernel_size == (7, 7) and conv.stride == (2, 2) and conv.padding == (3, 3)
+            and x.shape[1] <= 4 and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0)
+
+
+def _s2d_filter(w: torch.Tensor) -> torch.Tensor:
+    """(O,C,7,7) stride-2 filter -> (O,16,4,4) stride-1 filter over pixel_unshuffle(x, 2): tap
+    k' = k + 1 = 2a + b lands on phase b at offset a - 2 (taps padded to 8 with a leading zero)."""
+    o, c = w.shape[:2]
+    wp = F.pad(w, (1, 0, 1, 0)).reshape(o, c, 4, 2, 4, 2).permute(0, 1, 3, 5, 2, 4).reshape(o, 4 * c, 4, 4)
+    return F.pad(wp, (0, 0, 0, 0, 0, 16 - 4 * c)).contiguous(memory_format=torch.channels_last)
+
+
+def _s2d_input(x: torch.Tensor) -> torch.Tensor:
+    """(N,C,H,W) -> channels-last (N,16,H/2+3,W/2+3): phases as channels (c*4 + 2*by + bx), zero
+    channels up to 16, and the stride-1 filter's (2,1) zero border written in."""
+    s = F.pixel_unshuffle(x, 2)
+    return F.pad(s, (2, 1, 2, 1, 0, 16 - s.shape[1])).contiguous(memory_format=torch.channels_last)
+
+
+def _stem_cached(conv: nn.Conv2d, w: torch.Tensor) -> torch.Tensor:
+    key = (w.data_ptr(), w._version)
+    hit = conv.__dict__.get("_scflow_s2d")
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    with torch.no_grad():
+        val = _s2d_filter(w.detach().float())
+    conv.__dict__["_scflow_s2d"] = (key, val)
+    return val
+
+
 def _nhwc(x: torch.Tensor) -> torch.Tensor:
     return x.permute(0, 2, 3, 1)
 
@@ -181,13 +219,21 @@ class RAFTEncoder(nn.Module):
     def forward_fused(self, x: torch.Tensor) -> torch.Tensor:
         """Inference path: same values as forward() (the IN-cancelled conv bias aside, a rounding-
         level difference), channels-last activations, norms through csrc/norm_act.cu."""
-        x = x.contiguous(memory_format=torch.channels_last)
         n1 = getattr(self, self.norm1_name)
+        s2d = _s2d_enabled(self.conv1, x)
+        x = _s2d_input(x) if s2d else x.contiguous(memory_format=torch.channels_last)
         if isinstance(n1, nn.BatchNorm2d):
             w1, b1 = _bn_folded(self.conv1, n1)
-            y = torch.cudnn_convolution_relu(x, w1, b1, self.conv1.stride, self.conv1.padding, (1, 1), 1)
+            if s2d:
+                y = torch.cudnn_convolution_relu(x, _stem_cached(self.conv1, w1), b1, (1, 1), (0, 0), (1, 1), 1)
+            else:
+                y = torch.cudnn_convolution_relu(x, w1, b1, self.conv1.stride, self.conv1.padding, (1, 1), 1)
         else:
-            y = _conv_cl(self.conv1, x)
+            if s2d:
+                y = F.conv2d(x, _stem_cached(self.conv1, self.conv1.weight))
+                y = y.contiguous(memory_format=torch.channels_last)
+            else:
+                y = _conv_cl(self.conv1, x)
             kw, eps = _side(n1, _nhwc(y), self.conv1.bias)
             ops.norm_act(_nhwc(y), relu=True, eps=eps, **kw)
         for name in self.res_layers:
