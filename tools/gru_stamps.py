@@ -20,7 +20,7 @@ ws = mod.__dict__["_scflow_gru_ws"]
 off = ((N * 4 + 255) // 256) * 256 // 4
 ts = ws[off: off + 64].view(torch.int64).cpu().reshape(4, 8)
 names = ["item start (TMEM free)", "S1 issued", "s1_done seen by epilogue", "E1 done (rh published)",
-         "rh_ready seen by producer", "S2 issued", "s2_done seen by epilogue", "E2 done"]
+         "rh_ready seen by producer", "S2 issued", "s2_done seen by epilogue", "TMEM handed back"]
 t0 = int(ts[0, 0])
 for i in range(4):
     print(f"item {i}:")

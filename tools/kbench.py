@@ -79,23 +79,11 @@ if "gru" in a.which:
     hr = [gru_tc.round_tf32(t) for t in hs]
     rh = torch.empty_like(hs[0])
     fl = 3 * 2.0 * N * P * 128 * 1920
-    for tag, env, bk in (("two launches", "0", "32"), ("one launch, 3x64K ring", "1", "32"), ("one launch, 6x32K ring", "1", "16")):
-        os.environ["SCFLOW_GRU_FUSED"] = env; os.environ["SCFLOW_GRU_BK"] = bk
+    for tag, env in (("two launches", "0"), ("one launch", "1")):
+        os.environ["SCFLOW_GRU_FUSED"] = env
         us = timeit(lambda i: gru_tc.update_inplace(mod, hs[i % 3], hr[i % 3], xs[i % 3], rh)) / 2
-        print(f"convgru pass ({tag:24s}) {us:8.1f} us  {fl/us/1e6:6.1f} TFLOP/s tf32")
-    os.environ.pop("SCFLOW_GRU_FUSED", None); os.environ.pop("SCFLOW_GRU_BK", None)
-    os.environ["SCFLOW_GRU_BK"] = "32"
-    for tag, env in (("no weight loads", {"SCFLOW_GRU_DBG_BOXES": "0"}), ("no stage-1 q MMAs", {"SCFLOW_GRU_DBG_MMA": "1"}),
-                     ("no stage-1 MMAs at all", {"SCFLOW_GRU_DBG_MMA": "2"}),
-                     ("no stage-1 MMAs, no weight loads", {"SCFLOW_GRU_DBG_MMA": "2", "SCFLOW_GRU_DBG_BOXES": "0"}),
-                     ("no stage-1 MMAs, A tile from a dense 16 KB source", {"SCFLOW_GRU_DBG_MMA": "3"}),
-                     ("no stage-1 MMAs, no A loads", {"SCFLOW_GRU_DBG_MMA": "4"}),
-                     ("no stage-1 MMAs, no A loads, no weight loads", {"SCFLOW_GRU_DBG_MMA": "4", "SCFLOW_GRU_DBG_BOXES": "0"})):
-        os.environ.update(env)      # timing experiments: results are garbage
-        us = timeit(lambda i: gru_tc.update_inplace(mod, hs[i % 3], hr[i % 3], xs[i % 3], rh)) / 2
-        print(f"convgru pass, {tag}: {us:8.1f} us")
-        for k in env: os.environ.pop(k)
-    os.environ.pop("SCFLOW_GRU_BK", None)
+        print(f"convgru pass ({tag:12s}) {us:8.1f} us  {fl/us/1e6:6.1f} TFLOP/s tf32")
+    os.environ.pop("SCFLOW_GRU_FUSED", None)
 if "pose" in a.which:
     from scflow_b200 import synthetic as syn
     cr = {k: v.to(dev) for k, v in syn.make_crops(4, S, seed=1).items()}
