@@ -19,10 +19,18 @@
 //   * The MMA issue loop is written per (tap, k-block) with compile-time branches: the issuing
 //     thread is on the critical path (two extra predicated branches per k-step cost 10 %).
 //
-// What was measured and NOT adopted: a six-stage ring of 32 KB stages (16-channel k-blocks,
-// SWIZZLE_64B) is 26 % slower (per-k-block hand-shake cost dominates, not refill latency);
-// dropping every weight load changes nothing (203.8 -> 201.6 us): the ring is not bound by
-// L2 -> SM bandwidth.
+// What was measured and NOT adopted (tools/kbench.py gru, tools/gru_stamps.py):
+//   * a six-stage ring of 32 KB stages (16-channel k-blocks, SWIZZLE_64B): 26 % slower -- the cost
+//     per k-block hand-shake dominates, not the refill latency;
+//   * dropping every weight load changes nothing (203.8 -> 201.6 us): not L2 -> SM bandwidth;
+//   * busy-polling (mbarrier.test_wait) instead of try_wait in the ring: no change;
+//   * software-pipelining items (z and r both read out in epilogue 1, q alternating between two
+//     TMEM blocks, the next item's first k-blocks issued ahead of this item's stage 2): correct
+//     but 6-30 % SLOWER -- with the TMA stream running, the r.h epilogue (strided 16-byte stores
+//     + threadfence) takes 8-12 us instead of 5 and the gate epilogue ~20 us: the epilogue warps
+//     become the bottleneck.  What remains exposed per item (41 us = 29 stage 1 + 5 r.h epilogue
+//     + 6.5 stage 2) needs a coalesced epilogue store path first (no shared memory left for it
+//     next to the 192 KB ring).
 #include "convgru_common.cuh"
 #include <stdlib.h>
 
