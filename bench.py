@@ -34,12 +34,29 @@ def workload(S=256, B=64):
     return WORKLOAD.replace("256x256", f"{S}x{S}").replace("batch 64", f"batch {B}")
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full`
-# captures (profiles/): kernel -> bytes.  null where no capture exists for the current kernel.
-NCU_TRAFFIC = {            # profiles/r01_ncu_full_summary.txt (cfg2: 64 crops of 256x256)
-    "scflow_convgru_pass_fwd": 189.6e6, "scflow_corr_lookup_fwd": 208.8e6,
-    "scflow_corr_pyramid_fwd": 434.5e6, "scflow_pose_flow_fwd": 16.8e6,
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, read from the committed `ncu --set full`
+# summary (profiles/<round>_ncu_full_summary.txt, written by tools/make_profiles.py; cfg2 only):
+# launcher -> kernel-name fragment of the capture.  null where the capture holds no such kernel.
+NCU_KERNEL = {
+    "scflow_convgru_fwd": "convgru_fused_kernel", "scflow_convgru_pass_fwd": "convgru_pass_kernel",
+    "scflow_corr_lookup_fwd": "corr_lookup_v2_kernel", "scflow_corr_pyramid_fwd": "corr_tf32_kernel",
+    "scflow_pose_flow_fwd": "pose_flow_kernel",
 }
+
+
+def ncu_traffic(launcher):
+    frag = NCU_KERNEL.get(launcher)
+    files = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if f.endswith("_ncu_full_summary.txt")) \
+        if os.path.isdir(os.path.join(ROOT, "profiles")) else []
+    if not frag or not files:
+        return None
+    vals, take = [], False
+    for line in open(os.path.join(ROOT, "profiles", files[-1])):
+        if line.startswith("=="):
+            take = frag in line
+        elif take and line.strip().startswith("traffic (DRAM read + write)"):
+            vals.append(float(line.split()[-2]) * 1e6)
+    return sum(vals) / len(vals) if vals else None
 
 
 def peaks():
@@ -316,8 +333,19 @@ def ours(args):
     launches = ops.STATS.count
     state["prefetched"] = None
     ms_e2e = timed(step_e2e, args.steps, False)
-    # per-kernel attribution: the same steps run eagerly with CUDA events around every launcher
-    ms_eager = timed(step_eager, args.steps, True)
+    # per-kernel attribution: the same steps run eagerly with CUDA events around every launcher.
+    # Eager steps are CPU-bound (the host issues ~700 launches per step slower than the GPU retires
+    # them), so an event pair around a launcher would also time the GPU waiting for the host; each
+    # attributed step therefore starts with a device-side sleep of one step's length, which keeps
+    # the GPU behind the host and the event intervals equal to the kernels' own durations.
+    ms_eager = timed(step_eager, args.steps, False)
+    sleep_cycles = int(1.5 * ms_eager / args.steps * 1e-3 * 1.9e9)
+
+    def step_attr(i):
+        torch.cuda._sleep(sleep_cycles)
+        return step_eager(i)
+
+    timed(step_attr, args.steps, True)
     per_kernel = ops.STATS.summary()
     clocks = sampler.stop() if sampler else None
     tf32_peak = measure_tf32_peak(dev) if rank == 0 else None
@@ -343,11 +371,11 @@ def ours(args):
     # is listed in `kernels` with its own achieved GB/s)
     single = [k for k in kern if algorithmic_flops(k, B, S) or algorithmic_bytes(k, B, S)]
     top = max(single, key=lambda k: kern[k]["avg_ms"] * kern[k]["calls_per_step"])
-    traffic = NCU_TRAFFIC.get(top) if (B, S) == (64, 256) else None
+    traffic = ncu_traffic(top) if (B, S) == (64, 256) else None
     lk = kern.get("scflow_corr_lookup_fwd")
     roof_lookup = None if lk is None else {
         "kernel": "scflow_corr_lookup_fwd", "bound": "hbm", "achieved": lk["gbs"], "peak": pk["hbm"], "unit": "GB/s",
-        "frac": lk["hbm_frac"], "traffic": NCU_TRAFFIC.get("scflow_corr_lookup_fwd") if (B, S) == (64, 256) else None,
+        "frac": lk["hbm_frac"], "traffic": ncu_traffic("scflow_corr_lookup_fwd") if (B, S) == (64, 256) else None,
         "algorithmic_bytes_per_launch": algorithmic_bytes("scflow_corr_lookup_fwd", B, S)}
     if kern[top]["tflops"] is not None and top in ("scflow_convgru_pass_fwd", "scflow_convgru_fwd"):
         roof = {"kernel": top, "bound": "tensor", "achieved": kern[top]["tflops"], "peak": tf32_peak,

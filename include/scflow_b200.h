@@ -218,6 +218,13 @@ int scflow_conv_small_cin_fwd(const float* in, long long stride_n, long long str
                               const float* wpack, const float* bias, float* out, int n, int cin, int h,
                               int w, int cout, int ksize, int relu, void* stream);
 
+/* Stem input of the RAFT encoders (raft_encoder.py:286-288: conv1 7x7 stride 2 on 3 channels, the
+ * one layer cuDNN has no tensor-core kernel for) as the 2x2 space-to-depth image of the equivalent
+ * 4x4 stride-1 convolution: x planar (n, c <= 4, h, w), h and w even -> out channels-last
+ * (n, h/2+3, w/2+3, 16), channel 4*c + 2*by + bx = x[n, c, 2Y+by, 2X+bx] at (Y+2, X+2); zero in the
+ * unused channels and in the (2 before, 1 after) border = the stride-1 filter's padding. */
+int scflow_stem_s2d_fwd(const float* x, float* out, int n, int c, int h, int w, void* stream);
+
 /* out (n, cout, h, w) planar = conv(in) + bias.  in: (n, h, w, c) channels-last, c % 4 == 0;
  * wpack: [c][k*k][cout] (Conv2d weight (cout,c,k,k) permuted 1,2,3,0); cout in {1,2}, ksize in {1,3},
  * (4 + 2*(ksize/2)) * w <= 1024. */

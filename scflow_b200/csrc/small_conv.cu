@@ -283,3 +283,53 @@ extern "C" int scflow_conv_small_cout_fwd(const float* in, const float* wpack, c
   if (ksize == 1 && cout == 2) return sc::launch_cout<1, 2>(p, st);
   return SCFLOW_E_UNSUPPORTED;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Stem input of the RAFT encoders (raft_encoder.py:286-288, conv1 = 7x7 stride 2 on 3 channels)
+// rewritten as a 4x4 stride-1 convolution over the 2x2 space-to-depth image: this kernel
+// produces that image in one pass -- planar (n, c, H, W) in, channels-last (n, H/2+3, W/2+3, 16)
+// out with channel = 4*c + 2*by + bx for pixel (2Y+by, 2X+bx) at (Y+2, X+2), zero in the unused
+// channels and in the (2, 1) border that is the stride-1 filter's padding.  Replaces torch's
+// pixel_unshuffle + pad + layout copy (four passes).
+namespace scflow {
+namespace sc {
+__global__ void __launch_bounds__(256)
+stem_s2d_kernel(const float* __restrict__ x, float4* __restrict__ out, int n, int c, int H, int W) {
+  const int Wo = W / 2 + 3, Ho = H / 2 + 3;
+  const long long total = (long long)n * Ho * Wo;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int xo = (int)(i % Wo);
+    const long long r = i / Wo;
+    const int yo = (int)(r % Ho), img = (int)(r / Ho);
+    const int Y = yo - 2, X = xo - 2;
+    float v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = 0.0f;
+    if (Y >= 0 && Y < H / 2 && X >= 0 && X < W / 2) {
+      for (int ch = 0; ch < c; ++ch) {
+        const float* p = x + (((size_t)img * c + ch) * H + 2 * Y) * W + 2 * X;
+        const float2 a = __ldg(reinterpret_cast<const float2*>(p));
+        const float2 b = __ldg(reinterpret_cast<const float2*>(p + W));
+        v[4 * ch + 0] = a.x; v[4 * ch + 1] = a.y; v[4 * ch + 2] = b.x; v[4 * ch + 3] = b.y;
+      }
+    }
+    float4* o = out + i * 4;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) o[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+  }
+}
+}  // namespace sc
+}  // namespace scflow
+
+extern "C" int scflow_stem_s2d_fwd(const float* x, float* out, int n, int c, int h, int w, void* stream) {
+  using namespace scflow;
+  if (!x || !out) return SCFLOW_E_NULL;
+  if (n <= 0 || c <= 0 || c > 4 || h <= 0 || w <= 0 || (h & 1) || (w & 1)) return SCFLOW_E_BAD_SHAPE;
+  if (!aligned16(out) || (reinterpret_cast<uintptr_t>(x) & 7u)) return SCFLOW_E_MISALIGNED;
+  const long long total = (long long)n * (h / 2 + 3) * (w / 2 + 3);
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  sc::stem_s2d_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<float4*>(out), n, c, h, w);
+  return check_launch();
+}

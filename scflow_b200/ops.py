@@ -323,6 +323,19 @@ def conv_small_cin(x: torch.Tensor, conv: torch.nn.Conv2d, relu: bool) -> torch.
     return out.permute(0, 3, 1, 2)
 
 
+def stem_s2d(x: torch.Tensor) -> torch.Tensor:
+    """Planar (N,C<=4,H,W) image -> the 2x2 space-to-depth input of the stride-1 form of the encoder
+    stem: an (N,16,H/2+3,W/2+3)-shaped channels-last tensor (see scflow_stem_s2d_fwd)."""
+    lib = _lib.load()
+    x = _chk(x, "x")
+    n, c, h, w = x.shape
+    out = torch.empty((n, h // 2 + 3, w // 2 + 3, 16), device=x.device, dtype=torch.float32)
+    with _timed("scflow_stem_s2d_fwd", 1, 4 * (x.numel() + out.numel())):
+        rc = lib.scflow_stem_s2d_fwd(_ptr(x), _ptr(out), n, c, h, w, _stream())
+    _lib.check(rc, "scflow_stem_s2d_fwd")
+    return out.permute(0, 3, 1, 2)
+
+
 def conv_small_cout(x: torch.Tensor, conv: torch.nn.Conv2d) -> torch.Tensor:
     """conv(x) + bias for cout in {1,2} on a channels-last x: planar (n, cout, h, w)."""
     lib = _lib.load()

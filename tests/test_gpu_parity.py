@@ -323,6 +323,28 @@ def test_batch64_matches_per_crop_runs():
     assert float(O.rotation_geodesic(Ra.cpu(), Rb.cpu()).max()) < 1e-4
 
 
+# ------------------------------------------------------------------ f3 encoder stem (space-to-depth form)
+@pytest.mark.parametrize("n,c,h,w", [(2, 3, 256, 256), (1, 3, 64, 96), (3, 1, 16, 8)])
+def test_stem_space_to_depth_input(n, c, h, w):
+    """scflow_stem_s2d_fwd == pixel_unshuffle + channel / border padding, bit for bit, and the 4x4
+    stride-1 filter over it == the shipped 7x7 stride-2 convolution (raft_encoder.py:286-288)."""
+    from scflow_b200 import encoder as E
+    g = torch.Generator(device=DEV).manual_seed(31)
+    x = torch.rand(n, c, h, w, device=DEV, generator=g)
+    got = ops.stem_s2d(x)
+    want = torch.nn.functional.pad(torch.nn.functional.pixel_unshuffle(x, 2), (2, 1, 2, 1, 0, 16 - 4 * c))
+    assert got.shape == want.shape and torch.equal(got, want)
+    wgt = torch.randn(64, c, 7, 7, device=DEV, generator=g)
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        ref = torch.nn.functional.conv2d(x, wgt, None, 2, 3)
+        out = torch.nn.functional.conv2d(got, E._s2d_filter(wgt))
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    assert rel(out, ref) < 1e-5
+
+
 # ------------------------------------------------------------------ a3 ConvGRU (tcgen05)
 def _gru_sd(seed):
     shapes = {}
