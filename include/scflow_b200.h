@@ -182,6 +182,18 @@ int scflow_norm_act_nhwc(const float* x, const double* sums, const float* scale,
                          const float* res_shift, float* out, int n, int P, int C, float eps,
                          int relu, void* stream);
 
+/* InstanceNorm2d (no affine) + optional residual + optional ReLU in ONE launch (resnet.py:64-92 on
+ * the IN encoder): a thread-block cluster owns an image, takes the statistics, exchanges partial
+ * sums through distributed shared memory and normalises its slice while it is still in L2, so a
+ * layer costs one HBM read and one write instead of two reads and a write.  x (n, P, C) is
+ * normalised into out (may alias x); res (optional, same shape) is added as res*res_scale +
+ * res_shift (identity when the affine is NULL); sums_out (optional) receives the [n][C][2] fp64
+ * statistics.  Statistics are those of scflow_chan_stats_nhwc up to the order of the final fp64
+ * additions. */
+int scflow_instnorm_act_nhwc(float* x, const float* res, const float* res_scale, const float* res_shift,
+                             float* out, double* sums_out, int n, int P, int C, float eps, int relu,
+                             void* stream);
+
 /* (n, P, C) channels-last -> (n, C, P) planar, with optional round-to-nearest TF32: the hand-over
  * of channels-last encoder features to scflow_corr_pyramid_fwd (planar operands), replacing a
  * torch .contiguous() pass.  in != out. */

@@ -32,6 +32,7 @@ SIGNATURES = {
     "scflow_pack_nhwc": (c_int, [_P, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, ctypes.c_longlong, c_int,
                                  c_int, _P]),
     "scflow_chan_stats_nhwc": (c_int, [_P, _P, c_int, c_int, c_int, _P]),
+    "scflow_instnorm_act_nhwc": (c_int, [_P] * 6 + [c_int, c_int, c_int, ctypes.c_float, c_int, _P]),
     "scflow_norm_act_nhwc": (c_int, [_P] * 9 + [c_int, c_int, c_int, c_float, c_int, _P]),
     "scflow_nhwc_to_nchw": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P]),
     "scflow_lift_points": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P]),

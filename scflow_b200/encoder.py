@@ -122,6 +122,14 @@ def _side(norm: nn.Module, y: torch.Tensor, bias):
     raise NotImplementedError(type(norm))
 
 
+def _in_fused(norm: nn.Module) -> bool:
+    """Plain InstanceNorm2d layers take the one-launch cluster kernel (SCFLOW_IN_FUSED=0: the
+    statistics + normalise launch pair, kept as the cross-check)."""
+    import os
+    return (isinstance(norm, nn.InstanceNorm2d) and not norm.affine and not norm.track_running_stats
+            and os.environ.get("SCFLOW_IN_FUSED", "1") != "0")
+
+
 def _norm(kind: str, ch: int, postfix):
     if kind == "IN":
         return f"in{postfix}", nn.InstanceNorm2d(ch)
@@ -166,9 +174,15 @@ class BasicBlock(nn.Module):
             return torch.cudnn_convolution_add_relu(o, w2, idt, 1.0, b2, self.conv2.stride, self.conv2.padding,
                                                     (1, 1), 1)
         o = _conv_cl(self.conv1, x)
-        kw, eps = _side(n1, _nhwc(o), self.conv1.bias)
-        ops.norm_act(_nhwc(o), relu=True, eps=eps, **kw)
+        if _in_fused(n1):
+            ops.instnorm_act(_nhwc(o), relu=True, eps=n1.eps)
+        else:
+            kw, eps = _side(n1, _nhwc(o), self.conv1.bias)
+            ops.norm_act(_nhwc(o), relu=True, eps=eps, **kw)
         o2 = _conv_cl(self.conv2, o)
+        if self.downsample is None and _in_fused(n2):
+            ops.instnorm_act(_nhwc(o2), res=_nhwc(x), relu=True, eps=n2.eps)
+            return o2
         kw, eps = _side(n2, _nhwc(o2), self.conv2.bias)
         if self.downsample is not None:
             d = _conv_cl(self.downsample[0], x)
@@ -244,8 +258,11 @@ class RAFTEncoder(nn.Module):
                 y = y.contiguous(memory_format=torch.channels_last)
             else:
                 y = _conv_cl(self.conv1, x)
-            kw, eps = _side(n1, _nhwc(y), self.conv1.bias)
-            ops.norm_act(_nhwc(y), relu=True, eps=eps, **kw)
+            if _in_fused(n1):
+                ops.instnorm_act(_nhwc(y), relu=True, eps=n1.eps)
+            else:
+                kw, eps = _side(n1, _nhwc(y), self.conv1.bias)
+                ops.norm_act(_nhwc(y), relu=True, eps=eps, **kw)
         for name in self.res_layers:
             for block in getattr(self, name):
                 y = block.forward_fused(y)

@@ -216,6 +216,27 @@ def norm_act(x: torch.Tensor, sums=None, affine=None, res=None, res_sums=None, r
     return out
 
 
+def instnorm_act(x: torch.Tensor, res: Optional[torch.Tensor] = None, res_affine=None, relu: bool = True,
+                 eps: float = 1e-5, out: Optional[torch.Tensor] = None, want_sums: bool = False):
+    """InstanceNorm (+ residual) (+ ReLU) of a channels-last (N,H,W,C) tensor in one launch, in place
+    unless `out` is given (scflow_instnorm_act_nhwc)."""
+    lib = _lib.load()
+    x = _chk(x, "x")
+    n, H, W, C = x.shape
+    if res is not None:
+        res = _chk(res, "res")
+        assert res.shape == x.shape
+    if out is None:
+        out = x
+    rsc, rsh = res_affine if res_affine is not None else (None, None)
+    sums = torch.empty((n, C, 2), device=x.device, dtype=torch.float64) if want_sums else None
+    with _timed("scflow_instnorm_act_nhwc", 1, 4 * x.numel() * (3 if res is not None else 2)):
+        rc = lib.scflow_instnorm_act_nhwc(_ptr(x), _ptr(res), _ptr(rsc), _ptr(rsh), _ptr(out), _ptr(sums), n, H * W, C,
+                                          float(eps), 1 if relu else 0, _stream())
+    _lib.check(rc, "scflow_instnorm_act_nhwc")
+    return (out, sums) if want_sums else out
+
+
 def lift_points(depth, K, R0, t0):
     """Dense cal_3d_2d_corr (pose.py:44-64): points3d (N,3,H,W), mask (N,H,W) uint8."""
     lib = _lib.load()

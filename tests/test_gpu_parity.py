@@ -323,6 +323,30 @@ def test_batch64_matches_per_crop_runs():
     assert float(O.rotation_geodesic(Ra.cpu(), Rb.cpu()).max()) < 1e-4
 
 
+# ------------------------------------------------------------------ f3 InstanceNorm in one launch
+@pytest.mark.parametrize("n,h,w,c", [(3, 128, 128, 64), (2, 64, 64, 96), (5, 32, 32, 128), (1, 8, 12, 64), (2, 24, 40, 96)])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_instnorm_cluster_kernel_equals_two_launches(n, h, w, c, with_res):
+    """scflow_instnorm_act_nhwc (statistics + normalise in one cluster launch) against the
+    chan_stats + norm_act pair: statistics equal to fp64 rounding, outputs identical up to one
+    fp32 ulp of the coefficients, and against torch's instance_norm."""
+    g = torch.Generator(device=DEV).manual_seed(41)
+    x = torch.randn(n, h, w, c, device=DEV, generator=g) * 3.0 + 0.7
+    res = torch.randn(n, h, w, c, device=DEV, generator=g) if with_res else None
+    sums = ops.chan_stats(x)
+    want = ops.norm_act(x.clone(), sums=sums, res=res, relu=True)
+    got, gs = ops.instnorm_act(x.clone(), res=res, relu=True, want_sums=True)
+    assert float(((gs - sums).abs() / sums.abs().clamp_min(1.0)).max()) < 1e-13
+    assert float((got - want).abs().max()) <= 2e-6 * float(want.abs().max())
+    ref = torch.nn.functional.instance_norm(x.permute(0, 3, 1, 2)).permute(0, 2, 3, 1)
+    ref = torch.relu(ref + res) if with_res else torch.relu(ref)
+    assert float((got - ref).abs().max()) < 2e-5
+    # out-of-place and no activation
+    out = torch.empty_like(x)
+    ops.instnorm_act(x, relu=False, out=out)
+    assert float((out - torch.nn.functional.instance_norm(x.permute(0, 3, 1, 2)).permute(0, 2, 3, 1)).abs().max()) < 2e-5
+
+
 # ------------------------------------------------------------------ f3 encoder stem (space-to-depth form)
 @pytest.mark.parametrize("n,c,h,w", [(2, 3, 256, 256), (1, 3, 64, 96), (3, 1, 16, 8)])
 def test_stem_space_to_depth_input(n, c, h, w):

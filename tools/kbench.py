@@ -7,7 +7,7 @@ import torch
 from scflow_b200 import ops, gru_tc, modules
 
 ap = argparse.ArgumentParser()
-ap.add_argument("which", nargs="*", default=["lookup", "gru", "corr", "pose", "small"])
+ap.add_argument("which", nargs="*", default=["lookup", "gru", "corr", "pose", "small"])   # also: norm
 ap.add_argument("--n", type=int, default=64)
 ap.add_argument("--s", type=int, default=256)
 ap.add_argument("--reps", type=int, default=20)
@@ -130,3 +130,17 @@ if "posefc" in a.which:
             y = head.fc_layers(xs[i % 4]); return head.rotation_pred(y), head.translation_pred(y)
         r = timeit(ref)
     print(f"pose_fc (3 launches) {us:8.1f} us   (cuBLAS fp32 chain {r:.1f} us)")
+
+if "norm" in a.which:
+    # InstanceNorm + ReLU of the IN encoder's three activation shapes: statistics + normalise pair vs the
+    # one-launch cluster kernel (cluster size / CTAs per SM knobs)
+    for (hh, ww, cc) in ((128, 128, 64), (64, 64, 96), (32, 32, 128)):
+        xs_ = [torch.randn(N, hh, ww, cc, device=dev, generator=g) for _ in range(3)]
+        by = N * hh * ww * cc * 4
+        def pair(i):
+            x = xs_[i % 3]
+            ops.norm_act(x, sums=ops.chan_stats(x), relu=True)
+        us = timeit(pair)
+        print(f"IN {hh}x{ww}x{cc}: stats + normalise pair        {us:8.1f} us  ({3*by/us/1e3:7.1f} GB/s moved)")
+        us = timeit(lambda i: ops.instnorm_act(xs_[i % 3], relu=True))
+        print(f"IN {hh}x{ww}x{cc}: one cluster launch               {us:8.1f} us  ({2*by/us/1e3:7.1f} GB/s of HBM traffic)")
