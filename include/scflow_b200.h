@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define SCFLOW_ABI_VERSION 3
+#define SCFLOW_ABI_VERSION 4
 
 enum {
   SCFLOW_OK = 0,
