@@ -246,29 +246,47 @@ convgru_fused_kernel(const __grid_constant__ GruMaps maps, const __grid_constant
             next_stage();
           }
         }
-        // ---- stage 2: (r.h) . Wq[:, h part]^T.  The weight boxes do not depend on r.h: those of
-        // the first STAGES k-blocks (tap 0) are requested BEFORE the wait, their activations after
+        // ---- stage 2: (r.h) . Wq[:, h part]^T, TWO k-blocks per ring stage (2 x (16 KB pixels + 16 KB
+        // weights) = one 64 KB stage): the ring's cost is per hand-shake, and these MMAs are small.
+        // The weight boxes do not depend on r.h: those of the first STAGES stages are requested
+        // BEFORE the wait, their activations after it.
+        constexpr int kBox = CH * BK * 4;
+        auto s2_coords = [&](int j, int& t, int& kb) { t = j / KB_H; kb = j - t * KB_H; };
         int pre_stage[STAGES];
 #pragma unroll
-        for (int kb = 0; kb < STAGES; ++kb) {
+        for (int i = 0; i < STAGES; ++i) {
           tc::mbar_wait(&empty[stage], phase ^ 1);
-          tc::mbar_expect_tx(&full[stage], A_BYTES + CH * BK * 4);
-          tc::tma_load_2d(&maps.w[s], &full[stage], smem + stage * STAGE_BYTES + A_BYTES, 0, kb * ROWS + 2 * CH);
-          pre_stage[kb] = stage;
+          tc::mbar_expect_tx(&full[stage], 2 * (A_BYTES + kBox));
+          uint8_t* st = smem + stage * STAGE_BYTES;
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            int t, kb; s2_coords(2 * i + u, t, kb);
+            tc::tma_load_2d(&maps.w[s], &full[stage], st + 2 * A_BYTES + u * kBox, 0, (t * KB_ALL + kb) * ROWS + 2 * CH);
+          }
+          pre_stage[i] = stage;
           next_stage();
         }
         tc::mbar_wait(rh_ready, it_tile & 1);                          // r.h of this tile is in L2
         if (p.stamps && blockIdx.x == 0 && it_tile < 4) p.stamps[it_tile * 8 + 4] = clock64();
 #pragma unroll
-        for (int kb = 0; kb < STAGES; ++kb)
-          tc::tma_load_4d(&maps.rh[s], &full[pre_stage[kb]], smem + pre_stage[kb] * STAGE_BYTES, kb * BK, bx, by, item.n);
-        for (int j = STAGES; j < S2_ITERS; ++j) {
-          const int t = j / KB_H, kb = j % KB_H;
+        for (int i = 0; i < STAGES; ++i) {
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            int t, kb; s2_coords(2 * i + u, t, kb);
+            tc::tma_load_4d(&maps.rh[s], &full[pre_stage[i]], smem + pre_stage[i] * STAGE_BYTES + u * A_BYTES, kb * BK,
+                            bx + t * dx, by + t * dy, item.n);
+          }
+        }
+        for (int i = STAGES; i < S2_ITERS / 2; ++i) {
           tc::mbar_wait(&empty[stage], phase ^ 1);
-          uint8_t* a_s = smem + stage * STAGE_BYTES;
-          tc::mbar_expect_tx(&full[stage], A_BYTES + CH * BK * 4);
-          tc::tma_load_4d(&maps.rh[s], &full[stage], a_s, kb * BK, bx + t * dx, by + t * dy, item.n);
-          tc::tma_load_2d(&maps.w[s], &full[stage], a_s + A_BYTES, 0, (t * KB_ALL + kb) * ROWS + 2 * CH);
+          tc::mbar_expect_tx(&full[stage], 2 * (A_BYTES + kBox));
+          uint8_t* st = smem + stage * STAGE_BYTES;
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            int t, kb; s2_coords(2 * i + u, t, kb);
+            tc::tma_load_4d(&maps.rh[s], &full[stage], st + u * A_BYTES, kb * BK, bx + t * dx, by + t * dy, item.n);
+            tc::tma_load_2d(&maps.w[s], &full[stage], st + 2 * A_BYTES + u * kBox, 0, (t * KB_ALL + kb) * ROWS + 2 * CH);
+          }
           next_stage();
         }
       }
@@ -310,16 +328,19 @@ convgru_fused_kernel(const __grid_constant__ GruMaps maps, const __grid_constant
         }
         tc::tc_commit(s1_done);
         if (ts) ts[1] = clock64();
-        for (int it = 0; it < S2_ITERS; ++it) {
+        for (int it = 0; it < S2_ITERS / 2; ++it) {                     // two k-blocks per stage
           tc::mbar_wait(&full[stage], phase);
           tc::tc_fence_after();
           const uint32_t a_addr = smem_a0 + stage * STAGE_BYTES;
-          const uint32_t b_addr = a_addr + A_BYTES;
+          const uint32_t b_addr = a_addr + 2 * A_BYTES;
 #pragma unroll
-          for (int ks = 0; ks < BK / 8; ++ks) {
-            const uint64_t da = tc::make_smem_desc(a_addr + ks * 32, 16, 1024, tc::kLayoutSw128);
-            const uint64_t dq = tc::make_smem_desc(b_addr + ks * 32, 16, 1024, tc::kLayoutSw128);
-            tc::mma_tf32_ss(tmem_base + 2 * CH, da, dq, id128, 1u);
+          for (int u = 0; u < 2; ++u) {
+#pragma unroll
+            for (int ks = 0; ks < BK / 8; ++ks) {
+              const uint64_t da = tc::make_smem_desc(a_addr + u * A_BYTES + ks * 32, 16, 1024, tc::kLayoutSw128);
+              const uint64_t dq = tc::make_smem_desc(b_addr + u * (CH * BK * 4) + ks * 32, 16, 1024, tc::kLayoutSw128);
+              tc::mma_tf32_ss(tmem_base + 2 * CH, da, dq, id128, 1u);
+            }
           }
           tc::tc_commit(&empty[stage]);
           next_stage();
