@@ -111,11 +111,14 @@ if "small" in a.which:
     for k, cout in ((3, 2), (1, 1)):
         hd = XHead(128, [256], cout, x="flow" if k == 3 else "mask").to(dev)
         ys = [torch.randn(N, 256, h, w, device=dev, generator=g).contiguous(memory_format=torch.channels_last) for _ in range(4)]
-        with torch.no_grad():
-            us = timeit(lambda i: ops.conv_small_cout(ys[i % 4], hd.predict_layer))
-            ref = timeit(lambda i: hd.predict_layer(ys[i % 4]))
         by = N * P * (256 + cout) * 4
-        print(f"conv_small_cout 256->{cout} {k}x{k}  {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)  (cuDNN {ref:.1f} us)")
+        with torch.no_grad():
+            ref = timeit(lambda i: hd.predict_layer(ys[i % 4]))
+            for tag, env in (("plain loads", "0"), ("TMA-staged", "1")):
+                os.environ["SCFLOW_COUT_TMA"] = env
+                us = timeit(lambda i: ops.conv_small_cout(ys[i % 4], hd.predict_layer))
+                print(f"conv_small_cout 256->{cout} {k}x{k} {tag:11s} {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)  (cuDNN {ref:.1f} us)")
+            os.environ.pop("SCFLOW_COUT_TMA")
 if "posefc" in a.which:
     from scflow_b200.pose_head import MultiClassPoseHead
     head = MultiClassPoseHead(21, 224, "Basic", dict(type="GN", num_groups=32), dict(type="ReLU"),
