@@ -19,7 +19,7 @@
 namespace scflow {
 namespace sc {
 
-constexpr int kSegPx = 8;          // pixels per warp task (one row segment)
+constexpr int kSegPx = 8;          // minimum pixels per warp task (one row segment); 16 where the width allows
 constexpr int kTileW = 32;         // pixels per CTA tile (one row segment of <= 32)
 
 struct CinParams {
@@ -31,7 +31,10 @@ struct CinParams {
   int n, h, w, cout, relu;
 };
 
-template <int CIN, int KS>
+// SEG pixels of a row per lane: the inputs are broadcast LDS.128, the filter taps one LDS.32 per
+// lane; with 8 pixels that is 11 shared-memory reads per 56 FMAs and the two pipes tie (43 % of the
+// FP32 rate); 16 pixels halve the reads per FMA.
+template <int CIN, int KS, int SEG>
 __global__ void __launch_bounds__(256)
 conv_small_cin_kernel(const CinParams p) {
   constexpr int PAD = KS / 2;
@@ -98,22 +101,22 @@ conv_small_cin_kernel(const CinParams p) {
     const float* patch = patch0 + buf * PATCH;
     const bool more = tile + gridDim.x < tiles;
     if (more) fetch(tile + gridDim.x);               // next tile's loads fly under this tile's FMAs
-    const int segs = min(kTileW, p.w - x0) / kSegPx;
+    const int segs = min(kTileW, p.w - x0) / SEG;
     for (int task = warp; task < segs * groups; task += 8) {
       const int seg = task % segs, grp = task / segs;
       const int c = grp * 32 + lane;
-      float acc[kSegPx];
+      float acc[SEG];
       const float b = p.bias ? __ldg(p.bias + c) : 0.0f;
 #pragma unroll
-      for (int i = 0; i < kSegPx; ++i) acc[i] = b;
+      for (int i = 0; i < SEG; ++i) acc[i] = b;
 #pragma unroll
       for (int ci = 0; ci < CIN; ++ci) {
 #pragma unroll
         for (int ky = 0; ky < KS; ++ky) {
-          float xr[kSegPx + 8];
-          const float4* src = reinterpret_cast<const float4*>(patch + (ci * KS + ky) * ROWLEN + seg * kSegPx);
+          float xr[SEG + 8];
+          const float4* src = reinterpret_cast<const float4*>(patch + (ci * KS + ky) * ROWLEN + seg * SEG);
 #pragma unroll
-          for (int j = 0; j < (kSegPx + KS - 1 + 3) / 4; ++j) {
+          for (int j = 0; j < (SEG + KS - 1 + 3) / 4; ++j) {
             const float4 v = src[j];                 // same address in every lane: broadcast
             xr[4 * j] = v.x; xr[4 * j + 1] = v.y; xr[4 * j + 2] = v.z; xr[4 * j + 3] = v.w;
           }
@@ -122,13 +125,13 @@ conv_small_cin_kernel(const CinParams p) {
           for (int kx = 0; kx < KS; ++kx) {
             const float wv = wrow[kx * p.cout];
 #pragma unroll
-            for (int i = 0; i < kSegPx; ++i) acc[i] = fmaf(xr[kx + i], wv, acc[i]);
+            for (int i = 0; i < SEG; ++i) acc[i] = fmaf(xr[kx + i], wv, acc[i]);
           }
         }
       }
-      float* o = p.out + (((long long)n * p.h + y) * p.w + x0 + seg * kSegPx) * p.cout + c;
+      float* o = p.out + (((long long)n * p.h + y) * p.w + x0 + seg * SEG) * p.cout + c;
 #pragma unroll
-      for (int i = 0; i < kSegPx; ++i) o[(long long)i * p.cout] = p.relu ? fmaxf(acc[i], 0.0f) : acc[i];
+      for (int i = 0; i < SEG; ++i) o[(long long)i * p.cout] = p.relu ? fmaxf(acc[i], 0.0f) : acc[i];
     }
     if (more) stash(patch0 + (buf ^ 1) * PATCH);
     __syncthreads();                                 // next patch visible; this one free for reuse
@@ -141,13 +144,17 @@ static int launch_cin(const CinParams& p, cudaStream_t st) {
   const size_t smem = ((size_t)CIN * KS * KS * p.cout + 2 * (size_t)CIN * KS * (kTileW + 8)) * sizeof(float);
   static size_t attr = 0;
   if (smem > 48 * 1024 && smem > attr) {
-    cudaFuncSetAttribute(conv_small_cin_kernel<CIN, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(conv_small_cin_kernel<CIN, KS, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(conv_small_cin_kernel<CIN, KS, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     attr = smem;
   }
   const long long tiles = (long long)p.n * p.h * ((p.w + kTileW - 1) / kTileW);
   const int per_sm = smem > 100 * 1024 ? 2 : smem > 56 * 1024 ? 3 : 4;
   long long grid = tiles < 148LL * per_sm ? tiles : 148LL * per_sm;
-  conv_small_cin_kernel<CIN, KS><<<(unsigned)grid, 256, smem, st>>>(p);
+  const char* e = getenv("SCFLOW_CIN_SEG");
+  const bool wide = (p.w % 16) == 0 && !(e && atoi(e) == 8);
+  if (wide) conv_small_cin_kernel<CIN, KS, 16><<<(unsigned)grid, 256, smem, st>>>(p);
+  else conv_small_cin_kernel<CIN, KS, 8><<<(unsigned)grid, 256, smem, st>>>(p);
   return check_launch();
 }
 

@@ -104,6 +104,10 @@ if "small" in a.which:
         m = ConvModule(cin, cout, k, padding=k // 2).to(dev)
         xs = [torch.randn(N, cin, h, w, device=dev, generator=g) for _ in range(4)]
         with torch.no_grad():
+            os.environ["SCFLOW_CIN_SEG"] = "8"
+            us8 = timeit(lambda i: m(xs[i % 4]))
+            os.environ.pop("SCFLOW_CIN_SEG")
+            print(f"conv_small_cin {cin}->{cout} {k}x{k}, 8 px per lane {us8:8.1f} us")
             us = timeit(lambda i: m(xs[i % 4]))
             ref = timeit(lambda i: torch.relu_(F.conv2d(xs[i % 4].contiguous(memory_format=torch.channels_last), m.conv.weight, m.conv.bias, padding=k // 2)))
         by = N * P * (cin + cout) * 4
