@@ -174,8 +174,8 @@ corr_lookup_v2_kernel(const __grid_constant__ Maps maps, const __grid_constant__
   };
 
   // Phase A + TMA issue for the query at `c` (flow fx, fy) into buffer b.  Returns (warp-uniform)
-  // whether the query needs the slow phase B.
-  auto prepare = [&](const Cursor& c, float fx, float fy, int b) -> bool {
+  // the levels (bit l) whose y taps are not consecutive and need the per-tap form of phase B.
+  auto prepare = [&](const Cursor& c, float fx, float fy, int b) -> unsigned {
     const int y = (int)__umulhi((unsigned)c.qi, p.magic_w);
     const int x = c.qi - y * p.w;
     const float xf = __fadd_rn((float)x, fx), yf = __fadd_rn((float)y, fy);
@@ -198,7 +198,7 @@ corr_lookup_v2_kernel(const __grid_constant__ Maps maps, const __grid_constant__
     const float fly = floorf(ivy);
     const int iy = iclamp(fly, sy0);
     const int orgy = __shfl_sync(0xffffffffu, iy, grp0) - 1;
-    bool bad = put_y(lane < 27, yrec01 + rb, iy - orgy, __fsub_rn(ivy, fly), (uint32_t)g * kTileBytes);
+    const bool bad01 = put_y(lane < 27, yrec01 + rb, iy - orgy, __fsub_rn(ivy, fly), (uint32_t)g * kTileBytes);
     if (WIN && lane < 27) win[18 * g + kD + k] = (short)iy;
     // round 2: level 3, lanes 0..8 x, lanes 9..17 y
     const float iv3 = unnorm_coord<DIV>(__fmul_rn(yl3 ? yf : xf, 0.125f), offk, d3, r3, s3);
@@ -213,9 +213,13 @@ corr_lookup_v2_kernel(const __grid_constant__ Maps maps, const __grid_constant__
       rec.y = __float_as_uint(w13);
       *reinterpret_cast<uint2*>(smem_raw + xrec3 + rb) = rec;
     }
-    bad |= put_y(lane >= kD && lane < 2 * kD, yrec3 + rb, i3 - org3, w13, 3u * kTileBytes);
+    const bool bad3 = put_y(lane >= kD && lane < 2 * kD, yrec3 + rb, i3 - org3, w13, 3u * kTileBytes);
     if (WIN && lane < 2 * kD) win[18 * 3 + lane] = (short)i3;
-    const bool slow = __any_sync(0xffffffffu, bad);
+    // lanes 9g .. 9g+8 hold level g in round 1 (zero flow = integer coordinates makes level 0 slow
+    // for every background query, level l only where y % 2^l == 0)
+    const unsigned b01 = __ballot_sync(0xffffffffu, bad01);
+    const unsigned slow = ((b01 & 0x1ffu) ? 1u : 0u) | ((b01 & (0x1ffu << 9)) ? 2u : 0u) | ((b01 & (0x1ffu << 18)) ? 4u : 0u) |
+                          (__any_sync(0xffffffffu, bad3) ? 8u : 0u);
     // ---- staging: the bulk store of two queries ago used tile buffer b as its staging line
     const int ox3 = __shfl_sync(0xffffffffu, org3, 0), oy3 = __shfl_sync(0xffffffffu, org3, kD);
     if (lane == 0) {
@@ -236,7 +240,7 @@ corr_lookup_v2_kernel(const __grid_constant__ Maps maps, const __grid_constant__
   float fx0, fy0, fx1, fy1;
   load_flow(c0, fx0, fy0);
   load_flow(c1, fx1, fy1);
-  bool slow0 = false, slow1 = false;
+  unsigned slow0 = 0, slow1 = 0;
   if (c0.q < total) slow0 = prepare(c0, fx0, fy0, 0);
 
   for (uint32_t it = 0; c0.q < total; ++it) {
@@ -253,38 +257,30 @@ corr_lookup_v2_kernel(const __grid_constant__ Maps maps, const __grid_constant__
     float res[kLevels][3];
     const uint32_t tb = tiles + b * kBufBytes, rb = b * kRecBytes;
     if (lane < 27) {
-      if (!slow0) {
 #pragma unroll
-        for (int l = 0; l < kLevels; ++l) {
-          const uint2 xr = *reinterpret_cast<const uint2*>(smem_raw + xrecB + rb + l * (kD * 8));
-          const uint4 yr = *reinterpret_cast<const uint4*>(smem_raw + yrecB + rb + l * (3 * 16));
-          const uint32_t a0 = tb + (yr.x & 0xffffu) + xr.x;
-          const float wx1 = __uint_as_float(xr.y), wx0 = __fsub_rn(1.0f, wx1);
+      for (int l = 0; l < kLevels; ++l) {
+        const uint2 xr = *reinterpret_cast<const uint2*>(smem_raw + xrecB + rb + l * (kD * 8));
+        const uint4 yr = *reinterpret_cast<const uint4*>(smem_raw + yrecB + rb + l * (3 * 16));
+        const uint32_t a0 = tb + (yr.x & 0xffffu) + xr.x;
+        const float wx1 = __uint_as_float(xr.y), wx0 = __fsub_rn(1.0f, wx1);
+        const float v0 = __uint_as_float(yr.y), v1 = __uint_as_float(yr.z), v2 = __uint_as_float(yr.w);
+        if (!((slow0 >> l) & 1u)) {                   // consecutive floors: four shared tile rows
           const float h0 = fmaf(ldf(a0 + 4), wx1, ldf(a0) * wx0);
           const float h1 = fmaf(ldf(a0 + kRowBytes + 4), wx1, ldf(a0 + kRowBytes) * wx0);
           const float h2 = fmaf(ldf(a0 + 2 * kRowBytes + 4), wx1, ldf(a0 + 2 * kRowBytes) * wx0);
           const float h3 = fmaf(ldf(a0 + 3 * kRowBytes + 4), wx1, ldf(a0 + 3 * kRowBytes) * wx0);
-          const float v0 = __uint_as_float(yr.y), v1 = __uint_as_float(yr.z), v2 = __uint_as_float(yr.w);
           res[l][0] = fmaf(h1, v0, h0 * __fsub_rn(1.0f, v0));
           res[l][1] = fmaf(h2, v1, h1 * __fsub_rn(1.0f, v1));
           res[l][2] = fmaf(h3, v2, h2 * __fsub_rn(1.0f, v2));
-        }
-      } else {
-#pragma unroll
-        for (int l = 0; l < kLevels; ++l) {
-          const uint2 xr = *reinterpret_cast<const uint2*>(smem_raw + xrecB + rb + l * (kD * 8));
-          const uint4 yr = *reinterpret_cast<const uint4*>(smem_raw + yrecB + rb + l * (3 * 16));
-          const uint32_t a0 = tb + (yr.x & 0xffffu) + xr.x;
-          const float wx1 = __uint_as_float(xr.y), wx0 = __fsub_rn(1.0f, wx1);
-          const uint32_t wy[3] = {yr.y, yr.z, yr.w};
+        } else {                                      // per-tap rows
+          const float wy[3] = {v0, v1, v2};
           const uint32_t dr[3] = {0u, (yr.x >> 16) & 15u, (yr.x >> 20) & 15u};
 #pragma unroll
           for (int j = 0; j < 3; ++j) {
             const uint32_t a = a0 + dr[j] * kRowBytes;
             const float top = fmaf(ldf(a + 4), wx1, ldf(a) * wx0);
             const float bot = fmaf(ldf(a + kRowBytes + 4), wx1, ldf(a + kRowBytes) * wx0);
-            const float v = __uint_as_float(wy[j]);
-            res[l][j] = fmaf(bot, v, top * __fsub_rn(1.0f, v));
+            res[l][j] = fmaf(bot, wy[j], top * __fsub_rn(1.0f, wy[j]));
           }
         }
       }
