@@ -344,9 +344,9 @@ def ours(args):
     def step_attr(i):
         torch.cuda._sleep(sleep_cycles)
         out = step_eager(i)
-        for _ in range(16):        # what an event pair costs around a kernel that does nothing
+        for _ in range(16):        # what an event pair costs by itself (nothing launched in between)
             with ops._timed("__null_kernel__", 0):
-                torch.cuda._sleep(1)
+                pass
         return out
 
     timed(step_attr, args.steps, True)
@@ -361,9 +361,9 @@ def ours(args):
     value = B * world / (ms_step / 1e3)
     e2e_val = B * world / (ms_e2e / args.steps / 1e3)
     pk = peaks()
-    # An event pair around a launcher also times the two command gaps and the event records themselves
-    # (a few us, measured around a null kernel in the same pass): subtracted from every interval,
-    # the uncorrected value stays in `avg_ms_raw`.
+    # An event pair around a launcher also times the event records themselves (measured as empty pairs
+    # in the same pass: nothing launched in between, so a kernel's own launch latency is NOT removed):
+    # subtracted from every interval, the uncorrected value stays in `avg_ms_raw`.
     null = per_kernel.pop("__null_kernel__", None)
     ev_ms = (null[1] / null[0]) if null else 0.0
     kern = {}
@@ -577,9 +577,9 @@ def train_arm(args):
         return
     pk = peaks()
     nst = max(2, args.steps // 2)
-    # An event pair around a launcher also times the two command gaps and the event records themselves
-    # (a few us, measured around a null kernel in the same pass): subtracted from every interval,
-    # the uncorrected value stays in `avg_ms_raw`.
+    # An event pair around a launcher also times the event records themselves (measured as empty pairs
+    # in the same pass: nothing launched in between, so a kernel's own launch latency is NOT removed):
+    # subtracted from every interval, the uncorrected value stays in `avg_ms_raw`.
     null = per_kernel.pop("__null_kernel__", None)
     ev_ms = (null[1] / null[0]) if null else 0.0
     kern = {}
