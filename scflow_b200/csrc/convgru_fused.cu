@@ -24,6 +24,8 @@
 //     per k-block hand-shake dominates, not the refill latency;
 //   * dropping every weight load changes nothing (203.8 -> 201.6 us): not L2 -> SM bandwidth;
 //   * busy-polling (mbarrier.test_wait) instead of try_wait in the ring: no change;
+//   * L2 prefetch (cp.async.bulk.prefetch.tensor) of the next item's activation tiles: 164.6 ->
+//     168.3 us, slightly slower;
 //   * software-pipelining items (z and r both read out in epilogue 1, q alternating between two
 //     TMEM blocks, the next item's first k-blocks issued ahead of this item's stage 2): correct
 //     but 6-30 % SLOWER -- with the TMA stream running, the r.h epilogue (strided 16-byte stores
