@@ -461,7 +461,8 @@ extern "C" int scflow_instnorm_act_nhwc(float* x, const float* res, const float*
   // cluster size: every sub-block gets at least one chunk; 4 for the large maps (measured on B200 at
   // 64 x 128x128x64: cluster 4 137 us, 8 143 us, 16 245 us; the statistics + normalise pair 148 us.
   // The second read of such a 268 MB layer does NOT stay in L2 whatever the cluster size; the
-  // 64x64 and 32x32 layers gain 23-32 %)
+  // 64x64 and 32x32 layers gain 23-32 %.  Bounding the images in flight -- persistent clusters over
+  // 10 / 14 / 18 images, i.e. 40-72 MB between a slice's two reads -- is slower still: 151-190 us)
   int cl = 8;
   while (cl > 1 && cl * na::kSub > nchunks) cl >>= 1;
   if (nchunks >= 32) cl = 4;
