@@ -270,6 +270,51 @@ resize4_kernel(const float* __restrict__ in, const float* __restrict__ add, floa
   }
 }
 
+// Up-sampling by >= 4: the four outputs of a quad read at most three neighbouring source columns, so
+// the 2 x 3 source values (+ the optional addend) are loaded once per quad instead of four corner
+// loads per output (32 scalar loads per quad made the kernel LSU-bound: 18-20 us for 8.4 M outputs).
+// Same arithmetic per output as resize4_kernel.
+__global__ void __launch_bounds__(256)
+resize4_up_kernel(const float* __restrict__ in, const float* __restrict__ add, float* __restrict__ out,
+                  unsigned planes, int ih, int iw, int oh, int ow, float mul) {
+  const float sy = oh > 1 ? (float)(ih - 1) / (float)(oh - 1) : 0.0f;
+  const float sx = ow > 1 ? (float)(iw - 1) / (float)(ow - 1) : 0.0f;
+  const unsigned qw = (unsigned)ow >> 2;                 // quads per row
+  const unsigned total = planes * (unsigned)oh * qw;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const unsigned row = i / qw;                         // plane * oh + y
+    const int x4 = (int)(i - row * qw) * 4;
+    const unsigned pl = row / (unsigned)oh;
+    const int y = (int)(row - pl * (unsigned)oh);
+    const float srcy = sy * (float)y;
+    const int y0 = (int)srcy;
+    const int y1 = y0 + (y0 < ih - 1 ? 1 : 0);
+    const float ly1 = srcy - (float)y0, ly0 = 1.0f - ly1;
+    const size_t r0 = (size_t)pl * ih * iw + y0 * iw, r1 = (size_t)pl * ih * iw + y1 * iw;
+    const int xb = (int)(sx * (float)x4);                // first output's left column
+    float c0[3], c1[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int xc = min(xb + k, iw - 1);
+      c0[k] = __ldg(in + r0 + xc);
+      c1[k] = __ldg(in + r1 + xc);
+      if (add != nullptr) { c0[k] += __ldg(add + r0 + xc); c1[k] += __ldg(add + r1 + xc); }
+    }
+    float o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float srcx = sx * (float)(x4 + j);
+      const int x0 = (int)srcx;
+      const float lx1 = srcx - (float)x0, lx0 = 1.0f - lx1;
+      const bool hi = x0 != xb;                          // x0 - xb is 0 or 1 (scale >= 4)
+      const float v00 = hi ? c0[1] : c0[0], v01 = hi ? c0[2] : c0[1];
+      const float v10 = hi ? c1[1] : c1[0], v11 = hi ? c1[2] : c1[1];
+      o[j] = mul * (ly0 * (lx0 * v00 + lx1 * v01) + ly1 * (lx0 * v10 + lx1 * v11));
+    }
+    *reinterpret_cast<float4*>(out + (size_t)row * ow + x4) = make_float4(o[0], o[1], o[2], o[3]);
+  }
+}
+
 }  // namespace scflow
 
 extern "C" int scflow_pose_flow_fwd(const float* dR6, const float* dt, const float* R_prev,
@@ -324,8 +369,12 @@ static int launch_resize(const float* in, const float* add, float* out, long lon
   if ((ow & 3) == 0 && total < (1ll << 32) && scflow::aligned16(out)) {
     long long blocks4 = (total / 4 + 255) / 256;
     if (blocks4 > 148LL * 32) blocks4 = 148LL * 32;
-    scflow::resize4_kernel<<<(unsigned)blocks4, 256, 0, (cudaStream_t)stream>>>(in, add, out, (unsigned)planes,
-                                                                              ih, iw, oh, ow, mul);
+    if (ow >= 4 * iw && iw >= 2)
+      scflow::resize4_up_kernel<<<(unsigned)blocks4, 256, 0, (cudaStream_t)stream>>>(in, add, out, (unsigned)planes,
+                                                                                   ih, iw, oh, ow, mul);
+    else
+      scflow::resize4_kernel<<<(unsigned)blocks4, 256, 0, (cudaStream_t)stream>>>(in, add, out, (unsigned)planes,
+                                                                                ih, iw, oh, ow, mul);
     return scflow::check_launch();
   }
   long long blocks = (total + 255) / 256;
