@@ -16,6 +16,10 @@
 //     core already runs the next item's stage 1.  Clock stamps of the previous schedule (8 warps,
 //     TMEM held to the end): stage 1 29 us, r.h epilogue 4.2 us, stage 2 7.5 us, final epilogue
 //     8 us, hand-over 2 us per item -- the final epilogue and the hand-over are now hidden.
+//   * r.h leaves through shared memory: the epilogue warps write their 32 x 32 slices, swizzled, into
+//     the activation slots of the first two stage-2 ring stages (idle between stage 1 and the r.h
+//     loads) and ONE TMA tensor store per channel block carries them to L2 -- per-lane 16-byte global
+//     stores at a 512-byte stride back-pressured the LSU for 4 us per item (epilogue 1: 5.0 -> 1.8 us).
 //   * The MMA issue loop is written per (tap, k-block) with compile-time branches: the issuing
 //     thread is on the critical path (two extra predicated branches per k-step cost 10 %).
 //
@@ -92,7 +96,8 @@ __device__ __forceinline__ void epilogue_item(const FParams& p, const float* sbi
                                               bool live, int cbase, int lane, uint64_t* s1_done,
                                               uint64_t* s2_done, uint64_t* rh_ready, uint64_t* tmem_free,
                                               uint32_t parity, const int* wait_flag, int* post_flag,
-                                              long long* ts) {
+                                              long long* ts, uint8_t* rh_slot, const CUtensorMap* map_rh, int cx0,
+                                              int cy0, int n_img, int m) {
   if (wait_flag != nullptr) {
     if (lane == 0) while (ld_acquire(wait_flag) < p.need) __nanosleep(64);
     __syncwarp();
@@ -113,22 +118,32 @@ __device__ __forceinline__ void epilogue_item(const FParams& p, const float* sbi
     float v[FC];
     tc::tmem_ld_32x32(taddr + CH + cbase, v);
     tc::tmem_ld_wait();
-    if (live) {
-      float* rhp = p.rh + off + cbase;
+    // r.h of this warp's 32 pixels x 32 channels goes into the idle activation slot of a stage-2 ring
+    // stage, as one 128-byte row per pixel in the 128-byte swizzle (chunk j of row m at j ^ (m & 7):
+    // eight conflict-free STS.128), and leaves as ONE TMA tensor store per channel block: per-lane
+    // 16-byte global stores at a 512-byte stride back-pressured the LSU for 4 us per item.
+    {
+      uint8_t* row = rh_slot + m * 128;
 #pragma unroll
       for (int k = 0; k < FC / 4; ++k) {
-        float4 o;
-        o.x = rn_tf32(sigmoidf_(v[4 * k + 0] + sbias[CH + cbase + 4 * k + 0]) * h[4 * k + 0]);
-        o.y = rn_tf32(sigmoidf_(v[4 * k + 1] + sbias[CH + cbase + 4 * k + 1]) * h[4 * k + 1]);
-        o.z = rn_tf32(sigmoidf_(v[4 * k + 2] + sbias[CH + cbase + 4 * k + 2]) * h[4 * k + 2]);
-        o.w = rn_tf32(sigmoidf_(v[4 * k + 3] + sbias[CH + cbase + 4 * k + 3]) * h[4 * k + 3]);
-        *reinterpret_cast<float4*>(rhp + 4 * k) = o;
+        float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (live) {
+          o.x = rn_tf32(sigmoidf_(v[4 * k + 0] + sbias[CH + cbase + 4 * k + 0]) * h[4 * k + 0]);
+          o.y = rn_tf32(sigmoidf_(v[4 * k + 1] + sbias[CH + cbase + 4 * k + 1]) * h[4 * k + 1]);
+          o.z = rn_tf32(sigmoidf_(v[4 * k + 2] + sbias[CH + cbase + 4 * k + 2]) * h[4 * k + 2]);
+          o.w = rn_tf32(sigmoidf_(v[4 * k + 3] + sbias[CH + cbase + 4 * k + 3]) * h[4 * k + 3]);
+        }
+        *reinterpret_cast<float4*>(row + ((k ^ (m & 7)) << 4)) = o;
       }
     }
-    __threadfence();                       // r.h visible device-wide (L2) ...
-    tc::fence_proxy_async_all();           // ... and ordered before the async-proxy (TMA) reads
-    __syncwarp();
-    if (lane == 0) tc::mbar_arrive(rh_ready);
+    tc::fence_proxy_async();               // generic-proxy smem writes -> visible to the TMA store
+    asm volatile("bar.sync %0, 128;" ::"r"(1 + cbase / FC) : "memory");     // the four warps of this channel block
+    if (m == 0) {
+      tc::tma_store_4d(map_rh, rh_slot, cbase, cx0, cy0, n_img);
+      tc::bulk_commit();
+      tc::bulk_wait_all<0>();              // written (L2) and the slot is free again
+      tc::mbar_arrive(rh_ready);
+    }
     if (ts) ts[3] = clock64();
   }
 
@@ -183,7 +198,7 @@ convgru_fused_kernel(const __grid_constant__ GruMaps maps, const __grid_constant
   uint64_t* empty = bars + STAGES;          // [STAGES]
   uint64_t* s1_done = bars + 2 * STAGES;    // stage-1 accumulators complete
   uint64_t* s2_done = s1_done + 1;          // stage-2 accumulation complete
-  uint64_t* rh_ready = s1_done + 2;         // r.h tile written (16 epilogue warps)
+  uint64_t* rh_ready = s1_done + 2;         // r.h tile stored (one arrival per channel block)
   uint64_t* tmem_free = s1_done + 3;        // accumulators read out (16 epilogue warps)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s1_done + 4);
 
@@ -200,7 +215,7 @@ convgru_fused_kernel(const __grid_constant__ GruMaps maps, const __grid_constant
     if (lane == 0) {
       for (int i = 0; i < STAGES; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
       tc::mbar_init(s1_done, 1); tc::mbar_init(s2_done, 1);
-      tc::mbar_init(rh_ready, FEPI_WARPS); tc::mbar_init(tmem_free, FEPI_WARPS);
+      tc::mbar_init(rh_ready, CH / FC); tc::mbar_init(tmem_free, FEPI_WARPS);
       tc::fence_barrier_init();
     }
     __syncwarp();
@@ -374,7 +389,12 @@ convgru_fused_kernel(const __grid_constant__ GruMaps maps, const __grid_constant
                     tmem_free, it_tile & 1, fused && s == 1 ? p.flags + item.grp : nullptr,
                     fused && s == 0 ? p.flags + item.grp : nullptr,
                     (p.stamps && blockIdx.x == 0 && it_tile < 4 && warp == 2 && lane == 0) ? p.stamps + it_tile * 8
-                                                                                           : nullptr);
+                                                                                           : nullptr,
+                    // the ring stands at stage (70 * item + 60) % 3 when stage 2 begins (60 + 10 stages per
+                    // item); channel blocks 0, 1 use that stage's two activation slots, 2, 3 the next one's
+                    smem + ((70u * it_tile + 60u + (uint32_t)(cbase / (2 * FC))) % STAGES) * STAGE_BYTES +
+                        ((cbase / FC) & 1) * A_BYTES,
+                    &maps.rh[s], p.pass[s] == 0 ? 0 : item.tl * G, p.pass[s] == 0 ? item.tl * G : 0, item.n, m);
     }
   }
 
