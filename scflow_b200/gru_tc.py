@@ -1,4 +1,5 @@
-"""ConvGRU through the fused tcgen05 pass kernel (scflow_convgru_pass_fwd).
+"""ConvGRU through the fused tcgen05 kernels: scflow_convgru_fwd (both passes, one persistent launch;
+the default) and scflow_convgru_pass_fwd (one pass per launch; the cross-check).
 
 Weights stay fp32 nn.Parameters under the reference names; the packed [tap][k-block][z|r|q][32]
 copy is a derived cache keyed on the parameters' version counters and storage, rebuilt after
