@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define SCFLOW_ABI_VERSION 4
+#define SCFLOW_ABI_VERSION 5
 
 enum {
   SCFLOW_OK = 0,
@@ -236,12 +236,82 @@ int scflow_conv_small_cin_fwd(const float* in, long long stride_n, long long str
  * (n, h/2+3, w/2+3, 16), channel 4*c + 2*by + bx = x[n, c, 2Y+by, 2X+bx] at (Y+2, X+2); zero in the
  * unused channels and in the (2 before, 1 after) border = the stride-1 filter's padding. */
 int scflow_stem_s2d_fwd(const float* x, float* out, int n, int c, int h, int w, void* stream);
+/* The same image as two bf16 planes [hi | lo] of (n, h/2+3, w/2+3, 16) each (value = hi + lo): the operand
+ * of scflow_conv_tc_fwd, which reads the 4x4 stride-1 stem as 4 filter rows of 64 contiguous channels
+ * (four x-neighbours) through an overlapped-window view (x_stride_w = 16). */
+int scflow_stem_s2d_split_fwd(const float* x, void* out, int n, int c, int h, int w, void* stream);
 
 /* out (n, cout, h, w) planar = conv(in) + bias.  in: (n, h, w, c) channels-last, c % 4 == 0;
  * wpack: [c][k*k][cout] (Conv2d weight (cout,c,k,k) permuted 1,2,3,0); cout in {1,2}, ksize in {1,3},
  * (4 + 2*(ksize/2)) * w <= 1024. */
 int scflow_conv_small_cout_fwd(const float* in, const float* wpack, const float* bias, float* out, int n,
                                int c, int h, int w, int cout, int ksize, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * f1-f3  The convolution family on the tensor cores (csrc/conv_tc.cu).  Replaces the cuDNN calls
+ * behind nn.Conv2d / mmcv ConvModule in
+ *   models/encoder/raft_encoder.py:286-314 + models/backbone/resnet.py:12-92   (RAFT encoders)
+ *   models/decoder/raft_decoder.py:152-166                                     (MotionEncoder)
+ *   models/decoder/raft_decoder.py:256-294                                     (flow / mask heads)
+ *   models/decoder/scflow_decoder.py:101-106                                   (delta-flow / mask encoders)
+ *   models/head/pose_head.py:108-150                                           (pose-head stride-2 convs)
+ * Arithmetic: split-bf16 -- every operand is hi + lo (two bf16), a product is three tcgen05
+ * kind::f16 MMAs into one fp32 TMEM accumulator (a_lo.b_hi + a_hi.b_lo + a_hi.b_hi): relative error
+ * ~2^-17 per product, fp32 accumulation.  Activations are channels-last SPLIT PLANES: a pixel holds
+ * [hi C | lo C] bf16.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct scflow_conv_tc_desc {
+  /* geometry: input (n, h, w, cin), filter (cout, cin, kh, kw), stride 1 or 2, zero padding */
+  int n, h, w, cin, cout, kh, kw, stride, pad_h, pad_w;
+  int bk;                       /* k-block of the weight pack: 64 or 32 channels               */
+  /* input: hi plane at x, lo plane x_lo_off ELEMENTS further; element strides (bf16) between
+   * x-neighbours, rows and images (all multiples of 8).  Channels-last split planes of C
+   * channels: x_lo_off = C, x_stride_w = 2C, x_stride_h = w*2C, x_stride_n = h*w*2C.            */
+  const void* x;
+  long long x_lo_off, x_stride_w, x_stride_h, x_stride_n;
+  const void* wpack;            /* scflow_conv_tc_pack_weights                                    */
+  const float* bias;            /* [cout padded as the pack] or NULL                             */
+  int relu;
+  /* residual added before the ReLU: split planes (hi at res_split, lo res_lo elements further,
+   * res_pitch elements per pixel) or fp32 channels-last (resf_pitch floats per pixel); or NULL  */
+  const void* res_split; long long res_pitch; int res_lo;
+  const float* res_f32; long long resf_pitch;
+  /* outputs (any subset, at least one): split planes, fp32 channels-last, planar fp32 (n, cout, OH*OW)
+   * optionally rounded to the nearest TF32 (the correlation kernel's operand format)           */
+  void* out_split; long long out_pitch; int out_lo;
+  float* out_f32; long long outf_pitch; int f32_tf32;      /* f32_tf32: round to the nearest TF32 */
+  float* out_planar; int planar_tf32;
+  /* optional: per-(image, channel) sum and sum of squares of the value BEFORE residual/ReLU
+   * (after bias), added into stats[n][cout8][2] (zeroed by the caller) -- InstanceNorm statistics */
+  double* stats;
+} scflow_conv_tc_desc;
+
+/* Output spatial size: OH = (h + 2 pad_h - kh) / stride + 1, likewise OW.  Supported: OW a multiple of
+ * 128, or 128 % OW == 0 with OH a multiple of 128/OW or 128/OW a multiple of OH (whole small images per
+ * tile); cout <= 256 or split evenly into <= 256-channel tiles; cin any (zero-filled to k-steps of 16). */
+int scflow_conv_tc_fwd(const scflow_conv_tc_desc* desc, void* stream);
+
+/* Weight pack: fp32 (cout, cin, kh, kw) [times scale[cout], e.g. a folded eval BatchNorm] ->
+ * [tap][k-block][hi|lo][cout_pad][bk] bf16.  cout_pad = cout rounded up to 16 (<= 256) per tile. */
+size_t scflow_conv_tc_packed_bytes(int cout, int cin, int kh, int kw, int bk);
+int scflow_conv_tc_pack_weights(const float* w, const float* scale, void* packed, int cout, int cin, int kh,
+                                int kw, int bk, void* stream);
+
+/* fp32 channels-last (in_pitch floats per pixel) -> split planes (out_pitch bf16 per pixel, lo plane
+ * out_lo elements after the hi plane); channels rounded up to 8 are written (zeros beyond). */
+int scflow_split_bf16(const float* in, long long in_pitch, void* out, long long out_pitch, int out_lo,
+                      int channels, long long pixels, void* stream);
+
+/* InstanceNorm2d (+ residual) + ReLU of a raw convolution output (n, P, C) fp32 from the statistics
+ * scflow_conv_tc_fwd accumulated (sums[n][C][2]), written as split planes for the next convolution
+ * (models/backbone/resnet.py:64-92): y = act((x - mean) rstd + r), r = nothing | res_split (split planes,
+ * final values) | (res_raw - rmean) rrstd (the down-sampling branch: raw fp32 + its own statistics).
+ * Biased variance, as F.instance_norm.  out_f32 (n, P, C), optional: the same values in fp32. */
+int scflow_norm_apply_split(const float* x, const double* sums, const void* res_split, long long res_pitch,
+                            int res_lo, const float* res_raw, const double* res_sums, void* out,
+                            long long out_pitch, int out_lo, float* out_f32, int n, int P, int C, float eps,
+                            int relu, void* stream);
+
 
 /* ------------------------------------------------------------------ backward (training, cfg5)
  * The reference gets these from autograd through ATen (grid_sampler_2d_backward,

@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libscflow_b200.so")
 
 _P = c_void_p
-ABI_VERSION = 4
+ABI_VERSION = 5
 # name -> (restype, argtypes); mirrors include/scflow_b200.h one to one
 SIGNATURES = {
     "scflow_abi_version": (c_int, []),
@@ -43,9 +43,16 @@ SIGNATURES = {
     "scflow_pose_fc_workspace_floats": (c_size_t, [c_int, c_int, c_int, c_int]),
     "scflow_pose_fc_fwd": (c_int, [_P] * 13 + [c_int] * 6 + [_P]),
     "scflow_stem_s2d_fwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P]),
+    "scflow_stem_s2d_split_fwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P]),
     "scflow_conv_small_cin_fwd": (c_int, [_P, ctypes.c_longlong, ctypes.c_longlong, ctypes.c_longlong, _P, _P, _P,
                                           c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_conv_small_cout_fwd": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
+    "scflow_conv_tc_fwd": (c_int, [_P, _P]),
+    "scflow_conv_tc_packed_bytes": (c_size_t, [c_int] * 5),
+    "scflow_conv_tc_pack_weights": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
+    "scflow_norm_apply_split": (c_int, [_P, _P, _P, ctypes.c_longlong, c_int, _P, _P, _P, ctypes.c_longlong, c_int,
+                                        _P, c_int, c_int, c_int, c_float, c_int, _P]),
+    "scflow_split_bf16": (c_int, [_P, ctypes.c_longlong, _P, ctypes.c_longlong, c_int, c_int, ctypes.c_longlong, _P]),
     "scflow_corr_lookup_bwd": (c_int, [_P, c_int, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_corr_fold_bwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, _P]),
     "scflow_upsample_bwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, c_float, _P]),

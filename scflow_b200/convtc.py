@@ -1,0 +1,269 @@
+"""Host side of the tensor-core convolution family (csrc/conv_tc.cu, `scflow_conv_tc_fwd`).
+
+Activations travel between the convolutions as SPLIT planes: a channels-last buffer whose pixel holds
+[hi C | lo C] bf16 with value = hi + lo (16 significand bits).  `Split` describes such a buffer or a
+channel slice of one (so that producers write straight into the slices of what the reference builds with
+`torch.cat`).  Weights stay fp32 `nn.Parameter`s under the reference names; `pack()` derives the
+[tap][k-block][hi|lo][cout][bk] bf16 copy (optionally with an eval BatchNorm folded in), cached on the
+module and keyed on the parameters' version counters and storage, never saved.
+
+There is no other backend behind these functions: CPU tensors and unsupported shapes raise.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from .ops import _ptr, _stream, _timed
+
+
+class _Desc(ctypes.Structure):
+    """Mirror of scflow_conv_tc_desc (include/scflow_b200.h)."""
+    _fields_ = [(k, ctypes.c_int) for k in ("n", "h", "w", "cin", "cout", "kh", "kw", "stride", "pad_h", "pad_w",
+                                            "bk")] + [
+        ("x", ctypes.c_void_p), ("x_lo_off", ctypes.c_longlong), ("x_stride_w", ctypes.c_longlong),
+        ("x_stride_h", ctypes.c_longlong), ("x_stride_n", ctypes.c_longlong),
+        ("wpack", ctypes.c_void_p), ("bias", ctypes.c_void_p), ("relu", ctypes.c_int),
+        ("res_split", ctypes.c_void_p), ("res_pitch", ctypes.c_longlong), ("res_lo", ctypes.c_int),
+        ("res_f32", ctypes.c_void_p), ("resf_pitch", ctypes.c_longlong),
+        ("out_split", ctypes.c_void_p), ("out_pitch", ctypes.c_longlong), ("out_lo", ctypes.c_int),
+        ("out_f32", ctypes.c_void_p), ("outf_pitch", ctypes.c_longlong), ("f32_tf32", ctypes.c_int),
+        ("out_planar", ctypes.c_void_p), ("planar_tf32", ctypes.c_int),
+        ("stats", ctypes.c_void_p)]
+
+
+def _rup(v: int, m: int) -> int:
+    return (v + m - 1) // m * m
+
+
+@dataclass
+class Split:
+    """Channels [off, off + c) of a split-plane buffer `buf` (n, h, w, 2*cp) bf16."""
+    buf: torch.Tensor
+    c: int
+    off: int = 0
+
+    @property
+    def cp(self) -> int:
+        return self.buf.shape[-1] // 2
+
+    @property
+    def shape(self):
+        return self.buf.shape[:3]
+
+    @property
+    def pitch(self) -> int:
+        return self.buf.shape[-1]
+
+    def hi_ptr(self) -> int:
+        return self.buf.data_ptr() + 2 * self.off
+
+    def slice(self, off: int, c: int) -> "Split":
+        assert off % 8 == 0 and self.off + off + c <= self.cp
+        return Split(self.buf, c, self.off + off)
+
+    def float(self) -> torch.Tensor:
+        """(n, h, w, c) fp32 = hi + lo (test / debugging helper)."""
+        cp = self.cp
+        hi = self.buf[..., self.off:self.off + self.c].float()
+        lo = self.buf[..., cp + self.off:cp + self.off + self.c].float()
+        return hi + lo
+
+
+def alloc_split(n: int, h: int, w: int, c: int, device, zero: bool = False) -> Split:
+    cp = _rup(c, 8)
+    mk = torch.zeros if zero else torch.empty
+    return Split(mk((n, h, w, 2 * cp), device=device, dtype=torch.bfloat16), c)
+
+
+def to_split(x: torch.Tensor, out: Optional[Split] = None) -> Split:
+    """fp32 channels-last (n, h, w, c) tensor (any pixel pitch: a channel slice of a wider buffer is fine)
+    -> split planes (one launch)."""
+    if not x.is_cuda or x.dtype != torch.float32 or x.dim() != 4:
+        raise _lib.ScflowError("to_split: expected a CUDA fp32 (n,h,w,c) tensor")
+    n, h, w, c = x.shape
+    if x.stride(3) != 1 or x.stride(1) != w * x.stride(2) or x.stride(0) != h * x.stride(1):
+        x = x.contiguous()
+    if out is None:
+        out = alloc_split(n, h, w, c, x.device)
+    assert tuple(out.shape) == (n, h, w) and out.c == c
+    lib = _lib.load()
+    with _timed("scflow_split_bf16", 1, 8 * x.numel()):
+        rc = lib.scflow_split_bf16(_ptr(x), x.stride(2), ctypes.c_void_p(out.hi_ptr()), out.pitch, out.cp, c,
+                                   n * h * w, _stream())
+    _lib.check(rc, "scflow_split_bf16")
+    return out
+
+
+@dataclass
+class Packed:
+    w: torch.Tensor          # packed bf16 weights
+    bias: Optional[torch.Tensor]     # fp32, padded
+    cout: int
+    cin: int
+    kh: int
+    kw: int
+    stride: int
+    pad_h: int
+    pad_w: int
+    bk: int
+
+
+def choose_bk(cout: int) -> int:
+    """64-channel k-blocks (128-byte swizzle rows) while three ring stages fit next to the weight tile,
+    32-channel ones (64-byte rows) for the wide tiles."""
+    bn = _rup(cout, 16)
+    if bn > 256:
+        nt = (bn + 255) // 256
+        bn = _rup((bn + nt - 1) // nt, 16)
+    stage64 = 2 * (128 * 64 * 2 + bn * 64 * 2)
+    return 64 if (227 * 1024 - 2048) // stage64 >= 3 else 32
+
+
+def pack_weights(weight: torch.Tensor, bias: Optional[torch.Tensor], stride=1, padding=0, scale=None,
+                 bk: Optional[int] = None) -> Packed:
+    """weight (cout, cin, kh, kw) fp32 [* scale[cout]] -> Packed."""
+    lib = _lib.load()
+    if not weight.is_cuda:
+        raise _lib.ScflowError("pack_weights: expected CUDA parameters (scflow_b200 has no CPU path)")
+    w = weight.detach().float().contiguous()
+    cout, cin, kh, kw = w.shape
+    bk = bk or choose_bk(cout)
+    nbytes = lib.scflow_conv_tc_packed_bytes(cout, cin, kh, kw, bk)
+    if nbytes == 0:
+        raise _lib.ScflowError(f"conv_tc: unsupported filter {tuple(w.shape)}")
+    out = torch.empty(nbytes // 2, device=w.device, dtype=torch.bfloat16)
+    sc = None if scale is None else scale.detach().float().contiguous()
+    with _timed("scflow_conv_tc_pack_weights"):
+        rc = lib.scflow_conv_tc_pack_weights(_ptr(w), _ptr(sc), _ptr(out), cout, cin, kh, kw, bk, _stream())
+    _lib.check(rc, "scflow_conv_tc_pack_weights")
+    cpad = _rup(cout, 32) + 32
+    b = torch.zeros(cpad, device=w.device, dtype=torch.float32)
+    if bias is not None:
+        b[:cout] = bias.detach().float()
+    s = (stride, stride) if isinstance(stride, int) else tuple(stride)
+    p = (padding, padding) if isinstance(padding, int) else tuple(padding)
+    if s[0] != s[1]:
+        raise _lib.ScflowError("conv_tc: anisotropic stride")
+    return Packed(out, b if bias is not None else None, cout, cin, kh, kw, s[0], p[0], p[1], bk)
+
+
+def _key(*tensors):
+    return tuple((t.data_ptr(), t._version) for t in tensors if t is not None)
+
+
+def packed_conv(conv: nn.Conv2d, bn: Optional[nn.BatchNorm2d] = None, with_bias: bool = True,
+                tag: str = "") -> Packed:
+    """Cached pack of an nn.Conv2d, optionally with an eval BatchNorm folded in (y = conv*scale + shift)."""
+    ts = [conv.weight, conv.bias]
+    if bn is not None:
+        ts += [bn.weight, bn.bias, bn.running_mean, bn.running_var]
+    key = (_key(*ts), with_bias)
+    cache = conv.__dict__.setdefault("_scflow_ctc", {})
+    hit = cache.get(tag)
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    if conv.groups != 1 or conv.dilation != (1, 1):
+        raise _lib.ScflowError("conv_tc: groups / dilation are not supported")
+    with torch.no_grad():
+        if bn is not None:
+            scale = bn.weight.float() * torch.rsqrt(bn.running_var.float() + bn.eps)
+            b0 = conv.bias.float() if conv.bias is not None else 0.0
+            shift = bn.bias.float() + (b0 - bn.running_mean.float()) * scale
+            pk = pack_weights(conv.weight, shift, conv.stride, conv.padding, scale=scale)
+        else:
+            pk = pack_weights(conv.weight, conv.bias if with_bias else None, conv.stride, conv.padding)
+    cache[tag] = (key, pk)
+    return pk
+
+
+def out_hw(pk: Packed, h: int, w: int):
+    return (h + 2 * pk.pad_h - pk.kh) // pk.stride + 1, (w + 2 * pk.pad_w - pk.kw) // pk.stride + 1
+
+
+def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = None,
+         res_f32: Optional[torch.Tensor] = None, out: Optional[Split] = None,
+         out_f32: Optional[torch.Tensor] = None, out_planar: Optional[torch.Tensor] = None,
+         planar_tf32: bool = False, f32_tf32: bool = False, stats: Optional[torch.Tensor] = None, want: str = "split",
+         view=None):
+    """One convolution launch.  x: Split (n, h, w, cin).  Outputs: `out` (Split), `out_f32` (n, OH, OW, >=cout)
+    fp32 channels-last (may be a channel slice of a wider buffer), `out_planar` (n, cout, OH, OW); when none is
+    given one is allocated according to `want` ("split" | "f32" | "planar").  `view` = (h, w, cin, lo_off,
+    stride_w, stride_h, stride_n) overrides how the input buffer is addressed (the stem's overlapped window
+    view).  Returns the output object(s) in the order split, f32, planar (only those produced)."""
+    lib = _lib.load()
+    n, h, w = x.shape
+    cin = x.c
+    lo_off, sw, sh, sn = x.cp, x.pitch, w * x.pitch, h * w * x.pitch
+    if view is not None:
+        h, w, cin, lo_off, sw, sh, sn = view
+    if cin != pk.cin:
+        raise _lib.ScflowError(f"conv_tc: input has {cin} channels, the filter takes {pk.cin}")
+    oh, ow = out_hw(pk, h, w)
+    dev = x.buf.device
+    if out is None and out_f32 is None and out_planar is None:
+        if want == "split":
+            out = alloc_split(n, oh, ow, pk.cout, dev)
+        elif want == "f32":
+            out_f32 = torch.empty((n, oh, ow, _rup(pk.cout, 8)), device=dev, dtype=torch.float32)
+        else:
+            out_planar = torch.empty((n, _rup(pk.cout, 8), oh, ow), device=dev, dtype=torch.float32)
+    d = _Desc()
+    d.n, d.h, d.w, d.cin, d.cout = n, h, w, cin, pk.cout
+    d.kh, d.kw, d.stride, d.pad_h, d.pad_w, d.bk = pk.kh, pk.kw, pk.stride, pk.pad_h, pk.pad_w, pk.bk
+    d.x = x.hi_ptr()
+    d.x_lo_off, d.x_stride_w, d.x_stride_h, d.x_stride_n = lo_off, sw, sh, sn
+    d.wpack = pk.w.data_ptr()
+    d.bias = pk.bias.data_ptr() if pk.bias is not None else None
+    d.relu = int(relu)
+    c8 = _rup(pk.cout, 8)
+    if res is not None:
+        assert tuple(res.shape) == (n, oh, ow) and res.c >= pk.cout
+        d.res_split, d.res_pitch, d.res_lo = res.hi_ptr(), res.pitch, res.cp
+    if res_f32 is not None:
+        assert res_f32.shape[:3] == (n, oh, ow) and res_f32.stride(3) == 1 and res_f32.dtype == torch.float32
+        d.res_f32, d.resf_pitch = res_f32.data_ptr(), res_f32.stride(2)
+    if out is not None:
+        assert tuple(out.shape) == (n, oh, ow) and out.off + c8 <= out.cp, (out.shape, (n, oh, ow), out.off, c8, out.cp)
+        d.out_split, d.out_pitch, d.out_lo = out.hi_ptr(), out.pitch, out.cp
+    if out_f32 is not None:
+        assert out_f32.shape[:3] == (n, oh, ow) and out_f32.shape[3] >= c8 and out_f32.stride(3) == 1
+        assert out_f32.stride(1) == ow * out_f32.stride(2) and out_f32.stride(0) == oh * out_f32.stride(1)
+        d.out_f32, d.outf_pitch, d.f32_tf32 = out_f32.data_ptr(), out_f32.stride(2), int(f32_tf32)
+    if out_planar is not None:
+        assert out_planar.shape == (n, c8, oh, ow) and out_planar.is_contiguous()
+        d.out_planar, d.planar_tf32 = out_planar.data_ptr(), int(planar_tf32)
+    if stats is not None:
+        assert stats.dtype == torch.float64 and stats.shape == (n, c8, 2) and stats.is_contiguous()
+        d.stats = stats.data_ptr()
+    flops = 2 * n * oh * ow * pk.cout * pk.cin * pk.kh * pk.kw
+    with _timed("scflow_conv_tc_fwd", 1, flops):
+        rc = lib.scflow_conv_tc_fwd(ctypes.byref(d), _stream())
+    _lib.check(rc, f"scflow_conv_tc_fwd({n}x{h}x{w}x{cin} -> {pk.cout}, {pk.kh}x{pk.kw}/{pk.stride})")
+    res_ = tuple(o for o in (out, out_f32, out_planar) if o is not None)
+    return res_[0] if len(res_) == 1 else res_
+
+
+def norm_apply(x: torch.Tensor, sums: torch.Tensor, *, relu: bool = True, eps: float = 1e-5,
+               res: Optional[Split] = None, res_raw: Optional[torch.Tensor] = None,
+               res_sums: Optional[torch.Tensor] = None, out: Optional[Split] = None,
+               out_f32: Optional[torch.Tensor] = None) -> Split:
+    """InstanceNorm (+ residual) + ReLU of a raw conv output x (n, h, w, c) fp32 with the statistics of the
+    conv epilogue -> split planes (scflow_norm_apply_split)."""
+    lib = _lib.load()
+    n, h, w, c = x.shape
+    assert x.is_contiguous() and sums.shape == (n, c, 2) and sums.dtype == torch.float64
+    if out is None:
+        out = alloc_split(n, h, w, c, x.device)
+    with _timed("scflow_norm_apply_split", 1, (8 + (4 if res is not None or res_raw is not None else 0)) * x.numel()):
+        rc = lib.scflow_norm_apply_split(
+            _ptr(x), _ptr(sums), None if res is None else ctypes.c_void_p(res.hi_ptr()),
+            0 if res is None else res.pitch, 0 if res is None else res.cp, _ptr(res_raw), _ptr(res_sums),
+            ctypes.c_void_p(out.hi_ptr()), out.pitch, out.cp, _ptr(out_f32), n, h * w, c, eps, int(relu), _stream())
+    _lib.check(rc, "scflow_norm_apply_split")
+    return out

@@ -1,0 +1,667 @@
+// conv_tc: the convolution family of the refiner on the 5th-generation tensor cores, with fp32-grade
+// results: scflow_conv_tc_fwd / scflow_conv_tc_pack_weights / scflow_split_bf16.
+//
+// Replaces every cuDNN convolution of the path: the RAFT encoders (models/encoder/raft_encoder.py:286-314,
+// models/backbone/resnet.py:12-92), MotionEncoder (models/decoder/raft_decoder.py:152-166), the flow / mask
+// heads (raft_decoder.py:256-294), the delta-flow / mask encoders (models/decoder/scflow_decoder.py:101-106)
+// and the pose-head convolutions (models/head/pose_head.py:108-150).
+//
+// Arithmetic: SPLIT-BF16 ("bf16x3").  TF32 tensor-core convolutions put the 8-iteration refinement 3-6e-4 rad
+// from the fp32 reference (budget 1e-4 rad); fp32 SIMT convolutions are 5x slower.  Here every operand v is
+// carried as two bf16 numbers hi = rn(v), lo = rn(v - hi) (16 significand bits, |v - hi - lo| <= 2^-18 |v|),
+// and a product is three tcgen05 kind::f16 MMAs into ONE fp32 TMEM accumulator:
+//     a.b ~= a_lo.b_hi + a_hi.b_lo + a_hi.b_hi          (dropped: a_lo.b_lo <= 2^-18 |a.b|)
+// i.e. ~40x more accurate than TF32 at 1.5x the tensor time of one TF32 MMA (bf16 runs at twice the TF32
+// rate), and the same bytes as fp32 everywhere (2 + 2 per element) in HBM, L2 and shared memory.
+//
+// Layout: activations are channels-last split planes: pixel p holds [hi C | lo C] bf16 (the producer's
+// epilogue writes both), weights are packed once to [tap][k-block][hi|lo][Cout_pad][BK] bf16.
+//
+// Kernel: persistent, warp-specialised implicit GEMM.  A tile is 128 output pixels (a TW x TH rectangle of
+// one image, or whole small images) x up to 256 output channels.  The convolution is never unrolled in
+// memory: for tap (ky,kx) the A operand of a k-block is ONE TMA box of the input at the tile's origin
+// shifted by the tap -- out-of-bounds zero fill is the zero padding, elementStrides is the conv stride --
+// landing in the K-major 128B-swizzled layout tcgen05 reads.  warp 0: TMA producer; warp 1: MMA issuer
+// (one elected thread); warps 2..9: epilogue (tcgen05.ld -> bias / residual / ReLU -> split-bf16, fp32
+// channels-last or planar fp32 stores, optional per-(image, channel) sum and sum of squares for
+// InstanceNorm).  The fp32 accumulator is double-buffered in TMEM so the epilogue of tile i runs under the
+// MMAs of tile i+1.
+#include "common.cuh"
+#include "tc_common.cuh"
+#include <cuda_bf16.h>
+#include <string.h>
+
+namespace scflow {
+namespace ctc {
+
+constexpr int BM = 128;                        // output pixels per tile (TMEM lanes)
+constexpr int NEPI = 8;                        // epilogue warps: two per TMEM lane quarter
+constexpr int THREADS = 64 + 32 * NEPI;
+constexpr int TMEM_COLS = 512;                 // two accumulator buffers of up to 256 columns
+constexpr int SMEM_LIMIT = 227 * 1024;
+
+struct Maps {
+  CUtensorMap a_hi, a_lo, w;
+};
+
+struct Params {
+  int n, OH, OW;
+  int kh, kw, stride, pad_y, pad_x;
+  int kblocks, ksteps_last;                    // k-blocks per tap; k-steps (16 channels) in the last one
+  int TW, TH, NI, tiles_x, tiles_y;            // tile rectangle, images per tile, tiles per image
+  int m_tiles, n_tiles, bn;                    // bn = output channels per tile (multiple of 16, <= 256)
+  int cout_pad;                                // n_tiles * bn = packed weight rows per (tap, k-block, part)
+  int cout_store;                              // channels written per pixel (multiple of 8, <= cout_pad)
+  int stages, stage_bytes, a_bytes, b_bytes;   // ring geometry (a_bytes, b_bytes: ONE part)
+  // epilogue
+  const float* bias;                           // [cout_pad] or null
+  int relu;
+  const __nv_bfloat16* res_split;              // residual in split layout (hi plane), or null
+  long long res_pitch; int res_lo;             // elements per pixel; offset of the lo plane
+  const float* res_f32; long long resf_pitch;  // or fp32 channels-last residual
+  __nv_bfloat16* out_split; long long out_pitch; int out_lo;
+  float* out_f32; long long outf_pitch; int f32_tf32;   // fp32 channels-last, optionally RN to TF32
+  float* out_planar; int planar_tf32;          // (N, cout_store, OH*OW) fp32, optionally RN to TF32
+  double* stats;                               // [n][cout_store][2] sum, sum of squares (pre-activation)
+};
+
+__device__ __forceinline__ uint32_t make_idesc_bf16(int m, int n) {
+  // kind::f16: c_format F32 (1) at [4,6), a_format / b_format BF16 (1) at [7,10) / [10,13), K-major both
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void mma_bf16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+__device__ __forceinline__ float rn_tf32(float v) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+  return __uint_as_float(u);
+}
+
+// v -> (hi, lo) bf16 pair; two values packed per 32-bit word (low half = first value)
+__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+  const __nv_bfloat16 ah = __float2bfloat16_rn(a), bh = __float2bfloat16_rn(b);
+  const __nv_bfloat16 al = __float2bfloat16_rn(a - __bfloat162float(ah));
+  const __nv_bfloat16 bl = __float2bfloat16_rn(b - __bfloat162float(bh));
+  hi = (uint32_t)__bfloat16_as_ushort(ah) | ((uint32_t)__bfloat16_as_ushort(bh) << 16);
+  lo = (uint32_t)__bfloat16_as_ushort(al) | ((uint32_t)__bfloat16_as_ushort(bl) << 16);
+}
+__device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+
+struct Tile {
+  int n0, oy0, ox0, nt;
+};
+__device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
+  Tile r;
+  r.nt = t % p.n_tiles;
+  int m = t / p.n_tiles;
+  const int per_img = p.tiles_x * p.tiles_y;
+  const int g = m / per_img;
+  m -= g * per_img;
+  const int ty = m / p.tiles_x;
+  r.n0 = g * p.NI;
+  r.oy0 = ty * p.TH;
+  r.ox0 = (m - ty * p.tiles_x) * p.TW;
+  return r;
+}
+
+template <int BK>   // channels per k-block: 64 (128-byte swizzle) or 32 (64-byte swizzle)
+__global__ void __launch_bounds__(THREADS, 1)
+conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p) {
+  constexpr uint32_t kLayout = BK == 64 ? 2u : 4u;          // SWIZZLE_128B : SWIZZLE_64B
+  constexpr uint32_t kSbo = BK == 64 ? 1024u : 512u;        // 8 rows of the swizzle atom
+  constexpr int MAX_STAGES = 8;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * p.stage_bytes);
+  uint64_t* full = bars;                         // [stages]
+  uint64_t* empty = bars + MAX_STAGES;           // [stages]
+  uint64_t* acc_full = bars + 2 * MAX_STAGES;    // [2]
+  uint64_t* acc_empty = acc_full + 2;            // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total = p.m_tiles * p.n_tiles;
+  const int taps = p.kh * p.kw;
+
+  if (warp == 0 && lane == 0) {
+    tc::tma_prefetch_desc(&maps.a_hi); tc::tma_prefetch_desc(&maps.a_lo); tc::tma_prefetch_desc(&maps.w);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < p.stages; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
+      for (int i = 0; i < 2; ++i) { tc::mbar_init(&acc_full[i], 1); tc::mbar_init(&acc_empty[i], NEPI); }
+      tc::fence_barrier_init();
+    }
+    __syncwarp();
+    tc::tmem_alloc(tmem_slot, TMEM_COLS);
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const Tile tl = decode_tile(p, t);
+        const int wrow0 = tl.nt * p.bn;
+        for (int tap = 0; tap < taps; ++tap) {
+          const int ky = tap / p.kw, kx = tap - ky * p.kw;
+          const int ix = tl.ox0 * p.stride + kx - p.pad_x, iy = tl.oy0 * p.stride + ky - p.pad_y;
+          for (int kb = 0; kb < p.kblocks; ++kb) {
+            tc::mbar_wait(&empty[stage], phase ^ 1);
+            uint8_t* st = smem + (size_t)stage * p.stage_bytes;
+            tc::mbar_expect_tx(&full[stage], (uint32_t)p.stage_bytes);
+            tc::tma_load_4d(&maps.a_hi, &full[stage], st, kb * BK, ix, iy, tl.n0);
+            tc::tma_load_4d(&maps.a_lo, &full[stage], st + p.a_bytes, kb * BK, ix, iy, tl.n0);
+            const int wrow = ((tap * p.kblocks + kb) * 2) * p.cout_pad + wrow0;
+            tc::tma_load_2d(&maps.w, &full[stage], st + 2 * p.a_bytes, 0, wrow);
+            tc::tma_load_2d(&maps.w, &full[stage], st + 2 * p.a_bytes + p.b_bytes, 0, wrow + p.cout_pad);
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(BM, p.bn);
+      const uint32_t smem0 = tc::smem_u32(smem);
+      int stage = 0; uint32_t phase = 0; uint32_t it = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+        const uint32_t buf = it & 1;
+        tc::mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
+        tc::tc_fence_after();
+        const uint32_t d = tmem_base + buf * 256u;
+        uint32_t acc = 0;
+        for (int tap = 0; tap < taps; ++tap) {
+          for (int kb = 0; kb < p.kblocks; ++kb) {
+            tc::mbar_wait(&full[stage], phase);
+            tc::tc_fence_after();
+            const uint32_t a_hi = smem0 + stage * p.stage_bytes;
+            const uint32_t a_lo = a_hi + p.a_bytes;
+            const uint32_t b_hi = a_lo + p.a_bytes;
+            const uint32_t b_lo = b_hi + p.b_bytes;
+            const int nks = kb == p.kblocks - 1 ? p.ksteps_last : BK / 16;
+            for (int ks = 0; ks < nks; ++ks) {
+              // K-major swizzled: 8-row groups kSbo bytes apart; a k-step (16 bf16) is +32 bytes
+              const uint64_t dah = tc::make_smem_desc(a_hi + ks * 32, 16, kSbo, kLayout);
+              const uint64_t dal = tc::make_smem_desc(a_lo + ks * 32, 16, kSbo, kLayout);
+              const uint64_t dbh = tc::make_smem_desc(b_hi + ks * 32, 16, kSbo, kLayout);
+              const uint64_t dbl = tc::make_smem_desc(b_lo + ks * 32, 16, kSbo, kLayout);
+              mma_bf16_ss(d, dal, dbh, idesc, acc);          // small terms first
+              mma_bf16_ss(d, dah, dbl, idesc, 1u);
+              mma_bf16_ss(d, dah, dbh, idesc, 1u);
+              acc = 1u;
+            }
+            tc::tc_commit(&empty[stage]);
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          }
+        }
+        tc::tc_commit(&acc_full[buf]);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (8 warps)
+    const int quarter = warp & 3;                           // TMEM lanes this warp may read
+    const int half = (warp - 2) >> 2;                       // which 32-column chunks it takes
+    const int m = quarter * 32 + lane;                      // TMEM lane = pixel of the tile
+    const int per_tile_img = p.TW * p.TH;
+    const int mi = m / per_tile_img, mr = m - mi * per_tile_img;
+    const int my = mr / p.TW, mx = mr - my * p.TW;
+    const int chunks = (p.bn + 31) >> 5;
+    const long long plane = (long long)p.OH * p.OW;
+    uint32_t it = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+      const Tile tl = decode_tile(p, t);
+      const uint32_t buf = it & 1;
+      const int n = tl.n0 + mi, oy = tl.oy0 + my, ox = tl.ox0 + mx;
+      const bool live = n < p.n;
+      const long long pix = ((long long)n * p.OH + oy) * p.OW + ox;
+      tc::mbar_wait(&acc_full[buf], (it >> 1) & 1);
+      tc::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * 256u;
+      for (int j = half; j < chunks; j += 2) {
+        float v[32];
+        tc::tmem_ld_32x32(taddr + j * 32, v);
+        tc::tmem_ld_wait();
+        const int c0 = tl.nt * p.bn + j * 32;               // first output channel of the chunk
+        int nv = p.cout_store - c0;                          // channels of it that are stored
+        nv = nv > 32 ? 32 : nv;
+        if (tl.nt * p.bn + p.bn - c0 < nv) nv = tl.nt * p.bn + p.bn - c0;
+        if (nv <= 0) continue;
+        if (p.bias) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (i < nv) v[i] += __ldg(p.bias + c0 + i);                      // bias is padded to cout_pad
+        }
+        if (p.stats) {
+          // per-(image, channel) sum and sum of squares over the warp's 32 pixels (all of one image:
+          // host guarantees OH*OW >= 32 with stats), butterfly so that lane i ends with channel i
+          float s[32], q[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) { s[i] = live ? v[i] : 0.f; q[i] = s[i] * s[i]; }
+#pragma unroll
+          for (int w = 16; w >= 1; w >>= 1) {
+#pragma unroll
+            for (int i = 0; i < w; ++i) {
+              const bool up = (lane & w) != 0;
+              const float ss = up ? s[i] : s[i + w], sq = up ? q[i] : q[i + w];
+              const float rs = __shfl_xor_sync(0xffffffffu, ss, w), rq = __shfl_xor_sync(0xffffffffu, sq, w);
+              s[i] = (up ? s[i + w] : s[i]) + rs;
+              q[i] = (up ? q[i + w] : q[i]) + rq;
+            }
+          }
+          // lane i now holds channel bitrev-free index: after the halving steps element 0 of lane l is channel l
+          const int nw = __shfl_sync(0xffffffffu, n, 0);
+          if (lane < nv && nw < p.n) {
+            double* dst = p.stats + ((long long)nw * p.cout_store + c0 + lane) * 2;
+            atomicAdd(dst, (double)s[0]);
+            atomicAdd(dst + 1, (double)q[0]);
+          }
+        }
+        if (!live) continue;
+        if (p.res_split) {
+          const uint4* rh = reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + c0);
+          const uint4* rl = reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + p.res_lo + c0);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            if (8 * k < nv) {
+              const uint4 a = __ldg(rh + k), b = __ldg(rl + k);
+              const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                v[8 * k + 2 * e] += bf_lo(aw[e]) + bf_lo(bw[e]);
+                v[8 * k + 2 * e + 1] += bf_hi(aw[e]) + bf_hi(bw[e]);
+              }
+            }
+          }
+        } else if (p.res_f32) {
+          const float4* rp = reinterpret_cast<const float4*>(p.res_f32 + pix * p.resf_pitch + c0);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            if (4 * k < nv) {
+              const float4 a = __ldg(rp + k);
+              v[4 * k] += a.x; v[4 * k + 1] += a.y; v[4 * k + 2] += a.z; v[4 * k + 3] += a.w;
+            }
+          }
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+        }
+        if (p.out_split) {
+          uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + c0);
+          uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + c0);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            if (8 * k < nv) {
+              uint4 h, l;
+              split2(v[8 * k], v[8 * k + 1], h.x, l.x);
+              split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
+              split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
+              split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
+              oh[k] = h;
+              ol[k] = l;
+            }
+          }
+        }
+        if (p.out_f32) {
+          float4* op = reinterpret_cast<float4*>(p.out_f32 + pix * p.outf_pitch + c0);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            if (4 * k < nv) {
+              op[k] = p.f32_tf32 ? make_float4(rn_tf32(v[4 * k]), rn_tf32(v[4 * k + 1]), rn_tf32(v[4 * k + 2]),
+                                               rn_tf32(v[4 * k + 3]))
+                                 : make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+            }
+          }
+        }
+        if (p.out_planar) {
+          float* op = p.out_planar + ((long long)n * p.cout_store + c0) * plane + (long long)oy * p.OW + ox;
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (i < nv) op[i * plane] = p.planar_tf32 ? rn_tf32(v[i]) : v[i];
+        }
+      }
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&acc_empty[buf]);
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc::tc_fence_after();
+    tc::tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// fp32 (Cout,Cin,KH,KW) [* scale[co]] -> packed bf16 rows [tap][kb][part][cout_pad][bk]
+__global__ void pack_weights_kernel(const float* __restrict__ w, const float* __restrict__ scale,
+                                    __nv_bfloat16* __restrict__ out, int cout, int cin, int taps, int kblocks,
+                                    int cout_pad, int bk, long long total) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int kk = (int)(i % bk);
+    long long r = i / bk;
+    const int co = (int)(r % cout_pad); r /= cout_pad;
+    const int part = (int)(r & 1); r >>= 1;
+    const int kb = (int)(r % kblocks);
+    const int tap = (int)(r / kblocks);
+    const int ci = kb * bk + kk;
+    float v = 0.f;
+    if (co < cout && ci < cin) {
+      v = w[((long long)co * cin + ci) * taps + tap];
+      if (scale) v *= scale[co];
+    }
+    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    out[i] = part == 0 ? hi : __float2bfloat16_rn(v - __bfloat162float(hi));
+  }
+}
+
+// fp32 channels-last (pixel pitch in_pitch) -> split planes; 8 channels per thread
+__global__ void split_bf16_kernel(const float* __restrict__ in, long long in_pitch, __nv_bfloat16* __restrict__ out,
+                                  long long out_pitch, int out_lo, int c8, int c_valid, long long pixels) {
+  const long long total = pixels * c8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long pix = i / c8;
+    const int c = (int)(i - pix * c8) * 8;
+    float v[8];
+    if (c + 8 <= c_valid) {
+      const float4 a = *reinterpret_cast<const float4*>(in + pix * in_pitch + c);
+      const float4 b = *reinterpret_cast<const float4*>(in + pix * in_pitch + c + 4);
+      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = c + e < c_valid ? in[pix * in_pitch + c + e] : 0.f;
+    }
+    uint4 h, l;
+    split2(v[0], v[1], h.x, l.x);
+    split2(v[2], v[3], h.y, l.y);
+    split2(v[4], v[5], h.z, l.z);
+    split2(v[6], v[7], h.w, l.w);
+    *reinterpret_cast<uint4*>(out + pix * out_pitch + c) = h;
+    *reinterpret_cast<uint4*>(out + pix * out_pitch + out_lo + c) = l;
+  }
+}
+
+// InstanceNorm (+ residual) + ReLU of a raw fp32 convolution output, from the statistics the convolution's
+// epilogue accumulated, written as split planes for the next convolution (resnet.py:64-92):
+//   y = act( (x - mean) * rstd  +  [ res (split planes)  |  (rx - rmean) * rrstd (raw + its own statistics) ] )
+// One pass: 4 B read (+4 B residual) and 4 B written per element.  Thread = 8 channels of a pixel.
+struct ApplyParams {
+  const float* x; const double* sums;
+  const __nv_bfloat16* res_split; long long res_pitch; int res_lo;
+  const float* res_raw; const double* res_sums;
+  __nv_bfloat16* out; long long out_pitch; int out_lo;
+  float* out_f32;
+  int P, C, relu; float eps;
+};
+constexpr int kApplyThreads = 256;
+constexpr int kApplyChunk = 256;     // pixels per CTA
+
+__device__ __forceinline__ void in_coeffs(const double* sums, int n, int C, int c, int P, float eps, float* sc,
+                                          float* sh) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const double su = sums[((size_t)n * C + c + j) * 2], sq = sums[((size_t)n * C + c + j) * 2 + 1];
+    const double mean = su / P;
+    const double var = fmax(sq / P - mean * mean, 0.0);       // biased, as F.instance_norm
+    const float rstd = 1.0f / sqrtf((float)var + eps);
+    sc[j] = rstd;
+    sh[j] = -(float)mean * rstd;
+  }
+}
+
+__global__ void __launch_bounds__(kApplyThreads)
+norm_apply_split_kernel(const ApplyParams p) {
+  const int groups = p.C >> 3;
+  const int lanes = kApplyThreads / groups;
+  const int cg = threadIdx.x % groups, pl = threadIdx.x / groups;
+  if (pl >= lanes) return;
+  const int n = blockIdx.y;
+  const int p0 = blockIdx.x * kApplyChunk, p1 = min(p0 + kApplyChunk, p.P);
+  const int c = 8 * cg;
+  float sc[8], sh[8], rsc[8], rsh[8];
+  in_coeffs(p.sums, n, p.C, c, p.P, p.eps, sc, sh);
+  if (p.res_raw) in_coeffs(p.res_sums, n, p.C, c, p.P, p.eps, rsc, rsh);
+  for (int px = p0 + pl; px < p1; px += lanes) {
+    const size_t pix = (size_t)n * p.P + px;
+    const float4 a = *reinterpret_cast<const float4*>(p.x + pix * p.C + c);
+    const float4 b = *reinterpret_cast<const float4*>(p.x + pix * p.C + c + 4);
+    float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], sc[j], sh[j]);
+    if (p.res_raw) {
+      const float4 ra = *reinterpret_cast<const float4*>(p.res_raw + pix * p.C + c);
+      const float4 rb = *reinterpret_cast<const float4*>(p.res_raw + pix * p.C + c + 4);
+      const float r[8] = {ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += fmaf(r[j], rsc[j], rsh[j]);
+    } else if (p.res_split) {
+      const uint4 h = *reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + c);
+      const uint4 l = *reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + p.res_lo + c);
+      const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        v[2 * e] += bf_lo(hw[e]) + bf_lo(lw[e]);
+        v[2 * e + 1] += bf_hi(hw[e]) + bf_hi(lw[e]);
+      }
+    }
+    if (p.relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+    }
+    uint4 h, l;
+    split2(v[0], v[1], h.x, l.x);
+    split2(v[2], v[3], h.y, l.y);
+    split2(v[4], v[5], h.z, l.z);
+    split2(v[6], v[7], h.w, l.w);
+    *reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + c) = h;
+    *reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + p.out_lo + c) = l;
+    if (p.out_f32) {
+      *reinterpret_cast<float4*>(p.out_f32 + pix * p.C + c) = make_float4(v[0], v[1], v[2], v[3]);
+      *reinterpret_cast<float4*>(p.out_f32 + pix * p.C + c + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
+  }
+}
+
+static bool encode_bf16_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
+                            const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr, int bk) {
+  tc::EncodeTiledFn fn = tc::get_encode_tiled();
+  if (!fn) return false;
+  cuuint64_t gdim[5], gstr[4];
+  cuuint32_t bdim[5], es[5];
+  for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bdim[i] = box[i]; es[i] = estr ? estr[i] : 1; }
+  for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr,
+                  bdim, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  bk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+static int cout_pad_of(int cout, int* bn, int* n_tiles) {
+  int c16 = (cout + 15) / 16 * 16;
+  if (c16 <= 256) { *bn = c16; *n_tiles = 1; return c16; }
+  *n_tiles = (c16 + 255) / 256;
+  // equal tiles, multiples of 16
+  int b = ((c16 + *n_tiles - 1) / *n_tiles + 15) / 16 * 16;
+  *bn = b;
+  return b * *n_tiles;
+}
+
+}  // namespace ctc
+}  // namespace scflow
+
+using namespace scflow;
+
+extern "C" size_t scflow_conv_tc_packed_bytes(int cout, int cin, int kh, int kw, int bk) {
+  if (cout <= 0 || cin <= 0 || kh <= 0 || kw <= 0 || (bk != 64 && bk != 32)) return 0;
+  int bn, nt;
+  const int cp = ctc::cout_pad_of(cout, &bn, &nt);
+  const int kblocks = (cin + bk - 1) / bk;
+  return (size_t)kh * kw * kblocks * 2 * cp * bk * sizeof(__nv_bfloat16);
+}
+
+extern "C" int scflow_conv_tc_pack_weights(const float* w, const float* scale, void* packed, int cout, int cin,
+                                           int kh, int kw, int bk, void* stream) {
+  if (!w || !packed) return SCFLOW_E_NULL;
+  const size_t bytes = scflow_conv_tc_packed_bytes(cout, cin, kh, kw, bk);
+  if (bytes == 0) return SCFLOW_E_BAD_SHAPE;
+  int bn, nt;
+  const int cp = ctc::cout_pad_of(cout, &bn, &nt);
+  const int kblocks = (cin + bk - 1) / bk;
+  const long long total = (long long)(bytes / sizeof(__nv_bfloat16));
+  const int blocks = (int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096);
+  ctc::pack_weights_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+      w, scale, static_cast<__nv_bfloat16*>(packed), cout, cin, kh * kw, kblocks, cp, bk, total);
+  return check_launch();
+}
+
+extern "C" int scflow_split_bf16(const float* in, long long in_pitch, void* out, long long out_pitch, int out_lo,
+                                 int channels, long long pixels, void* stream) {
+  if (!in || !out) return SCFLOW_E_NULL;
+  if (channels <= 0 || pixels < 0 || (out_pitch % 8) || (out_lo % 8)) return SCFLOW_E_BAD_SHAPE;
+  if (!aligned16(out)) return SCFLOW_E_MISALIGNED;
+  if (pixels == 0) return SCFLOW_OK;
+  const int c8 = (channels + 7) / 8;
+  // the vector path reads float4s: needs an aligned base and pitch; otherwise every group is the tail
+  const bool vec = aligned16(in) && (in_pitch % 4) == 0;
+  const long long total = pixels * c8;
+  const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  ctc::split_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+      in, in_pitch, static_cast<__nv_bfloat16*>(out), out_pitch, out_lo, c8, vec ? channels : 0, pixels);
+  return check_launch();
+}
+
+extern "C" int scflow_norm_apply_split(const float* x, const double* sums, const void* res_split, long long res_pitch,
+                                       int res_lo, const float* res_raw, const double* res_sums, void* out,
+                                       long long out_pitch, int out_lo, float* out_f32, int n, int P, int C,
+                                       float eps, int relu, void* stream) {
+  using namespace scflow::ctc;
+  if (!x || !sums || !out) return SCFLOW_E_NULL;
+  if ((res_raw == nullptr) != (res_sums == nullptr)) return SCFLOW_E_NULL;
+  if (n <= 0 || P <= 0 || C < 8 || (C & 7) || (C >> 3) > kApplyThreads || n > 65535) return SCFLOW_E_BAD_SHAPE;
+  if (!aligned16(x) || !aligned16(out) || !aligned16(res_split) || !aligned16(res_raw) || !aligned16(out_f32) ||
+      (out_pitch % 8) || (out_lo % 8) || (res_split && ((res_pitch % 8) || (res_lo % 8))))
+    return SCFLOW_E_MISALIGNED;
+  ApplyParams p{x, sums, static_cast<const __nv_bfloat16*>(res_split), res_pitch, res_lo, res_raw, res_sums,
+                static_cast<__nv_bfloat16*>(out), out_pitch, out_lo, out_f32, P, C, relu, eps};
+  dim3 grid((P + kApplyChunk - 1) / kApplyChunk, n);
+  norm_apply_split_kernel<<<grid, kApplyThreads, 0, (cudaStream_t)stream>>>(p);
+  return check_launch();
+}
+
+extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
+  using namespace scflow::ctc;
+  if (!d || !d->x || !d->wpack) return SCFLOW_E_NULL;
+  if (d->bk != 64 && d->bk != 32) return SCFLOW_E_BAD_SHAPE;
+  if (d->n <= 0 || d->h <= 0 || d->w <= 0 || d->cin <= 0 || d->cout <= 0 || d->kh <= 0 || d->kw <= 0 ||
+      d->stride < 1 || d->stride > 2 || d->kh * d->kw > 64)
+    return SCFLOW_E_BAD_SHAPE;
+  Params p;
+  memset(&p, 0, sizeof(p));
+  p.n = d->n;
+  p.OH = (d->h + 2 * d->pad_h - d->kh) / d->stride + 1;
+  p.OW = (d->w + 2 * d->pad_w - d->kw) / d->stride + 1;
+  if (p.OH <= 0 || p.OW <= 0) return SCFLOW_E_BAD_SHAPE;
+  p.kh = d->kh; p.kw = d->kw; p.stride = d->stride; p.pad_y = d->pad_h; p.pad_x = d->pad_w;
+  // tile rectangle: 128 output pixels
+  if (p.OW >= BM) {
+    if (p.OW % BM) return SCFLOW_E_BAD_SHAPE;
+    p.TW = BM; p.TH = 1; p.NI = 1;
+  } else {
+    if (BM % p.OW) return SCFLOW_E_BAD_SHAPE;
+    p.TW = p.OW;
+    const int rows = BM / p.OW;
+    if (p.OH >= rows) {
+      if (p.OH % rows) return SCFLOW_E_BAD_SHAPE;
+      p.TH = rows; p.NI = 1;
+    } else {
+      if (rows % p.OH) return SCFLOW_E_BAD_SHAPE;
+      p.TH = p.OH; p.NI = rows / p.OH;
+    }
+  }
+  p.tiles_x = p.OW / p.TW; p.tiles_y = p.OH / p.TH;
+  const int groups = (p.n + p.NI - 1) / p.NI;
+  p.m_tiles = groups * p.tiles_x * p.tiles_y;
+  p.cout_pad = cout_pad_of(d->cout, &p.bn, &p.n_tiles);
+  p.cout_store = (d->cout + 7) / 8 * 8;
+  const int bk = d->bk;
+  p.kblocks = (d->cin + bk - 1) / bk;
+  p.ksteps_last = ((d->cin - (p.kblocks - 1) * bk) + 15) / 16;
+  p.a_bytes = BM * bk * 2;
+  p.b_bytes = p.bn * bk * 2;
+  p.stage_bytes = 2 * (p.a_bytes + p.b_bytes);
+  p.stages = (SMEM_LIMIT - 2048) / p.stage_bytes;
+  if (p.stages > 8) p.stages = 8;
+  if (p.stages < 2) return SCFLOW_E_BAD_SHAPE;
+  const size_t smem_bytes = 1024 + (size_t)p.stages * p.stage_bytes + 256;
+  // epilogue
+  p.bias = d->bias; p.relu = d->relu;
+  p.res_split = static_cast<const __nv_bfloat16*>(d->res_split); p.res_pitch = d->res_pitch; p.res_lo = d->res_lo;
+  p.res_f32 = d->res_f32; p.resf_pitch = d->resf_pitch;
+  p.out_split = static_cast<__nv_bfloat16*>(d->out_split); p.out_pitch = d->out_pitch; p.out_lo = d->out_lo;
+  p.out_f32 = d->out_f32; p.outf_pitch = d->outf_pitch; p.f32_tf32 = d->f32_tf32;
+  p.out_planar = d->out_planar; p.planar_tf32 = d->planar_tf32;
+  p.stats = d->stats;
+  if (!p.out_split && !p.out_f32 && !p.out_planar) return SCFLOW_E_NULL;
+  if (p.stats && p.OH * p.OW < 32) return SCFLOW_E_BAD_SHAPE;
+  if ((p.out_split && (!aligned16(p.out_split) || (p.out_pitch % 8) || (p.out_lo % 8))) ||
+      (p.out_f32 && (!aligned16(p.out_f32) || (p.outf_pitch % 4))) ||
+      (p.res_split && (!aligned16(p.res_split) || (p.res_pitch % 8) || (p.res_lo % 8))) ||
+      (p.res_f32 && (!aligned16(p.res_f32) || (p.resf_pitch % 4))) || !aligned16(d->x) || !aligned16(d->wpack) ||
+      (d->x_lo_off % 8) || (d->x_stride_w % 8) || (d->x_stride_h % 8) || (d->x_stride_n % 8))
+    return SCFLOW_E_MISALIGNED;
+
+  Maps maps;
+  {
+    const uint64_t dims[4] = {(uint64_t)d->cin, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
+    const uint64_t strides[3] = {(uint64_t)d->x_stride_w * 2, (uint64_t)d->x_stride_h * 2,
+                                 (uint64_t)d->x_stride_n * 2};
+    const uint32_t box[4] = {(uint32_t)bk, (uint32_t)((p.TW - 1) * p.stride + 1),
+                             (uint32_t)((p.TH - 1) * p.stride + 1), (uint32_t)p.NI};
+    const uint32_t es[4] = {1, (uint32_t)p.stride, (uint32_t)p.stride, 1};
+    const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(d->x);
+    if (!encode_bf16_map(&maps.a_hi, xb, 4, dims, strides, box, es, bk) ||
+        !encode_bf16_map(&maps.a_lo, xb + d->x_lo_off, 4, dims, strides, box, es, bk))
+      return SCFLOW_E_DRIVER;
+    const uint64_t wd[2] = {(uint64_t)bk, (uint64_t)d->kh * d->kw * p.kblocks * 2 * p.cout_pad};
+    const uint64_t ws[1] = {(uint64_t)bk * 2};
+    const uint32_t wb[2] = {(uint32_t)bk, (uint32_t)p.bn};
+    if (!encode_bf16_map(&maps.w, d->wpack, 2, wd, ws, wb, nullptr, bk)) return SCFLOW_E_DRIVER;
+  }
+  int sms = 0, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (sms <= 0) sms = 148;
+  const int total = p.m_tiles * p.n_tiles;
+  const int grid = total < sms ? total : sms;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (bk == 64) {
+    cudaFuncSetAttribute(conv_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    conv_tc_kernel<64><<<grid, THREADS, smem_bytes, st>>>(maps, p);
+  } else {
+    cudaFuncSetAttribute(conv_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    conv_tc_kernel<32><<<grid, THREADS, smem_bytes, st>>>(maps, p);
+  }
+  return check_launch();
+}

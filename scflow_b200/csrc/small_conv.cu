@@ -14,6 +14,7 @@
 //
 // Exact fp32 accumulation (tighter than the TF32 cuDNN kernels they replace).
 #include "common.cuh"
+#include <cuda_bf16.h>
 #include <stdlib.h>
 
 namespace scflow {
@@ -485,8 +486,60 @@ stem_s2d_kernel(const float* __restrict__ x, float4* __restrict__ out, int n, in
     for (int k = 0; k < 4; ++k) o[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
   }
 }
+
+// the same image as two bf16 planes (hi = rn(v), lo = rn(v - hi)), each (n, H/2+3, W/2+3, 16): the operand
+// format of the tensor-core convolution family (conv_tc.cu), which reads four x-neighbours (64 contiguous
+// channels) per filter row through an overlapped-window tensor map
+__global__ void __launch_bounds__(256)
+stem_s2d_split_kernel(const float* __restrict__ x, uint4* __restrict__ out, int n, int c, int H, int W) {
+  const int Wo = W / 2 + 3, Ho = H / 2 + 3;
+  const long long total = (long long)n * Ho * Wo;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int xo = (int)(i % Wo);
+    const long long r = i / Wo;
+    const int yo = (int)(r % Ho), img = (int)(r / Ho);
+    const int Y = yo - 2, X = xo - 2;
+    float v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = 0.0f;
+    if (Y >= 0 && Y < H / 2 && X >= 0 && X < W / 2) {
+      for (int ch = 0; ch < c; ++ch) {
+        const float* p = x + (((size_t)img * c + ch) * H + 2 * Y) * W + 2 * X;
+        const float2 a = __ldg(reinterpret_cast<const float2*>(p));
+        const float2 b = __ldg(reinterpret_cast<const float2*>(p + W));
+        v[4 * ch + 0] = a.x; v[4 * ch + 1] = a.y; v[4 * ch + 2] = b.x; v[4 * ch + 3] = b.y;
+      }
+    }
+    uint32_t hi[8], lo[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const __nv_bfloat16 ah = __float2bfloat16_rn(v[2 * k]), bh = __float2bfloat16_rn(v[2 * k + 1]);
+      const __nv_bfloat16 al = __float2bfloat16_rn(v[2 * k] - __bfloat162float(ah));
+      const __nv_bfloat16 bl = __float2bfloat16_rn(v[2 * k + 1] - __bfloat162float(bh));
+      hi[k] = (uint32_t)__bfloat16_as_ushort(ah) | ((uint32_t)__bfloat16_as_ushort(bh) << 16);
+      lo[k] = (uint32_t)__bfloat16_as_ushort(al) | ((uint32_t)__bfloat16_as_ushort(bl) << 16);
+    }
+    uint4* oh = out + i * 2;
+    uint4* ol = out + (total + i) * 2;
+    oh[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]); oh[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+    ol[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]); ol[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+  }
+}
 }  // namespace sc
 }  // namespace scflow
+
+extern "C" int scflow_stem_s2d_split_fwd(const float* x, void* out, int n, int c, int h, int w, void* stream) {
+  using namespace scflow;
+  if (!x || !out) return SCFLOW_E_NULL;
+  if (n <= 0 || c <= 0 || c > 4 || h <= 0 || w <= 0 || (h & 1) || (w & 1)) return SCFLOW_E_BAD_SHAPE;
+  if (!aligned16(out) || (reinterpret_cast<uintptr_t>(x) & 7u)) return SCFLOW_E_MISALIGNED;
+  const long long total = (long long)n * (h / 2 + 3) * (w / 2 + 3);
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  sc::stem_s2d_split_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<uint4*>(out), n, c, h, w);
+  return check_launch();
+}
 
 extern "C" int scflow_stem_s2d_fwd(const float* x, float* out, int n, int c, int h, int w, void* stream) {
   using namespace scflow;

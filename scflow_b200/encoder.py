@@ -12,30 +12,16 @@ from . import ops
 from .registry import register
 
 
-# ------------------------------------------------------------------ fused inference path
-# Convolutions stay on cuDNN (SURVEY 8f-3 "next") but run channels-last end to end, and every
-# norm + ReLU (+ residual add) is two launches of our HBM-bound kernels (csrc/norm_act.cu)
-# instead of the reference's bias add_ / batch_norm / relu_ / add / relu_ chain.
-def _conv_cl(conv: nn.Conv2d, x: torch.Tensor, with_bias: bool = False) -> torch.Tensor:
-    """cuDNN convolution on a channels-last (N,C,H,W)-shaped tensor; the filter is re-laid once."""
-    w = conv.weight
-    if not w.is_contiguous(memory_format=torch.channels_last):
-        conv.weight.data = w.data.contiguous(memory_format=torch.channels_last)
-        w = conv.weight
-    y = F.conv2d(x, w, conv.bias if with_bias else None, conv.stride, conv.padding)
-    return y.contiguous(memory_format=torch.channels_last)      # no-op when cuDNN kept the layout
-
-
-def _s2d_enabled(conv: nn.Conv2d, x: torch.Tensor) -> bool:
-    """The 7x7 stride-2 stem on 3 channels is the one layer cuDNN has no tensor-core kernel for
-    (it runs a generic 3-channel implicit GEMM: 416 us per 64 crops, 7 % of the step).  Rewritten
-    as the equivalent 4x4 stride-1 convolution on the 2x2 space-to-depth input (12 -> 16 channels)
-    it takes cuDNN's regular TF32 path.  Only where TF32 convolutions are allowed (the mode the
-    reference itself runs in on a GPU): the strict-fp32 parity mode keeps the filter as shipped."""
-    import os
-    return (os.environ.get("SCFLOW_STEM_S2D", "1") != "0" and torch.backends.cudnn.allow_tf32
-            and conv.kernel_size == (7, 7) and conv.stride == (2, 2) and conv.padding == (3, 3)
-            and x.shape[1] <= 4 and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0)
+# ------------------------------------------------------------------ tensor-core inference path
+# Every convolution of the encoders runs on scflow_conv_tc_fwd (split-bf16, three tcgen05 MMAs per product:
+# fp32-grade results, csrc/conv_tc.cu) with channels-last split-plane activations end to end:
+#   * eval BatchNorm is folded into the packed filters, so a BN block is three launches (conv+bias+ReLU,
+#     [1x1 down-sample], conv+bias+residual+ReLU) and nothing else;
+#   * an InstanceNorm layer is the convolution (raw fp32 out, per-(image, channel) sum / sum of squares
+#     accumulated by its epilogue) + ONE normalise(+residual)+ReLU pass that writes the next operand;
+#   * the 7x7 stride-2 stem on 3 channels is the equivalent 4x4 stride-1 convolution on the 2x2 space-to-depth
+#     image (12 -> 16 channels), read as 4 filter rows of 64 contiguous channels (four x-neighbours).
+from . import convtc as C
 
 
 def _s2d_filter(w: torch.Tensor) -> torch.Tensor:
@@ -43,91 +29,78 @@ def _s2d_filter(w: torch.Tensor) -> torch.Tensor:
     k' = k + 1 = 2a + b lands on phase b at offset a - 2 (taps padded to 8 with a leading zero)."""
     o, c = w.shape[:2]
     wp = F.pad(w, (1, 0, 1, 0)).reshape(o, c, 4, 2, 4, 2).permute(0, 1, 3, 5, 2, 4).reshape(o, 4 * c, 4, 4)
-    return F.pad(wp, (0, 0, 0, 0, 0, 16 - 4 * c)).contiguous(memory_format=torch.channels_last)
+    return F.pad(wp, (0, 0, 0, 0, 0, 16 - 4 * c))
 
 
-_S2D_LAST = [None, None, None]     # (weakref to the image tensor, its version, transformed tensor)
+class StemInput:
+    """2x2 space-to-depth image of a planar (N,C<=4,H,W) batch as two bf16 planes (scflow_stem_s2d_split_fwd);
+    computed once per image batch and shared by the encoders that read it (scflow_refiner.py:84-106 feeds the
+    rendered images to both the feature and the context encoder)."""
+
+    def __init__(self, x: torch.Tensor):
+        n, c, h, w = x.shape
+        if not x.is_cuda or x.dtype != torch.float32 or c > 4 or h % 2 or w % 2:
+            raise ops._lib.ScflowError(f"encoder stem: expected a CUDA fp32 (N,<=4,even,even) batch, got "
+                                       f"{tuple(x.shape)} {x.dtype} {x.device}")
+        self.n, self.h2, self.w2 = n, h // 2, w // 2
+        self.planes = ops.stem_s2d_split(x)                    # (2, n, h/2+3, w/2+3, 16) bf16
+
+    def split(self) -> "C.Split":
+        """The planes as a Split the conv launcher can address, plus the overlapped-window view."""
+        _, n, ho, wo, _ = self.planes.shape
+        buf = self.planes.view(2 * n, ho, wo, 16)               # only data_ptr / device are used with `view`
+        view = (ho, wo - 3, 64, n * ho * wo * 16, 16, wo * 16, ho * wo * 16)
+        return C.Split(buf, 64), view
 
 
-def _s2d_input(x: torch.Tensor) -> torch.Tensor:
-    """(N,C,H,W) -> channels-last (N,16,H/2+3,W/2+3): phases as channels (c*4 + 2*by + bx), zero
-    channels up to 16, and the stride-1 filter's (2,1) zero border written in -- one launch
-    (scflow_stem_s2d_fwd).  The feature and the context encoder are fed the same rendered images
-    (scflow_refiner.py:84-106): the last transform is kept and reused for the same, unmodified tensor."""
-    import weakref
-    ref, ver, val = _S2D_LAST
-    if ref is not None and ref() is x and ver == x._version and val.device == x.device:
-        return val
-    val = ops.stem_s2d(x)
-    _S2D_LAST[:] = [weakref.ref(x), x._version, val]
-    return val
-
-
-def _stem_cached(conv: nn.Conv2d, w: torch.Tensor) -> torch.Tensor:
-    key = (w.data_ptr(), w._version)
-    hit = conv.__dict__.get("_scflow_s2d")
+def _stem_pack(conv: nn.Conv2d, bn=None) -> "C.Packed":
+    ts = [conv.weight, conv.bias] + ([bn.weight, bn.bias, bn.running_mean, bn.running_var] if bn is not None else [])
+    key = C._key(*ts)
+    hit = conv.__dict__.get("_scflow_stem")
     if hit is not None and hit[0] == key:
         return hit[1]
+    if conv.kernel_size != (7, 7) or conv.stride != (2, 2) or conv.padding != (3, 3):
+        raise ops._lib.ScflowError("encoder stem: expected the 7x7 stride-2 pad-3 convolution")
     with torch.no_grad():
-        val = _s2d_filter(w.detach().float())
-    conv.__dict__["_scflow_s2d"] = (key, val)
-    return val
+        w = _s2d_filter(conv.weight.detach().float())                       # (O, 16, dy, dx)
+        w = w.permute(0, 3, 1, 2).reshape(w.shape[0], 64, 4, 1).contiguous()   # cin = dx*16 + ch, kh = dy
+        if bn is not None:
+            scale = bn.weight.float() * torch.rsqrt(bn.running_var.float() + bn.eps)
+            b0 = conv.bias.float() if conv.bias is not None else 0.0
+            shift = bn.bias.float() + (b0 - bn.running_mean.float()) * scale
+            pk = C.pack_weights(w, shift, 1, 0, scale=scale)
+        else:
+            pk = C.pack_weights(w, None, 1, 0)                 # InstanceNorm cancels the bias
+    conv.__dict__["_scflow_stem"] = (key, pk)
+    return pk
 
 
-def _nhwc(x: torch.Tensor) -> torch.Tensor:
-    return x.permute(0, 2, 3, 1)
+class _Stats:
+    """One zeroed fp64 buffer per encoder pass for the InstanceNorm statistics of all its layers."""
+
+    def __init__(self, n: int, device, floats: int):
+        self.buf = torch.zeros(floats, device=device, dtype=torch.float64)
+        self.n, self.used = n, 0
+
+    def take(self, c: int) -> torch.Tensor:
+        k = self.n * c * 2
+        out = self.buf[self.used:self.used + k].view(self.n, c, 2)
+        self.used += k
+        assert self.used <= self.buf.numel()
+        return out
 
 
-def _bn_affine(bn: nn.BatchNorm2d, bias):
-    """Eval BatchNorm2d folded with the preceding convolution bias: y = conv*scale + shift."""
-    key = tuple((t.data_ptr(), t._version) for t in (bn.weight, bn.bias, bn.running_mean, bn.running_var, bias)
-                if t is not None)
-    hit = bn.__dict__.get("_scflow_affine")
-    if hit is not None and hit[0] == key:
-        return hit[1]
-    with torch.no_grad():
-        scale = bn.weight.float() * torch.rsqrt(bn.running_var.float() + bn.eps)
-        b = bias.float() if bias is not None else 0.0
-        shift = bn.bias.float() + (b - bn.running_mean.float()) * scale
-        val = (scale.contiguous(), shift.contiguous())
-    bn.__dict__["_scflow_affine"] = (key, val)
-    return val
+def _plain_in(norm: nn.Module) -> None:
+    if not isinstance(norm, nn.InstanceNorm2d) or norm.affine or norm.track_running_stats:
+        raise NotImplementedError(f"{type(norm).__name__}(affine/track_running_stats) on the tensor-core path")
 
 
-def _bn_folded(conv: nn.Conv2d, bn: nn.BatchNorm2d):
-    """Eval BatchNorm2d folded INTO the preceding convolution: (w * scale[cout], shift) as a
-    channels-last filter + bias, so cuDNN's fused conv+bias(+residual)+ReLU kernels produce the
-    block's output in one launch.  Cached on the conv, keyed on every tensor involved."""
-    key = tuple((t.data_ptr(), t._version) for t in (conv.weight, conv.bias, bn.weight, bn.bias,
-                                                     bn.running_mean, bn.running_var) if t is not None)
-    hit = conv.__dict__.get("_scflow_folded")
-    if hit is not None and hit[0] == key:
-        return hit[1]
-    scale, shift = _bn_affine(bn, conv.bias)
-    with torch.no_grad():
-        w = (conv.weight.float() * scale.view(-1, 1, 1, 1)).contiguous(memory_format=torch.channels_last)
-    conv.__dict__["_scflow_folded"] = (key, (w, shift))
-    return w, shift
-
-
-def _side(norm: nn.Module, y: torch.Tensor, bias):
-    """Normalisation coefficients of conv output y (channels-last view): kwargs for ops.norm_act."""
-    if isinstance(norm, nn.InstanceNorm2d):
-        # the convolution bias cancels in (v - mean): it is never added
-        if norm.affine or norm.track_running_stats:
-            raise NotImplementedError("InstanceNorm2d(affine/track_running_stats) on the fused path")
-        return dict(sums=ops.chan_stats(y)), norm.eps
-    if isinstance(norm, nn.BatchNorm2d):
-        return dict(affine=_bn_affine(norm, bias)), norm.eps
-    raise NotImplementedError(type(norm))
-
-
-def _in_fused(norm: nn.Module) -> bool:
-    """Plain InstanceNorm2d layers take the one-launch cluster kernel (SCFLOW_IN_FUSED=0: the
-    statistics + normalise launch pair, kept as the cross-check)."""
-    import os
-    return (isinstance(norm, nn.InstanceNorm2d) and not norm.affine and not norm.track_running_stats
-            and os.environ.get("SCFLOW_IN_FUSED", "1") != "0")
+def _conv_raw(x, conv: nn.Conv2d, st: _Stats, view=None, pk=None):
+    """Convolution without bias (InstanceNorm cancels it) -> raw fp32 output + its statistics."""
+    pk = pk or C.packed_conv(conv, with_bias=False, tag="in")
+    sums = st.take(pk.cout)
+    raw = C.conv(x, pk, want="f32", stats=sums, view=view)
+    return raw, sums
 
 
 def _norm(kind: str, ch: int, postfix):
@@ -158,40 +131,24 @@ class BasicBlock(nn.Module):
             identity = self.downsample(x)
         return self.relu(out + identity)
 
-    def forward_fused(self, x: torch.Tensor) -> torch.Tensor:
-        """x, result: channels-last (N,C,H,W)-shaped tensors."""
+    def forward_tc(self, x, st):
+        """x, result: split-plane activations (convtc.Split); st: the pass's statistics pool."""
         n1, n2 = getattr(self, self.norm1_name), getattr(self, self.norm2_name)
         if isinstance(n1, nn.BatchNorm2d):
-            # eval BN folded into the filters: three cuDNN launches per block, no separate norm pass
-            w1, b1 = _bn_folded(self.conv1, n1)
-            w2, b2 = _bn_folded(self.conv2, n2)
-            o = torch.cudnn_convolution_relu(x, w1, b1, self.conv1.stride, self.conv1.padding, (1, 1), 1)
+            o = C.conv(x, C.packed_conv(self.conv1, bn=n1, tag="bn"), relu=True)
             idt = x
             if self.downsample is not None:
-                wd, bd = _bn_folded(self.downsample[0], self.downsample[1])
-                idt = F.conv2d(x, wd, bd, self.downsample[0].stride, self.downsample[0].padding)
-                idt = idt.contiguous(memory_format=torch.channels_last)
-            return torch.cudnn_convolution_add_relu(o, w2, idt, 1.0, b2, self.conv2.stride, self.conv2.padding,
-                                                    (1, 1), 1)
-        o = _conv_cl(self.conv1, x)
-        if _in_fused(n1):
-            ops.instnorm_act(_nhwc(o), relu=True, eps=n1.eps)
-        else:
-            kw, eps = _side(n1, _nhwc(o), self.conv1.bias)
-            ops.norm_act(_nhwc(o), relu=True, eps=eps, **kw)
-        o2 = _conv_cl(self.conv2, o)
-        if self.downsample is None and _in_fused(n2):
-            ops.instnorm_act(_nhwc(o2), res=_nhwc(x), relu=True, eps=n2.eps)
-            return o2
-        kw, eps = _side(n2, _nhwc(o2), self.conv2.bias)
-        if self.downsample is not None:
-            d = _conv_cl(self.downsample[0], x)
-            kr, _ = _side(self.downsample[1], _nhwc(d), self.downsample[0].bias)
-            kw.update({"res_" + k: v for k, v in kr.items()})
-            ops.norm_act(_nhwc(o2), res=_nhwc(d), relu=True, eps=eps, **kw)
-        else:
-            ops.norm_act(_nhwc(o2), res=_nhwc(x), relu=True, eps=eps, **kw)
-        return o2
+                idt = C.conv(x, C.packed_conv(self.downsample[0], bn=self.downsample[1], tag="bn"))
+            return C.conv(o, C.packed_conv(self.conv2, bn=n2, tag="bn"), relu=True, res=idt)
+        _plain_in(n1), _plain_in(n2)
+        raw, sums = _conv_raw(x, self.conv1, st)
+        o = C.norm_apply(raw, sums, relu=True, eps=n1.eps)
+        raw2, sums2 = _conv_raw(o, self.conv2, st)
+        if self.downsample is None:
+            return C.norm_apply(raw2, sums2, relu=True, eps=n2.eps, res=x)
+        _plain_in(self.downsample[1])
+        rawd, sumsd = _conv_raw(x, self.downsample[0], st)
+        return C.norm_apply(raw2, sums2, relu=True, eps=n2.eps, res_raw=rawd, res_sums=sumsd)
 
 
 def _res_layer(inplanes, planes, stride, norm):
@@ -226,44 +183,41 @@ class RAFTEncoder(nn.Module):
             inpl = planes
         self.conv2 = nn.Conv2d(128, out_channels, 1)
 
-    def _fused_ok(self, x: torch.Tensor) -> bool:
+    def forward(self, x: torch.Tensor, stem: "StemInput" = None, planar_tf32: bool = False) -> torch.Tensor:
+        """Inference (no autograd): the tensor-core path, CUDA only.  With autograd recording (training,
+        BASELINE.json configs[4]) the layers run as the nn.Modules they are, so that autograd supplies the
+        backward.  `stem`: a StemInput of x computed by the caller (shared between encoders);
+        `planar_tf32`: return the features NCHW-contiguous and rounded to the nearest TF32 -- the correlation
+        kernel's operand format -- instead of a channels-last tensor."""
         n1 = getattr(self, self.norm1_name)
-        if torch.is_grad_enabled() or not x.is_cuda or x.dtype != torch.float32:
-            return False
-        return isinstance(n1, nn.InstanceNorm2d) or not self.training
+        if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters())):
+            x = self.relu(n1(self.conv1(x)))
+            for name in self.res_layers:
+                x = getattr(self, name)(x)
+            return self.conv2(x)
+        if isinstance(n1, nn.BatchNorm2d) and self.training:
+            raise NotImplementedError("RAFTEncoder(BN) in train mode without autograd: no batch-statistics kernel")
+        return self.forward_tc(x, stem, planar_tf32)
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if self._fused_ok(x):
-            return self.forward_fused(x)
-        x = self.relu(getattr(self, self.norm1_name)(self.conv1(x)))
-        for name in self.res_layers:
-            x = getattr(self, name)(x)
-        return self.conv2(x)
-
-    def forward_fused(self, x: torch.Tensor) -> torch.Tensor:
-        """Inference path: same values as forward() (the IN-cancelled conv bias aside, a rounding-
-        level difference), channels-last activations, norms through csrc/norm_act.cu."""
+    def forward_tc(self, x: torch.Tensor, stem=None, planar_tf32: bool = False) -> torch.Tensor:
         n1 = getattr(self, self.norm1_name)
-        s2d = _s2d_enabled(self.conv1, x)
-        x = _s2d_input(x) if s2d else x.contiguous(memory_format=torch.channels_last)
+        stem = stem or StemInput(x)
+        xs, view = stem.split()
+        n = stem.n
+        st = None
         if isinstance(n1, nn.BatchNorm2d):
-            w1, b1 = _bn_folded(self.conv1, n1)
-            if s2d:
-                y = torch.cudnn_convolution_relu(x, _stem_cached(self.conv1, w1), b1, (1, 1), (0, 0), (1, 1), 1)
-            else:
-                y = torch.cudnn_convolution_relu(x, w1, b1, self.conv1.stride, self.conv1.padding, (1, 1), 1)
+            y = C.conv(xs, _stem_pack(self.conv1, n1), relu=True, view=view)
         else:
-            if s2d:
-                y = F.conv2d(x, _stem_cached(self.conv1, self.conv1.weight))
-                y = y.contiguous(memory_format=torch.channels_last)
-            else:
-                y = _conv_cl(self.conv1, x)
-            if _in_fused(n1):
-                ops.instnorm_act(_nhwc(y), relu=True, eps=n1.eps)
-            else:
-                kw, eps = _side(n1, _nhwc(y), self.conv1.bias)
-                ops.norm_act(_nhwc(y), relu=True, eps=eps, **kw)
+            _plain_in(n1)
+            st = _Stats(n, x.device, n * 2 * (64 * 5 + 96 * 5 + 128 * 5))
+            raw, sums = _conv_raw(xs, self.conv1, st, view=view, pk=_stem_pack(self.conv1))
+            y = C.norm_apply(raw, sums, relu=True, eps=n1.eps)
         for name in self.res_layers:
             for block in getattr(self, name):
-                y = block.forward_fused(y)
-        return _conv_cl(self.conv2, y, with_bias=True)
+                y = block.forward_tc(y, st)
+        pk = C.packed_conv(self.conv2)
+        if planar_tf32:
+            out = C.conv(y, pk, want="planar", planar_tf32=True)
+            out._scflow_planar_tf32 = True          # ops.corr_pyramid takes it as is
+            return out
+        return C.conv(y, pk, want="f32").permute(0, 3, 1, 2)     # NCHW-shaped view of channels-last memory

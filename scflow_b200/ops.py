@@ -82,6 +82,8 @@ def _planar_tf32(t: torch.Tensor, name: str) -> torch.Tensor:
     lib = _lib.load()
     if not t.is_cuda or t.dtype != torch.float32:
         _chk(t, name)
+    if getattr(t, "_scflow_planar_tf32", False) and t.is_contiguous():
+        return t        # the encoder's last convolution already wrote this format (encoder.forward_tc)
     n, c, h, w = t.shape
     out = torch.empty((n, c, h, w), device=t.device, dtype=torch.float32)
     if t.is_contiguous(memory_format=torch.channels_last) and not t.is_contiguous():
@@ -355,6 +357,19 @@ def stem_s2d(x: torch.Tensor) -> torch.Tensor:
         rc = lib.scflow_stem_s2d_fwd(_ptr(x), _ptr(out), n, c, h, w, _stream())
     _lib.check(rc, "scflow_stem_s2d_fwd")
     return out.permute(0, 3, 1, 2)
+
+
+def stem_s2d_split(x: torch.Tensor) -> torch.Tensor:
+    """The same space-to-depth image as two bf16 planes (2, N, H/2+3, W/2+3, 16), value = hi + lo: the
+    operand of the tensor-core stem convolution (scflow_stem_s2d_split_fwd)."""
+    lib = _lib.load()
+    x = _chk(x, "x")
+    n, c, h, w = x.shape
+    out = torch.empty((2, n, h // 2 + 3, w // 2 + 3, 16), device=x.device, dtype=torch.bfloat16)
+    with _timed("scflow_stem_s2d_split_fwd", 1, 4 * x.numel() + 2 * out.numel()):
+        rc = lib.scflow_stem_s2d_split_fwd(_ptr(x), _ptr(out), n, c, h, w, _stream())
+    _lib.check(rc, "scflow_stem_s2d_split_fwd")
+    return out
 
 
 def conv_small_cout(x: torch.Tensor, conv: torch.nn.Conv2d) -> torch.Tensor:

@@ -50,12 +50,19 @@ class SCFlowRefinerCore(nn.Module):
         assert self.cxt_channels == self.decoder.cxt_channels
 
     def extract_feat(self, render_images, real_images):
-        # (Running both image sets through the shared encoder as one 2N batch is 2.5 % faster, but cuDNN then
-        # picks other algorithms and the 512x512 fixture moves from 8.9e-5 to 1.04e-4 rad -- across the 1e-4
-        # budget -- so the two calls are kept)
-        real_feat = self.encoder(real_images)
-        render_feat = self.encoder(render_images)
-        cxt = self.context(render_images)
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            real_feat = self.encoder(real_images)                # training: nn.Module layers under autograd
+            render_feat = self.encoder(render_images)
+            cxt = self.context(render_images)
+        else:
+            # inference: tensor-core encoders; the rendered batch's space-to-depth stem input is computed once
+            # and read by both the feature and the context encoder (scflow_refiner.py:84-106); the features
+            # come back planar and TF32-rounded, the correlation kernel's operand format
+            from .encoder import StemInput
+            real_feat = self.encoder(real_images, planar_tf32=True)
+            stem = StemInput(render_images)
+            render_feat = self.encoder(render_images, stem=stem, planar_tf32=True)
+            cxt = self.context(render_images, stem=stem)
         h_feat, cxt_feat = torch.split(cxt, [self.h_channels, self.cxt_channels], dim=1)
         return render_feat, real_feat, torch.tanh(h_feat), torch.relu(cxt_feat)
 

@@ -1,0 +1,118 @@
+"""GPU tier: the split-bf16 tensor-core convolution family (csrc/conv_tc.cu) through the C ABI against
+ATen's convolution evaluated in fp64 on the CPU (what the reference's nn.Conv2d computes, models/
+encoder/raft_encoder.py:286-314, models/decoder/raft_decoder.py:152-166,256-294, models/head/pose_head.py:
+108-150).  Tolerance: 2e-5 of the output's max magnitude (three bf16 MMAs per product: ~2^-17 relative
+per product, fp32 accumulation); TF32 sits at ~5e-4 on the same inputs.  The tensor core adds into its
+fp32 accumulator with truncation, a drift of <= 2^-24 per MMA that grows with the number of accumulation
+steps (3 K / 16): the bound is widened by that amount for the deep filters."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from scflow_b200 import convtc as C
+
+DEV = "cuda"
+TOL = 2e-5
+
+
+def _ref(x, w, b, stride, pad, relu=False, res=None):
+    y = F.conv2d(x.double().permute(0, 3, 1, 2), w.double(), None if b is None else b.double(), stride, pad)
+    if res is not None:
+        y = y + res.double().permute(0, 3, 1, 2)
+    if relu:
+        y = torch.relu(y)
+    return y.permute(0, 2, 3, 1)
+
+
+def _err(got, want):
+    want = want.double()
+    return float((got.double().cpu() - want).abs().max() / want.abs().max().clamp_min(1e-30))
+
+
+CASES = [
+    # n, h, w, cin, cout, k, stride, pad, bk
+    (3, 32, 32, 64, 64, 3, 1, 1, 64),
+    (3, 32, 32, 64, 64, 3, 1, 1, 32),
+    (2, 32, 32, 64, 96, 3, 2, 1, 64),        # stride 2 through elementStrides
+    (2, 32, 32, 64, 96, 1, 2, 0, 64),        # 1x1 stride-2 downsample
+    (2, 16, 16, 96, 128, 3, 1, 1, 64),       # cin not a multiple of the k-block
+    (2, 32, 32, 128, 256, 1, 1, 0, 64),
+    (2, 32, 32, 128, 256, 1, 1, 0, 32),
+    (2, 32, 32, 128, 512, 3, 1, 1, 32),      # two output-channel tiles
+    (3, 32, 32, 224, 128, 3, 2, 1, 64),      # pose head: 32 -> 16
+    (3, 16, 16, 128, 128, 3, 2, 1, 64),      # 16 -> 8: two images per tile, n not a multiple
+    (11, 8, 8, 128, 128, 3, 2, 1, 64),       # 8 -> 4: eight images per tile
+    (1, 8, 128, 16, 64, 3, 1, 1, 64),        # full-width tile rows
+    (1, 4, 256, 32, 32, 3, 1, 1, 64),        # two tiles per row
+    (2, 32, 32, 336, 256, 1, 1, 0, 32),      # lookup width (324 padded to 336)
+    (2, 32, 32, 256, 126, 3, 1, 1, 64),      # 126 output channels
+    (1, 64, 64, 128, 64, 3, 1, 1, 64),
+    (2, 32, 32, 384, 128, 5, 1, 2, 64),      # wide taps
+]
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k,stride,pad,bk", CASES)
+def test_conv_tc_vs_fp64(n, h, w, cin, cout, k, stride, pad, bk):
+    g = torch.Generator().manual_seed(n * 1000 + cin + cout + k)
+    x = torch.randn(n, h, w, cin, generator=g)
+    wt = torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5
+    b = torch.randn(cout, generator=g)
+    pk = C.pack_weights(wt.to(DEV), b.to(DEV), stride, pad, bk=bk)
+    xs = C.to_split(x.to(DEV))
+    assert _err(xs.float(), x) < 2e-5
+    got = C.conv(xs, pk, relu=True)
+    torch.cuda.synchronize()
+    want = _ref(x, wt, b, stride, pad, relu=True)
+    assert tuple(got.shape) == tuple(want.shape[:3])
+    e = _err(got.float(), want)
+    assert e < TOL + 3 * (cin * k * k / 16) * 2.0 ** -24, e
+
+
+def test_conv_tc_outputs_residuals_stats():
+    g = torch.Generator().manual_seed(7)
+    n, h, w, cin, cout = 3, 16, 16, 64, 96
+    x = torch.randn(n, h, w, cin, generator=g)
+    wt = torch.randn(cout, cin, 3, 3, generator=g) / 24
+    b = torch.randn(cout, generator=g)
+    r = torch.randn(n, h, w, cout, generator=g)
+    pk = C.pack_weights(wt.to(DEV), b.to(DEV), 1, 1)
+    xs = C.to_split(x.to(DEV))
+    want = _ref(x, wt, b, 1, 1, relu=True, res=r)
+    # split residual -> all three outputs at once, into channel slices of wider buffers
+    rs = C.to_split(r.to(DEV))
+    wide = C.alloc_split(n, h, w, 224, DEV, zero=True)
+    wide_f = torch.zeros(n, h, w, 160, device=DEV)
+    planar = torch.empty(n, cout, h, w, device=DEV)
+    C.conv(xs, pk, relu=True, res=rs, out=wide.slice(64, cout), out_f32=wide_f[..., 32:32 + cout],
+           out_planar=planar)
+    torch.cuda.synchronize()
+    assert _err(wide.slice(64, cout).float(), want) < TOL
+    assert float(wide.slice(0, 64).float().abs().max()) == 0 and float(wide.slice(160, 64).float().abs().max()) == 0
+    assert _err(wide_f[..., 32:32 + cout], want) < TOL
+    assert float(wide_f[..., :32].abs().max()) == 0 and float(wide_f[..., 32 + cout:].abs().max()) == 0
+    assert _err(planar.permute(0, 2, 3, 1), want) < TOL
+    # fp32 residual + InstanceNorm statistics of the pre-residual value
+    stats = torch.zeros(n, cout, 2, device=DEV, dtype=torch.float64)
+    got = C.conv(xs, pk, relu=True, res_f32=r.to(DEV), stats=stats, want="f32")
+    torch.cuda.synchronize()
+    assert _err(got[..., :cout], want) < TOL
+    pre = _ref(x, wt, b, 1, 1)
+    assert _err(stats[:, :, 0], pre.sum((1, 2))) < 1e-5
+    assert _err(stats[:, :, 1], (pre * pre).sum((1, 2))) < 1e-5
+    # planar output rounded to TF32: low 13 mantissa bits are zero
+    pl = C.conv(xs, pk, want="planar", planar_tf32=True)
+    torch.cuda.synchronize()
+    assert int((pl.view(torch.int32) & 0x1FFF).abs().max()) == 0
+    assert _err(pl.permute(0, 2, 3, 1), pre) < 5e-4
+
+
+def test_conv_tc_rejects():
+    from scflow_b200._lib import ScflowError
+    x = C.alloc_split(1, 24, 24, 64, DEV, zero=True)            # 24 does not tile 128 pixels
+    pk = C.pack_weights(torch.zeros(64, 64, 3, 3, device=DEV), None, 1, 1)
+    with pytest.raises(ScflowError):
+        C.conv(x, pk)
+    with pytest.raises(ScflowError):
+        C.to_split(torch.zeros(1, 8, 8, 8))                    # CPU tensor
