@@ -343,7 +343,8 @@ def decoder_forward(sd: Dict[str, Tensor], feat_render, feat_real, h_feat, cxt_f
 # RAFTEncoder 'Basic' (upstream of the hot path; inside the timed end-to-end metric)
 #     models/encoder/raft_encoder.py:286-314, models/backbone/resnet.py:12-92,676-771
 # ----------------------------------------------------------------------------------------
-def raft_encoder(x: Tensor, sd: Dict[str, Tensor], norm: str, p: str = "") -> Tensor:
+def raft_encoder(x: Tensor, sd: Dict[str, Tensor], norm: str, p: str = "", taps: list = None) -> Tensor:
+    """`taps`, when given, collects the stem output and each residual block's output (per-layer parity)."""
     def nrm(y, key):
         if norm == "IN":
             return F.instance_norm(y)
@@ -351,6 +352,8 @@ def raft_encoder(x: Tensor, sd: Dict[str, Tensor], norm: str, p: str = "") -> Te
                             sd[key + ".weight"], sd[key + ".bias"], False)
     n1, n2 = ("in1", "in2") if norm == "IN" else ("bn1", "bn2")
     y = F.relu(nrm(F.conv2d(x, sd[p + "conv1.weight"], sd[p + "conv1.bias"], stride=2, padding=3), p + n1))
+    if taps is not None:
+        taps.append(y)
     for li, stride in ((1, 1), (2, 2), (3, 2)):
         for bi in range(2):
             q = f"{p}res_layer{li}.{bi}."
@@ -361,6 +364,8 @@ def raft_encoder(x: Tensor, sd: Dict[str, Tensor], norm: str, p: str = "") -> Te
                 y = nrm(F.conv2d(y, sd[q + "downsample.0.weight"], sd[q + "downsample.0.bias"], stride=s),
                         q + "downsample.1")
             y = F.relu(o + y)
+            if taps is not None:
+                taps.append(y)
     return F.conv2d(y, sd[p + "conv2.weight"], sd[p + "conv2.bias"])
 
 

@@ -193,7 +193,7 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
          view=None):
     """One convolution launch.  x: Split (n, h, w, cin).  Outputs: `out` (Split), `out_f32` (n, OH, OW, >=cout)
     fp32 channels-last (may be a channel slice of a wider buffer), `out_planar` (n, cout, OH, OW); when none is
-    given one is allocated according to `want` ("split" | "f32" | "planar").  `view` = (h, w, cin, lo_off,
+    given one is allocated according to `want` ("split" | "f32" | "planar").  `view` = (n, h, w, cin, lo_off,
     stride_w, stride_h, stride_n) overrides how the input buffer is addressed (the stem's overlapped window
     view).  Returns the output object(s) in the order split, f32, planar (only those produced)."""
     lib = _lib.load()
@@ -201,7 +201,7 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
     cin = x.c
     lo_off, sw, sh, sn = x.cp, x.pitch, w * x.pitch, h * w * x.pitch
     if view is not None:
-        h, w, cin, lo_off, sw, sh, sn = view
+        n, h, w, cin, lo_off, sw, sh, sn = view
     if cin != pk.cin:
         raise _lib.ScflowError(f"conv_tc: input has {cin} channels, the filter takes {pk.cin}")
     oh, ow = out_hw(pk, h, w)

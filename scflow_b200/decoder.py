@@ -20,6 +20,7 @@ from typing import Optional, Sequence, Union
 import torch
 import torch.nn as nn
 
+from . import convtc as C
 from . import gru, gru_tc, ops
 from .modules import (ConvGRU, ConvModule, CorrelationPyramid, CorrLookup, MotionEncoder, XHead,
                       _needs_grad)
@@ -76,15 +77,6 @@ class SCFlowDecoder(nn.Module):
         self.mask_encoder = nn.Sequential(ConvModule(1, 64, 3, padding=1, **kw),
                                           ConvModule(64, 32, 3, padding=1, **kw))
 
-    def _convs_channels_last(self) -> None:
-        """cuDNN-side convolutions of the loop take channels-last activations (what the lookup
-        and GRU kernels produce); their filters are re-laid once, values unchanged."""
-        mods = (self.encoder, self.flow_pred, self.mask_pred, self.delta_flow_encoder, self.mask_encoder,
-                self.pose_pred)
-        for m in (c for top in mods for c in top.modules()):
-            if isinstance(m, nn.Conv2d) and not m.weight.is_contiguous(memory_format=torch.channels_last):
-                m.weight.data = m.weight.data.contiguous(memory_format=torch.channels_last)
-
     def forward(self, feat_render: torch.Tensor, feat_real: torch.Tensor, h_feat: torch.Tensor,
                 cxt_feat: torch.Tensor, ref_rotation: torch.Tensor, ref_translation: torch.Tensor,
                 depth: torch.Tensor, internel_k: torch.Tensor, label: torch.Tensor,
@@ -106,42 +98,38 @@ class SCFlowDecoder(nn.Module):
         flow_from_pose, flow_from_pred, mask_preds = [], [], []
         # scflow_decoder.py:197-198 on the caller-supplied init flow (zeros from the refiner)
         flow = ops.downsample(init_flow.float(), scale, 1.0 / scale)
-        fused_gru = gru.BACKEND == "tcgen05"
-        if fused_gru:
-            # Channels-last state for the whole loop.  x = cat[cxt | motion | flow] lives in one
-            # (N,h,w,256) buffer: the context half is packed once, the motion half every iteration
-            # (scflow_pack_nhwc, rounding to nearest TF32 for the tensor core); h is updated in
-            # place together with its TF32 copy.  Values equal the reference's NCHW tensors.
-            self._convs_channels_last()
-            n_, _, hh, ww = h_feat.shape
-            h_state = h_feat.float().permute(0, 2, 3, 1).contiguous()
-            h_round = gru_tc.round_tf32(h_state)
-            rh = torch.empty_like(h_state)
-            x_buf = torch.empty((n_, hh, ww, self.gru.x_channels), device=h_state.device, dtype=torch.float32)
-            ops.pack_nhwc(x_buf, 0, a=cxt_feat.float().permute(0, 2, 3, 1).contiguous())
-            h_feat = h_state.permute(0, 3, 1, 2)
+        # Channels-last state for the whole loop, no torch.cat anywhere:
+        #   x = cat[cxt | motion | flow] is ONE (N,h,w,256) fp32 buffer (TF32-rounded, the ConvGRU operand): the
+        #     context half is packed once, out_net's epilogue writes the motion half every iteration;
+        #   pose_in = cat[h | delta-flow feat | mask feat] is ONE 224-channel split-plane buffer: the hidden
+        #     state's split copy doubles as the heads' operand, the two small encoders write their slices.
+        n_, _, hh, ww = h_feat.shape
+        dev = h_feat.device
+        h_state = h_feat.float().permute(0, 2, 3, 1).contiguous()
+        h_round = gru_tc.round_tf32(h_state)
+        rh = torch.empty_like(h_state)
+        cx, hc = self.cxt_channels, self.h_channels
+        if self.encoder.out_channels[0] != 126 or self.gru.x_channels != 256 or cx != 128:
+            raise NotImplementedError("decoder widths other than the Basic net's 128 | 126 + 2")
+        x_buf = torch.empty((n_, hh, ww, self.gru.x_channels), device=dev, dtype=torch.float32)
+        ops.pack_nhwc(x_buf, 0, a=cxt_feat.float().permute(0, 2, 3, 1).contiguous())
+        dfe, me = self.delta_flow_encoder, self.mask_encoder
+        c_df, c_m = dfe[1].conv.out_channels, me[1].conv.out_channels
+        pose_in = C.alloc_split(n_, hh, ww, hc + c_df + c_m, dev)
+        h_split = pose_in.slice(0, hc)
         for _ in range(self.iters):
             corr = self.corr_lookup(corr_pyramid, flow)
-            if fused_gru:
-                if self.encoder.out_channels[0] == 126 and self.cxt_channels == 128:
-                    # 128-channel motion tensor (2 zero channels) packed as float4s, then the flow pair
-                    motion = self.encoder.features_padded(corr, flow)
-                    ops.pack_nhwc(x_buf, self.cxt_channels, a=motion.permute(0, 2, 3, 1))
-                    ops.pack_nhwc(x_buf, self.cxt_channels + 126, planar=flow)
-                else:
-                    motion = self.encoder.features(corr, flow)
-                    ops.pack_nhwc(x_buf, self.cxt_channels, a=motion.permute(0, 2, 3, 1), planar=flow)
-                gru_tc.update_inplace(self.gru, h_state, h_round, x_buf, rh)
-            else:
-                motion_feat = self.encoder(corr, flow)
-                x = torch.cat([cxt_feat, motion_feat], dim=1)
-                h_feat = self.gru(h_feat, x)
-            delta_flow_pred = self.flow_pred(h_feat)
-            mask = torch.sigmoid(self.mask_pred(h_feat))
-            delta_flow_feat = self.delta_flow_encoder(delta_flow_pred)
-            mask_feat = self.mask_encoder(mask)
-            delta_rotation, delta_translation = self.pose_pred(
-                torch.cat([h_feat, delta_flow_feat, mask_feat], axis=1), label)
+            self.encoder.features_into(corr, flow, x_buf, cx)
+            ops.pack_nhwc(x_buf, cx + 126, planar=flow)
+            gru_tc.update_inplace(self.gru, h_state, h_round, x_buf, rh)
+            C.to_split(h_state, out=h_split)
+            delta_flow_pred = self.flow_pred.forward_split(h_split)
+            mask = torch.sigmoid(self.mask_pred.forward_split(h_split))
+            d0 = dfe[0](delta_flow_pred)                               # 7x7 on 2 channels: FMA kernel
+            dfe[1].forward_split(C.to_split(d0.permute(0, 2, 3, 1)), out=pose_in.slice(hc, c_df))
+            m0 = me[0](mask)                                           # 3x3 on 1 channel
+            me[1].forward_split(C.to_split(m0.permute(0, 2, 3, 1)), out=pose_in.slice(hc + c_df, c_m))
+            delta_rotation, delta_translation = self.pose_pred.forward_split(pose_in, label)
             flow_pred = ops.upsample(flow, delta_flow_pred, scale, float(scale))
             upsample_mask_pred = ops.upsample(mask, None, scale, 1.0)
             # pose compose + pose-induced flow + next iteration's 1/8 flow: one launch

@@ -49,7 +49,7 @@ class StemInput:
         """The planes as a Split the conv launcher can address, plus the overlapped-window view."""
         _, n, ho, wo, _ = self.planes.shape
         buf = self.planes.view(2 * n, ho, wo, 16)               # only data_ptr / device are used with `view`
-        view = (ho, wo - 3, 64, n * ho * wo * 16, 16, wo * 16, ho * wo * 16)
+        view = (n, ho, wo - 3, 64, n * ho * wo * 16, 16, wo * 16, ho * wo * 16)
         return C.Split(buf, 64), view
 
 
@@ -183,7 +183,8 @@ class RAFTEncoder(nn.Module):
             inpl = planes
         self.conv2 = nn.Conv2d(128, out_channels, 1)
 
-    def forward(self, x: torch.Tensor, stem: "StemInput" = None, planar_tf32: bool = False) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, stem: "StemInput" = None, planar_tf32: bool = False,
+                taps: list = None) -> torch.Tensor:
         """Inference (no autograd): the tensor-core path, CUDA only.  With autograd recording (training,
         BASELINE.json configs[4]) the layers run as the nn.Modules they are, so that autograd supplies the
         backward.  `stem`: a StemInput of x computed by the caller (shared between encoders);
@@ -197,9 +198,10 @@ class RAFTEncoder(nn.Module):
             return self.conv2(x)
         if isinstance(n1, nn.BatchNorm2d) and self.training:
             raise NotImplementedError("RAFTEncoder(BN) in train mode without autograd: no batch-statistics kernel")
-        return self.forward_tc(x, stem, planar_tf32)
+        return self.forward_tc(x, stem, planar_tf32, taps)
 
-    def forward_tc(self, x: torch.Tensor, stem=None, planar_tf32: bool = False) -> torch.Tensor:
+    def forward_tc(self, x: torch.Tensor, stem=None, planar_tf32: bool = False, taps: list = None) -> torch.Tensor:
+        """`taps` (tests): collects the stem output and every residual block's output as fp32 (n,h,w,c)."""
         n1 = getattr(self, self.norm1_name)
         stem = stem or StemInput(x)
         xs, view = stem.split()
@@ -212,9 +214,13 @@ class RAFTEncoder(nn.Module):
             st = _Stats(n, x.device, n * 2 * (64 * 5 + 96 * 5 + 128 * 5))
             raw, sums = _conv_raw(xs, self.conv1, st, view=view, pk=_stem_pack(self.conv1))
             y = C.norm_apply(raw, sums, relu=True, eps=n1.eps)
+        if taps is not None:
+            taps.append(y.float())
         for name in self.res_layers:
             for block in getattr(self, name):
                 y = block.forward_tc(y, st)
+                if taps is not None:
+                    taps.append(y.float())
         pk = C.packed_conv(self.conv2)
         if planar_tf32:
             out = C.conv(y, pk, want="planar", planar_tf32=True)

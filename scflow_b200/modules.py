@@ -15,6 +15,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from . import convtc as C
 from . import ops
 
 
@@ -59,55 +60,46 @@ class ConvModule(nn.Module):
         if self.with_activation:
             self.activate = _ACT[act_cfg["type"]]()
 
-    def _fused_ok(self, x) -> bool:
-        return (not torch.is_grad_enabled() and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4
-                and not self.with_norm and self.conv.bias is not None and self.conv.groups == 1
-                and self.with_activation and isinstance(self.activate, nn.ReLU)
-                and x.is_contiguous(memory_format=torch.channels_last))
-
     def _small_cin_ok(self, x) -> bool:
         c = self.conv
-        return (not torch.is_grad_enabled() and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4
-                and not self.with_norm and c.in_channels <= 2 and c.kernel_size in ((3, 3), (7, 7))
+        return (not self.with_norm and c.in_channels <= 2 and c.kernel_size in ((3, 3), (7, 7))
                 and c.stride == (1, 1) and c.padding == (c.kernel_size[0] // 2,) * 2 and c.dilation == (1, 1)
                 and c.groups == 1 and c.out_channels % 32 == 0 and c.out_channels <= 256
                 and x.shape[-1] % 8 == 0
                 and (not self.with_activation or isinstance(self.activate, nn.ReLU)))
 
-    def _gn_fused_ok(self, x) -> bool:
-        if not (self.with_norm and self.norm_name == "gn"):
-            return False
-        gn = self.gn
-        return (not torch.is_grad_enabled() and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4
-                and gn.affine and gn.num_channels == 4 * gn.num_groups and 512 % gn.num_groups == 0
-                and (not self.with_activation or isinstance(self.activate, nn.ReLU)))
+    def forward_split(self, x: "C.Split", **kw):
+        """Tensor-core form on split-plane activations (convtc.Split in; kwargs as convtc.conv: out=, out_f32=,
+        want=, res=, f32_tf32=).  conv -> bias -> ReLU in one launch; a GroupNorm layer is the raw convolution
+        followed by the one-launch GN+ReLU kernel, returned as the fp32 channels-last tensor."""
+        relu = self.with_activation and isinstance(self.activate, nn.ReLU)
+        if self.with_activation and not relu:
+            raise NotImplementedError(f"ConvModule activation {type(self.activate).__name__} on the tensor-core path")
+        if not self.with_norm:
+            return C.conv(x, C.packed_conv(self.conv), relu=relu, **kw)
+        if self.norm_name != "gn" or not (self.gn.affine and self.gn.num_channels == 4 * self.gn.num_groups):
+            raise NotImplementedError(f"ConvModule norm {self.norm_name} on the tensor-core path")
+        raw = C.conv(x, C.packed_conv(self.conv, with_bias=False), want="f32")
+        return ops.group_norm4_act(raw, self.gn, relu=relu)
 
     def forward(self, x):
-        if self._gn_fused_ok(x):
-            # conv (cuDNN, channels-last) -> GroupNorm + ReLU in ONE in-place launch
-            c = self.conv
-            if not c.weight.is_contiguous(memory_format=torch.channels_last):
-                c.weight.data = c.weight.data.contiguous(memory_format=torch.channels_last)
-            y = F.conv2d(x.contiguous(memory_format=torch.channels_last), c.weight, None, c.stride,
-                         c.padding).contiguous(memory_format=torch.channels_last)
-            ops.group_norm4_act(y.permute(0, 2, 3, 1), self.gn, relu=self.with_activation)
-            return y
+        if _needs_grad(x, *self.parameters()):
+            # training (BASELINE.json configs[4]): the nn.Modules under autograd supply the backward
+            x = self.conv(x)
+            if self.with_norm:
+                x = getattr(self, self.norm_name)(x)
+            if self.with_activation:
+                x = self.activate(x)
+            return x
+        if not x.is_cuda or x.dtype != torch.float32 or x.dim() != 4:
+            raise ops._lib.ScflowError("ConvModule: expected a CUDA fp32 NCHW tensor (scflow_b200 has no CPU path)")
         if self._small_cin_ok(x):
             # 1-2 input channels: FP32-FMA kernel with bias + ReLU fused (csrc/small_conv.cu)
             return ops.conv_small_cin(x, self.conv, relu=self.with_activation)
-        if self._fused_ok(x):
-            # channels-last inference: cuDNN's fused convolution + bias + ReLU (one launch, same bits as
-            # conv followed by a separate bias/ReLU pass, which it saves)
-            c = self.conv
-            if not c.weight.is_contiguous(memory_format=torch.channels_last):
-                c.weight.data = c.weight.data.contiguous(memory_format=torch.channels_last)
-            return torch.cudnn_convolution_relu(x, c.weight, c.bias, c.stride, c.padding, c.dilation, 1)
-        x = self.conv(x)
-        if self.with_norm:
-            x = getattr(self, self.norm_name)(x)
-        if self.with_activation:
-            x = self.activate(x)
-        return x
+        # stand-alone call on an NCHW-shaped tensor: one layout/split pass in, channels-last fp32 out
+        xs = C.to_split(x.permute(0, 2, 3, 1))
+        y = self.forward_split(xs, want="f32") if not self.with_norm else self.forward_split(xs)
+        return y[..., :self.conv.out_channels].permute(0, 3, 1, 2)
 
 
 class CorrelationPyramid(nn.Module):
@@ -196,25 +188,29 @@ class MotionEncoder(nn.Module):
         """The 126 learned motion channels (raft_decoder.py:162-165), before `flow` is appended."""
         return self.out_net(torch.cat([self.corr_net(corr), self.flow_net(flow)], dim=1))
 
-    def features_padded(self, corr: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
-        """Inference only: the 126 motion channels as a 128-channel channels-last tensor whose last
-        two channels are exactly zero (two zero filters appended to out_net, cached): cuDNN's
-        128-channel kernel is 1.8x faster than its 126-channel one, and the consumer packs float4s."""
-        conv = self.out_net[0].conv
-        key = (conv.weight._version, conv.weight.data_ptr(), conv.bias._version)
-        hit = self.__dict__.get("_scflow_out128")
-        if hit is None or hit[0] != key:
-            pad = 128 - conv.out_channels
-            w = torch.cat([conv.weight.detach(), conv.weight.new_zeros((pad,) + tuple(conv.weight.shape[1:]))])
-            b = torch.cat([conv.bias.detach(), conv.bias.new_zeros(pad)])
-            hit = (key, (w.contiguous(memory_format=torch.channels_last), b))
-            self.__dict__["_scflow_out128"] = hit
-        w, b = hit[1]
-        x = torch.cat([self.corr_net(corr), self.flow_net(flow)], dim=1)
-        return torch.cudnn_convolution_relu(x, w, b, conv.stride, conv.padding, conv.dilation, 1)
+    def features_into(self, corr: torch.Tensor, flow: torch.Tensor, x_buf: torch.Tensor, off: int) -> None:
+        """Inference: the motion channels written, rounded to the nearest TF32 (the ConvGRU's operand format),
+        into x_buf[..., off:off+128] (126 channels + 2 zeros; the caller packs the flow pair over the zeros).
+        corr: (N,324,h,w)-shaped channels-last lookup result; flow: planar (N,2,h,w); x_buf (N,h,w,256) fp32.
+        Five tensor-core / FMA launches; what the reference concatenates is written in place: corr_net and
+        flow_net store into the two channel slices of one split buffer that out_net reads."""
+        n, _, h, w = corr.shape
+        cs = C.to_split(corr.permute(0, 2, 3, 1))
+        a = self.corr_net[0].forward_split(cs)
+        cat = C.alloc_split(n, h, w, 256, corr.device)
+        c1 = self.corr_net[1].conv.out_channels
+        self.corr_net[1].forward_split(a, out=cat.slice(0, c1))
+        f0 = self.flow_net[0](flow)                                     # 7x7 on 2 channels: FMA kernel
+        self.flow_net[1].forward_split(C.to_split(f0.permute(0, 2, 3, 1)), out=cat.slice(c1, 256 - c1))
+        self.out_net[0].forward_split(cat, out_f32=x_buf[..., off:off + 128], f32_tf32=True)
 
     def forward(self, corr: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
-        return torch.cat([self.features(corr, flow), flow], dim=1)
+        if _needs_grad(corr, flow, *self.parameters()):
+            return torch.cat([self.features(corr, flow), flow], dim=1)
+        n, _, h, w = corr.shape
+        buf = torch.empty((n, h, w, 128), device=corr.device, dtype=torch.float32)
+        self.features_into(corr.contiguous(memory_format=torch.channels_last), flow.contiguous(), buf, 0)
+        return torch.cat([buf[..., :126].permute(0, 3, 1, 2), flow], dim=1)
 
 
 class XHead(nn.Module):
@@ -232,12 +228,17 @@ class XHead(nn.Module):
         else:
             raise ValueError(f"x must be 'flow' or 'mask', but got {x}")
 
+    def forward_split(self, hs: "C.Split") -> torch.Tensor:
+        """Inference on the split-plane hidden state: 3x3 convs on the tensor cores, the 1-2 channel
+        predictor as one pass over the fp32 feature map (csrc/small_conv.cu); planar (N, x_channels, h, w)."""
+        y = hs
+        for i, layer in enumerate(self.layers):
+            y = layer.forward_split(y, want="f32" if i == len(self.layers) - 1 else "split")
+        return ops.conv_small_cout(y.permute(0, 3, 1, 2), self.predict_layer)
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        y = self.layers(x)
-        p = self.predict_layer
-        if (not torch.is_grad_enabled() and y.is_cuda and y.dtype == torch.float32
-                and y.is_contiguous(memory_format=torch.channels_last) and y.shape[1] % 32 == 0
-                and (4 + 2 * (p.kernel_size[0] // 2)) * y.shape[-1] <= 1024 and y.shape[-1] % 8 == 0):
-            # 1-2 output channels: one pass over the feature map (csrc/small_conv.cu)
-            return ops.conv_small_cout(y, p)
-        return p(y)
+        if _needs_grad(x, *self.parameters()):
+            return self.predict_layer(self.layers(x))
+        if not x.is_cuda or x.dtype != torch.float32:
+            raise ops._lib.ScflowError("XHead: expected a CUDA fp32 tensor (scflow_b200 has no CPU path)")
+        return self.forward_split(C.to_split(x.permute(0, 2, 3, 1)))

@@ -1,5 +1,5 @@
-"""MultiClassPoseHead (models/head/pose_head.py:111-211) -- on the loop, stays PyTorch/cuDNN in
-this round.  Same parameter names/shapes; zero-initialised output layers."""
+"""MultiClassPoseHead (models/head/pose_head.py:111-211).  Same parameter names/shapes; zero-initialised
+output layers.  Inference: tensor-core stride-2 convolutions (csrc/conv_tc.cu) + GN/ReLU and FC kernels."""
 from __future__ import annotations
 
 import torch
@@ -62,15 +62,28 @@ class MultiClassPoseHead(nn.Module):
             self.__dict__["_scflow_fc0"] = hit
         return hit[1]
 
+    def forward_split(self, xs, label: torch.Tensor):
+        """Inference on a split-plane input (convtc.Split of cat[h | delta-flow feat | mask feat]): three
+        stride-2 tensor-core convolutions, each followed by the one-launch GN+ReLU kernel, then the whole FC
+        tail in three launches (csrc/pose_head.cu)."""
+        from . import convtc as C, ops
+        if self.fc_layers[1][0].out_features + self.fc_layers[0][0].out_features > 12288:
+            raise NotImplementedError("pose head FC widths beyond the split-K kernel's workspace")
+        y = xs
+        for i, layer in enumerate(self.conv_layers):
+            raw = layer.forward_split(y)                               # fp32 channels-last, GN+ReLU applied
+            y = C.to_split(raw) if i + 1 < len(self.conv_layers) else raw
+        n, hs, ws, c = y.shape
+        return ops.pose_fc(y.reshape(n, hs * ws * c), self._fc0_permuted(hs * ws), self, label)
+
     def forward(self, x: torch.Tensor, label: torch.Tensor):
-        if (not torch.is_grad_enabled() and x.is_cuda and x.dtype == torch.float32
-                and self.fc_layers[1][0].out_features + self.fc_layers[0][0].out_features <= 12288):
-            # inference: conv -> GN+ReLU (fused) x3 in channels-last, then the whole FC tail in two launches
-            from . import ops
-            y = self.conv_layers(x)
-            n, c, hs, ws = y.shape
-            y2d = y.permute(0, 2, 3, 1).reshape(n, hs * ws * c)          # a view for channels-last y
-            return ops.pose_fc(y2d, self._fc0_permuted(hs * ws), self, label)
+        if not (torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters()))):
+            if not x.is_cuda or x.dtype != torch.float32:
+                from ._lib import ScflowError
+                raise ScflowError("MultiClassPoseHead: expected a CUDA fp32 tensor (scflow_b200 has no CPU path)")
+            from . import convtc as C
+            return self.forward_split(C.to_split(x.permute(0, 2, 3, 1)), label)
+        # training (configs[4]): nn.Modules under autograd
         x = self.fc_layers(self.flatten_op(self.conv_layers(x)))
         dt = self.translation_pred(x).view(-1, self.num_class, 3)
         dr = self.rotation_pred(x).view(-1, self.num_class, self.rotation_out_channels)

@@ -116,3 +116,60 @@ def test_conv_tc_rejects():
         C.conv(x, pk)
     with pytest.raises(ScflowError):
         C.to_split(torch.zeros(1, 8, 8, 8))                    # CPU tensor
+
+
+# ------------------------------------------------------------------ f3: the RAFT encoders, layer by layer
+@pytest.mark.parametrize("norm", ["IN", "BN"])
+@pytest.mark.parametrize("n,s", [(2, 64), (1, 256)])
+def test_encoder_layers_vs_oracle(golden_dir, norm, n, s):
+    """RAFTEncoder on the tensor-core convolution family against the oracle's restatement of
+    raft_encoder.py:286-314 / resnet.py:12-92 (ATen fp32 on the CPU): the stem, every residual block and the
+    final features, each within 1e-4 of the layer's max magnitude (cuDNN TF32 reads ~3e-3 here)."""
+    import json, os
+    from oracle import scflow_oracle as O
+    from scflow_b200 import synthetic as syn
+    from scflow_b200.encoder import RAFTEncoder
+    es = json.load(open(os.path.join(golden_dir, "encoder_state_shapes.json")))
+    sd = syn.fill_state_dict(es[norm], seed=61, gain=1.7)
+    enc = RAFTEncoder(3, 256, net_type="Basic", norm_cfg=dict(type=norm)).eval()
+    enc.load_state_dict(sd)
+    enc.to(DEV)
+    x = syn.make_crops(n, s, seed=5)["rendered_images"]
+    want_taps = []
+    want = O.raft_encoder(x, sd, norm, taps=want_taps)
+    got_taps = []
+    with torch.no_grad():
+        got = enc(x.to(DEV), taps=got_taps)
+        planar = enc(x.to(DEV), planar_tf32=True)
+    torch.cuda.synchronize()
+    assert len(got_taps) == len(want_taps) == 7
+    for i, (g, w) in enumerate(zip(got_taps, want_taps)):
+        e = _err(g, w.permute(0, 2, 3, 1))
+        assert e < 1e-4, (i, e)
+    assert got.shape == want.shape
+    assert _err(got, want) < 1e-4
+    # the correlation kernel's operand format: NCHW-contiguous, rounded to the nearest TF32
+    assert planar.is_contiguous() and planar.shape == want.shape
+    assert int((planar.view(torch.int32) & 0x1FFF).abs().max()) == 0
+    assert _err(planar, want) < 6e-4
+
+
+def test_norm_apply_split_vs_torch():
+    """InstanceNorm + residual + ReLU from epilogue statistics (resnet.py:64-92) against F.instance_norm."""
+    g = torch.Generator().manual_seed(11)
+    n, h, w, c = 3, 16, 8, 96
+    x = torch.randn(n, h, w, c, generator=g) * 3 + 1
+    r = torch.randn(n, h, w, c, generator=g)
+    xd, rd = x.to(DEV), r.to(DEV)
+    def sums(t):
+        d = t.double()
+        return torch.stack([d.sum((1, 2)), (d * d).sum((1, 2))], -1).contiguous()
+    inorm = lambda t: F.instance_norm(t.double().permute(0, 3, 1, 2)).permute(0, 2, 3, 1)
+    got = C.norm_apply(xd, sums(xd), relu=True).float()
+    assert _err(got, torch.relu(inorm(x))) < 2e-5
+    got = C.norm_apply(xd, sums(xd), relu=True, res=C.to_split(rd)).float()
+    assert _err(got, torch.relu(inorm(x) + r.double())) < 2e-5
+    f32 = torch.empty(n, h, w, c, device=DEV)
+    got = C.norm_apply(xd, sums(xd), relu=False, res_raw=rd, res_sums=sums(rd), out_f32=f32).float()
+    assert _err(got, inorm(x) + inorm(r)) < 2e-5
+    assert _err(f32, inorm(x) + inorm(r)) < 2e-6
