@@ -2,12 +2,14 @@
 """bench.py -- object-crops/sec of the SCFlow refiner forward (3 encoder passes + 8-iteration
 decoder) on synthetic YCB-V-shaped 256x256 crops.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference|torch-gpu] [--batch B]
 
 One "step" = one refinement of a batch of B=64 crops per GPU (BASELINE.json configs[1]; with
 N GPUs every rank refines its own 64 crops and the (B,12) poses are all-gathered: weak scaling,
 N=8 is configs[2]'s 512 crops).  Rank 0 prints ONE JSON line (contract in the task statement).
-`--impl reference` times the CPU oracle port of the reference path on the host cores.
+`--impl reference` times the reference's own modules (unmodified files staged under baseline/_ref; the oracle
+port if they are absent) on the host cores, same step; `--impl torch-gpu` the same modules on the B200 with
+PyTorch's defaults (an extra line: the GPU bar SURVEY names).
 """
 from __future__ import annotations
 
@@ -26,6 +28,10 @@ import torch
 import torch.distributed as dist
 
 METRIC = "object-crops/sec (8-iter refine)"
+PRECISION_DTYPE = "bf16x3 (split-bf16, fp32 accumulate); tf32 correlation"
+PRECISION_TEXT = ("every convolution incl. the ConvGRU gates: split-bf16 tcgen05 (3 bf16 MMAs per product, fp32 TMEM "
+                  "accumulate, ~2^-17 per product); correlation: tcgen05 TF32 with operands rounded to nearest; "
+                  "everything else fp32")
 UNIT = "crops/s"
 WORKLOAD = "SCFlow refiner inference, batch 64 YCB-V-shaped 256x256 crops per GPU, 8 iters"
 
@@ -38,14 +44,14 @@ def workload(S=256, B=64):
 # summary (profiles/<round>_ncu_full_summary.txt, written by tools/make_profiles.py; cfg2 only):
 # launcher -> kernel-name fragment of the capture.  null where the capture holds no such kernel.
 NCU_KERNEL = {
-    "scflow_convgru_fwd": "convgru_fused_kernel", "scflow_convgru_pass_fwd": "convgru_pass_kernel",
+    "scflow_conv_tc_fwd": "conv_tc_kernel",
     "scflow_corr_lookup_fwd": "corr_lookup_v2_kernel", "scflow_corr_pyramid_fwd": "corr_tf32_kernel",
     "scflow_pose_flow_fwd": "pose_flow_kernel",
 }
 
 
 def ncu_traffic(launcher):
-    frag = NCU_KERNEL.get(launcher)
+    frag = NCU_KERNEL.get(launcher.split("[")[0])
     files = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if f.endswith("_ncu_full_summary.txt")) \
         if os.path.isdir(os.path.join(ROOT, "profiles")) else []
     if not frag or not files:
@@ -159,16 +165,33 @@ def cpu_refiner_state():
             syn.fill_state_dict(ds, seed=64))
 
 
-def cpu_run(batch, state, reps, warm):
-    """Reference path on the host cores (oracle port of the reference's PyTorch CPU code)."""
+def reference_model(S=256):
+    """The UNMODIFIED reference files (staged under baseline/_ref by oracle/stage_ref.py, imported through
+    the third-party shims) when they are there: kind "reference"; else the oracle port: kind "port"."""
+    try:
+        from oracle import _ref_shims as RS
+        if RS.reference_available():
+            return RS.ReferenceRefiner(S, cpu_refiner_state()), "reference"
+    except Exception as e:                                  # pragma: no cover - reported in the line
+        sys.stderr.write(f"reference files unavailable ({e}); timing the oracle port\n")
+    return None, "port"
+
+
+def cpu_run(batch, state, reps, warm, model=None):
+    """Reference path on the host cores: the reference's own modules when `model` is given, else the oracle
+    port of them."""
     from oracle import scflow_oracle as O
     se, sc, sd = state
     n = batch["depth"].shape[0]
     last = {}
     def once():
         with torch.no_grad():
-            last["out"] = O.refiner_forward(se, sc, sd, batch["rendered_images"], batch["real_images"], batch["R0"],
-                                            batch["t0"], batch["depth"], batch["K"], batch["labels"])
+            if model is not None:
+                last["pose"] = model(batch)
+            else:
+                o = O.refiner_forward(se, sc, sd, batch["rendered_images"], batch["real_images"], batch["R0"],
+                                      batch["t0"], batch["depth"], batch["K"], batch["labels"])
+                last["pose"] = (o["rotations"][-1], o["translations"][-1])
     for _ in range(warm):
         once()
     ts = []
@@ -176,40 +199,93 @@ def cpu_run(batch, state, reps, warm):
         t0 = time.perf_counter()
         once()
         ts.append(time.perf_counter() - t0)
-    cpu_run.last_pose = (last["out"]["rotations"][-1], last["out"]["translations"][-1])
+    cpu_run.last_pose = last["pose"]
     return n, ts
 
 
 def reference_arm(args):
+    """The reference's own CPU implementation of the path on this box's host cores, all threads, on the SAME
+    step as our arm (one batch of args.batch crops), with the steps / warm-up the driver asked for."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    sample_n = 8
-    batch = tile_batch(make_batch(2, 1234), sample_n)
-    n, ts = cpu_run(batch, cpu_refiner_state(), max(1, args.steps), max(1, min(args.warmup, 2)))
+    B, S = args.batch, args.image
+    batch = tile_batch(make_batch(4, 1234, S), B)
+    model, kind = reference_model(S)
+    n, ts = cpu_run(batch, cpu_refiner_state(), max(1, args.steps), max(0, args.warmup), model)
     ms = 1e3 * sum(ts) / len(ts)
     val = n / (ms / 1e3)
-    sample = f"{n} of the 64 crops of one step per timed step (same refiner, weights and input generator)"
+    sample = f"the full step: {n} crops per timed step (same refiner, weights and input generator as our arm)"
     _emit(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": len(ts), "warmup": max(1, min(args.warmup, 2)), "ms_per_step": ms, "higher_is_better": True,
+        "steps": len(ts), "warmup": max(0, args.warmup), "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": sample, "threads": torch.get_num_threads()},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
+        "config": {"workload": workload(S, B), "crops_per_gpu_per_step": B, "image": S, "iters": 8,
+                   "threads": torch.get_num_threads(),
+                   "what_runs": "unmodified reference files (baseline/_ref) + third-party shims, PyTorch CPU"
+                   if kind == "reference" else "oracle port of the reference path, PyTorch CPU"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+    }))
+
+
+def torch_gpu_arm(args):
+    """Extra line: the reference's own modules on the SAME B200 with PyTorch's defaults
+    (cuDNN TF32 convolutions, cuBLAS fp32 bmm, grid_sample, ~6k launches and 64 host syncs per step): the bar
+    SURVEY names for the GPU path, with its deviation from the fp32 CPU run of the same modules."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import scflow_oracle as O
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    B, S = args.batch, args.image
+    model, kind = reference_model(S)
+    if model is None:
+        _emit(json.dumps({"impl": "torch-gpu", "unavailable": "reference files not staged under baseline/_ref"}))
+        return
+    host = tile_batch(make_batch(4, 1234, S), B)
+    small = {k: v[:8] for k, v in host.items()}
+    torch.set_num_threads(os.cpu_count() or 1)
+    Rc, tc_ = model(small)                                           # fp32 CPU run of the same 8 crops
+    model.to(dev)
+    batch = {k: v.to(dev) for k, v in host.items()}
+    dev_small = {k: v.to(dev) for k, v in small.items()}
+    out = {}
+    for name, flag in (("tf32_default", True), ("fp32_strict", False)):
+        torch.backends.cudnn.allow_tf32 = flag
+        W = max(args.warmup, 3)
+        for _ in range(W):
+            model(batch)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(args.steps):
+            model(batch)
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / args.steps
+        Rg, tg = model(dev_small)
+        out[name] = {"value": B / (ms / 1e3), "ms_per_step": ms,
+                     "deviation_from_cpu_fp32": {"rot_rad_max": float(O.rotation_geodesic(Rg.cpu(), Rc).max()),
+                                                 "trans_mm_max": float((tg.cpu() - tc_).abs().max()), "crops": 8}}
+    torch.backends.cudnn.allow_tf32 = True
+    d = out["tf32_default"]
+    _emit(json.dumps({
+        "impl": "torch-gpu", "metric": METRIC, "value": d["value"], "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": d["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "tf32 (cuDNN default) / fp32 bmm", "data": "synthetic",
+        "config": {"workload": workload(S, B), "what_runs": "unmodified reference files (baseline/_ref) + shims, "
+                   "PyTorch %s eager on cuda, library defaults" % torch.__version__},
+        "precision": out, "gpu_launches": 0,
     }))
 
 
 # --------------------------------------------------------------------------- our arm
 def algorithmic_flops(name, B, S=256):
     P = (S // 8) ** 2
-    if name == "scflow_convgru_pass_fwd":
-        return B * 3 * 2.0 * P * 128 * 1920            # three gate convolutions of one pass
-    if name == "scflow_convgru_fwd":
-        return 2 * B * 3 * 2.0 * P * 128 * 1920        # both passes in one persistent launch
     if name == "scflow_corr_pyramid_fwd":
         return B * 2.0 * P * P * 256
     return None
@@ -242,9 +318,7 @@ def ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B, S = args.batch, args.image
-    # cuDNN parts at the reference's own GPU default (TF32 allowed) unless --strict-fp32
-    torch.backends.cudnn.allow_tf32 = not args.strict_fp32
-    torch.backends.cudnn.benchmark = True
+    # no cuDNN / cuBLAS call is on the inference path: torch's TF32 switches do not matter here
     core = seeded_weights(SCFlowRefinerCore(S)).eval().to(dev)
     # two distinct input sets, alternated, so no step re-reads the previous step's inputs from L2;
     # a step's working set (118 MB inputs, 340 MB pyramid, activations) is several times the L2
@@ -254,7 +328,7 @@ def ours(args):
     h2d = sum(v.numel() * v.element_size() for v in host[0].values())
     d2h = B * 12 * 4
     W = max(args.warmup, 3)
-    for i in range(W):                          # eager warm-up: cuDNN autotune, weight packs, folded BN
+    for i in range(W):                          # eager warm-up: weight packs (folded BN), allocator
         core.refine(resident[i % 2])
     torch.cuda.synchronize()
     if args.no_graph:
@@ -384,93 +458,105 @@ def ours(args):
     null = per_kernel.pop("__null_kernel__", None)
     ev_ms = (null[1] / null[0]) if null else 0.0
     kern = {}
-    for name, (calls, tot, nbytes) in per_kernel.items():
+    for name, (calls, tot, nbytes, nflops) in per_kernel.items():
         raw_ms = tot / calls
         avg_ms = max(raw_ms - ev_ms, 0.25 * raw_ms)
         tot = avg_ms * calls
         ab = algorithmic_bytes(name, B, S) or (nbytes / calls if nbytes else None)
-        fl = algorithmic_flops(name, B, S)
+        fl = algorithmic_flops(name, B, S) or (nflops / calls if nflops else None)
         kern[name] = {"calls_per_step": calls / args.steps, "avg_ms": avg_ms, "avg_ms_raw": raw_ms,
                       "share_of_eager_step": tot / ms_eager,
                       "gbs": (ab / (avg_ms * 1e-3) / 1e9) if ab else None,
                       "hbm_frac": (ab / (avg_ms * 1e-3) / 1e9 / pk["hbm"]) if ab else None,
-                      "tflops": (fl / (avg_ms * 1e-3) / 1e12) if fl else None}
-    # roofline object: the single-shape kernel of ours with the largest share of the step (the
-    # norm/act glue launcher has a comparable total but is ~120 launches of 9 different shapes; it
-    # is listed in `kernels` with its own achieved GB/s)
-    single = [k for k in kern if algorithmic_flops(k, B, S) or algorithmic_bytes(k, B, S)]
-    top = max(single, key=lambda k: kern[k]["avg_ms"] * kern[k]["calls_per_step"])
+                      "tflops": (fl / (avg_ms * 1e-3) / 1e12) if fl else None,
+                      "flops_per_launch": fl, "bytes_per_launch": ab}
+    # roofline object: the launcher + shape of ours with the largest share of the step.  Tensor-bound kernels
+    # are measured against MEASURED_PEAKS.json's bf16 figure (sustained: they are timed inside a long step).
+    # `achieved` counts ALGORITHMIC flops: the split-bf16 convolutions execute three bf16 MMAs per algorithmic
+    # product (fp32-grade results), so their ceiling on that scale is 1/3; `tensor_pipe_frac` = executed MMA
+    # flops / peak is printed beside it.  The TF32 kernels (correlation, ConvGRU) execute one TF32 MMA per
+    # product: ceiling 1/2 of the bf16 peak; the TF32 cuBLAS figure measured in this run is printed too.
+    def mma_per_product(k):
+        return 3.0 if k.startswith("scflow_conv_tc_fwd") else 2.0
+    single = [k for k in kern if kern[k]["flops_per_launch"] or algorithmic_bytes(k, B, S)]
+    share = lambda k: kern[k]["avg_ms"] * kern[k]["calls_per_step"]
+    top = max(single, key=share)
+    conv_shapes = sorted((k for k in kern if k.startswith("scflow_conv_tc_fwd[")), key=share, reverse=True)
     traffic = ncu_traffic(top) if (B, S) == (64, 256) else None
     lk = kern.get("scflow_corr_lookup_fwd")
     roof_lookup = None if lk is None else {
         "kernel": "scflow_corr_lookup_fwd", "bound": "hbm", "achieved": lk["gbs"], "peak": pk["hbm"], "unit": "GB/s",
         "frac": lk["hbm_frac"], "traffic": ncu_traffic("scflow_corr_lookup_fwd") if (B, S) == (64, 256) else None,
         "algorithmic_bytes_per_launch": algorithmic_bytes("scflow_corr_lookup_fwd", B, S)}
-    if kern[top]["tflops"] is not None and top in ("scflow_convgru_pass_fwd", "scflow_convgru_fwd"):
-        roof = {"kernel": top, "bound": "tensor", "achieved": kern[top]["tflops"], "peak": tf32_peak,
-                "unit": "TFLOP/s", "frac": kern[top]["tflops"] / tf32_peak, "traffic": traffic,
-                "peak_source": "cuBLAS TF32 8192^3 sustained, measured in this run (bf16 figure of "
-                               "MEASURED_PEAKS.json: %.0f sustained)" % pk["bf16_sustained"],
-                "algorithmic_flops_per_launch": algorithmic_flops(top, B, S)}
+
+    def tensor_roof(k):
+        t = kern[k]["tflops"]
+        return {"kernel": k, "bound": "tensor", "achieved": t, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
+                "frac": t / pk["bf16_sustained"], "traffic": ncu_traffic(k) if (B, S) == (64, 256) else None,
+                "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (%s)" % pk["src"],
+                "mma_per_product": mma_per_product(k) if mma_per_product(k) == 3.0 else 1.0,
+                "tensor_pipe_frac": t * mma_per_product(k) / pk["bf16_sustained"],
+                "note": "frac counts algorithmic flops; tensor_pipe_frac = executed MMA work in bf16-equivalents "
+                        "(3 bf16 MMAs per product for the split-bf16 kernels, 1 TF32 MMA = 2 bf16-equivalents)",
+                "tf32_cublas_peak_this_run": tf32_peak,
+                "algorithmic_flops_per_launch": kern[k]["flops_per_launch"], "avg_ms": kern[k]["avg_ms"],
+                "share_of_eager_step": kern[k]["share_of_eager_step"]}
+    if kern[top]["tflops"] is not None and kern[top]["tflops"] * 1e12 * 219e-12 > (kern[top]["gbs"] or 0):
+        roof = tensor_roof(top)
     else:
         roof = {"kernel": top, "bound": "hbm", "achieved": kern[top]["gbs"], "peak": pk["hbm"], "unit": "GB/s",
                 "frac": kern[top]["hbm_frac"], "traffic": traffic, "peak_source": pk["src"],
-                "algorithmic_bytes_per_launch": algorithmic_bytes(top, B, S)}
-    # bounded CPU baseline on this box's host cores (rank 0, N=1 only)
-    cpu = parity = strict = None
+                "algorithmic_bytes_per_launch": kern[top]["bytes_per_launch"]}
+    roof_convs = [tensor_roof(k) for k in conv_shapes[:6]]
+    conv_ms = sum(share(k) for k in conv_shapes)
+    conv_fl = sum(kern[k]["flops_per_launch"] * kern[k]["calls_per_step"] for k in conv_shapes)
+    conv_family = None if not conv_shapes else {
+        "launcher": "scflow_conv_tc_fwd", "shapes": len(conv_shapes),
+        "launches_per_step": sum(kern[k]["calls_per_step"] for k in conv_shapes), "ms_per_step": conv_ms,
+        "tflops": conv_fl / (conv_ms * 1e-3) / 1e12,
+        "frac": conv_fl / (conv_ms * 1e-3) / 1e12 / pk["bf16_sustained"],
+        "tensor_pipe_frac": 3 * conv_fl / (conv_ms * 1e-3) / 1e12 / pk["bf16_sustained"]}
+    # CPU baseline on this box's host cores (rank 0, N=1 only): the reference's own modules (unmodified files
+    # staged under baseline/_ref; the oracle port if absent) on a bounded sample of the step
+    cpu = parity = None
     if world == 1 and not args.no_cpu_baseline:
         from oracle import scflow_oracle as O          # checker only: the CPU leg and the parity read-out
         from scflow_b200.refiner import unpack_pose
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
-        sample = tile_batch(make_batch(2, 1234, S), 8)
-        n, ts = cpu_run(sample, cpu_refiner_state(), 2, 1)
-        cpu = {"value": n / (sum(ts) / len(ts)), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-               "sample": f"{n} crops per run, 1 warm-up + 2 timed runs of the oracle port (reference CPU path)"}
-        # deviation of the TIMED configuration from the fp32 CPU oracle on the same 8 crops, and the same
-        # read-out + a short timing with cuDNN in plain fp32 (the mode tests/ pin to 1e-4 rad)
+        ns = 16
+        sample = tile_batch(make_batch(4, 1234, S), ns)
+        model, kind = reference_model(S)
+        n, ts = cpu_run(sample, cpu_refiner_state(), 2, 1, model)
+        cpu = {"value": n / (sum(ts) / len(ts)), "unit": UNIT, "cores": torch.get_num_threads(), "kind": kind,
+               "sample": f"{n} of the step's {B} crops per run, 1 warm-up + 2 timed runs of "
+                         + ("the unmodified reference modules (baseline/_ref + shims)" if kind == "reference"
+                            else "the oracle port of the reference path") + ", PyTorch CPU fp32"}
+        # deviation of the TIMED configuration (there is only one) from that fp32 CPU run on the same crops
         Rc, tc_ = cpu_run.last_pose
         dsample = {k: v.to(dev) for k, v in sample.items()}
-
-        def deviation():
-            Rg, tg = unpack_pose(core.refine(dsample).cpu())
-            return {"rot_rad_max": float(O.rotation_geodesic(Rg, Rc).max()),
-                    "trans_mm_max": float((tg - tc_).abs().max())}
-        parity = dict(deviation(), crops=n, against="fp32 CPU oracle, same inputs and weights",
-                      cudnn_allow_tf32=torch.backends.cudnn.allow_tf32)
-        if not args.strict_fp32:
-            torch.backends.cudnn.allow_tf32 = False
-            for i in range(2):
-                core.refine(resident[i % 2])
-            torch.cuda.synchronize()
-            ms_s = timed(step_eager, 3, False) / 3
-            strict = dict(deviation(), value=B / (ms_s / 1e3), unit=UNIT, ms_per_step=ms_s, steps=3,
-                          execution="eager launches", cudnn_allow_tf32=False)
-            # cudnn.benchmark picks among several fp32 algorithms from run to run (summation orders differ;
-            # the read-out above moved between 8.6e-5 and 1.1e-4 rad over this round's boxes); the same
-            # read-out with the library's default algorithms -- the setting tests/ run in -- next to it
-            torch.backends.cudnn.benchmark = False
-            d0 = deviation()
-            torch.backends.cudnn.benchmark = True
-            strict["default_algorithms"] = {"rot_rad_max": d0["rot_rad_max"], "trans_mm_max": d0["trans_mm_max"]}
-            torch.backends.cudnn.allow_tf32 = True
+        Rg, tg = unpack_pose(core.refine(dsample).cpu())
+        parity = {"rot_rad_max": float(O.rotation_geodesic(Rg, Rc).max()),
+                  "trans_mm_max": float((tg - tc_).abs().max()), "crops": n,
+                  "budget": "1e-4 rad / 0.1 mm (north_star)",
+                  "against": "fp32 CPU run of the reference modules, same inputs and weights"}
     _emit(json.dumps({
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "tf32", "data": "synthetic",
+        "dtype": PRECISION_DTYPE, "data": "synthetic",
         "config": {"workload": workload(S, B), "crops_per_gpu_per_step": B, "image": S, "iters": 8,
                    "parallelism": f"batch-shard x{world} + pose all-gather",
                    "l2": "two alternating input sets; per-step working set (>450 MB) exceeds the 126 MB L2",
-                   "execution": "eager launches" if args.no_graph else "CUDA graph replay per step",
-                   "gru_backend": __import__("scflow_b200.gru", fromlist=["BACKEND"]).BACKEND,
-                   "cudnn_allow_tf32": not args.strict_fp32},
+                   "execution": "eager launches" if args.no_graph else "CUDA graph replay per step"},
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": launches, "roofline": roof, "roofline_lookup": roof_lookup, "tf32_peak_tflops": tf32_peak,
-        "eager_ms_per_step": ms_eager / args.steps, "event_pair_overhead_us": ev_ms * 1e3, "kernels": kern, "cpu_baseline": cpu, "clocks": clocks,
-        "precision": {"ours": "tcgen05 TF32 (correlation, ConvGRU; operands rounded to nearest), fp32 elsewhere",
-                      "cudnn": "fp32 (allow_tf32=False)" if args.strict_fp32 else
-                               "TF32 allowed (torch default = what the reference runs on a GPU)",
-                      "deviation_from_oracle": parity, "strict_fp32_cudnn": strict},
+        "gpu_launches": launches, "roofline": roof, "roofline_lookup": roof_lookup, "roofline_conv_shapes": roof_convs,
+        "conv_family": conv_family, "tf32_peak_tflops": tf32_peak,
+        "tf32_peak_note": "cuBLAS TF32 8192^3 back to back, builder-measured in this run (MEASURED_PEAKS.json has "
+                          "no TF32 entry)",
+        "eager_ms_per_step": ms_eager / args.steps, "event_pair_overhead_us": ev_ms * 1e3, "kernels": kern,
+        "cpu_baseline": cpu, "clocks": clocks,
+        "precision": {"ours": PRECISION_TEXT, "library_calls_on_the_path": "none (no cuDNN / cuBLAS)",
+                      "deviation_from_oracle": parity},
     }))
     if world > 1:
         dist.destroy_process_group()
@@ -607,7 +693,7 @@ def train_arm(args):
     null = per_kernel.pop("__null_kernel__", None)
     ev_ms = (null[1] / null[0]) if null else 0.0
     kern = {}
-    for name, (calls, tot, nbytes) in per_kernel.items():
+    for name, (calls, tot, nbytes, _fl) in per_kernel.items():
         raw_ms = tot / calls
         avg_ms = max(raw_ms - ev_ms, 0.25 * raw_ms)
         tot = avg_ms * calls
@@ -654,12 +740,10 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=64)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch-gpu"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--image", type=int, default=256, help="crop side (256 = configs[1]; 512 = configs[3])")
-    ap.add_argument("--strict-fp32", action="store_true",
-                    help="cuDNN convolutions in plain fp32 (torch.backends.cudnn.allow_tf32=False), the mode the parity tests pin")
     ap.add_argument("--train", action="store_true", help="configs[4]: forward+backward+optimizer step, batch 32/GPU")
     args = ap.parse_args()
     # libraries (NCCL's version banner, cuDNN warnings) write to fd 1: keep the real stdout for the
@@ -672,6 +756,8 @@ def main():
         train_arm(args)
     elif args.impl == "reference":
         reference_arm(args)
+    elif args.impl == "torch-gpu":
+        torch_gpu_arm(args)
     else:
         ours(args)
 

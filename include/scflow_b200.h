@@ -37,6 +37,11 @@ enum {
   SCFLOW_E_UNIMPLEMENTED = -8
 };
 
+/* scflow_conv_tc_desc.epi */
+#define SCFLOW_EPI_PLAIN 0
+#define SCFLOW_EPI_GRU_ZR 1
+#define SCFLOW_EPI_GRU_GATE 2
+
 /* correlation arithmetic */
 #define SCFLOW_PREC_FP32 0      /* CUDA-core fp32 FMA (exact-mode parity anchor)          */
 #define SCFLOW_PREC_TF32 1      /* tcgen05 kind::tf32, fp32 accumulate in TMEM (default)  */
@@ -83,34 +88,11 @@ int scflow_corr_lookup_fwd(const float* const* levels, int num_levels, const flo
 /* ---------------------------------------------------------------------------------------------
  * a3  ConvGRU.forward (SeqConv)    models/decoder/raft_decoder.py:235-253
  *     replaces 6 cuDNN convs + 6 activation kernels + 4 cat + 8 elementwise per iteration.
- * Channels-last activations: h_in/h_out (n, hgt, wid, ch) , x (n, hgt, wid, cx); fp32.
- * wpack: weights re-laid by scflow_convgru_pack_weights (device, size from _packed_floats).
- * rh_scratch: caller-owned (n, hgt, wid, ch) fp32 buffer for r*h (written and re-read by the
- * same CTA through L2).  h_out may alias h_in.  h_in_tf32 (optional): copy of h_in rounded to
- * nearest TF32, read by the tensor core instead of h_in (which tcgen05 would truncate); the
- * gating still uses the exact h_in.  h_out_tf32 (optional): receives that copy of h_out; may
- * alias h_in_tf32.  x is read by the tensor core as is (see scflow_pack_nhwc).  ch = 128, cx = 256, wid | 128 (pass 0) or
- * hgt | 128 (pass 1).  One call = one pass (pass 0: (1,5) taps along x, pass 1: (5,1) along y).
+ * Since ABI v5 the gates run on the split-bf16 convolution family below (scflow_conv_tc_fwd with
+ * epi = SCFLOW_EPI_GRU_ZR / SCFLOW_EPI_GRU_GATE: three launches per pass, fp32-grade products) instead of
+ * the TF32 kernels of ABI v4 (scflow_convgru_fwd / _pass_fwd: one TF32 MMA per product cost 5.7e-5 -
+ * 8.9e-5 rad of the 1e-4 rad pose budget in this module alone).
  * ------------------------------------------------------------------------------------------- */
-size_t scflow_convgru_packed_floats(int ch, int cx);
-int scflow_convgru_pack_weights(const float* wz, const float* wr, const float* wq,
-                                const float* bz, const float* br, const float* bq,
-                                float* wpack, int ch, int cx, int pass, void* stream);
-int scflow_convgru_pass_fwd(const float* h_in, const float* h_in_tf32, const float* x,
-                            const float* wpack, float* h_out, float* h_out_tf32, float* rh_scratch,
-                            int n, int hgt, int wid, int ch, int cx, int pass, void* stream);
-/* Both passes of ConvGRU.forward (raft_decoder.py:245-252) in ONE persistent launch, in place:
- * h (exact fp32 state) and h_tf32 (its nearest-TF32 copy, optional) are read and overwritten.
- * The (1,5) and (5,1) passes become one list of work items; a (5,1) item waits on a per-image
- * counter (workspace) that the (1,5) items of the same image release, so the two passes fill
- * the SMs as 7 waves instead of 2 x 4 at 64 crops.  workspace: scflow_convgru_workspace_bytes()
- * bytes of device memory, 4-byte aligned, zeroed by the call itself (a memset node on `stream`).
- * wpack0 / wpack1: packed weights of pass 0 / pass 1.  Results are bit-identical to two
- * scflow_convgru_pass_fwd calls. */
-size_t scflow_convgru_workspace_bytes(int n, int hgt, int wid);
-int scflow_convgru_fwd(float* h, float* h_tf32, const float* x, const float* wpack0,
-                       const float* wpack1, float* rh_scratch, void* workspace,
-                       size_t workspace_bytes, int n, int hgt, int wid, int ch, int cx, void* stream);
 
 /* Channels-last packing of the GRU input x = cat[cxt, motion, flow] (raft_decoder.py:166 and
  * scflow_decoder.py:208) with round-to-nearest TF32, replacing two torch.cat and a layout pass.
@@ -284,6 +266,18 @@ typedef struct scflow_conv_tc_desc {
   /* optional: per-(image, channel) sum and sum of squares of the value BEFORE residual/ReLU
    * (after bias), added into stats[n][cout8][2] (zeroed by the caller) -- InstanceNorm statistics */
   double* stats;
+  /* tile width override: output channels per tile (multiple of 16 that divides the padded cout), 0 = the
+   * widest tile (<= 256).  Narrower tiles trade operand re-reads for fuller waves. */
+  int bn;
+  /* epilogue: SCFLOW_EPI_PLAIN, or the two ConvGRU epilogues (models/decoder/raft_decoder.py:245-252) over
+   * gru_h (n, OH, OW, gru_c) exact fp32 hidden state and gru_z (same shape) update gate:
+   *   GRU_ZR    cout = 2 gru_c = [z | r] pre-activations: z = sigmoid(.) -> gru_z; r = sigmoid(.),
+   *             r * gru_h -> out_split (gru_c channels)
+   *   GRU_GATE  cout = gru_c, res_f32 = the x-part of the q convolution: q = tanh(acc + res + bias);
+   *             gru_h = (1 - z) gru_h + z q in place, and as split planes -> out_split */
+  int epi, gru_c;
+  float* gru_h;
+  float* gru_z;
 } scflow_conv_tc_desc;
 
 /* Output spatial size: OH = (h + 2 pad_h - kh) / stride + 1, likewise OW.  Supported: OW a multiple of
@@ -301,6 +295,12 @@ int scflow_conv_tc_pack_weights(const float* w, const float* scale, void* packed
  * out_lo elements after the hi plane); channels rounded up to 8 are written (zeros beyond). */
 int scflow_split_bf16(const float* in, long long in_pitch, void* out, long long out_pitch, int out_lo,
                       int channels, long long pixels, void* stream);
+
+/* planar fp32 (n, cf, pixels) -> channels [0, cf) of a split-plane slice starting at `out` (hi plane; lo plane
+ * out_lo elements further; out_pitch elements per pixel): the flow pair appended to the motion features
+ * (raft_decoder.py:165). */
+int scflow_split_planar(const float* in, void* out, long long out_pitch, int out_lo, int n, int cf,
+                        long long pixels, void* stream);
 
 /* InstanceNorm2d (+ residual) + ReLU of a raw convolution output (n, P, C) fp32 from the statistics
  * scflow_conv_tc_fwd accumulated (sums[n][C][2]), written as split planes for the next convolution

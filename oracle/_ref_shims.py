@@ -23,7 +23,11 @@ import types
 import torch
 import torch.nn as nn
 
-REF_ROOT = os.environ.get("SCFLOW_REFERENCE_ROOT", "/root/reference")
+_STAGED = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "_ref")
+# the read-only mount in the dev container; on the GPU box the byte-identical copies staged by
+# oracle/stage_ref.py under baseline/_ref/ (git-ignored, travels with the snapshot)
+REF_ROOT = os.environ.get("SCFLOW_REFERENCE_ROOT") or (
+    "/root/reference" if os.path.isfile("/root/reference/models/decoder/scflow_decoder.py") else _STAGED)
 
 
 def reference_available() -> bool:
@@ -213,3 +217,37 @@ DECODER_CFG = dict(
                        norm_cfg=dict(type="GN", num_groups=32, requires_grad=True),
                        act_cfg=dict(type="ReLU")),
     corr_lookup_cfg=dict(align_corners=True), gru_type="SeqConv", act_cfg=dict(type="ReLU"))
+
+
+class ReferenceRefiner(nn.Module):
+    """The part of SCFlowRefiner.get_pose the metric covers (models/refiner/scflow_refiner.py:84-138), assembled
+    from the UNMODIFIED reference classes: shared IN RAFTEncoder on real and rendered images, BN context
+    RAFTEncoder on the rendered images, tanh / relu split, SCFlowDecoder with a zero init flow and
+    invalid_flow_num = 0.  (scflow_refiner.py itself needs the pytorch3d renderer to import.)"""
+
+    def __init__(self, image_size: int = 256, state=None):
+        super().__init__()
+        import copy
+        R = load_reference()
+        self.encoder = R.RAFTEncoder(in_channels=3, out_channels=256, net_type="Basic", norm_cfg=dict(type="IN"))
+        self.context = R.RAFTEncoder(in_channels=3, out_channels=256, net_type="Basic", norm_cfg=dict(type="BN"))
+        cfg = copy.deepcopy(DECODER_CFG)
+        cfg["pose_head_cfg"]["feat_size"] = (image_size // 8, image_size // 8)
+        self.decoder = R.SCFlowDecoder(**cfg)
+        if state is not None:
+            self.encoder.load_state_dict(state[0])
+            self.context.load_state_dict(state[1])
+            self.decoder.load_state_dict(state[2])
+        self.eval()
+
+    @torch.no_grad()
+    def forward(self, batch):
+        real_feat = self.encoder(batch["real_images"])
+        render_feat = self.encoder(batch["rendered_images"])
+        cxt = self.context(batch["rendered_images"])
+        h, c = torch.split(cxt, [128, 128], dim=1)
+        n, _, hh, ww = batch["real_images"].shape
+        init_flow = torch.zeros((n, 2, hh, ww), dtype=torch.float32, device=real_feat.device)
+        out = self.decoder(render_feat, real_feat, torch.tanh(h), torch.relu(c), batch["R0"], batch["t0"],
+                           batch["depth"], batch["K"], batch["labels"], init_flow, 0.)
+        return out[2][-1], out[3][-1]

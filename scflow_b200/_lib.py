@@ -24,11 +24,6 @@ SIGNATURES = {
     "scflow_corr_pyramid_fwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                                         _P, c_size_t, _P]),
     "scflow_corr_lookup_fwd": (c_int, [_P, c_int, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
-    "scflow_convgru_packed_floats": (c_size_t, [c_int, c_int]),
-    "scflow_convgru_pack_weights": (c_int, [_P] * 7 + [c_int, c_int, c_int, _P]),
-    "scflow_convgru_pass_fwd": (c_int, [_P] * 7 + [c_int, c_int, c_int, c_int, c_int, c_int, _P]),
-    "scflow_convgru_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
-    "scflow_convgru_fwd": (c_int, [_P] * 7 + [c_size_t, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_pack_nhwc": (c_int, [_P, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, ctypes.c_longlong, c_int,
                                  c_int, _P]),
     "scflow_chan_stats_nhwc": (c_int, [_P, _P, c_int, c_int, c_int, _P]),
@@ -50,6 +45,7 @@ SIGNATURES = {
     "scflow_conv_tc_fwd": (c_int, [_P, _P]),
     "scflow_conv_tc_packed_bytes": (c_size_t, [c_int] * 5),
     "scflow_conv_tc_pack_weights": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
+    "scflow_split_planar": (c_int, [_P, _P, ctypes.c_longlong, c_int, c_int, c_int, ctypes.c_longlong, _P]),
     "scflow_norm_apply_split": (c_int, [_P, _P, _P, ctypes.c_longlong, c_int, _P, _P, _P, ctypes.c_longlong, c_int,
                                         _P, c_int, c_int, c_int, c_float, c_int, _P]),
     "scflow_split_bf16": (c_int, [_P, ctypes.c_longlong, _P, ctypes.c_longlong, c_int, c_int, ctypes.c_longlong, _P]),

@@ -34,7 +34,11 @@ class _Desc(ctypes.Structure):
         ("out_split", ctypes.c_void_p), ("out_pitch", ctypes.c_longlong), ("out_lo", ctypes.c_int),
         ("out_f32", ctypes.c_void_p), ("outf_pitch", ctypes.c_longlong), ("f32_tf32", ctypes.c_int),
         ("out_planar", ctypes.c_void_p), ("planar_tf32", ctypes.c_int),
-        ("stats", ctypes.c_void_p)]
+        ("stats", ctypes.c_void_p), ("bn", ctypes.c_int), ("epi", ctypes.c_int), ("gru_c", ctypes.c_int),
+        ("gru_h", ctypes.c_void_p), ("gru_z", ctypes.c_void_p)]
+
+
+EPI_PLAIN, EPI_GRU_ZR, EPI_GRU_GATE = 0, 1, 2
 
 
 def _rup(v: int, m: int) -> int:
@@ -190,7 +194,8 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
          res_f32: Optional[torch.Tensor] = None, out: Optional[Split] = None,
          out_f32: Optional[torch.Tensor] = None, out_planar: Optional[torch.Tensor] = None,
          planar_tf32: bool = False, f32_tf32: bool = False, stats: Optional[torch.Tensor] = None, want: str = "split",
-         view=None):
+         view=None, bn: int = 0, epi: int = EPI_PLAIN, gru_h: Optional[torch.Tensor] = None,
+         gru_z: Optional[torch.Tensor] = None):
     """One convolution launch.  x: Split (n, h, w, cin).  Outputs: `out` (Split), `out_f32` (n, OH, OW, >=cout)
     fp32 channels-last (may be a channel slice of a wider buffer), `out_planar` (n, cout, OH, OW); when none is
     given one is allocated according to `want` ("split" | "f32" | "planar").  `view` = (n, h, w, cin, lo_off,
@@ -222,6 +227,12 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
     d.bias = pk.bias.data_ptr() if pk.bias is not None else None
     d.relu = int(relu)
     c8 = _rup(pk.cout, 8)
+    d.bn, d.epi = bn, epi
+    if epi != EPI_PLAIN:
+        # ConvGRU epilogues: exact fp32 state + update gate, (n, oh, ow, C) contiguous; out = a C-channel slice
+        assert gru_h.is_contiguous() and gru_z.is_contiguous() and gru_h.shape == gru_z.shape
+        d.gru_c, d.gru_h, d.gru_z = gru_h.shape[-1], gru_h.data_ptr(), gru_z.data_ptr()
+        c8 = gru_h.shape[-1]
     if res is not None:
         assert tuple(res.shape) == (n, oh, ow) and res.c >= pk.cout
         d.res_split, d.res_pitch, d.res_lo = res.hi_ptr(), res.pitch, res.cp
@@ -242,11 +253,26 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
         assert stats.dtype == torch.float64 and stats.shape == (n, c8, 2) and stats.is_contiguous()
         d.stats = stats.data_ptr()
     flops = 2 * n * oh * ow * pk.cout * pk.cin * pk.kh * pk.kw
-    with _timed("scflow_conv_tc_fwd", 1, flops):
+    # algorithmic bytes: split-plane input once, packed filter once, every output written once
+    nbytes = (4 * n * h * w * cin + pk.w.numel() * 2
+              + n * oh * ow * c8 * 4 * sum(o is not None for o in (out, out_f32, out_planar))
+              + (4 * n * oh * ow * c8 if (res is not None or res_f32 is not None) else 0))
+    name = f"scflow_conv_tc_fwd[{pk.kh}x{pk.kw}/{pk.stride} {cin}->{pk.cout} @{oh}x{ow}]"
+    with _timed(name, 1, nbytes, flops):
         rc = lib.scflow_conv_tc_fwd(ctypes.byref(d), _stream())
     _lib.check(rc, f"scflow_conv_tc_fwd({n}x{h}x{w}x{cin} -> {pk.cout}, {pk.kh}x{pk.kw}/{pk.stride})")
     res_ = tuple(o for o in (out, out_f32, out_planar) if o is not None)
     return res_[0] if len(res_) == 1 else res_
+
+
+def split_planar(x: torch.Tensor, out: Split) -> None:
+    """planar fp32 (n, cf, h, w) -> the cf channels of the split slice `out` (scflow_split_planar)."""
+    lib = _lib.load()
+    n, cf, h, w = x.shape
+    assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and tuple(out.shape) == (n, h, w) and out.c == cf
+    with _timed("scflow_split_planar", 1, 8 * x.numel()):
+        rc = lib.scflow_split_planar(_ptr(x), ctypes.c_void_p(out.hi_ptr()), out.pitch, out.cp, n, cf, h * w, _stream())
+    _lib.check(rc, "scflow_split_planar")
 
 
 def norm_apply(x: torch.Tensor, sums: torch.Tensor, *, relu: bool = True, eps: float = 1e-5,

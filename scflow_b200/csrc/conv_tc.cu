@@ -63,6 +63,11 @@ struct Params {
   float* out_f32; long long outf_pitch; int f32_tf32;   // fp32 channels-last, optionally RN to TF32
   float* out_planar; int planar_tf32;          // (N, cout_store, OH*OW) fp32, optionally RN to TF32
   double* stats;                               // [n][cout_store][2] sum, sum of squares (pre-activation)
+  int fold;                                    // bn <= 128: A_hi x [B_hi;B_lo] as ONE N = 2 bn MMA (see the issuer)
+  // ConvGRU epilogues (epi = SCFLOW_EPI_*): exact fp32 hidden state (n, OH, OW, gru_c), update gate z
+  int epi, gru_c;
+  float* gru_h;
+  float* gru_z;
 };
 
 __device__ __forceinline__ uint32_t make_idesc_bf16(int m, int n) {
@@ -86,6 +91,14 @@ __device__ __forceinline__ float rn_tf32(float v) {
   uint32_t u;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
   return __uint_as_float(u);
+}
+
+// sigmoid / tanh from one ex2.approx and one rcp.approx each (a few ulp of fp32: well below the 2^-17 of the
+// split operands they feed)
+__device__ __forceinline__ float sigmoidf_(float v) { return __fdividef(1.0f, 1.0f + __expf(-v)); }
+__device__ __forceinline__ float tanhf_(float v) {
+  const float e = __expf(-2.0f * fabsf(v));                 // in (0, 1]: no overflow
+  return copysignf(__fdividef(1.0f - e, 1.0f + e), v);
 }
 
 // v -> (hi, lo) bf16 pair; two values packed per 32-bit word (low half = first value)
@@ -180,6 +193,7 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       const uint32_t idesc = make_idesc_bf16(BM, p.bn);
+      const uint32_t idesc2 = make_idesc_bf16(BM, 2 * p.bn);
       const uint32_t smem0 = tc::smem_u32(smem);
       int stage = 0; uint32_t phase = 0; uint32_t it = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
@@ -203,9 +217,18 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
               const uint64_t dal = tc::make_smem_desc(a_lo + ks * 32, 16, kSbo, kLayout);
               const uint64_t dbh = tc::make_smem_desc(b_hi + ks * 32, 16, kSbo, kLayout);
               const uint64_t dbl = tc::make_smem_desc(b_lo + ks * 32, 16, kSbo, kLayout);
-              mma_bf16_ss(d, dal, dbh, idesc, acc);          // small terms first
-              mma_bf16_ss(d, dah, dbl, idesc, 1u);
-              mma_bf16_ss(d, dah, dbh, idesc, 1u);
+              if (p.fold) {
+                // An M = 128 MMA occupies the pipe for >= 64 cycles whatever N is (measured: 32-, 64- and
+                // 128-channel tiles took the same time), so narrow tiles fold two of the three products
+                // into one instruction: [B_hi;B_lo] are adjacent in the stage = one 2 bn-row operand;
+                // columns [0,bn) get a_hi.b_hi, [bn,2bn) a_hi.b_lo, the epilogue adds the halves
+                mma_bf16_ss(d, dah, dbh, idesc2, acc);
+                mma_bf16_ss(d, dal, dbh, idesc, 1u);
+              } else {
+                mma_bf16_ss(d, dal, dbh, idesc, acc);        // small terms first
+                mma_bf16_ss(d, dah, dbl, idesc, 1u);
+                mma_bf16_ss(d, dah, dbh, idesc, 1u);
+              }
               acc = 1u;
             }
             tc::tc_commit(&empty[stage]);
@@ -238,7 +261,15 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
       for (int j = half; j < chunks; j += 2) {
         float v[32];
         tc::tmem_ld_32x32(taddr + j * 32, v);
-        tc::tmem_ld_wait();
+        if (p.fold) {
+          float u[32];
+          tc::tmem_ld_32x32(taddr + p.bn + j * 32, u);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] += u[i];
+        } else {
+          tc::tmem_ld_wait();
+        }
         const int c0 = tl.nt * p.bn + j * 32;               // first output channel of the chunk
         int nv = p.cout_store - c0;                          // channels of it that are stored
         nv = nv > 32 ? 32 : nv;
@@ -275,6 +306,68 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
           }
         }
         if (!live) continue;
+        if (p.epi == SCFLOW_EPI_GRU_ZR) {
+          // raft_decoder.py:247-250, first half: channels [0,C) z = sigmoid(.) -> gru_z (fp32);
+          // channels [C,2C) r = sigmoid(.), r.h -> split planes (the operand of the q convolution)
+          if (c0 < p.gru_c) {
+            float4* zp = reinterpret_cast<float4*>(p.gru_z + pix * p.gru_c + c0);
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              zp[k] = make_float4(sigmoidf_(v[4 * k]), sigmoidf_(v[4 * k + 1]), sigmoidf_(v[4 * k + 2]),
+                                  sigmoidf_(v[4 * k + 3]));
+          } else {
+            const int cc = c0 - p.gru_c;
+            const float4* hp = reinterpret_cast<const float4*>(p.gru_h + pix * p.gru_c + cc);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              const float4 h = __ldg(hp + k);
+              v[4 * k] = sigmoidf_(v[4 * k]) * h.x; v[4 * k + 1] = sigmoidf_(v[4 * k + 1]) * h.y;
+              v[4 * k + 2] = sigmoidf_(v[4 * k + 2]) * h.z; v[4 * k + 3] = sigmoidf_(v[4 * k + 3]) * h.w;
+            }
+            uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + cc);
+            uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + cc);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              uint4 h, l;
+              split2(v[8 * k], v[8 * k + 1], h.x, l.x);
+              split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
+              split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
+              split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
+              oh[k] = h;
+              ol[k] = l;
+            }
+          }
+          continue;
+        }
+        if (p.epi == SCFLOW_EPI_GRU_GATE) {
+          // raft_decoder.py:251-252: q = tanh(conv(r.h) + [x part of the q convolution, res_f32] + b);
+          // h = (1 - z) h + z q, in place in the exact fp32 state, and as split planes for the next operand
+          const float4* qp = reinterpret_cast<const float4*>(p.res_f32 + pix * p.resf_pitch + c0);
+          const float4* zp = reinterpret_cast<const float4*>(p.gru_z + pix * p.gru_c + c0);
+          float4* hp = reinterpret_cast<float4*>(p.gru_h + pix * p.gru_c + c0);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float4 qx = __ldg(qp + k), z = __ldg(zp + k), h = hp[k];
+            v[4 * k] = (1.0f - z.x) * h.x + z.x * tanhf_(v[4 * k] + qx.x);
+            v[4 * k + 1] = (1.0f - z.y) * h.y + z.y * tanhf_(v[4 * k + 1] + qx.y);
+            v[4 * k + 2] = (1.0f - z.z) * h.z + z.z * tanhf_(v[4 * k + 2] + qx.z);
+            v[4 * k + 3] = (1.0f - z.w) * h.w + z.w * tanhf_(v[4 * k + 3] + qx.w);
+            hp[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+          }
+          uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + c0);
+          uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + c0);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            uint4 h, l;
+            split2(v[8 * k], v[8 * k + 1], h.x, l.x);
+            split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
+            split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
+            split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
+            oh[k] = h;
+            ol[k] = l;
+          }
+          continue;
+        }
         if (p.res_split) {
           const uint4* rh = reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + c0);
           const uint4* rl = reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + p.res_lo + c0);
@@ -483,6 +576,24 @@ norm_apply_split_kernel(const ApplyParams p) {
   }
 }
 
+// planar fp32 (n, cf, P) -> channels [0, cf) of a split-plane slice (element stores: cf is 1-2 channels,
+// the flow pair the reference concatenates behind the motion features, raft_decoder.py:165)
+__global__ void split_planar_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long out_pitch,
+                                    int out_lo, int cf, long long P, long long total) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long pix = i % P;
+    const long long r = i / P;
+    const int c = (int)(r % cf);
+    const long long n = r / cf;
+    const float v = in[i];
+    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    __nv_bfloat16* o = out + (n * P + pix) * out_pitch + c;
+    o[0] = hi;
+    o[out_lo] = __float2bfloat16_rn(v - __bfloat162float(hi));
+  }
+}
+
 static bool encode_bf16_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
                             const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr, int bk) {
   tc::EncodeTiledFn fn = tc::get_encode_tiled();
@@ -552,6 +663,17 @@ extern "C" int scflow_split_bf16(const float* in, long long in_pitch, void* out,
   return check_launch();
 }
 
+extern "C" int scflow_split_planar(const float* in, void* out, long long out_pitch, int out_lo, int n, int cf,
+                                   long long pixels, void* stream) {
+  if (!in || !out) return SCFLOW_E_NULL;
+  if (n <= 0 || cf <= 0 || pixels <= 0) return SCFLOW_E_BAD_SHAPE;
+  const long long total = (long long)n * cf * pixels;
+  const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+  ctc::split_planar_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(in, static_cast<__nv_bfloat16*>(out), out_pitch,
+                                                                     out_lo, cf, pixels, total);
+  return check_launch();
+}
+
 extern "C" int scflow_norm_apply_split(const float* x, const double* sums, const void* res_split, long long res_pitch,
                                        int res_lo, const float* res_raw, const double* res_sums, void* out,
                                        long long out_pitch, int out_lo, float* out_f32, int n, int P, int C,
@@ -604,6 +726,12 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
   const int groups = (p.n + p.NI - 1) / p.NI;
   p.m_tiles = groups * p.tiles_x * p.tiles_y;
   p.cout_pad = cout_pad_of(d->cout, &p.bn, &p.n_tiles);
+  if (d->bn > 0) {                             // caller-chosen tile width (wave quantisation): must tile the pack
+    if ((d->bn % 16) || d->bn > 256 || (p.cout_pad % d->bn)) return SCFLOW_E_BAD_SHAPE;
+    p.bn = d->bn;
+    p.n_tiles = p.cout_pad / d->bn;
+  }
+  p.fold = p.bn <= 128 ? 1 : 0;
   p.cout_store = (d->cout + 7) / 8 * 8;
   const int bk = d->bk;
   p.kblocks = (d->cin + bk - 1) / bk;
@@ -623,6 +751,15 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
   p.out_f32 = d->out_f32; p.outf_pitch = d->outf_pitch; p.f32_tf32 = d->f32_tf32;
   p.out_planar = d->out_planar; p.planar_tf32 = d->planar_tf32;
   p.stats = d->stats;
+  p.epi = d->epi; p.gru_c = d->gru_c; p.gru_h = d->gru_h; p.gru_z = d->gru_z;
+  if (p.epi != SCFLOW_EPI_PLAIN) {
+    // the gate epilogues work on whole 32-channel chunks of a 32-aligned hidden width
+    if (p.epi != SCFLOW_EPI_GRU_ZR && p.epi != SCFLOW_EPI_GRU_GATE) return SCFLOW_E_UNSUPPORTED;
+    if (!p.gru_h || !p.gru_z || !p.out_split || p.gru_c <= 0 || (p.gru_c % 32) || (p.bn % 32) || p.stats ||
+        d->cout != (p.epi == SCFLOW_EPI_GRU_ZR ? 2 : 1) * p.gru_c || (p.epi == SCFLOW_EPI_GRU_GATE && !p.res_f32))
+      return SCFLOW_E_BAD_SHAPE;
+    if (!aligned16(p.gru_h) || !aligned16(p.gru_z)) return SCFLOW_E_MISALIGNED;
+  }
   if (!p.out_split && !p.out_f32 && !p.out_planar) return SCFLOW_E_NULL;
   if (p.stats && p.OH * p.OW < 32) return SCFLOW_E_BAD_SHAPE;
   if ((p.out_split && (!aligned16(p.out_split) || (p.out_pitch % 8) || (p.out_lo % 8))) ||

@@ -21,7 +21,7 @@ import torch
 import torch.nn as nn
 
 from . import convtc as C
-from . import gru, gru_tc, ops
+from . import gru_tc, ops
 from .modules import (ConvGRU, ConvModule, CorrelationPyramid, CorrLookup, MotionEncoder, XHead,
                       _needs_grad)
 from .registry import MODELS, register
@@ -98,31 +98,31 @@ class SCFlowDecoder(nn.Module):
         flow_from_pose, flow_from_pred, mask_preds = [], [], []
         # scflow_decoder.py:197-198 on the caller-supplied init flow (zeros from the refiner)
         flow = ops.downsample(init_flow.float(), scale, 1.0 / scale)
-        # Channels-last state for the whole loop, no torch.cat anywhere:
-        #   x = cat[cxt | motion | flow] is ONE (N,h,w,256) fp32 buffer (TF32-rounded, the ConvGRU operand): the
-        #     context half is packed once, out_net's epilogue writes the motion half every iteration;
-        #   pose_in = cat[h | delta-flow feat | mask feat] is ONE 224-channel split-plane buffer: the hidden
-        #     state's split copy doubles as the heads' operand, the two small encoders write their slices.
+        # Channels-last state for the whole loop, no torch.cat anywhere.  ONE split-plane buffer per pixel
+        #   [ cxt 128 | motion 126 + flow 2 | h 128 | delta-flow feat 64 | mask feat 32 ]
+        # so that every consumer reads a contiguous channel range: the ConvGRU [x | h] = channels 0..383, the
+        # heads h = 256..383, the pose head cat[h | delta-flow feat | mask feat] = 256..479; every producer's
+        # epilogue writes its slice.  The exact fp32 hidden state (the gate arithmetic) lives beside it.
         n_, _, hh, ww = h_feat.shape
         dev = h_feat.device
-        h_state = h_feat.float().permute(0, 2, 3, 1).contiguous()
-        h_round = gru_tc.round_tf32(h_state)
-        rh = torch.empty_like(h_state)
         cx, hc = self.cxt_channels, self.h_channels
-        if self.encoder.out_channels[0] != 126 or self.gru.x_channels != 256 or cx != 128:
+        mo = self.encoder.out_channels[0] + 2
+        if self.gru.x_channels != cx + mo or mo % 8:
             raise NotImplementedError("decoder widths other than the Basic net's 128 | 126 + 2")
-        x_buf = torch.empty((n_, hh, ww, self.gru.x_channels), device=dev, dtype=torch.float32)
-        ops.pack_nhwc(x_buf, 0, a=cxt_feat.float().permute(0, 2, 3, 1).contiguous())
         dfe, me = self.delta_flow_encoder, self.mask_encoder
         c_df, c_m = dfe[1].conv.out_channels, me[1].conv.out_channels
-        pose_in = C.alloc_split(n_, hh, ww, hc + c_df + c_m, dev)
-        h_split = pose_in.slice(0, hc)
+        S = C.alloc_split(n_, hh, ww, cx + mo + hc + c_df + c_m, dev)
+        h_state = h_feat.float().permute(0, 2, 3, 1).contiguous().clone()
+        C.to_split(cxt_feat.float().permute(0, 2, 3, 1), out=S.slice(0, cx))
+        h_split = S.slice(cx + mo, hc)
+        C.to_split(h_state, out=h_split)
+        xh, motion = S.slice(0, cx + mo + hc), S.slice(cx, mo)
+        pose_in = S.slice(cx + mo, hc + c_df + c_m)
+        scratch = gru_tc.Scratch(n_, hh, ww, hc, dev)
         for _ in range(self.iters):
             corr = self.corr_lookup(corr_pyramid, flow)
-            self.encoder.features_into(corr, flow, x_buf, cx)
-            ops.pack_nhwc(x_buf, cx + 126, planar=flow)
-            gru_tc.update_inplace(self.gru, h_state, h_round, x_buf, rh)
-            C.to_split(h_state, out=h_split)
+            self.encoder.features_into(corr, flow, motion)
+            gru_tc.update_inplace(self.gru, xh, h_state, scratch)
             delta_flow_pred = self.flow_pred.forward_split(h_split)
             mask = torch.sigmoid(self.mask_pred.forward_split(h_split))
             d0 = dfe[0](delta_flow_pred)                               # 7x7 on 2 channels: FMA kernel

@@ -188,11 +188,11 @@ class MotionEncoder(nn.Module):
         """The 126 learned motion channels (raft_decoder.py:162-165), before `flow` is appended."""
         return self.out_net(torch.cat([self.corr_net(corr), self.flow_net(flow)], dim=1))
 
-    def features_into(self, corr: torch.Tensor, flow: torch.Tensor, x_buf: torch.Tensor, off: int) -> None:
-        """Inference: the motion channels written, rounded to the nearest TF32 (the ConvGRU's operand format),
-        into x_buf[..., off:off+128] (126 channels + 2 zeros; the caller packs the flow pair over the zeros).
-        corr: (N,324,h,w)-shaped channels-last lookup result; flow: planar (N,2,h,w); x_buf (N,h,w,256) fp32.
-        Five tensor-core / FMA launches; what the reference concatenates is written in place: corr_net and
+    def features_into(self, corr: torch.Tensor, flow: torch.Tensor, out: "C.Split") -> None:
+        """Inference: motion features + flow (raft_decoder.py:162-166) written as split planes into `out`, a
+        128-channel slice (126 motion channels, then the flow pair) of the ConvGRU's operand buffer.
+        corr: (N,324,h,w)-shaped channels-last lookup result; flow: planar (N,2,h,w).
+        Tensor-core / FMA launches only; what the reference concatenates is written in place: corr_net and
         flow_net store into the two channel slices of one split buffer that out_net reads."""
         n, _, h, w = corr.shape
         cs = C.to_split(corr.permute(0, 2, 3, 1))
@@ -202,15 +202,18 @@ class MotionEncoder(nn.Module):
         self.corr_net[1].forward_split(a, out=cat.slice(0, c1))
         f0 = self.flow_net[0](flow)                                     # 7x7 on 2 channels: FMA kernel
         self.flow_net[1].forward_split(C.to_split(f0.permute(0, 2, 3, 1)), out=cat.slice(c1, 256 - c1))
-        self.out_net[0].forward_split(cat, out_f32=x_buf[..., off:off + 128], f32_tf32=True)
+        co = self.out_net[0].conv.out_channels
+        self.out_net[0].forward_split(cat, out=out.slice(0, co))        # writes co rounded up to 8 (zeros)
+        C.split_planar(flow, C.Split(out.buf, 2, out.off + co))        # the flow pair over those zeros
 
     def forward(self, corr: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
         if _needs_grad(corr, flow, *self.parameters()):
             return torch.cat([self.features(corr, flow), flow], dim=1)
         n, _, h, w = corr.shape
-        buf = torch.empty((n, h, w, 128), device=corr.device, dtype=torch.float32)
-        self.features_into(corr.contiguous(memory_format=torch.channels_last), flow.contiguous(), buf, 0)
-        return torch.cat([buf[..., :126].permute(0, 3, 1, 2), flow], dim=1)
+        co = self.out_net[0].conv.out_channels
+        buf = C.alloc_split(n, h, w, co + 2, corr.device)
+        self.features_into(corr.contiguous(memory_format=torch.channels_last), flow.contiguous(), buf)
+        return buf.float().permute(0, 3, 1, 2)
 
 
 class XHead(nn.Module):

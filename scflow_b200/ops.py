@@ -24,17 +24,19 @@ class LaunchStats:
     def __init__(self):
         self.count = 0
         self.timing = False
-        self.events = []          # (name, kernels_in_call, start, end, algorithmic bytes or None)
+        self.events = []          # (name, kernels_in_call, start, end, algorithmic bytes or None, flops or None)
 
     def reset(self, timing: bool = False):
         self.count, self.timing, self.events = 0, timing, []
 
     def summary(self):
-        """{name: (calls, total_ms, total algorithmic bytes or None)} -- call after a synchronize."""
+        """{name: (calls, total_ms, total algorithmic bytes or None, total algorithmic flops or None)} -- call
+        after a synchronize."""
         out = {}
-        for name, _, a, b, nb in self.events:
-            c, t, by = out.get(name, (0, 0.0, 0))
-            out[name] = (c + 1, t + a.elapsed_time(b), None if (nb is None or by is None) else by + nb)
+        for name, _, a, b, nb, fl in self.events:
+            c, t, by, f = out.get(name, (0, 0.0, 0, 0))
+            out[name] = (c + 1, t + a.elapsed_time(b), None if (nb is None or by is None) else by + nb,
+                         None if (fl is None or f is None) else f + fl)
         return out
 
 
@@ -42,8 +44,8 @@ STATS = LaunchStats()
 
 
 class _timed:
-    def __init__(self, name, kernels=1, nbytes=None):
-        self.name, self.kernels, self.nbytes = name, kernels, nbytes
+    def __init__(self, name, kernels=1, nbytes=None, flops=None):
+        self.name, self.kernels, self.nbytes, self.flops = name, kernels, nbytes, flops
 
     def __enter__(self):
         STATS.count += self.kernels
@@ -56,7 +58,7 @@ class _timed:
     def __exit__(self, *exc):
         if STATS.timing:
             self.b.record()
-            STATS.events.append((self.name, self.kernels, self.a, self.b, self.nbytes))
+            STATS.events.append((self.name, self.kernels, self.a, self.b, self.nbytes, self.flops))
         return False
 
 

@@ -44,5 +44,5 @@ print(f"eager step {tot:.2f} ms")
 for (name, ty), (c, t) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:45]:
     print(f"{t:8.3f} ms  {100*t/tot:5.1f}%  x{c:3d}  {t/c*1e3:7.1f} us  {ty:14s} {name}")
 print("-- our launchers")
-for name, (c, t, nb) in sorted(ops.STATS.summary().items(), key=lambda kv: -kv[1][1]):
+for name, (c, t, nb, _fl) in sorted(ops.STATS.summary().items(), key=lambda kv: -kv[1][1]):
     print(f"{t:8.3f} ms  {100*t/tot:5.1f}%  x{c:3d}  {t/c*1e3:7.1f} us  {name}")
