@@ -34,7 +34,8 @@ enum {
   SCFLOW_E_LAUNCH = -5,         /* cudaGetLastError() after the launch was not success    */
   SCFLOW_E_WORKSPACE = -6,      /* workspace too small                                    */
   SCFLOW_E_DRIVER = -7,         /* driver entry point (cuTensorMapEncodeTiled) missing    */
-  SCFLOW_E_UNIMPLEMENTED = -8
+  SCFLOW_E_UNIMPLEMENTED = -8,
+  SCFLOW_E_STATIC_SCRATCH = -9  /* problem needs more scratch than the library's static device array */
 };
 
 /* scflow_conv_tc_desc.epi */
@@ -197,6 +198,21 @@ int scflow_pose_fc_fwd(const float* x, const float* w0, const float* b0, const f
                        const float* wr, const float* br, const float* wt, const float* bt,
                        const long long* label, float* workspace, float* dr, float* dt, int M, int K, int n0,
                        int n1, int num_class, int splitk, void* stream);
+
+/* scflow_pose_fc_fwd without a workspace argument and without any allocation: the split-K partial sums live
+ * in a file-scope `static __device__` array of the library (SCFLOW_POSE_FC_STATIC_MAX_FLOATS floats = 4 MiB,
+ * held by every GPU that loads the library until exit).  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, results and launches as scflow_pose_fc_fwd otherwise.
+ * Limit: scflow_pose_fc_workspace_floats(M, n0, n1, splitk) <= SCFLOW_POSE_FC_STATIC_MAX_FLOATS, else
+ * SCFLOW_E_STATIC_SCRATCH (the shipped head, n0 = 1024, n1 = 256, splitk = 4, fits up to M = 204 crops).
+ * Every call on a device shares the array: nothing in it needs clearing (it is fully overwritten before it
+ * is read), but calls that overlap on the GPU (different streams or threads) race -- serialise them. */
+#define SCFLOW_POSE_FC_STATIC_MAX_FLOATS (1 << 20)
+int scflow_pose_fc_fwd_static(const float* x, const float* w0, const float* b0, const float* w1, const float* b1,
+                              const float* wr, const float* br, const float* wt, const float* bt,
+                              const long long* label, float* dr, float* dt, int M, int K, int n0, int n1,
+                              int num_class, int splitk, void* stream);
 
 /* ------------------------------------------------------------------ degenerate convolutions (8f-f2)
  * Convolutions of the decoder with 1-2 input or 1-2 output channels, which cuDNN serves with generic

@@ -20,6 +20,7 @@ extern "C" const char* scflow_strerror(int rc) {
     case SCFLOW_E_WORKSPACE: return "workspace too small";
     case SCFLOW_E_DRIVER: return "CUDA driver entry point unavailable";
     case SCFLOW_E_UNIMPLEMENTED: return "kernel not implemented yet";
+    case SCFLOW_E_STATIC_SCRATCH: return "problem exceeds the static device scratch of the no-allocation entry point";
     default: return "unknown scflow error";
   }
 }

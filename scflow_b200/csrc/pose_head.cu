@@ -157,3 +157,59 @@ extern "C" int scflow_pose_fc_fwd(const float* x, const float* w0, const float* 
   ph::pose_tail_kernel<<<M, 320, (size_t)n1 * sizeof(float), st>>>(p);
   return check_launch();
 }
+
+// ---------------------------------------------------------------------------------------------
+// scflow_pose_fc_fwd_static: the same three launches with the split-K partials in a file-scope device array
+// instead of a caller-supplied workspace, for callers that cannot allocate device memory (CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The array (SCFLOW_POSE_FC_STATIC_MAX_FLOATS floats = 4 MiB) is held by every
+// GPU that loads the library until the process exits.  In host code `g_pose_fc_scratch` is only a stand-in
+// for the symbol: its DEVICE address is looked up once per device, with that device current, through
+// cudaGetSymbolAddress, and that pointer is what the kernels get.  Every call on a device shares the array:
+// nothing in it has to start at zero (both partial-sum blocks are fully overwritten before they are read),
+// but calls that overlap on the GPU (two streams, two threads) race on it -- serialise them.
+namespace scflow {
+namespace ph {
+static __device__ __align__(256) float g_pose_fc_scratch[SCFLOW_POSE_FC_STATIC_MAX_FLOATS];
+
+constexpr int kMaxDevices = 64;
+static float* g_scratch_addr[kMaxDevices];      // device address of the array on device i, 0 = not looked up
+
+static int scratch_address(float** out) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    g_last_cuda_error = (int)cudaGetLastError();
+    return SCFLOW_E_LAUNCH;
+  }
+  float* p = __atomic_load_n(&g_scratch_addr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    void* sym = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&sym, g_pose_fc_scratch);     // the current device's copy
+    if (e != cudaSuccess || sym == nullptr) {
+      g_last_cuda_error = (int)e;
+      cudaGetLastError();
+      return SCFLOW_E_LAUNCH;
+    }
+    p = static_cast<float*>(sym);
+    __atomic_store_n(&g_scratch_addr[dev], p, __ATOMIC_RELEASE);             // idempotent: same value from any thread
+  }
+  *out = p;
+  return SCFLOW_OK;
+}
+}  // namespace ph
+}  // namespace scflow
+
+extern "C" int scflow_pose_fc_fwd_static(const float* x, const float* w0, const float* b0, const float* w1,
+                                         const float* b1, const float* wr, const float* br, const float* wt,
+                                         const float* bt, const long long* label, float* dr, float* dt, int M,
+                                         int K, int n0, int n1, int num_class, int splitk, void* stream) {
+  using namespace scflow;
+  if (M <= 0 || n0 <= 0 || n1 <= 0 || splitk <= 0) return SCFLOW_E_BAD_SHAPE;
+  // the partial sums must fit the static array: reject, never truncate
+  if (scflow_pose_fc_workspace_floats(M, n0, n1, splitk) > (size_t)SCFLOW_POSE_FC_STATIC_MAX_FLOATS)
+    return SCFLOW_E_STATIC_SCRATCH;
+  float* scratch = nullptr;
+  if (int rc = ph::scratch_address(&scratch)) return rc;
+  return scflow_pose_fc_fwd(x, w0, b0, w1, b1, wr, br, wt, bt, label, scratch, dr, dt, M, K, n0, n1, num_class,
+                            splitk, stream);
+}
