@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define SCFLOW_ABI_VERSION 5
+#define SCFLOW_ABI_VERSION 6
 
 enum {
   SCFLOW_OK = 0,
@@ -42,6 +42,12 @@ enum {
 #define SCFLOW_EPI_PLAIN 0
 #define SCFLOW_EPI_GRU_ZR 1
 #define SCFLOW_EPI_GRU_GATE 2
+
+/* scflow_conv_tc_desc.algo */
+#define SCFLOW_CONV_AUTO 0
+#define SCFLOW_CONV_TAP_BOXES 1
+#define SCFLOW_CONV_PATCH 2
+#define SCFLOW_CONV_PATCH_PAIR 3
 
 /* correlation arithmetic */
 #define SCFLOW_PREC_FP32 0      /* CUDA-core fp32 FMA (exact-mode parity anchor)          */
@@ -294,6 +300,13 @@ typedef struct scflow_conv_tc_desc {
   int epi, gru_c;
   float* gru_h;
   float* gru_z;
+  /* operand movement (ABI v6): SCFLOW_CONV_AUTO picks per layer; the others force one kernel (tests, tools):
+   *   TAP_BOXES   one shifted TMA box per (tap, k-block), the filter slab re-read per tile (any stride)
+   *   PATCH       stride 1, OW % 8 == 0, OH % 16 == 0, bk = 64: the input patch of a 16 x 8 tile is loaded
+   *               once per k-block and every tap reads it through a shifted shared-memory descriptor;
+   *               small filters stay resident in shared memory
+   *   PATCH_PAIR  the same on CTA pairs (tcgen05 cta_group::2, M = 256): each CTA loads half the filter rows */
+  int algo;
 } scflow_conv_tc_desc;
 
 /* Output spatial size: OH = (h + 2 pad_h - kh) / stride + 1, likewise OW.  Supported: OW a multiple of

@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libscflow_b200.so")
 
 _P = c_void_p
-ABI_VERSION = 5
+ABI_VERSION = 6
 # name -> (restype, argtypes); mirrors include/scflow_b200.h one to one
 SIGNATURES = {
     "scflow_abi_version": (c_int, []),

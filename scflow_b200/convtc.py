@@ -35,10 +35,12 @@ class _Desc(ctypes.Structure):
         ("out_f32", ctypes.c_void_p), ("outf_pitch", ctypes.c_longlong), ("f32_tf32", ctypes.c_int),
         ("out_planar", ctypes.c_void_p), ("planar_tf32", ctypes.c_int),
         ("stats", ctypes.c_void_p), ("bn", ctypes.c_int), ("epi", ctypes.c_int), ("gru_c", ctypes.c_int),
-        ("gru_h", ctypes.c_void_p), ("gru_z", ctypes.c_void_p)]
+        ("gru_h", ctypes.c_void_p), ("gru_z", ctypes.c_void_p), ("algo", ctypes.c_int)]
 
 
 EPI_PLAIN, EPI_GRU_ZR, EPI_GRU_GATE = 0, 1, 2
+# scflow_conv_tc_desc.algo: operand movement (include/scflow_b200.h)
+ALGO_AUTO, ALGO_TAP_BOXES, ALGO_PATCH, ALGO_PATCH_PAIR = 0, 1, 2, 3
 
 
 def _rup(v: int, m: int) -> int:
@@ -118,9 +120,12 @@ class Packed:
     bk: int
 
 
-def choose_bk(cout: int) -> int:
-    """64-channel k-blocks (128-byte swizzle rows) while three ring stages fit next to the weight tile,
-    32-channel ones (64-byte rows) for the wide tiles."""
+def choose_bk(cout: int, stride: int = 2) -> int:
+    """Stride-1 filters: 64-channel k-blocks (128-byte swizzle rows), what the patch-resident kernel reads.
+    Others (per-tap kernel): 64 while three ring stages fit next to the weight tile, 32-channel k-blocks
+    (64-byte rows) for the wide tiles."""
+    if stride == 1:
+        return 64
     bn = _rup(cout, 16)
     if bn > 256:
         nt = (bn + 255) // 256
@@ -137,7 +142,8 @@ def pack_weights(weight: torch.Tensor, bias: Optional[torch.Tensor], stride=1, p
         raise _lib.ScflowError("pack_weights: expected CUDA parameters (scflow_b200 has no CPU path)")
     w = weight.detach().float().contiguous()
     cout, cin, kh, kw = w.shape
-    bk = bk or choose_bk(cout)
+    s = (stride, stride) if isinstance(stride, int) else tuple(stride)
+    bk = bk or choose_bk(cout, s[0])
     nbytes = lib.scflow_conv_tc_packed_bytes(cout, cin, kh, kw, bk)
     if nbytes == 0:
         raise _lib.ScflowError(f"conv_tc: unsupported filter {tuple(w.shape)}")
@@ -150,7 +156,6 @@ def pack_weights(weight: torch.Tensor, bias: Optional[torch.Tensor], stride=1, p
     b = torch.zeros(cpad, device=w.device, dtype=torch.float32)
     if bias is not None:
         b[:cout] = bias.detach().float()
-    s = (stride, stride) if isinstance(stride, int) else tuple(stride)
     p = (padding, padding) if isinstance(padding, int) else tuple(padding)
     if s[0] != s[1]:
         raise _lib.ScflowError("conv_tc: anisotropic stride")
@@ -195,7 +200,7 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
          out_f32: Optional[torch.Tensor] = None, out_planar: Optional[torch.Tensor] = None,
          planar_tf32: bool = False, f32_tf32: bool = False, stats: Optional[torch.Tensor] = None, want: str = "split",
          view=None, bn: int = 0, epi: int = EPI_PLAIN, gru_h: Optional[torch.Tensor] = None,
-         gru_z: Optional[torch.Tensor] = None):
+         gru_z: Optional[torch.Tensor] = None, algo: int = ALGO_AUTO):
     """One convolution launch.  x: Split (n, h, w, cin).  Outputs: `out` (Split), `out_f32` (n, OH, OW, >=cout)
     fp32 channels-last (may be a channel slice of a wider buffer), `out_planar` (n, cout, OH, OW); when none is
     given one is allocated according to `want` ("split" | "f32" | "planar").  `view` = (n, h, w, cin, lo_off,
@@ -227,7 +232,7 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
     d.bias = pk.bias.data_ptr() if pk.bias is not None else None
     d.relu = int(relu)
     c8 = _rup(pk.cout, 8)
-    d.bn, d.epi = bn, epi
+    d.bn, d.epi, d.algo = bn, epi, algo
     if epi != EPI_PLAIN:
         # ConvGRU epilogues: exact fp32 state + update gate, (n, oh, ow, C) contiguous; out = a C-channel slice
         assert gru_h.is_contiguous() and gru_z.is_contiguous() and gru_h.shape == gru_z.shape

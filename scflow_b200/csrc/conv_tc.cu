@@ -68,6 +68,12 @@ struct Params {
   int epi, gru_c;
   float* gru_h;
   float* gru_z;
+  // patch-resident kernel (conv_patch_kernel): input patch of a tile = PH x pitch pixel rows of 128 bytes per part
+  int PH, pitch;                               // patch rows; patch row pitch in pixels (= box width)
+  int patch_tx, patch_bytes;                   // bytes one part's TMA box writes; the same rounded up to 1024
+  int a_stages, a_stage_bytes;                 // ring of patches: one entry = one 64-channel k-block, hi + lo
+  int w_stages, w_stage_bytes, wb_bytes;       // ring of filter slabs: one entry = one (k-block, tap), hi + lo
+  int w_resident;                              // the whole filter stays in shared memory (w_stages = all entries)
 };
 
 __device__ __forceinline__ uint32_t make_idesc_bf16(int m, int n) {
@@ -87,6 +93,31 @@ __device__ __forceinline__ void mma_bf16_ss(uint32_t d_tmem, uint64_t a_desc, ui
       : "memory");
 }
 
+__device__ __forceinline__ void mma_bf16_ss_2cta(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                                 uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// shared::cluster address of the object at this CTA-local shared address in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t map_to_rank(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+
+// Arrive on a barrier of another CTA of the cluster without the release fence of mbar_arrive_remote (MEMBAR +
+// ERRBAR per arrival, 15 % of the pair kernel's stall samples): the epilogue hands back TMEM, whose reads are
+// complete (tcgen05.wait::ld) and ordered (tcgen05.fence::before_thread_sync) before this instruction issues.
+__device__ __forceinline__ void mbar_arrive_remote_relaxed(uint32_t bar_addr) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_addr) : "memory");
+}
+
 __device__ __forceinline__ float rn_tf32(float v) {
   uint32_t u;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
@@ -101,13 +132,17 @@ __device__ __forceinline__ float tanhf_(float v) {
   return copysignf(__fdividef(1.0f - e, 1.0f + e), v);
 }
 
-// v -> (hi, lo) bf16 pair; two values packed per 32-bit word (low half = first value)
+// v -> (hi, lo) bf16 pair; two values packed per 32-bit word (low half = first value).  The PACKED conversion
+// (cvt.rn.bf16x2.f32 = one F2FP in the ALU pipe): the scalar __float2bfloat16_rn compiles to F2F.BF16.F32, a
+// quarter-rate conversion-pipe instruction that headed the epilogue's stall samples (four per pair of values).
+__device__ __forceinline__ uint32_t cvt_bf16x2(float lo_half, float hi_half) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_half), "f"(lo_half));
+  return r;
+}
 __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
-  const __nv_bfloat16 ah = __float2bfloat16_rn(a), bh = __float2bfloat16_rn(b);
-  const __nv_bfloat16 al = __float2bfloat16_rn(a - __bfloat162float(ah));
-  const __nv_bfloat16 bl = __float2bfloat16_rn(b - __bfloat162float(bh));
-  hi = (uint32_t)__bfloat16_as_ushort(ah) | ((uint32_t)__bfloat16_as_ushort(bh) << 16);
-  lo = (uint32_t)__bfloat16_as_ushort(al) | ((uint32_t)__bfloat16_as_ushort(bl) << 16);
+  hi = cvt_bf16x2(a, b);
+  lo = cvt_bf16x2(a - __uint_as_float(hi << 16), b - __uint_as_float(hi & 0xFFFF0000u));
 }
 __device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
@@ -127,6 +162,188 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
   r.oy0 = ty * p.TH;
   r.ox0 = (m - ty * p.tiles_x) * p.TW;
   return r;
+}
+
+// One accumulator tile (128 pixels x bn channels in TMEM at taddr) through the epilogue of this warp:
+// chunks of 32 columns j = half, half + 2, ...; lane = pixel (n, oy, ox).  `live`: the pixel exists.
+__device__ __forceinline__ void epilogue_tile(const Params& p, const Tile& tl, uint32_t taddr, int half, int lane,
+                                              int n, int oy, int ox, bool live) {
+  const int chunks = (p.bn + 31) >> 5;
+  const long long plane = (long long)p.OH * p.OW;
+  const long long pix = ((long long)n * p.OH + oy) * p.OW + ox;
+  for (int j = half; j < chunks; j += 2) {
+    float v[32];
+    tc::tmem_ld_32x32(taddr + j * 32, v);
+    if (p.fold) {
+      float u[32];
+      tc::tmem_ld_32x32(taddr + p.bn + j * 32, u);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += u[i];
+    } else {
+      tc::tmem_ld_wait();
+    }
+    const int c0 = tl.nt * p.bn + j * 32;               // first output channel of the chunk
+    int nv = p.cout_store - c0;                          // channels of it that are stored
+    nv = nv > 32 ? 32 : nv;
+    if (tl.nt * p.bn + p.bn - c0 < nv) nv = tl.nt * p.bn + p.bn - c0;
+    if (nv <= 0) continue;
+    if (p.bias) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (i < nv) v[i] += __ldg(p.bias + c0 + i);                      // bias is padded to cout_pad
+    }
+    if (p.stats) {
+      // per-(image, channel) sum and sum of squares over the warp's 32 pixels (all of one image:
+      // host guarantees OH*OW >= 32 with stats), butterfly so that lane i ends with channel i
+      float s[32], q[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) { s[i] = live ? v[i] : 0.f; q[i] = s[i] * s[i]; }
+#pragma unroll
+      for (int w = 16; w >= 1; w >>= 1) {
+#pragma unroll
+        for (int i = 0; i < w; ++i) {
+          const bool up = (lane & w) != 0;
+          const float ss = up ? s[i] : s[i + w], sq = up ? q[i] : q[i + w];
+          const float rs = __shfl_xor_sync(0xffffffffu, ss, w), rq = __shfl_xor_sync(0xffffffffu, sq, w);
+          s[i] = (up ? s[i + w] : s[i]) + rs;
+          q[i] = (up ? q[i + w] : q[i]) + rq;
+        }
+      }
+      // lane i now holds channel bitrev-free index: after the halving steps element 0 of lane l is channel l
+      const int nw = __shfl_sync(0xffffffffu, n, 0);
+      if (lane < nv && nw < p.n) {
+        double* dst = p.stats + ((long long)nw * p.cout_store + c0 + lane) * 2;
+        atomicAdd(dst, (double)s[0]);
+        atomicAdd(dst + 1, (double)q[0]);
+      }
+    }
+    if (!live) continue;
+    if (p.epi == SCFLOW_EPI_GRU_ZR) {
+      // raft_decoder.py:247-250, first half: channels [0,C) z = sigmoid(.) -> gru_z (fp32);
+      // channels [C,2C) r = sigmoid(.), r.h -> split planes (the operand of the q convolution)
+      if (c0 < p.gru_c) {
+        float4* zp = reinterpret_cast<float4*>(p.gru_z + pix * p.gru_c + c0);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          zp[k] = make_float4(sigmoidf_(v[4 * k]), sigmoidf_(v[4 * k + 1]), sigmoidf_(v[4 * k + 2]),
+                              sigmoidf_(v[4 * k + 3]));
+      } else {
+        const int cc = c0 - p.gru_c;
+        const float4* hp = reinterpret_cast<const float4*>(p.gru_h + pix * p.gru_c + cc);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float4 h = __ldg(hp + k);
+          v[4 * k] = sigmoidf_(v[4 * k]) * h.x; v[4 * k + 1] = sigmoidf_(v[4 * k + 1]) * h.y;
+          v[4 * k + 2] = sigmoidf_(v[4 * k + 2]) * h.z; v[4 * k + 3] = sigmoidf_(v[4 * k + 3]) * h.w;
+        }
+        uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + cc);
+        uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + cc);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          uint4 h, l;
+          split2(v[8 * k], v[8 * k + 1], h.x, l.x);
+          split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
+          split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
+          split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
+          oh[k] = h;
+          ol[k] = l;
+        }
+      }
+      continue;
+    }
+    if (p.epi == SCFLOW_EPI_GRU_GATE) {
+      // raft_decoder.py:251-252: q = tanh(conv(r.h) + [x part of the q convolution, res_f32] + b);
+      // h = (1 - z) h + z q, in place in the exact fp32 state, and as split planes for the next operand
+      const float4* qp = reinterpret_cast<const float4*>(p.res_f32 + pix * p.resf_pitch + c0);
+      const float4* zp = reinterpret_cast<const float4*>(p.gru_z + pix * p.gru_c + c0);
+      float4* hp = reinterpret_cast<float4*>(p.gru_h + pix * p.gru_c + c0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float4 qx = __ldg(qp + k), z = __ldg(zp + k), h = hp[k];
+        v[4 * k] = (1.0f - z.x) * h.x + z.x * tanhf_(v[4 * k] + qx.x);
+        v[4 * k + 1] = (1.0f - z.y) * h.y + z.y * tanhf_(v[4 * k + 1] + qx.y);
+        v[4 * k + 2] = (1.0f - z.z) * h.z + z.z * tanhf_(v[4 * k + 2] + qx.z);
+        v[4 * k + 3] = (1.0f - z.w) * h.w + z.w * tanhf_(v[4 * k + 3] + qx.w);
+        hp[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+      }
+      uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + c0);
+      uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + c0);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        uint4 h, l;
+        split2(v[8 * k], v[8 * k + 1], h.x, l.x);
+        split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
+        split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
+        split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
+        oh[k] = h;
+        ol[k] = l;
+      }
+      continue;
+    }
+    if (p.res_split) {
+      const uint4* rh = reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + c0);
+      const uint4* rl = reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + p.res_lo + c0);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (8 * k < nv) {
+          const uint4 a = __ldg(rh + k), b = __ldg(rl + k);
+          const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            v[8 * k + 2 * e] += bf_lo(aw[e]) + bf_lo(bw[e]);
+            v[8 * k + 2 * e + 1] += bf_hi(aw[e]) + bf_hi(bw[e]);
+          }
+        }
+      }
+    } else if (p.res_f32) {
+      const float4* rp = reinterpret_cast<const float4*>(p.res_f32 + pix * p.resf_pitch + c0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (4 * k < nv) {
+          const float4 a = __ldg(rp + k);
+          v[4 * k] += a.x; v[4 * k + 1] += a.y; v[4 * k + 2] += a.z; v[4 * k + 3] += a.w;
+        }
+      }
+    }
+    if (p.relu) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+    }
+    if (p.out_split) {
+      uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + c0);
+      uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + c0);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (8 * k < nv) {
+          uint4 h, l;
+          split2(v[8 * k], v[8 * k + 1], h.x, l.x);
+          split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
+          split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
+          split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
+          oh[k] = h;
+          ol[k] = l;
+        }
+      }
+    }
+    if (p.out_f32) {
+      float4* op = reinterpret_cast<float4*>(p.out_f32 + pix * p.outf_pitch + c0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (4 * k < nv) {
+          op[k] = p.f32_tf32 ? make_float4(rn_tf32(v[4 * k]), rn_tf32(v[4 * k + 1]), rn_tf32(v[4 * k + 2]),
+                                           rn_tf32(v[4 * k + 3]))
+                             : make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+        }
+      }
+    }
+    if (p.out_planar) {
+      float* op = p.out_planar + ((long long)n * p.cout_store + c0) * plane + (long long)oy * p.OW + ox;
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (i < nv) op[i * plane] = p.planar_tf32 ? rn_tf32(v[i]) : v[i];
+    }
+  }
 }
 
 template <int BK>   // channels per k-block: 64 (128-byte swizzle) or 32 (64-byte swizzle)
@@ -191,10 +408,14 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // The whole warp walks the loops (warp-uniform control flow keeps descriptors and addresses in uniform
+    // registers); one elected lane issues the MMAs and commits.  Issued from a single diverged lane the same
+    // loop cost ~55 SASS instructions per MMA (broadcast + elect sequences) and bound the narrow tiles.
+    {
       const uint32_t idesc = make_idesc_bf16(BM, p.bn);
       const uint32_t idesc2 = make_idesc_bf16(BM, 2 * p.bn);
       const uint32_t smem0 = tc::smem_u32(smem);
+      const bool fold = p.fold != 0;
       int stage = 0; uint32_t phase = 0; uint32_t it = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
         const uint32_t buf = it & 1;
@@ -211,31 +432,38 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
             const uint32_t b_hi = a_lo + p.a_bytes;
             const uint32_t b_lo = b_hi + p.b_bytes;
             const int nks = kb == p.kblocks - 1 ? p.ksteps_last : BK / 16;
-            for (int ks = 0; ks < nks; ++ks) {
-              // K-major swizzled: 8-row groups kSbo bytes apart; a k-step (16 bf16) is +32 bytes
-              const uint64_t dah = tc::make_smem_desc(a_hi + ks * 32, 16, kSbo, kLayout);
-              const uint64_t dal = tc::make_smem_desc(a_lo + ks * 32, 16, kSbo, kLayout);
-              const uint64_t dbh = tc::make_smem_desc(b_hi + ks * 32, 16, kSbo, kLayout);
-              const uint64_t dbl = tc::make_smem_desc(b_lo + ks * 32, 16, kSbo, kLayout);
-              if (p.fold) {
-                // An M = 128 MMA occupies the pipe for >= 64 cycles whatever N is (measured: 32-, 64- and
-                // 128-channel tiles took the same time), so narrow tiles fold two of the three products
-                // into one instruction: [B_hi;B_lo] are adjacent in the stage = one 2 bn-row operand;
-                // columns [0,bn) get a_hi.b_hi, [bn,2bn) a_hi.b_lo, the epilogue adds the halves
-                mma_bf16_ss(d, dah, dbh, idesc2, acc);
-                mma_bf16_ss(d, dal, dbh, idesc, 1u);
-              } else {
-                mma_bf16_ss(d, dal, dbh, idesc, acc);        // small terms first
-                mma_bf16_ss(d, dah, dbl, idesc, 1u);
-                mma_bf16_ss(d, dah, dbh, idesc, 1u);
+            // K-major swizzled: 8-row groups kSbo bytes apart; a k-step (16 bf16) is +32 bytes (+2 in the
+            // descriptor's address field)
+            const uint64_t dah = tc::make_smem_desc(a_hi, 16, kSbo, kLayout);
+            const uint64_t dal = tc::make_smem_desc(a_lo, 16, kSbo, kLayout);
+            const uint64_t dbh = tc::make_smem_desc(b_hi, 16, kSbo, kLayout);
+            const uint64_t dbl = tc::make_smem_desc(b_lo, 16, kSbo, kLayout);
+            if (tc::elect_one()) {
+#pragma unroll
+              for (int ks = 0; ks < BK / 16; ++ks) {
+                if (ks < nks) {
+                  if (fold) {
+                    // narrow tiles fold two of the three products into one instruction: [B_hi;B_lo] are
+                    // adjacent in the stage = one 2 bn-row operand; columns [0,bn) get a_hi.b_hi, [bn,2bn)
+                    // a_hi.b_lo, the epilogue adds the halves
+                    mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc2, acc | (uint32_t)ks);
+                    mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                  } else {
+                    mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);   // small terms first
+                    mma_bf16_ss(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
+                    mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                  }
+                }
               }
-              acc = 1u;
+              tc::tc_commit(&empty[stage]);
             }
-            tc::tc_commit(&empty[stage]);
+            __syncwarp();
+            acc = 1u;
             if (++stage == p.stages) { stage = 0; phase ^= 1; }
           }
         }
-        tc::tc_commit(&acc_full[buf]);
+        if (tc::elect_one()) tc::tc_commit(&acc_full[buf]);
+        __syncwarp();
       }
     }
   } else {
@@ -246,191 +474,16 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
     const int per_tile_img = p.TW * p.TH;
     const int mi = m / per_tile_img, mr = m - mi * per_tile_img;
     const int my = mr / p.TW, mx = mr - my * p.TW;
-    const int chunks = (p.bn + 31) >> 5;
-    const long long plane = (long long)p.OH * p.OW;
     uint32_t it = 0;
     for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
       const Tile tl = decode_tile(p, t);
       const uint32_t buf = it & 1;
       const int n = tl.n0 + mi, oy = tl.oy0 + my, ox = tl.ox0 + mx;
       const bool live = n < p.n;
-      const long long pix = ((long long)n * p.OH + oy) * p.OW + ox;
       tc::mbar_wait(&acc_full[buf], (it >> 1) & 1);
       tc::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * 256u;
-      for (int j = half; j < chunks; j += 2) {
-        float v[32];
-        tc::tmem_ld_32x32(taddr + j * 32, v);
-        if (p.fold) {
-          float u[32];
-          tc::tmem_ld_32x32(taddr + p.bn + j * 32, u);
-          tc::tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] += u[i];
-        } else {
-          tc::tmem_ld_wait();
-        }
-        const int c0 = tl.nt * p.bn + j * 32;               // first output channel of the chunk
-        int nv = p.cout_store - c0;                          // channels of it that are stored
-        nv = nv > 32 ? 32 : nv;
-        if (tl.nt * p.bn + p.bn - c0 < nv) nv = tl.nt * p.bn + p.bn - c0;
-        if (nv <= 0) continue;
-        if (p.bias) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (i < nv) v[i] += __ldg(p.bias + c0 + i);                      // bias is padded to cout_pad
-        }
-        if (p.stats) {
-          // per-(image, channel) sum and sum of squares over the warp's 32 pixels (all of one image:
-          // host guarantees OH*OW >= 32 with stats), butterfly so that lane i ends with channel i
-          float s[32], q[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) { s[i] = live ? v[i] : 0.f; q[i] = s[i] * s[i]; }
-#pragma unroll
-          for (int w = 16; w >= 1; w >>= 1) {
-#pragma unroll
-            for (int i = 0; i < w; ++i) {
-              const bool up = (lane & w) != 0;
-              const float ss = up ? s[i] : s[i + w], sq = up ? q[i] : q[i + w];
-              const float rs = __shfl_xor_sync(0xffffffffu, ss, w), rq = __shfl_xor_sync(0xffffffffu, sq, w);
-              s[i] = (up ? s[i + w] : s[i]) + rs;
-              q[i] = (up ? q[i + w] : q[i]) + rq;
-            }
-          }
-          // lane i now holds channel bitrev-free index: after the halving steps element 0 of lane l is channel l
-          const int nw = __shfl_sync(0xffffffffu, n, 0);
-          if (lane < nv && nw < p.n) {
-            double* dst = p.stats + ((long long)nw * p.cout_store + c0 + lane) * 2;
-            atomicAdd(dst, (double)s[0]);
-            atomicAdd(dst + 1, (double)q[0]);
-          }
-        }
-        if (!live) continue;
-        if (p.epi == SCFLOW_EPI_GRU_ZR) {
-          // raft_decoder.py:247-250, first half: channels [0,C) z = sigmoid(.) -> gru_z (fp32);
-          // channels [C,2C) r = sigmoid(.), r.h -> split planes (the operand of the q convolution)
-          if (c0 < p.gru_c) {
-            float4* zp = reinterpret_cast<float4*>(p.gru_z + pix * p.gru_c + c0);
-#pragma unroll
-            for (int k = 0; k < 8; ++k)
-              zp[k] = make_float4(sigmoidf_(v[4 * k]), sigmoidf_(v[4 * k + 1]), sigmoidf_(v[4 * k + 2]),
-                                  sigmoidf_(v[4 * k + 3]));
-          } else {
-            const int cc = c0 - p.gru_c;
-            const float4* hp = reinterpret_cast<const float4*>(p.gru_h + pix * p.gru_c + cc);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              const float4 h = __ldg(hp + k);
-              v[4 * k] = sigmoidf_(v[4 * k]) * h.x; v[4 * k + 1] = sigmoidf_(v[4 * k + 1]) * h.y;
-              v[4 * k + 2] = sigmoidf_(v[4 * k + 2]) * h.z; v[4 * k + 3] = sigmoidf_(v[4 * k + 3]) * h.w;
-            }
-            uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + cc);
-            uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + cc);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              uint4 h, l;
-              split2(v[8 * k], v[8 * k + 1], h.x, l.x);
-              split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
-              split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
-              split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
-              oh[k] = h;
-              ol[k] = l;
-            }
-          }
-          continue;
-        }
-        if (p.epi == SCFLOW_EPI_GRU_GATE) {
-          // raft_decoder.py:251-252: q = tanh(conv(r.h) + [x part of the q convolution, res_f32] + b);
-          // h = (1 - z) h + z q, in place in the exact fp32 state, and as split planes for the next operand
-          const float4* qp = reinterpret_cast<const float4*>(p.res_f32 + pix * p.resf_pitch + c0);
-          const float4* zp = reinterpret_cast<const float4*>(p.gru_z + pix * p.gru_c + c0);
-          float4* hp = reinterpret_cast<float4*>(p.gru_h + pix * p.gru_c + c0);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const float4 qx = __ldg(qp + k), z = __ldg(zp + k), h = hp[k];
-            v[4 * k] = (1.0f - z.x) * h.x + z.x * tanhf_(v[4 * k] + qx.x);
-            v[4 * k + 1] = (1.0f - z.y) * h.y + z.y * tanhf_(v[4 * k + 1] + qx.y);
-            v[4 * k + 2] = (1.0f - z.z) * h.z + z.z * tanhf_(v[4 * k + 2] + qx.z);
-            v[4 * k + 3] = (1.0f - z.w) * h.w + z.w * tanhf_(v[4 * k + 3] + qx.w);
-            hp[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
-          }
-          uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + c0);
-          uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + c0);
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            uint4 h, l;
-            split2(v[8 * k], v[8 * k + 1], h.x, l.x);
-            split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
-            split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
-            split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
-            oh[k] = h;
-            ol[k] = l;
-          }
-          continue;
-        }
-        if (p.res_split) {
-          const uint4* rh = reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + c0);
-          const uint4* rl = reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + p.res_lo + c0);
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            if (8 * k < nv) {
-              const uint4 a = __ldg(rh + k), b = __ldg(rl + k);
-              const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                v[8 * k + 2 * e] += bf_lo(aw[e]) + bf_lo(bw[e]);
-                v[8 * k + 2 * e + 1] += bf_hi(aw[e]) + bf_hi(bw[e]);
-              }
-            }
-          }
-        } else if (p.res_f32) {
-          const float4* rp = reinterpret_cast<const float4*>(p.res_f32 + pix * p.resf_pitch + c0);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            if (4 * k < nv) {
-              const float4 a = __ldg(rp + k);
-              v[4 * k] += a.x; v[4 * k + 1] += a.y; v[4 * k + 2] += a.z; v[4 * k + 3] += a.w;
-            }
-          }
-        }
-        if (p.relu) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
-        }
-        if (p.out_split) {
-          uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + c0);
-          uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + c0);
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            if (8 * k < nv) {
-              uint4 h, l;
-              split2(v[8 * k], v[8 * k + 1], h.x, l.x);
-              split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
-              split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
-              split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
-              oh[k] = h;
-              ol[k] = l;
-            }
-          }
-        }
-        if (p.out_f32) {
-          float4* op = reinterpret_cast<float4*>(p.out_f32 + pix * p.outf_pitch + c0);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            if (4 * k < nv) {
-              op[k] = p.f32_tf32 ? make_float4(rn_tf32(v[4 * k]), rn_tf32(v[4 * k + 1]), rn_tf32(v[4 * k + 2]),
-                                               rn_tf32(v[4 * k + 3]))
-                                 : make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
-            }
-          }
-        }
-        if (p.out_planar) {
-          float* op = p.out_planar + ((long long)n * p.cout_store + c0) * plane + (long long)oy * p.OW + ox;
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (i < nv) op[i * plane] = p.planar_tf32 ? rn_tf32(v[i]) : v[i];
-        }
-      }
+      epilogue_tile(p, tl, taddr, half, lane, n, oy, ox, live);
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&acc_empty[buf]);
@@ -442,6 +495,249 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
   if (warp == 1) {
     tc::tc_fence_after();
     tc::tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ================================================================================================
+// Second generation for stride-1 filters: PATCH-RESIDENT operands.
+//
+// The kernel above pulls one shifted TMA box per (tap, k-block) and the whole filter slab per tile: a 3x3
+// layer reads its input nine times and its filter once per 128 pixels through L2, and every layer shape
+// of the refiner sat at the L2 -> SM throughput cap (10-14 TB/s of TMA traffic, tensor pipe 30-65 % busy;
+// profiles/r02_conv_ncu.txt).  Here
+//   * a tile is 16 rows x 8 pixels, and the (16 + kh - 1) x (8 + kw - 1) input PATCH of a 64-channel k-block
+//     is loaded ONCE (one TMA box per part; out-of-bounds zero fill is the padding).  A pixel is one 128-byte
+//     swizzled row, an output row of the tile is exactly one 8-row swizzle atom, so the A operand of tap
+//     (ky, kx) is the same patch read through a descriptor whose start is advanced by (ky pitch + kx) rows
+//     and whose stride between atoms is the patch pitch: no data moves between taps.  (Measured on B200: the
+//     128-byte swizzle XOR comes from ABSOLUTE shared-memory address bits [7,10), so a start advanced by whole
+//     rows and an atom stride that is not a multiple of 1024 bytes read exactly the rows TMA wrote, with the
+//     descriptor's base-offset field left 0; setting it to (start >> 7) & 7 gives wrong products.);
+//   * PAIR: a cluster of two CTAs computes two tiles as one M = 256 tcgen05.mma.cta_group::2, each CTA
+//     loading only HALF of the filter rows -- filter traffic per pixel halves;
+//   * small filters (<= 32 (k-block, tap) slabs that fit next to two patches) stay resident in shared
+//     memory for the whole launch.
+// Barrier waits are plain CTA-scope try_waits also in PAIR mode: what they guard is written by the async
+// proxy (TMA, tcgen05.commit) and read by the async proxy; the cluster-scope acquire form costs an L1
+// invalidate (CCTL.IVALL) per wait.
+// warp 0: patch producer, warp 1: MMA issuer (PAIR: rank 0's), warps 2..9: epilogue, warp 10: filter producer.
+constexpr int P_THREADS = THREADS + 32;
+constexpr int MAX_A_STAGES = 4, MAX_W_STAGES = 32;
+constexpr int P_BAR_BYTES = 1024;
+
+template <bool PAIR>
+__global__ void __launch_bounds__(P_THREADS, 1)
+conv_patch_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p) {
+  constexpr uint32_t kLayout = 2u;                          // SWIZZLE_128B
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* a_ring = smem;
+  uint8_t* w_ring = smem + (size_t)p.a_stages * p.a_stage_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(w_ring + (size_t)p.w_stages * p.w_stage_bytes);
+  uint64_t* a_full = bars;                                  // PAIR: rank 0's collect both CTAs' bytes
+  uint64_t* a_empty = a_full + MAX_A_STAGES;
+  uint64_t* w_full = a_empty + MAX_A_STAGES;
+  uint64_t* w_empty = w_full + MAX_W_STAGES;
+  uint64_t* acc_full = w_empty + MAX_W_STAGES;              // [2]
+  uint64_t* acc_empty = acc_full + 2;                       // [2] PAIR: rank 0's, armed by both CTAs' epilogues
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = PAIR ? tc::cluster_ctarank() : 0u;
+  const int unit0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int units_grid = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int m_units = PAIR ? (p.m_tiles + 1) >> 1 : p.m_tiles;
+  const int total = m_units * p.n_tiles;
+  const int taps = p.kh * p.kw;
+
+  if (warp == 0 && lane == 0) {
+    tc::tma_prefetch_desc(&maps.a_hi); tc::tma_prefetch_desc(&maps.a_lo); tc::tma_prefetch_desc(&maps.w);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < p.a_stages; ++i) { tc::mbar_init(&a_full[i], 1); tc::mbar_init(&a_empty[i], 1); }
+      for (int i = 0; i < p.w_stages; ++i) { tc::mbar_init(&w_full[i], 1); tc::mbar_init(&w_empty[i], 1); }
+      for (int i = 0; i < 2; ++i) {
+        tc::mbar_init(&acc_full[i], 1);
+        tc::mbar_init(&acc_empty[i], PAIR ? 2 * NEPI : NEPI);
+      }
+      tc::fence_barrier_init();
+    }
+    __syncwarp();
+    if (PAIR) tc::tmem_alloc_2cta(tmem_slot, TMEM_COLS); else tc::tmem_alloc(tmem_slot, TMEM_COLS);
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (PAIR) tc::cluster_sync();                  // the peer's barriers exist before anything signals them
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // this CTA's tile of unit u (PAIR: tile 2 m + rank of pair m; an odd tile count leaves the last one dead)
+  auto tile_of = [&](int u, bool* alive) -> Tile {
+    const int mu = u / p.n_tiles, nt = u - mu * p.n_tiles;
+    int mt = PAIR ? 2 * mu + (int)rank : mu;
+    *alive = mt < p.m_tiles;
+    if (!*alive) mt = p.m_tiles - 1;
+    return decode_tile(p, mt * p.n_tiles + nt);
+  };
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ patch producer
+    if (lane == 0) {
+      int as = 0; uint32_t aph = 0;
+      for (int u = unit0; u < total; u += units_grid) {
+        bool alive;
+        const Tile tl = tile_of(u, &alive);
+        const int ix = tl.ox0 - p.pad_x, iy = tl.oy0 - p.pad_y;
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          uint8_t* st = a_ring + (size_t)as * p.a_stage_bytes;
+          if (PAIR) {
+            tc::mbar_wait(&a_empty[as], aph ^ 1);
+            const uint32_t fb = map_to_rank(tc::smem_u32(&a_full[as]), 0);
+            if (rank == 0) tc::mbar_expect_tx(&a_full[as], 4u * (uint32_t)p.patch_tx);
+            tc::tma_load_4d_2cta(&maps.a_hi, fb, st, kb * 64, ix, iy, tl.n0);
+            tc::tma_load_4d_2cta(&maps.a_lo, fb, st + p.patch_bytes, kb * 64, ix, iy, tl.n0);
+          } else {
+            tc::mbar_wait(&a_empty[as], aph ^ 1);
+            tc::mbar_expect_tx(&a_full[as], 2u * (uint32_t)p.patch_tx);
+            tc::tma_load_4d(&maps.a_hi, &a_full[as], st, kb * 64, ix, iy, tl.n0);
+            tc::tma_load_4d(&maps.a_lo, &a_full[as], st + p.patch_bytes, kb * 64, ix, iy, tl.n0);
+          }
+          if (++as == p.a_stages) { as = 0; aph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 10) {
+    // ------------------------------------------------------------------ filter producer
+    if (lane == 0) {
+      int ws = 0; uint32_t wph = 0;
+      const int rows = PAIR ? p.bn >> 1 : p.bn;               // filter rows this CTA holds per part
+      for (int u = unit0; u < total; u += units_grid) {
+        const int nt = u % p.n_tiles;
+        const int wrow0 = nt * p.bn + (int)rank * rows;
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          for (int tap = 0; tap < taps; ++tap) {
+            uint8_t* st = w_ring + (size_t)ws * p.w_stage_bytes;
+            const int wrow = ((tap * p.kblocks + kb) * 2) * p.cout_pad + wrow0;
+            if (PAIR) {
+              if (!p.w_resident) tc::mbar_wait(&w_empty[ws], wph ^ 1);
+              const uint32_t fb = map_to_rank(tc::smem_u32(&w_full[ws]), 0);
+              if (rank == 0) tc::mbar_expect_tx(&w_full[ws], 4u * (uint32_t)p.wb_bytes);
+              tc::tma_load_2d_2cta(&maps.w, fb, st, 0, wrow);
+              tc::tma_load_2d_2cta(&maps.w, fb, st + p.wb_bytes, 0, wrow + p.cout_pad);
+            } else {
+              if (!p.w_resident) tc::mbar_wait(&w_empty[ws], wph ^ 1);
+              tc::mbar_expect_tx(&w_full[ws], 2u * (uint32_t)p.wb_bytes);
+              tc::tma_load_2d(&maps.w, &w_full[ws], st, 0, wrow);
+              tc::tma_load_2d(&maps.w, &w_full[ws], st + p.wb_bytes, 0, wrow + p.cout_pad);
+            }
+            if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
+          }
+        }
+        if (p.w_resident) break;                              // every slab is in place for the whole launch
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (warp-uniform; see above)
+    if (rank == 0) {
+      const uint32_t idesc = make_idesc_bf16(PAIR ? 2 * BM : BM, p.bn);
+      const uint32_t idesc2 = make_idesc_bf16(BM, 2 * p.bn);
+      const uint32_t a0 = tc::smem_u32(a_ring), w0 = tc::smem_u32(w_ring);
+      const uint32_t sbo = (uint32_t)p.pitch * 128u;          // one output row of the tile = one swizzle atom
+      const bool fold = p.fold != 0, resident = p.w_resident != 0;
+      int as = 0, ws = 0; uint32_t aph = 0, wph = 0, it = 0;
+      for (int u = unit0; u < total; u += units_grid, ++it) {
+        const uint32_t buf = it & 1;
+        tc::mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
+        tc::tc_fence_after();
+        const uint32_t d = tmem_base + buf * 256u;
+        uint32_t acc = 0;
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          tc::mbar_wait(&a_full[as], aph);
+          tc::tc_fence_after();
+          const uint32_t a_hi = a0 + as * p.a_stage_bytes, a_lo = a_hi + p.patch_bytes;
+          const int nks = kb == p.kblocks - 1 ? p.ksteps_last : 4;
+          int ky = 0, kx = 0;
+          for (int tap = 0; tap < taps; ++tap) {
+            // a resident slab's barrier completes its phase 0 once and is waited on with parity 0 ever after
+            tc::mbar_wait(&w_full[ws], wph);
+            tc::tc_fence_after();
+            const uint32_t shift = (uint32_t)(ky * p.pitch + kx) * 128u;
+            const uint32_t b_hi = w0 + ws * p.w_stage_bytes, b_lo = b_hi + p.wb_bytes;
+            const uint64_t dah = tc::make_smem_desc(a_hi + shift, 16, sbo, kLayout);
+            const uint64_t dal = tc::make_smem_desc(a_lo + shift, 16, sbo, kLayout);
+            const uint64_t dbh = tc::make_smem_desc(b_hi, 16, 1024, kLayout);
+            const uint64_t dbl = tc::make_smem_desc(b_lo, 16, 1024, kLayout);
+            if (tc::elect_one()) {
+#pragma unroll
+              for (int ks = 0; ks < 4; ++ks) {
+                if (ks < nks) {
+                  if (PAIR) {
+                    mma_bf16_ss_2cta(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
+                    mma_bf16_ss_2cta(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
+                    mma_bf16_ss_2cta(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                  } else if (fold) {
+                    mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc2, acc | (uint32_t)ks);   // [B_hi;B_lo]: 2 bn rows
+                    mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                  } else {
+                    mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
+                    mma_bf16_ss(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
+                    mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                  }
+                }
+              }
+              if (!resident) {
+                if (PAIR) tc::tc_commit_2cta(&w_empty[ws]); else tc::tc_commit(&w_empty[ws]);
+              }
+            }
+            __syncwarp();
+            acc = 1u;
+            if (++kx == p.kw) { kx = 0; ++ky; }
+            if (++ws == p.w_stages) { ws = 0; if (!resident) wph ^= 1; }
+          }
+          if (tc::elect_one()) {
+            if (PAIR) tc::tc_commit_2cta(&a_empty[as]); else tc::tc_commit(&a_empty[as]);
+          }
+          __syncwarp();
+          if (++as == p.a_stages) { as = 0; aph ^= 1; }
+        }
+        if (tc::elect_one()) {
+          if (PAIR) tc::tc_commit_2cta(&acc_full[buf]); else tc::tc_commit(&acc_full[buf]);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp >= 2 && warp < 2 + NEPI) {
+    // ------------------------------------------------------------------ epilogue (8 warps, own TMEM)
+    const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int m = quarter * 32 + lane;
+    const int my = m >> 3, mx = m & 7;                       // TW = 8
+    const uint32_t empty0 = PAIR ? map_to_rank(tc::smem_u32(&acc_empty[0]), 0) : 0u;
+    uint32_t it = 0;
+    for (int u = unit0; u < total; u += units_grid, ++it) {
+      bool alive;
+      const Tile tl = tile_of(u, &alive);
+      const uint32_t buf = it & 1;
+      const int n = alive ? tl.n0 : p.n, oy = tl.oy0 + my, ox = tl.ox0 + mx;
+      tc::mbar_wait(&acc_full[buf], (it >> 1) & 1);
+      tc::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * 256u;
+      epilogue_tile(p, tl, taddr, half, lane, n, oy, ox, alive);
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (PAIR) mbar_arrive_remote_relaxed(empty0 + buf * 8u); else tc::mbar_arrive(&acc_empty[buf]);
+      }
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (PAIR) tc::cluster_sync();                  // nobody leaves while the pair's MMAs may touch its memory
+  if (warp == 1) {
+    tc::tc_fence_after();
+    if (PAIR) tc::tmem_dealloc_2cta(tmem_base, TMEM_COLS); else tc::tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
@@ -619,6 +915,63 @@ static int cout_pad_of(int cout, int* bn, int* n_tiles) {
   return b * *n_tiles;
 }
 
+// Geometry of the patch-resident kernel for this layer, or false when the layer is outside it (stride 2,
+// 32-channel k-blocks, maps that 16 x 8 tiles do not cover, rings that do not fit): the caller then takes the
+// per-tap kernel.  algo: SCFLOW_CONV_AUTO | _PATCH | _PATCH_PAIR.
+static bool plan_patch(const scflow_conv_tc_desc* d, Params& p, int algo, bool* pair, size_t* smem_bytes) {
+  if (d->stride != 1 || d->bk != 64 || (p.OW % 8) || (p.OH % 16) || d->kw > 9 || d->kh * d->kw > MAX_W_STAGES)
+    return false;
+  const int taps = d->kh * d->kw;
+  const int budget = SMEM_LIMIT - 1024 - P_BAR_BYTES;
+  const int tiles = p.n * (p.OW / 8) * (p.OH / 16);
+  // PAIR halves the filter traffic per pixel; it needs an even split of the filter rows into 8-row atoms
+  bool want_pair = algo == SCFLOW_CONV_PATCH_PAIR || (algo == SCFLOW_CONV_AUTO && tiles >= 2);
+  if (want_pair && (p.bn % 16)) {
+    if (algo == SCFLOW_CONV_PATCH_PAIR) return false;
+    want_pair = false;
+  }
+  p.PH = 16 + d->kh - 1;
+  p.pitch = 8 + d->kw - 1;
+  p.patch_tx = p.PH * p.pitch * 128;
+  p.patch_bytes = (p.patch_tx + 1023) / 1024 * 1024;
+  p.a_stage_bytes = 2 * p.patch_bytes;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    const bool pr = want_pair && attempt == 0;
+    p.wb_bytes = (pr ? p.bn / 2 : p.bn) * 128;
+    p.w_stage_bytes = 2 * p.wb_bytes;
+    const int entries = taps * p.kblocks;
+    bool ok = false;
+    if (entries <= MAX_W_STAGES && p.n_tiles == 1 && entries * p.w_stage_bytes + 2 * p.a_stage_bytes <= budget) {
+      p.w_resident = 1;
+      p.w_stages = entries;
+      p.a_stages = (budget - entries * p.w_stage_bytes) / p.a_stage_bytes;
+      ok = true;
+    } else {
+      p.w_resident = 0;
+      p.a_stages = 2;
+      p.w_stages = (budget - 2 * p.a_stage_bytes) / p.w_stage_bytes;
+      if (p.w_stages >= 6 && budget - 3 * p.a_stage_bytes >= 4 * p.w_stage_bytes) {
+        p.a_stages = 3;
+        p.w_stages = (budget - 3 * p.a_stage_bytes) / p.w_stage_bytes;
+      }
+      ok = p.w_stages >= 2;
+    }
+    if (p.a_stages > MAX_A_STAGES) p.a_stages = MAX_A_STAGES;
+    if (p.w_stages > MAX_W_STAGES) p.w_stages = MAX_W_STAGES;
+    if (ok) {
+      *pair = pr;
+      p.TW = 8; p.TH = 16; p.NI = 1;
+      p.tiles_x = p.OW / 8; p.tiles_y = p.OH / 16;
+      p.m_tiles = tiles;
+      p.fold = (!pr && p.bn <= 128) ? 1 : 0;
+      *smem_bytes = 1024 + (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.w_stages * p.w_stage_bytes + P_BAR_BYTES;
+      return true;
+    }
+    if (algo == SCFLOW_CONV_PATCH_PAIR || !want_pair) break;
+  }
+  return false;
+}
+
 }  // namespace ctc
 }  // namespace scflow
 
@@ -706,43 +1059,55 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
   p.OW = (d->w + 2 * d->pad_w - d->kw) / d->stride + 1;
   if (p.OH <= 0 || p.OW <= 0) return SCFLOW_E_BAD_SHAPE;
   p.kh = d->kh; p.kw = d->kw; p.stride = d->stride; p.pad_y = d->pad_h; p.pad_x = d->pad_w;
-  // tile rectangle: 128 output pixels
-  if (p.OW >= BM) {
-    if (p.OW % BM) return SCFLOW_E_BAD_SHAPE;
-    p.TW = BM; p.TH = 1; p.NI = 1;
-  } else {
-    if (BM % p.OW) return SCFLOW_E_BAD_SHAPE;
-    p.TW = p.OW;
-    const int rows = BM / p.OW;
-    if (p.OH >= rows) {
-      if (p.OH % rows) return SCFLOW_E_BAD_SHAPE;
-      p.TH = rows; p.NI = 1;
-    } else {
-      if (rows % p.OH) return SCFLOW_E_BAD_SHAPE;
-      p.TH = p.OH; p.NI = rows / p.OH;
-    }
-  }
-  p.tiles_x = p.OW / p.TW; p.tiles_y = p.OH / p.TH;
-  const int groups = (p.n + p.NI - 1) / p.NI;
-  p.m_tiles = groups * p.tiles_x * p.tiles_y;
   p.cout_pad = cout_pad_of(d->cout, &p.bn, &p.n_tiles);
   if (d->bn > 0) {                             // caller-chosen tile width (wave quantisation): must tile the pack
     if ((d->bn % 16) || d->bn > 256 || (p.cout_pad % d->bn)) return SCFLOW_E_BAD_SHAPE;
     p.bn = d->bn;
     p.n_tiles = p.cout_pad / d->bn;
   }
-  p.fold = p.bn <= 128 ? 1 : 0;
   p.cout_store = (d->cout + 7) / 8 * 8;
   const int bk = d->bk;
   p.kblocks = (d->cin + bk - 1) / bk;
   p.ksteps_last = ((d->cin - (p.kblocks - 1) * bk) + 15) / 16;
-  p.a_bytes = BM * bk * 2;
-  p.b_bytes = p.bn * bk * 2;
-  p.stage_bytes = 2 * (p.a_bytes + p.b_bytes);
-  p.stages = (SMEM_LIMIT - 2048) / p.stage_bytes;
-  if (p.stages > 8) p.stages = 8;
-  if (p.stages < 2) return SCFLOW_E_BAD_SHAPE;
-  const size_t smem_bytes = 1024 + (size_t)p.stages * p.stage_bytes + 256;
+  const int algo = d->algo & 0xff;
+  if (algo > SCFLOW_CONV_PATCH_PAIR) return SCFLOW_E_BAD_SHAPE;
+  bool pair = false;
+  size_t smem_bytes = 0;
+  // AUTO: 1x1 filters have no taps to share a patch between and measured 5-9 % faster on the per-tap kernel
+  // (its 128-pixel row tiles store wider runs); everything else stride-1 goes to the patch kernel, on CTA
+  // pairs where the filter rows split evenly (measured faster on every 3x3 / 1x5 / 5x1 shape of the refiner)
+  const bool patch = algo != SCFLOW_CONV_TAP_BOXES && !(algo == SCFLOW_CONV_AUTO && d->kh * d->kw == 1) &&
+                     plan_patch(d, p, algo, &pair, &smem_bytes);
+  if (!patch && (algo == SCFLOW_CONV_PATCH || algo == SCFLOW_CONV_PATCH_PAIR)) return SCFLOW_E_BAD_SHAPE;
+  if (!patch) {
+    // tile rectangle: 128 output pixels
+    if (p.OW >= BM) {
+      if (p.OW % BM) return SCFLOW_E_BAD_SHAPE;
+      p.TW = BM; p.TH = 1; p.NI = 1;
+    } else {
+      if (BM % p.OW) return SCFLOW_E_BAD_SHAPE;
+      p.TW = p.OW;
+      const int rows = BM / p.OW;
+      if (p.OH >= rows) {
+        if (p.OH % rows) return SCFLOW_E_BAD_SHAPE;
+        p.TH = rows; p.NI = 1;
+      } else {
+        if (rows % p.OH) return SCFLOW_E_BAD_SHAPE;
+        p.TH = p.OH; p.NI = rows / p.OH;
+      }
+    }
+    p.tiles_x = p.OW / p.TW; p.tiles_y = p.OH / p.TH;
+    const int groups = (p.n + p.NI - 1) / p.NI;
+    p.m_tiles = groups * p.tiles_x * p.tiles_y;
+    p.fold = p.bn <= 128 ? 1 : 0;
+    p.a_bytes = BM * bk * 2;
+    p.b_bytes = p.bn * bk * 2;
+    p.stage_bytes = 2 * (p.a_bytes + p.b_bytes);
+    p.stages = (SMEM_LIMIT - 2048) / p.stage_bytes;
+    if (p.stages > 8) p.stages = 8;
+    if (p.stages < 2) return SCFLOW_E_BAD_SHAPE;
+    smem_bytes = 1024 + (size_t)p.stages * p.stage_bytes + 256;
+  }
   // epilogue
   p.bias = d->bias; p.relu = d->relu;
   p.res_split = static_cast<const __nv_bfloat16*>(d->res_split); p.res_pitch = d->res_pitch; p.res_lo = d->res_lo;
@@ -774,25 +1139,56 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
     const uint64_t dims[4] = {(uint64_t)d->cin, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
     const uint64_t strides[3] = {(uint64_t)d->x_stride_w * 2, (uint64_t)d->x_stride_h * 2,
                                  (uint64_t)d->x_stride_n * 2};
-    const uint32_t box[4] = {(uint32_t)bk, (uint32_t)((p.TW - 1) * p.stride + 1),
-                             (uint32_t)((p.TH - 1) * p.stride + 1), (uint32_t)p.NI};
+    const uint32_t box_tap[4] = {(uint32_t)bk, (uint32_t)((p.TW - 1) * p.stride + 1),
+                                 (uint32_t)((p.TH - 1) * p.stride + 1), (uint32_t)p.NI};
+    const uint32_t box_patch[4] = {64u, (uint32_t)p.pitch, (uint32_t)p.PH, 1u};
     const uint32_t es[4] = {1, (uint32_t)p.stride, (uint32_t)p.stride, 1};
+    const uint32_t* box = patch ? box_patch : box_tap;
     const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(d->x);
     if (!encode_bf16_map(&maps.a_hi, xb, 4, dims, strides, box, es, bk) ||
         !encode_bf16_map(&maps.a_lo, xb + d->x_lo_off, 4, dims, strides, box, es, bk))
       return SCFLOW_E_DRIVER;
     const uint64_t wd[2] = {(uint64_t)bk, (uint64_t)d->kh * d->kw * p.kblocks * 2 * p.cout_pad};
     const uint64_t ws[1] = {(uint64_t)bk * 2};
-    const uint32_t wb[2] = {(uint32_t)bk, (uint32_t)p.bn};
+    const uint32_t wb[2] = {(uint32_t)bk, (uint32_t)(pair ? p.bn / 2 : p.bn)};
     if (!encode_bf16_map(&maps.w, d->wpack, 2, wd, ws, wb, nullptr, bk)) return SCFLOW_E_DRIVER;
   }
   int sms = 0, dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (sms <= 0) sms = 148;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (patch) {
+    const int units = (pair ? (p.m_tiles + 1) / 2 : p.m_tiles) * p.n_tiles;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.blockDim = dim3(P_THREADS);
+    cfg.dynamicSmemBytes = smem_bytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = pair ? 2 : 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (pair) {
+      cudaFuncSetAttribute(conv_patch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+      int clusters = 0;
+      cfg.gridDim = dim3(2 * (sms / 2));
+      if (cudaOccupancyMaxActiveClusters(&clusters, conv_patch_kernel<true>, &cfg) != cudaSuccess || clusters <= 0) {
+        cudaGetLastError();
+        return SCFLOW_E_LAUNCH;
+      }
+      if (clusters > sms / 2) clusters = sms / 2;
+      cfg.gridDim = dim3(2 * (units < clusters ? units : clusters));
+      if (cudaLaunchKernelEx(&cfg, conv_patch_kernel<true>, maps, p) != cudaSuccess) return check_launch();
+    } else {
+      cudaFuncSetAttribute(conv_patch_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+      cfg.gridDim = dim3(units < sms ? units : sms);
+      if (cudaLaunchKernelEx(&cfg, conv_patch_kernel<false>, maps, p) != cudaSuccess) return check_launch();
+    }
+    return check_launch();
+  }
   const int total = p.m_tiles * p.n_tiles;
   const int grid = total < sms ? total : sms;
-  cudaStream_t st = (cudaStream_t)stream;
   if (bk == 64) {
     cudaFuncSetAttribute(conv_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
     conv_tc_kernel<64><<<grid, THREADS, smem_bytes, st>>>(maps, p);

@@ -70,6 +70,46 @@ def test_conv_tc_vs_fp64(n, h, w, cin, cout, k, stride, pad, bk):
     assert e < TOL + 3 * (cin * k * k / 16) * 2.0 ** -24, e
 
 
+PATCH_CASES = [
+    # n, h, w, cin, cout, kh, kw, pad_h, pad_w      (stride 1, bk 64: the patch-resident kernel's domain)
+    (2, 32, 32, 64, 64, 1, 1, 0, 0),             # patch = the tile itself
+    (2, 32, 32, 64, 64, 3, 3, 1, 1),             # resident filter
+    (3, 16, 8, 96, 96, 3, 3, 1, 1),              # one tile per image: an odd tile count (PAIR: one dead tile)
+    (2, 32, 32, 384, 256, 1, 5, 0, 2),           # ConvGRU (1,5): streamed filter, 6 k-blocks
+    (2, 32, 32, 128, 256, 5, 1, 2, 0),           # (5,1)
+    (1, 64, 64, 128, 64, 3, 3, 1, 1),
+    (2, 32, 32, 324, 256, 1, 1, 0, 0),           # lookup width: last k-block has one k-step
+    (2, 32, 32, 256, 126, 3, 3, 1, 1),           # 126 output channels (tile of 128)
+    (1, 128, 128, 64, 64, 3, 3, 1, 1),           # 128 tiles per image
+    (1, 16, 8, 128, 512, 3, 3, 1, 1),            # one tile per image, two output-channel tiles
+    (2, 32, 32, 128, 128, 7, 7, 3, 3),           # wide patch (22 x 14 rows), 49 taps > 32: per-tap kernel unless forced
+]
+
+
+@pytest.mark.parametrize("algo", [C.ALGO_TAP_BOXES, C.ALGO_PATCH, C.ALGO_PATCH_PAIR])
+@pytest.mark.parametrize("n,h,w,cin,cout,kh,kw,ph,pw", PATCH_CASES)
+def test_conv_tc_algorithms_vs_fp64(n, h, w, cin, cout, kh, kw, ph, pw, algo):
+    """The three operand-movement variants of scflow_conv_tc_fwd (per-tap boxes, patch-resident, patch-resident
+    on CTA pairs) against fp64, and against each other: same products, same accumulation order per output."""
+    from scflow_b200._lib import ScflowError
+    g = torch.Generator().manual_seed(n * 1000 + cin + cout + kh)
+    x = torch.randn(n, h, w, cin, generator=g)
+    wt = torch.randn(cout, cin, kh, kw, generator=g) / (cin * kh * kw) ** 0.5
+    b = torch.randn(cout, generator=g)
+    pk = C.pack_weights(wt.to(DEV), b.to(DEV), 1, (ph, pw))
+    assert pk.bk == 64
+    xs = C.to_split(x.to(DEV))
+    if kh * kw > 32 and algo != C.ALGO_TAP_BOXES:
+        with pytest.raises(ScflowError):
+            C.conv(xs, pk, relu=True, algo=algo)
+        return
+    got = C.conv(xs, pk, relu=True, algo=algo)
+    torch.cuda.synchronize()
+    want = F.conv2d(x.double().permute(0, 3, 1, 2), wt.double(), b.double(), 1, (ph, pw)).relu().permute(0, 2, 3, 1)
+    e = _err(got.float(), want)
+    assert e < TOL + 3 * (cin * kh * kw / 16) * 2.0 ** -24, e
+
+
 def test_conv_tc_outputs_residuals_stats():
     g = torch.Generator().manual_seed(7)
     n, h, w, cin, cout = 3, 16, 16, 64, 96
