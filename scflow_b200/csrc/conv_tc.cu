@@ -74,6 +74,7 @@ struct Params {
   int a_stages, a_stage_bytes;                 // ring of patches: one entry = one 64-channel k-block, hi + lo
   int w_stages, w_stage_bytes, wb_bytes;       // ring of filter slabs: one entry = one (k-block, tap), hi + lo
   int w_resident;                              // the whole filter stays in shared memory (w_stages = all entries)
+  int wide;                                    // epilogue pointers / pitches are 32-byte aligned: 256-bit accesses
 };
 
 __device__ __forceinline__ uint32_t make_idesc_bf16(int m, int n) {
@@ -164,14 +165,95 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
   return r;
 }
 
+// 32 bytes per lane per instruction (LDG/STG.256, sm_100): a lane of the epilogue owns a PIXEL, so a warp-wide
+// access touches 32 different 128-byte lines whatever its width, and the L1/LSU pipe (one line per cycle) bounds
+// the heavier epilogues: the 16-byte form moved 16 bytes per line-cycle.  `wide`: pointers and pitches allow it.
+__device__ __forceinline__ void ld8(const float* src, float* v, bool wide) {
+  if (wide) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "l"(src));
+  } else {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src) + 1);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+}
+// same, through the coherent path (the ConvGRU state is read and rewritten by the same launch)
+__device__ __forceinline__ void ld8_rw(const float* src, float* v, bool wide) {
+  if (wide) {
+    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "l"(src) : "memory");
+  } else {
+    const float4 a = *reinterpret_cast<const float4*>(src), b = *(reinterpret_cast<const float4*>(src) + 1);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+}
+__device__ __forceinline__ void st8(float* dst, const float* v, bool wide) {
+  if (wide) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(dst), "f"(v[0]), "f"(v[1]), "f"(v[2]),
+                 "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+  } else {
+    reinterpret_cast<float4*>(dst)[0] = make_float4(v[0], v[1], v[2], v[3]);
+    reinterpret_cast<float4*>(dst)[1] = make_float4(v[4], v[5], v[6], v[7]);
+  }
+}
+// 16 values -> 16 bf16 hi at dst_hi and 16 bf16 lo at dst_lo (32 bytes each)
+__device__ __forceinline__ void st_split16(__nv_bfloat16* dst_hi, __nv_bfloat16* dst_lo, const float* v, bool wide) {
+  uint32_t h[8], l[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) split2(v[2 * e], v[2 * e + 1], h[e], l[e]);
+  if (wide) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(dst_hi), "r"(h[0]), "r"(h[1]), "r"(h[2]),
+                 "r"(h[3]), "r"(h[4]), "r"(h[5]), "r"(h[6]), "r"(h[7]) : "memory");
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(dst_lo), "r"(l[0]), "r"(l[1]), "r"(l[2]),
+                 "r"(l[3]), "r"(l[4]), "r"(l[5]), "r"(l[6]), "r"(l[7]) : "memory");
+  } else {
+    reinterpret_cast<uint4*>(dst_hi)[0] = make_uint4(h[0], h[1], h[2], h[3]);
+    reinterpret_cast<uint4*>(dst_hi)[1] = make_uint4(h[4], h[5], h[6], h[7]);
+    reinterpret_cast<uint4*>(dst_lo)[0] = make_uint4(l[0], l[1], l[2], l[3]);
+    reinterpret_cast<uint4*>(dst_lo)[1] = make_uint4(l[4], l[5], l[6], l[7]);
+  }
+}
+// 16 bf16 hi + 16 bf16 lo added into 16 values
+__device__ __forceinline__ void add_split16(const __nv_bfloat16* src_hi, const __nv_bfloat16* src_lo, float* v, bool wide) {
+  uint32_t h[8], l[8];
+  if (wide) {
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(h[0]), "=r"(h[1]), "=r"(h[2]), "=r"(h[3]), "=r"(h[4]), "=r"(h[5]), "=r"(h[6]), "=r"(h[7])
+                 : "l"(src_hi));
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(l[0]), "=r"(l[1]), "=r"(l[2]), "=r"(l[3]), "=r"(l[4]), "=r"(l[5]), "=r"(l[6]), "=r"(l[7])
+                 : "l"(src_lo));
+  } else {
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(src_hi)), b = __ldg(reinterpret_cast<const uint4*>(src_hi) + 1);
+    const uint4 c = __ldg(reinterpret_cast<const uint4*>(src_lo)), d = __ldg(reinterpret_cast<const uint4*>(src_lo) + 1);
+    h[0] = a.x; h[1] = a.y; h[2] = a.z; h[3] = a.w; h[4] = b.x; h[5] = b.y; h[6] = b.z; h[7] = b.w;
+    l[0] = c.x; l[1] = c.y; l[2] = c.z; l[3] = c.w; l[4] = d.x; l[5] = d.y; l[6] = d.z; l[7] = d.w;
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    v[2 * e] += bf_lo(h[e]) + bf_lo(l[e]);
+    v[2 * e + 1] += bf_hi(h[e]) + bf_hi(l[e]);
+  }
+}
+
 // One accumulator tile (128 pixels x bn channels in TMEM at taddr) through the epilogue of this warp:
 // chunks of 32 columns j = half, half + 2, ...; lane = pixel (n, oy, ox).  `live`: the pixel exists.
-__device__ __forceinline__ void epilogue_tile(const Params& p, const Tile& tl, uint32_t taddr, int half, int lane,
-                                              int n, int oy, int ox, bool live) {
+__device__ __forceinline__ void epilogue_plain(const Params& p, const Tile& tl, uint32_t taddr, int half, int lane,
+                                              int n, int oy, int ox, bool live, uint64_t* acc_full, uint32_t parity) {
   const int chunks = (p.bn + 31) >> 5;
   const long long plane = (long long)p.OH * p.OW;
   const long long pix = ((long long)n * p.OH + oy) * p.OW + ox;
+  const bool wide = p.wide != 0;
+  bool waited = false;
   for (int j = half; j < chunks; j += 2) {
+    const int c0 = tl.nt * p.bn + j * 32;               // first output channel of the chunk
+    if (!waited) {
+      tc::mbar_wait(acc_full, parity);
+      tc::tc_fence_after();
+      waited = true;
+    }
     float v[32];
     tc::tmem_ld_32x32(taddr + j * 32, v);
     if (p.fold) {
@@ -183,7 +265,6 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const Tile& tl, u
     } else {
       tc::tmem_ld_wait();
     }
-    const int c0 = tl.nt * p.bn + j * 32;               // first output channel of the chunk
     int nv = p.cout_store - c0;                          // channels of it that are stored
     nv = nv > 32 ? 32 : nv;
     if (tl.nt * p.bn + p.bn - c0 < nv) nv = tl.nt * p.bn + p.bn - c0;
@@ -219,90 +300,31 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const Tile& tl, u
       }
     }
     if (!live) continue;
-    if (p.epi == SCFLOW_EPI_GRU_ZR) {
-      // raft_decoder.py:247-250, first half: channels [0,C) z = sigmoid(.) -> gru_z (fp32);
-      // channels [C,2C) r = sigmoid(.), r.h -> split planes (the operand of the q convolution)
-      if (c0 < p.gru_c) {
-        float4* zp = reinterpret_cast<float4*>(p.gru_z + pix * p.gru_c + c0);
-#pragma unroll
-        for (int k = 0; k < 8; ++k)
-          zp[k] = make_float4(sigmoidf_(v[4 * k]), sigmoidf_(v[4 * k + 1]), sigmoidf_(v[4 * k + 2]),
-                              sigmoidf_(v[4 * k + 3]));
-      } else {
-        const int cc = c0 - p.gru_c;
-        const float4* hp = reinterpret_cast<const float4*>(p.gru_h + pix * p.gru_c + cc);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const float4 h = __ldg(hp + k);
-          v[4 * k] = sigmoidf_(v[4 * k]) * h.x; v[4 * k + 1] = sigmoidf_(v[4 * k + 1]) * h.y;
-          v[4 * k + 2] = sigmoidf_(v[4 * k + 2]) * h.z; v[4 * k + 3] = sigmoidf_(v[4 * k + 3]) * h.w;
-        }
-        uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + cc);
-        uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + cc);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          uint4 h, l;
-          split2(v[8 * k], v[8 * k + 1], h.x, l.x);
-          split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
-          split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
-          split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
-          oh[k] = h;
-          ol[k] = l;
-        }
-      }
-      continue;
-    }
-    if (p.epi == SCFLOW_EPI_GRU_GATE) {
-      // raft_decoder.py:251-252: q = tanh(conv(r.h) + [x part of the q convolution, res_f32] + b);
-      // h = (1 - z) h + z q, in place in the exact fp32 state, and as split planes for the next operand
-      const float4* qp = reinterpret_cast<const float4*>(p.res_f32 + pix * p.resf_pitch + c0);
-      const float4* zp = reinterpret_cast<const float4*>(p.gru_z + pix * p.gru_c + c0);
-      float4* hp = reinterpret_cast<float4*>(p.gru_h + pix * p.gru_c + c0);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float4 qx = __ldg(qp + k), z = __ldg(zp + k), h = hp[k];
-        v[4 * k] = (1.0f - z.x) * h.x + z.x * tanhf_(v[4 * k] + qx.x);
-        v[4 * k + 1] = (1.0f - z.y) * h.y + z.y * tanhf_(v[4 * k + 1] + qx.y);
-        v[4 * k + 2] = (1.0f - z.z) * h.z + z.z * tanhf_(v[4 * k + 2] + qx.z);
-        v[4 * k + 3] = (1.0f - z.w) * h.w + z.w * tanhf_(v[4 * k + 3] + qx.w);
-        hp[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
-      }
-      uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + c0);
-      uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + c0);
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        uint4 h, l;
-        split2(v[8 * k], v[8 * k + 1], h.x, l.x);
-        split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
-        split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
-        split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
-        oh[k] = h;
-        ol[k] = l;
-      }
-      continue;
-    }
     if (p.res_split) {
-      const uint4* rh = reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + c0);
-      const uint4* rl = reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + p.res_lo + c0);
+      const __nv_bfloat16* rh = p.res_split + pix * p.res_pitch + c0;
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        if (8 * k < nv) {
-          const uint4 a = __ldg(rh + k), b = __ldg(rl + k);
+      for (int k = 0; k < 2; ++k) {
+        if (16 * k + 8 < nv) add_split16(rh + 16 * k, rh + p.res_lo + 16 * k, v + 16 * k, wide);
+        else if (16 * k < nv) {                      // a last group of 8 channels
+          const uint4 a = __ldg(reinterpret_cast<const uint4*>(rh + 16 * k));
+          const uint4 b = __ldg(reinterpret_cast<const uint4*>(rh + p.res_lo + 16 * k));
           const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            v[8 * k + 2 * e] += bf_lo(aw[e]) + bf_lo(bw[e]);
-            v[8 * k + 2 * e + 1] += bf_hi(aw[e]) + bf_hi(bw[e]);
+            v[16 * k + 2 * e] += bf_lo(aw[e]) + bf_lo(bw[e]);
+            v[16 * k + 2 * e + 1] += bf_hi(aw[e]) + bf_hi(bw[e]);
           }
         }
       }
     } else if (p.res_f32) {
-      const float4* rp = reinterpret_cast<const float4*>(p.res_f32 + pix * p.resf_pitch + c0);
+      const float* rp = p.res_f32 + pix * p.resf_pitch + c0;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        if (4 * k < nv) {
-          const float4 a = __ldg(rp + k);
-          v[4 * k] += a.x; v[4 * k + 1] += a.y; v[4 * k + 2] += a.z; v[4 * k + 3] += a.w;
+      for (int k = 0; k < 4; ++k) {
+        if (8 * k < nv) {
+          float r[8];
+          ld8(rp + 8 * k, r, wide);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[8 * k + e] += r[e];
         }
       }
     }
@@ -311,31 +333,28 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const Tile& tl, u
       for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
     }
     if (p.out_split) {
-      uint4* oh = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + c0);
-      uint4* ol = reinterpret_cast<uint4*>(p.out_split + pix * p.out_pitch + p.out_lo + c0);
+      __nv_bfloat16* oh = p.out_split + pix * p.out_pitch + c0;
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        if (8 * k < nv) {
+      for (int k = 0; k < 2; ++k) {
+        if (16 * k + 8 < nv) st_split16(oh + 16 * k, oh + p.out_lo + 16 * k, v + 16 * k, wide);
+        else if (16 * k < nv) {                      // a last group of 8 channels: 16-byte stores
           uint4 h, l;
-          split2(v[8 * k], v[8 * k + 1], h.x, l.x);
-          split2(v[8 * k + 2], v[8 * k + 3], h.y, l.y);
-          split2(v[8 * k + 4], v[8 * k + 5], h.z, l.z);
-          split2(v[8 * k + 6], v[8 * k + 7], h.w, l.w);
-          oh[k] = h;
-          ol[k] = l;
+          split2(v[16 * k], v[16 * k + 1], h.x, l.x); split2(v[16 * k + 2], v[16 * k + 3], h.y, l.y);
+          split2(v[16 * k + 4], v[16 * k + 5], h.z, l.z); split2(v[16 * k + 6], v[16 * k + 7], h.w, l.w);
+          *reinterpret_cast<uint4*>(oh + 16 * k) = h;
+          *reinterpret_cast<uint4*>(oh + p.out_lo + 16 * k) = l;
         }
       }
     }
     if (p.out_f32) {
-      float4* op = reinterpret_cast<float4*>(p.out_f32 + pix * p.outf_pitch + c0);
+      float* op = p.out_f32 + pix * p.outf_pitch + c0;
+      if (p.f32_tf32) {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        if (4 * k < nv) {
-          op[k] = p.f32_tf32 ? make_float4(rn_tf32(v[4 * k]), rn_tf32(v[4 * k + 1]), rn_tf32(v[4 * k + 2]),
-                                           rn_tf32(v[4 * k + 3]))
-                             : make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
-        }
+        for (int i = 0; i < 32; ++i) v[i] = rn_tf32(v[i]);
       }
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (8 * k < nv) st8(op + 8 * k, v + 8 * k, wide);
     }
     if (p.out_planar) {
       float* op = p.out_planar + ((long long)n * p.cout_store + c0) * plane + (long long)oy * p.OW + ox;
@@ -344,9 +363,108 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const Tile& tl, u
         if (i < nv) op[i * plane] = p.planar_tf32 ? rn_tf32(v[i]) : v[i];
     }
   }
+  if (!waited) {                                       // a warp without a chunk of this tile still hands it back
+    tc::mbar_wait(acc_full, parity);
+    tc::tc_fence_after();
+  }
 }
 
-template <int BK>   // channels per k-block: 64 (128-byte swizzle) or 32 (64-byte swizzle)
+// The ConvGRU epilogues (SCFLOW_EPI_GRU_ZR / _GATE) of one accumulator tile.  The wait for the accumulator
+// happens after the chunk's operands (update gate, state, x part of q: up to 384 bytes per lane) have been
+// requested: they do not depend on the accumulator, and with eight epilogue warps per SM their latency was
+// otherwise exposed once per chunk.  (With a folded accumulator the registers are needed for its second half
+// first, and the operands are requested after it.)
+__device__ __forceinline__ void epilogue_gru(const Params& p, const Tile& tl, uint32_t taddr, int half, int lane,
+                                             int n, int oy, int ox, bool live, uint64_t* acc_full, uint32_t parity) {
+  const int chunks = (p.bn + 31) >> 5;
+  const long long pix = ((long long)n * p.OH + oy) * p.OW + ox;
+  const bool wide = p.wide != 0, gate = p.epi == SCFLOW_EPI_GRU_GATE, fold = p.fold != 0;
+  bool waited = false;
+  for (int j = half; j < chunks; j += 2) {
+    const int c0 = tl.nt * p.bn + j * 32;               // first output channel of the chunk
+    const bool zhalf = !gate && c0 < p.gru_c;           // GRU_ZR: update-gate half | reset-gate half
+    float ga[32], gb[32];
+    auto load_operands = [&]() {
+      if (gate) {
+        const float* zp = p.gru_z + pix * p.gru_c + c0;
+        const float* hp = p.gru_h + pix * p.gru_c + c0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { ld8(zp + 8 * k, ga + 8 * k, wide); ld8_rw(hp + 8 * k, gb + 8 * k, wide); }
+      } else if (!zhalf) {
+        const float* hp = p.gru_h + pix * p.gru_c + (c0 - p.gru_c);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) ld8(hp + 8 * k, gb + 8 * k, wide);
+      }
+    };
+    if (live && !fold) load_operands();
+    if (!waited) {
+      tc::mbar_wait(acc_full, parity);
+      tc::tc_fence_after();
+      waited = true;
+    }
+    float v[32];
+    tc::tmem_ld_32x32(taddr + j * 32, v);
+    if (fold) {
+      float u[32];
+      tc::tmem_ld_32x32(taddr + p.bn + j * 32, u);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += u[i];
+    } else {
+      tc::tmem_ld_wait();
+    }
+    if (!live) continue;
+    if (fold) load_operands();
+    if (p.bias) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += __ldg(p.bias + c0 + i);       // bias is padded to cout_pad
+    }
+    if (!gate) {
+      // raft_decoder.py:247-250, first half: channels [0,C) z = sigmoid(.) -> gru_z (fp32);
+      // channels [C,2C) r = sigmoid(.), r.h -> split planes (the operand of the q convolution)
+      if (zhalf) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = sigmoidf_(v[i]);
+        float* zp = p.gru_z + pix * p.gru_c + c0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) st8(zp + 8 * k, v + 8 * k, wide);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = sigmoidf_(v[i]) * gb[i];
+        __nv_bfloat16* oh = p.out_split + pix * p.out_pitch + (c0 - p.gru_c);
+        st_split16(oh, oh + p.out_lo, v, wide);
+        st_split16(oh + 16, oh + p.out_lo + 16, v + 16, wide);
+      }
+    } else {
+      // raft_decoder.py:251-252: q = tanh(conv(r.h) + [x part of the q convolution, res_f32] + b);
+      // h = (1 - z) h + z q, in place in the exact fp32 state, and as split planes for the next operand
+      float* hp = p.gru_h + pix * p.gru_c + c0;
+      if (p.res_f32) {
+        const float* qp = p.res_f32 + pix * p.resf_pitch + c0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float qx[8];
+          ld8(qp + 8 * k, qx, wide);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[8 * k + e] += qx[e];
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = (1.0f - ga[i]) * gb[i] + ga[i] * tanhf_(v[i]);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) st8(hp + 8 * k, v + 8 * k, wide);
+      __nv_bfloat16* oh = p.out_split + pix * p.out_pitch + c0;
+      st_split16(oh, oh + p.out_lo, v, wide);
+      st_split16(oh + 16, oh + p.out_lo + 16, v + 16, wide);
+    }
+  }
+  if (!waited) {
+    tc::mbar_wait(acc_full, parity);
+    tc::tc_fence_after();
+  }
+}
+
+template <int BK, bool GRU>   // channels per k-block: 64 (128-byte swizzle) or 32 (64-byte swizzle); ConvGRU epilogues
 __global__ void __launch_bounds__(THREADS, 1)
 conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p) {
   constexpr uint32_t kLayout = BK == 64 ? 2u : 4u;          // SWIZZLE_128B : SWIZZLE_64B
@@ -480,10 +598,9 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
       const uint32_t buf = it & 1;
       const int n = tl.n0 + mi, oy = tl.oy0 + my, ox = tl.ox0 + mx;
       const bool live = n < p.n;
-      tc::mbar_wait(&acc_full[buf], (it >> 1) & 1);
-      tc::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * 256u;
-      epilogue_tile(p, tl, taddr, half, lane, n, oy, ox, live);
+      if (GRU) epilogue_gru(p, tl, taddr, half, lane, n, oy, ox, live, &acc_full[buf], (it >> 1) & 1);
+      else epilogue_plain(p, tl, taddr, half, lane, n, oy, ox, live, &acc_full[buf], (it >> 1) & 1);
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&acc_empty[buf]);
@@ -525,7 +642,7 @@ constexpr int P_THREADS = THREADS + 32;
 constexpr int MAX_A_STAGES = 4, MAX_W_STAGES = 32;
 constexpr int P_BAR_BYTES = 1024;
 
-template <bool PAIR>
+template <bool PAIR, bool GRU>
 __global__ void __launch_bounds__(P_THREADS, 1)
 conv_patch_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p) {
   constexpr uint32_t kLayout = 2u;                          // SWIZZLE_128B
@@ -720,10 +837,9 @@ conv_patch_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Par
       const Tile tl = tile_of(u, &alive);
       const uint32_t buf = it & 1;
       const int n = alive ? tl.n0 : p.n, oy = tl.oy0 + my, ox = tl.ox0 + mx;
-      tc::mbar_wait(&acc_full[buf], (it >> 1) & 1);
-      tc::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * 256u;
-      epilogue_tile(p, tl, taddr, half, lane, n, oy, ox, alive);
+      if (GRU) epilogue_gru(p, tl, taddr, half, lane, n, oy, ox, alive, &acc_full[buf], (it >> 1) & 1);
+      else epilogue_plain(p, tl, taddr, half, lane, n, oy, ox, alive, &acc_full[buf], (it >> 1) & 1);
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) {
@@ -1060,7 +1176,7 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
   if (p.OH <= 0 || p.OW <= 0) return SCFLOW_E_BAD_SHAPE;
   p.kh = d->kh; p.kw = d->kw; p.stride = d->stride; p.pad_y = d->pad_h; p.pad_x = d->pad_w;
   p.cout_pad = cout_pad_of(d->cout, &p.bn, &p.n_tiles);
-  if (d->bn > 0) {                             // caller-chosen tile width (wave quantisation): must tile the pack
+  if (d->bn > 0) {                             // caller-chosen tile width: must tile the pack
     if ((d->bn % 16) || d->bn > 256 || (p.cout_pad % d->bn)) return SCFLOW_E_BAD_SHAPE;
     p.bn = d->bn;
     p.n_tiles = p.cout_pad / d->bn;
@@ -1071,42 +1187,72 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
   p.ksteps_last = ((d->cin - (p.kblocks - 1) * bk) + 15) / 16;
   const int algo = d->algo & 0xff;
   if (algo > SCFLOW_CONV_PATCH_PAIR) return SCFLOW_E_BAD_SHAPE;
-  bool pair = false;
+  int sms = 0, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (sms <= 0) sms = 148;
+  bool pair = false, patch = false;
   size_t smem_bytes = 0;
+  // Geometry for tile width q.bn; returns the number of waves of the persistent grid, or a negative error.
   // AUTO: 1x1 filters have no taps to share a patch between and measured 5-9 % faster on the per-tap kernel
   // (its 128-pixel row tiles store wider runs); everything else stride-1 goes to the patch kernel, on CTA
   // pairs where the filter rows split evenly (measured faster on every 3x3 / 1x5 / 5x1 shape of the refiner)
-  const bool patch = algo != SCFLOW_CONV_TAP_BOXES && !(algo == SCFLOW_CONV_AUTO && d->kh * d->kw == 1) &&
-                     plan_patch(d, p, algo, &pair, &smem_bytes);
-  if (!patch && (algo == SCFLOW_CONV_PATCH || algo == SCFLOW_CONV_PATCH_PAIR)) return SCFLOW_E_BAD_SHAPE;
-  if (!patch) {
-    // tile rectangle: 128 output pixels
-    if (p.OW >= BM) {
-      if (p.OW % BM) return SCFLOW_E_BAD_SHAPE;
-      p.TW = BM; p.TH = 1; p.NI = 1;
-    } else {
-      if (BM % p.OW) return SCFLOW_E_BAD_SHAPE;
-      p.TW = p.OW;
-      const int rows = BM / p.OW;
-      if (p.OH >= rows) {
-        if (p.OH % rows) return SCFLOW_E_BAD_SHAPE;
-        p.TH = rows; p.NI = 1;
+  auto plan = [&](Params& q, bool* q_pair, bool* q_patch, size_t* q_smem) -> int {
+    *q_pair = false;
+    *q_patch = algo != SCFLOW_CONV_TAP_BOXES && !(algo == SCFLOW_CONV_AUTO && d->kh * d->kw == 1) &&
+               plan_patch(d, q, algo, q_pair, q_smem);
+    if (!*q_patch && (algo == SCFLOW_CONV_PATCH || algo == SCFLOW_CONV_PATCH_PAIR)) return SCFLOW_E_BAD_SHAPE;
+    if (!*q_patch) {
+      // tile rectangle: 128 output pixels
+      if (q.OW >= BM) {
+        if (q.OW % BM) return SCFLOW_E_BAD_SHAPE;
+        q.TW = BM; q.TH = 1; q.NI = 1;
       } else {
-        if (rows % p.OH) return SCFLOW_E_BAD_SHAPE;
-        p.TH = p.OH; p.NI = rows / p.OH;
+        if (BM % q.OW) return SCFLOW_E_BAD_SHAPE;
+        q.TW = q.OW;
+        const int rows = BM / q.OW;
+        if (q.OH >= rows) {
+          if (q.OH % rows) return SCFLOW_E_BAD_SHAPE;
+          q.TH = rows; q.NI = 1;
+        } else {
+          if (rows % q.OH) return SCFLOW_E_BAD_SHAPE;
+          q.TH = q.OH; q.NI = rows / q.OH;
+        }
+      }
+      q.tiles_x = q.OW / q.TW; q.tiles_y = q.OH / q.TH;
+      const int groups = (q.n + q.NI - 1) / q.NI;
+      q.m_tiles = groups * q.tiles_x * q.tiles_y;
+      q.fold = q.bn <= 128 ? 1 : 0;
+      q.a_bytes = BM * bk * 2;
+      q.b_bytes = q.bn * bk * 2;
+      q.stage_bytes = 2 * (q.a_bytes + q.b_bytes);
+      q.stages = (SMEM_LIMIT - 2048) / q.stage_bytes;
+      if (q.stages > 8) q.stages = 8;
+      if (q.stages < 2) return SCFLOW_E_BAD_SHAPE;
+      *q_smem = 1024 + (size_t)q.stages * q.stage_bytes + 256;
+    }
+    const int units = (*q_pair ? (q.m_tiles + 1) / 2 : q.m_tiles) * q.n_tiles;
+    const int slots = *q_pair ? sms / 2 : sms;
+    return (units + slots - 1) / slots;
+  };
+  {
+    const int waves = plan(p, &pair, &patch, &smem_bytes);
+    if (waves < 0) return waves;
+    // Wave quantisation: the grid is persistent (one CTA per SM), so a launch costs whole waves of tiles.  Half
+    // as wide a tile doubles the units (and the activation reads) at about half the cost each; taken when it
+    // fills the last wave enough to win under cost ~ waves x (bn + 32) (the 32: the activation side of a tile).
+    // 64 crops of 32 x 32 and 256 filters: 4 waves of 256 -> 7 waves of 128 (measured 131 -> 123 us, 86 -> 77 us).
+    const int half = p.bn / 2;
+    if (d->bn == 0 && p.n_tiles == 1 && half >= 64 && (half % (d->epi != SCFLOW_EPI_PLAIN ? 32 : 16)) == 0) {
+      Params q = p;
+      q.bn = half; q.n_tiles = 2;
+      bool q_pair = false, q_patch = false;
+      size_t q_smem = 0;
+      const int w2 = plan(q, &q_pair, &q_patch, &q_smem);
+      if (w2 > 0 && (long long)w2 * (half + 32) < (long long)waves * (p.bn + 32)) {
+        p = q; pair = q_pair; patch = q_patch; smem_bytes = q_smem;
       }
     }
-    p.tiles_x = p.OW / p.TW; p.tiles_y = p.OH / p.TH;
-    const int groups = (p.n + p.NI - 1) / p.NI;
-    p.m_tiles = groups * p.tiles_x * p.tiles_y;
-    p.fold = p.bn <= 128 ? 1 : 0;
-    p.a_bytes = BM * bk * 2;
-    p.b_bytes = p.bn * bk * 2;
-    p.stage_bytes = 2 * (p.a_bytes + p.b_bytes);
-    p.stages = (SMEM_LIMIT - 2048) / p.stage_bytes;
-    if (p.stages > 8) p.stages = 8;
-    if (p.stages < 2) return SCFLOW_E_BAD_SHAPE;
-    smem_bytes = 1024 + (size_t)p.stages * p.stage_bytes + 256;
   }
   // epilogue
   p.bias = d->bias; p.relu = d->relu;
@@ -1126,6 +1272,12 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
     if (!aligned16(p.gru_h) || !aligned16(p.gru_z)) return SCFLOW_E_MISALIGNED;
   }
   if (!p.out_split && !p.out_f32 && !p.out_planar) return SCFLOW_E_NULL;
+  {
+    auto a32 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 31u) == 0; };
+    p.wide = a32(p.out_split) && (p.out_pitch % 16) == 0 && (p.out_lo % 16) == 0 && a32(p.out_f32) &&
+             (p.outf_pitch % 8) == 0 && a32(p.res_split) && (p.res_pitch % 16) == 0 && (p.res_lo % 16) == 0 &&
+             a32(p.res_f32) && (p.resf_pitch % 8) == 0 && a32(p.gru_h) && a32(p.gru_z) && (p.gru_c % 8) == 0;
+  }
   if (p.stats && p.OH * p.OW < 32) return SCFLOW_E_BAD_SHAPE;
   if ((p.out_split && (!aligned16(p.out_split) || (p.out_pitch % 8) || (p.out_lo % 8))) ||
       (p.out_f32 && (!aligned16(p.out_f32) || (p.outf_pitch % 4))) ||
@@ -1153,10 +1305,6 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
     const uint32_t wb[2] = {(uint32_t)bk, (uint32_t)(pair ? p.bn / 2 : p.bn)};
     if (!encode_bf16_map(&maps.w, d->wpack, 2, wd, ws, wb, nullptr, bk)) return SCFLOW_E_DRIVER;
   }
-  int sms = 0, dev = 0;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (sms <= 0) sms = 148;
   cudaStream_t st = (cudaStream_t)stream;
   if (patch) {
     const int units = (pair ? (p.m_tiles + 1) / 2 : p.m_tiles) * p.n_tiles;
@@ -1169,32 +1317,35 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = pair ? 2 : 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    if (pair) {
-      cudaFuncSetAttribute(conv_patch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
-      int clusters = 0;
-      cfg.gridDim = dim3(2 * (sms / 2));
-      if (cudaOccupancyMaxActiveClusters(&clusters, conv_patch_kernel<true>, &cfg) != cudaSuccess || clusters <= 0) {
-        cudaGetLastError();
-        return SCFLOW_E_LAUNCH;
+    const bool gru = p.epi != SCFLOW_EPI_PLAIN;
+    auto launch = [&](auto kern) -> int {
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+      if (pair) {
+        int clusters = 0;
+        cfg.gridDim = dim3(2 * (sms / 2));
+        if (cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg) != cudaSuccess || clusters <= 0) {
+          cudaGetLastError();
+          return SCFLOW_E_LAUNCH;
+        }
+        if (clusters > sms / 2) clusters = sms / 2;
+        cfg.gridDim = dim3(2 * (units < clusters ? units : clusters));
+      } else {
+        cfg.gridDim = dim3(units < sms ? units : sms);
       }
-      if (clusters > sms / 2) clusters = sms / 2;
-      cfg.gridDim = dim3(2 * (units < clusters ? units : clusters));
-      if (cudaLaunchKernelEx(&cfg, conv_patch_kernel<true>, maps, p) != cudaSuccess) return check_launch();
-    } else {
-      cudaFuncSetAttribute(conv_patch_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
-      cfg.gridDim = dim3(units < sms ? units : sms);
-      if (cudaLaunchKernelEx(&cfg, conv_patch_kernel<false>, maps, p) != cudaSuccess) return check_launch();
-    }
-    return check_launch();
+      cudaLaunchKernelEx(&cfg, kern, maps, p);
+      return check_launch();
+    };
+    if (pair) return gru ? launch(conv_patch_kernel<true, true>) : launch(conv_patch_kernel<true, false>);
+    return gru ? launch(conv_patch_kernel<false, true>) : launch(conv_patch_kernel<false, false>);
   }
   const int total = p.m_tiles * p.n_tiles;
   const int grid = total < sms ? total : sms;
-  if (bk == 64) {
-    cudaFuncSetAttribute(conv_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
-    conv_tc_kernel<64><<<grid, THREADS, smem_bytes, st>>>(maps, p);
-  } else {
-    cudaFuncSetAttribute(conv_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
-    conv_tc_kernel<32><<<grid, THREADS, smem_bytes, st>>>(maps, p);
-  }
+  auto launch1 = [&](auto kern) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    kern<<<grid, THREADS, smem_bytes, st>>>(maps, p);
+  };
+  const bool gru = p.epi != SCFLOW_EPI_PLAIN;
+  if (bk == 64) { if (gru) launch1(conv_tc_kernel<64, true>); else launch1(conv_tc_kernel<64, false>); }
+  else { if (gru) launch1(conv_tc_kernel<32, true>); else launch1(conv_tc_kernel<32, false>); }
   return check_launch();
 }

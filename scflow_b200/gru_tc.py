@@ -72,7 +72,7 @@ def update_inplace(mod, xh: "C.Split", h_state: torch.Tensor, scratch: Scratch =
     x_part, h_part = xh.slice(0, cx), xh.slice(cx, ch)
     for p in (0, 1):
         zr, qx, qh = packs(mod, p)
-        C.conv(xh, zr, out=sc.rh, epi=C.EPI_GRU_ZR, gru_h=h_state, gru_z=sc.z, bn=ch if ch <= 128 else 0)
+        C.conv(xh, zr, out=sc.rh, epi=C.EPI_GRU_ZR, gru_h=h_state, gru_z=sc.z)
         C.conv(x_part, qx, out_f32=sc.qx)
         C.conv(sc.rh, qh, res_f32=sc.qx, out=h_part, epi=C.EPI_GRU_GATE, gru_h=h_state, gru_z=sc.z)
 

@@ -17,6 +17,7 @@ ap.add_argument("--n", type=int, default=64)
 ap.add_argument("--reps", type=int, default=10)
 ap.add_argument("--only", default="")
 ap.add_argument("--once", action="store_true")
+ap.add_argument("--bn", type=int, default=0, help="output-channel tile width override (0: widest)")
 ap.add_argument("--algo", type=int, default=0, help="0 auto, 1 per-tap boxes, 2 patch, 3 patch on CTA pairs")
 a = ap.parse_args()
 dev = "cuda"
@@ -48,6 +49,8 @@ SHAPES = [
     ("head 3x3 64->32 @32", 32, 32, 64, 32, 3, 3, 1, 1, 1, "split", 8),
     ("pose 3x3/2 224->128 @32->16", 32, 32, 224, 128, 3, 3, 2, 1, 1, "f32", 8),
     ("pose 3x3/2 128->128 @16->8", 16, 16, 128, 128, 3, 3, 2, 1, 1, "f32", 8),
+    ("GRU zr epilogue 1x5 384->256 @32", 32, 32, 384, 256, 1, 5, 1, 0, 2, "gru_zr", 16),
+    ("GRU gate epilogue 1x5 128->128 @32", 32, 32, 128, 128, 1, 5, 1, 0, 2, "gru_gate", 16),
 ]
 
 
@@ -86,10 +89,20 @@ for name, h, w, cin, cout, kh, kw, s, ph, pw, out, calls in SHAPES:
             kw_.append(dict(out_f32=torch.empty(N, oh, ow, c8, device=dev), relu=True))
         elif out == "planar":
             kw_.append(dict(out_planar=torch.empty(N, c8, oh, ow, device=dev), planar_tf32=True))
+        elif out == "gru_zr":
+            kw_.append(dict(out=C.alloc_split(N, oh, ow, 128, dev), epi=C.EPI_GRU_ZR, bn=128,
+                            gru_h=torch.randn(N, oh, ow, 128, device=dev), gru_z=torch.empty(N, oh, ow, 128, device=dev)))
+        elif out == "gru_gate":
+            kw_.append(dict(out=C.alloc_split(N, oh, ow, 128, dev), epi=C.EPI_GRU_GATE,
+                            res_f32=torch.randn(N, oh, ow, 128, device=dev),
+                            gru_h=torch.randn(N, oh, ow, 128, device=dev), gru_z=torch.rand(N, oh, ow, 128, device=dev)))
         else:
             kw_.append(dict(out_f32=torch.empty(N, oh, ow, c8, device=dev),
                             stats=torch.zeros(N, c8, 2, device=dev, dtype=torch.float64)))
     algo = a.algo if (s == 1 or a.algo <= 1) else 1
+    if a.bn and cout % a.bn == 0 and cout > a.bn and "bn" not in kw_[0]:
+        for k_ in kw_:
+            k_["bn"] = a.bn
     run = lambda i: C.conv(xs[i % sets], pk, algo=algo, **kw_[i % sets])
     if a.once:
         run(0)
