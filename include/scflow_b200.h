@@ -88,6 +88,7 @@ int scflow_corr_pyramid_fwd(const float* feat1, const float* feat2, float* const
  * ------------------------------------------------------------------------------------------- */
 #define SCFLOW_LAYOUT_NCHW 0
 #define SCFLOW_LAYOUT_NHWC 1
+#define SCFLOW_LAYOUT_NHWC_GEN1 2   /* NHWC through the first-generation kernel: the cross-check of the tests */
 int scflow_corr_lookup_fwd(const float* const* levels, int num_levels, const float* flow,
                            float* out, short* windows, int n, int h, int w, int radius,
                            int div_mode, int out_layout, void* stream);
@@ -154,35 +155,12 @@ int scflow_downsample_fwd(const float* in, float* out, int n, int c, int H, int 
                           float mul, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
- * f3 (glue)  InstanceNorm2d / eval BatchNorm2d + ReLU + residual add of the RAFT encoders
- *            models/encoder/raft_encoder.py:286-314, BasicBlock models/backbone/resnet.py:12-92
- *            replaces per layer: conv-bias add_, native_batch_norm (2 kernels), relu_, add, relu_.
- * Channels-last activations (n, P, C) fp32, C % 4 == 0.
- * scflow_chan_stats_nhwc: sums[n][C][2] (fp64) = per image and channel (sum, sum of squares).
- * scflow_norm_act_nhwc:   out = act( N(x) [+ N_r(res)] ), act = ReLU if relu != 0, where each side
- *   is normalised by its statistics (sums != NULL: (v - mean) * rsqrt(var_biased + eps), the
- *   affine=False InstanceNorm2d of the encoder), or mapped by a per-channel affine (scale/shift
- *   != NULL: eval BatchNorm2d folded with the convolution bias), or passed through (both NULL).
- *   res may be NULL.  out may alias x or res.
+ * f3 (glue)  The InstanceNorm2d / eval BatchNorm2d + ReLU + residual passes of the RAFT encoders
+ *            (models/encoder/raft_encoder.py:286-314, BasicBlock models/backbone/resnet.py:12-92) are part
+ *            of the convolution family below: InstanceNorm statistics are accumulated by the convolution
+ *            epilogue (scflow_conv_tc_desc.stats) and applied by scflow_norm_apply_split; eval BatchNorm
+ *            is folded into the packed filters.  What remains here is layout glue.
  * ------------------------------------------------------------------------------------------- */
-int scflow_chan_stats_nhwc(const float* x, double* sums, int n, int P, int C, void* stream);
-int scflow_norm_act_nhwc(const float* x, const double* sums, const float* scale, const float* shift,
-                         const float* res, const double* res_sums, const float* res_scale,
-                         const float* res_shift, float* out, int n, int P, int C, float eps,
-                         int relu, void* stream);
-
-/* InstanceNorm2d (no affine) + optional residual + optional ReLU in ONE launch (resnet.py:64-92 on
- * the IN encoder): a thread-block cluster owns an image, takes the statistics, exchanges partial
- * sums through distributed shared memory and normalises its slice while it is still in L2, so a
- * layer costs one HBM read and one write instead of two reads and a write.  x (n, P, C) is
- * normalised into out (may alias x); res (optional, same shape) is added as res*res_scale +
- * res_shift (identity when the affine is NULL); sums_out (optional) receives the [n][C][2] fp64
- * statistics.  Statistics are those of scflow_chan_stats_nhwc up to the order of the final fp64
- * additions. */
-int scflow_instnorm_act_nhwc(float* x, const float* res, const float* res_scale, const float* res_shift,
-                             float* out, double* sums_out, int n, int P, int C, float eps, int relu,
-                             void* stream);
-
 /* (n, P, C) channels-last -> (n, C, P) planar, with optional round-to-nearest TF32: the hand-over
  * of channels-last encoder features to scflow_corr_pyramid_fwd (planar operands), replacing a
  * torch .contiguous() pass.  in != out. */
@@ -234,13 +212,10 @@ int scflow_conv_small_cin_fwd(const float* in, long long stride_n, long long str
                               const float* wpack, const float* bias, float* out, int n, int cin, int h,
                               int w, int cout, int ksize, int relu, void* stream);
 
-/* Stem input of the RAFT encoders (raft_encoder.py:286-288: conv1 7x7 stride 2 on 3 channels, the
- * one layer cuDNN has no tensor-core kernel for) as the 2x2 space-to-depth image of the equivalent
- * 4x4 stride-1 convolution: x planar (n, c <= 4, h, w), h and w even -> out channels-last
- * (n, h/2+3, w/2+3, 16), channel 4*c + 2*by + bx = x[n, c, 2Y+by, 2X+bx] at (Y+2, X+2); zero in the
- * unused channels and in the (2 before, 1 after) border = the stride-1 filter's padding. */
-int scflow_stem_s2d_fwd(const float* x, float* out, int n, int c, int h, int w, void* stream);
-/* The same image as two bf16 planes [hi | lo] of (n, h/2+3, w/2+3, 16) each (value = hi + lo): the operand
+/* Stem input of the RAFT encoders (raft_encoder.py:286-288: conv1 7x7 stride 2 on 3 channels) as the 2x2
+ * space-to-depth image of the equivalent 4x4 stride-1 convolution: x planar (n, c <= 4, h, w), h and w even
+ * -> (n, h/2+3, w/2+3, 16), channel 4*c + 2*by + bx = x[n, c, 2Y+by, 2X+bx] at (Y+2, X+2); zero in the
+ * unused channels and in the (2 before, 1 after) border = the stride-1 filter's padding.  Written as two bf16 planes [hi | lo] of (n, h/2+3, w/2+3, 16) each (value = hi + lo): the operand
  * of scflow_conv_tc_fwd, which reads the 4x4 stride-1 stem as 4 filter rows of 64 contiguous channels
  * (four x-neighbours) through an overlapped-window view (x_stride_w = 16). */
 int scflow_stem_s2d_split_fwd(const float* x, void* out, int n, int c, int h, int w, void* stream);

@@ -26,9 +26,6 @@ SIGNATURES = {
     "scflow_corr_lookup_fwd": (c_int, [_P, c_int, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_pack_nhwc": (c_int, [_P, c_int, _P, c_int, _P, c_int, _P, c_int, c_int, ctypes.c_longlong, c_int,
                                  c_int, _P]),
-    "scflow_chan_stats_nhwc": (c_int, [_P, _P, c_int, c_int, c_int, _P]),
-    "scflow_instnorm_act_nhwc": (c_int, [_P] * 6 + [c_int, c_int, c_int, ctypes.c_float, c_int, _P]),
-    "scflow_norm_act_nhwc": (c_int, [_P] * 9 + [c_int, c_int, c_int, c_float, c_int, _P]),
     "scflow_nhwc_to_nchw": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P]),
     "scflow_lift_points": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P]),
     "scflow_pose_flow_fwd": (c_int, [_P] * 14 + [c_int, c_int, c_int, c_int, c_float, c_float, _P]),
@@ -38,7 +35,6 @@ SIGNATURES = {
     "scflow_pose_fc_workspace_floats": (c_size_t, [c_int, c_int, c_int, c_int]),
     "scflow_pose_fc_fwd": (c_int, [_P] * 13 + [c_int] * 6 + [_P]),
     "scflow_pose_fc_fwd_static": (c_int, [_P] * 12 + [c_int] * 6 + [_P]),
-    "scflow_stem_s2d_fwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P]),
     "scflow_stem_s2d_split_fwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P]),
     "scflow_conv_small_cin_fwd": (c_int, [_P, ctypes.c_longlong, ctypes.c_longlong, ctypes.c_longlong, _P, _P, _P,
                                           c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P]),

@@ -143,11 +143,7 @@ extern "C" int scflow_corr_lookup_bwd(const float* grad_out, int grad_layout, co
   p.plane_off[bw::kLevels] = off;
   const size_t smem = (size_t)bw::kLBWarps * off * sizeof(float);
   if (smem > 200 * 1024) return SCFLOW_E_BAD_SHAPE;
-  static size_t attr_smem = 0;
-  if (smem > attr_smem) {
-    cudaFuncSetAttribute(bw::corr_lookup_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr_smem = smem;
-  }
+  cudaFuncSetAttribute(bw::corr_lookup_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   // per device
   const long long total_q = (long long)n * P;
   long long blocks = (total_q + bw::kLBWarps - 1) / bw::kLBWarps;
   const long long cap = 148LL * (smem > 64 * 1024 ? 2 : 8);

@@ -326,12 +326,12 @@ int launch_corr_lookup_v2(const float* const* levels, const float* flow, float* 
                           int n, int h, int w, int div_mode, cudaStream_t stream);
 
 int launch_corr_lookup_nhwc(const float* const* levels, const float* flow, float* out, short* windows,
-                            int n, int h, int w, int div_mode, cudaStream_t stream) {
+                            int n, int h, int w, int div_mode, bool gen1, cudaStream_t stream) {
   using namespace lk;
-  // second-generation kernel (corr_lookup_v2.cu) wherever every level row is a 16-byte multiple;
-  // SCFLOW_LK=v1 keeps this file's kernel (cross-check and A/B timing)
-  const char* gen = getenv("SCFLOW_LK");
-  if (!(gen && strcmp(gen, "v1") == 0)) {
+  // second-generation kernel (corr_lookup_v2.cu) wherever every level row is a 16-byte multiple; this file's
+  // kernel takes the other shapes, and any shape when the caller asks for it (SCFLOW_LAYOUT_NHWC_GEN1: the
+  // tests hold the two independently written kernels to identical windows and values)
+  if (!gen1) {
     const int rc = launch_corr_lookup_v2(levels, flow, out, windows, n, h, w, div_mode, stream);
     if (rc != SCFLOW_E_UNSUPPORTED) return rc;
   }
@@ -380,16 +380,10 @@ int launch_corr_lookup_nhwc(const float* const* levels, const float* flow, float
   p.n = n; p.h = h; p.w = w; p.div_mode = div_mode; p.total_q = total_q;
   if ((double)h * w * w >= 4294967296.0) return SCFLOW_E_BAD_SHAPE;
   p.magic_w = (w & (w - 1)) == 0 ? (unsigned)(4294967296ull / (unsigned)w) : (unsigned)(4294967296ull / (unsigned)w) + 1u;
-  const char* mb = getenv("SCFLOW_LK_MINB");
-  const int minb = (mb && atoi(mb) == 4) ? 4 : 3;   // 3 CTAs/SM (78 registers, no spills) measured faster
-  auto kern = div_mode == SCFLOW_DIV_IEEE
-                  ? (minb == 3 ? corr_lookup_nhwc_kernel<SCFLOW_DIV_IEEE, 3> : corr_lookup_nhwc_kernel<SCFLOW_DIV_IEEE, 4>)
-                  : (minb == 3 ? corr_lookup_nhwc_kernel<SCFLOW_DIV_RCP, 3> : corr_lookup_nhwc_kernel<SCFLOW_DIV_RCP, 4>);
-  static int attr_bytes[2][2] = {{0, 0}, {0, 0}};
-  if (smem_bytes > attr_bytes[div_mode][minb - 3]) {
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-    attr_bytes[div_mode][minb - 3] = smem_bytes;
-  }
+  constexpr int minb = 3;                           // 3 CTAs/SM (78 registers, no spills) measured faster than 4
+  auto kern = div_mode == SCFLOW_DIV_IEEE ? corr_lookup_nhwc_kernel<SCFLOW_DIV_IEEE, 3>
+                                          : corr_lookup_nhwc_kernel<SCFLOW_DIV_RCP, 3>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);   // per device: every launch
   int sms = 0, dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -344,30 +344,17 @@ int launch_corr_lookup_v2(const float* const* levels, const float* flow, float* 
   p.flow = flow; p.out = out; p.windows = windows;
   p.h = h; p.w = w; p.total_q = (int)total_q;
   p.magic_w = (w & (w - 1)) == 0 ? (unsigned)(4294967296ull / (unsigned)w) : (unsigned)(4294967296ull / (unsigned)w) + 1u;
-  // occupancy variants (warps per CTA x CTAs per SM), SCFLOW_LK2_CFG: measured at cfg2 on B200:
-  // 0: 8 x 3 47.7 us (default), 1: 6 x 5 54.9 us, 2: 7 x 4 51.8 us -- more resident warps lose
-  static const int kCfg[7][2] = {{8, 3}, {6, 5}, {7, 4}, {8, 2}, {6, 3}, {12, 2}, {4, 6}};
-  const char* e = getenv("SCFLOW_LK2_CFG");
-  int cfg = e ? atoi(e) : 0;
-  if (cfg < 0 || cfg > 6) cfg = 0;
-  const int warps = kCfg[cfg][0], minb = kCfg[cfg][1];
+  // 8 warps per CTA x 3 CTAs per SM.  Measured at cfg2 on B200: 8 x 3 47.7 us, 7 x 4 51.8 us, 6 x 5 54.9 us,
+  // 8 x 2 / 6 x 3 / 12 x 2 / 4 x 6 all 47-48 us: more resident warps lose, fewer change nothing
+  constexpr int warps = 8, minb = 3;
   typedef void (*Kern)(const Maps, const Params);
   const bool ieee = div_mode == SCFLOW_DIV_IEEE, win = windows != nullptr;
-#define SCFLOW_LK2_PICK(W, B)                                                                      \
-  (ieee ? (win ? (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_IEEE, W, B, true>                          \
-               : (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_IEEE, W, B, false>)                        \
-        : (win ? (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_RCP, W, B, true>                           \
-               : (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_RCP, W, B, false>))
-  Kern kern = cfg == 0 ? SCFLOW_LK2_PICK(8, 3) : cfg == 1 ? SCFLOW_LK2_PICK(6, 5) : cfg == 2 ? SCFLOW_LK2_PICK(7, 4)
-            : cfg == 3 ? SCFLOW_LK2_PICK(8, 2) : cfg == 4 ? SCFLOW_LK2_PICK(6, 3) : cfg == 5 ? SCFLOW_LK2_PICK(12, 2)
-                       : SCFLOW_LK2_PICK(4, 6);
-#undef SCFLOW_LK2_PICK
+  Kern kern = ieee ? (win ? (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_IEEE, warps, minb, true>
+                          : (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_IEEE, warps, minb, false>)
+                   : (win ? (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_RCP, warps, minb, true>
+                          : (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_RCP, warps, minb, false>);
   const int smem_bytes = warps * kWarpBytes;
-  static bool attr_set[7][2][2] = {};
-  if (!attr_set[cfg][ieee][win]) {
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-    attr_set[cfg][ieee][win] = true;
-  }
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);   // per device: every launch
   int sms = 0, dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -151,17 +151,12 @@ struct Params {
   int tiles_m, tiles_y, tiles_x;
   float scale, inv_scale;
   int scale_is_pow2;
-  int dbg;              // SCFLOW_CORR_DBG bits (profiling only): 1 no L0 stores, 2 no L1-3 stores, 4 no loads, 8 no MMA
 };
 
 __device__ __forceinline__ void decode_tile(const Params& p, int tile, int tiles_per_m, int& pj, int& mt, int& n) {
-  if (p.dbg & 16) {       // query tile fastest: CTAs running side by side share the TARGET tile
-    mt = tile % p.tiles_m;
-    pj = (tile / p.tiles_m) % tiles_per_m;
-  } else {                // target tile fastest: neighbours share the QUERY tile
-    pj = tile % tiles_per_m;
-    mt = (tile / tiles_per_m) % p.tiles_m;
-  }
+  // target tile fastest: neighbours share the QUERY tile (query-tile-fastest measured the same)
+  pj = tile % tiles_per_m;
+  mt = (tile / tiles_per_m) % p.tiles_m;
   n = tile / (tiles_per_m * p.tiles_m);
 }
 
@@ -215,12 +210,9 @@ corr_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int kb = 0; kb < KB; ++kb) {
           tc::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* a_s = smem + stage * STAGE_BYTES;
-          if (p.dbg & 4) { tc::mbar_arrive(&full[stage]); }
-          else {
           tc::mbar_expect_tx(&full[stage], STAGE_BYTES);
           tc::tma_load_4d(&mapA, &full[stage], a_s, 0, kb * BK, mt * (BM / 32), n);
           tc::tma_load_4d(&mapB, &full[stage], a_s + A_BYTES, tx * 32, kb * BK, ty * 8, n);
-          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -240,7 +232,6 @@ corr_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           tc::tc_fence_after();
           const uint32_t a_addr = tc::smem_u32(smem + stage * STAGE_BYTES);
           const uint32_t b_addr = a_addr + A_BYTES;
-          if (!(p.dbg & 8))
 #pragma unroll
           for (int kk = 0; kk < BK / UK; ++kk) {
             // MN-major 32-bit operands: SWIZZLE_128B_BASE32B is the only layout tcgen05 accepts.
@@ -290,7 +281,6 @@ corr_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int j = 0; j < 32; ++j) v[j] = POW2 ? v[j] * p.inv_scale : __fdiv_rn(v[j], p.scale);
         // level 0: the warp's 32 queries x 32 targets of row r go out as one TMA box; the store
         // issued two rows ago must have drained this staging buffer
-        if (!(p.dbg & 1)) {
         if (lane == 0) tc::bulk_wait_read<1>();
         __syncwarp();
         {
@@ -307,11 +297,10 @@ corr_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           tc::tma_store_3d(&mapC, stg + (r & 1) * EPI_BUF_BYTES, tx * 32, ty * 8 + r, (int)qbase);
           tc::bulk_commit();
         }
-        }
         if ((r & 1) == 0) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) prev0[j] = v[j];
-        } else if (p.num_levels > 1 && !(p.dbg & 2)) {
+        } else if (p.num_levels > 1) {
           float l1[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) l1[j] = pool4(prev0[2 * j], prev0[2 * j + 1], v[2 * j], v[2 * j + 1]);
@@ -407,13 +396,9 @@ static int corr_tf32(const float* f1, const float* f2, float* const* levels, int
   p.inv_scale = 1.0f / p.scale;
   int e; const float fr = frexpf(p.scale, &e);
   p.scale_is_pow2 = (fr == 0.5f) ? 1 : 0;
-  { const char* e = getenv("SCFLOW_CORR_DBG"); p.dbg = e ? atoi(e) : 0; }
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(corr_tf32_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
-    cudaFuncSetAttribute(corr_tf32_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
-    attr_set = true;
-  }
+  // function attributes are per device: set on every launch (cheap), no process-wide guard
+  cudaFuncSetAttribute(corr_tf32_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+  cudaFuncSetAttribute(corr_tf32_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
   const long long total = (long long)n * p.tiles_m * p.tiles_y * p.tiles_x;
   const int grid = (int)(total < device_sm_count() ? total : device_sm_count());
   if (p.scale_is_pow2)

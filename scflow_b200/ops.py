@@ -123,16 +123,18 @@ def corr_pyramid(feat1: torch.Tensor, feat2: torch.Tensor, num_levels: int = 4,
     return levels
 
 
-LAYOUT_NCHW, LAYOUT_NHWC = 0, 1
+LAYOUT_NCHW, LAYOUT_NHWC, LAYOUT_NHWC_GEN1 = 0, 1, 2
 
 
 def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int = 4,
-                div_mode: int = DIV_IEEE, return_windows: bool = False, channels_last: bool = True):
+                div_mode: int = DIV_IEEE, return_windows: bool = False, channels_last: bool = True,
+                gen1: bool = False):
     """CorrLookup.forward (corr_lookup.py:102-136): (N, L*(2r+1)^2, H, W).
 
     With `channels_last` (default) the result has the reference's shape but channels-last
     strides (memory (N, H, W, 324)): what the warp-per-query kernel writes and what the
-    downstream convolutions consume without a layout pass."""
+    downstream convolutions consume without a layout pass.  `gen1`: the first-generation kernel on any
+    shape (the tests' cross-check; the second generation runs wherever it applies otherwise)."""
     lib = _lib.load()
     fl = _chk(flow, "flow")
     n, two, h, w = fl.shape
@@ -151,7 +153,8 @@ def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int
     arr = (ctypes.c_void_p * L)(*[p.data_ptr() for p in lv])
     with _timed("scflow_corr_lookup_fwd", 1):
         rc = lib.scflow_corr_lookup_fwd(arr, L, _ptr(fl), _ptr(out), _ptr(win), n, h, w, radius, div_mode,
-                                        LAYOUT_NHWC if channels_last else LAYOUT_NCHW, _stream())
+                                        (LAYOUT_NHWC_GEN1 if gen1 else LAYOUT_NHWC) if channels_last else LAYOUT_NCHW,
+                                        _stream())
     _lib.check(rc, "scflow_corr_lookup_fwd")
     return (out, win) if return_windows else out
 
@@ -180,65 +183,6 @@ def pack_nhwc(dst: torch.Tensor, dst_off: int, a: Optional[torch.Tensor] = None,
                                   n * H * W, H * W, 1 if round_tf32 else 0, _stream())
     _lib.check(rc, "scflow_pack_nhwc")
     return dst
-
-
-def chan_stats(x: torch.Tensor) -> torch.Tensor:
-    """(N,H,W,C) channels-last -> (N,C,2) fp64 per-image, per-channel (sum, sum of squares)."""
-    lib = _lib.load()
-    x = _chk(x, "x")
-    n, H, W, C = x.shape
-    sums = torch.empty((n, C, 2), device=x.device, dtype=torch.float64)
-    with _timed("scflow_chan_stats_nhwc", 1, 4 * x.numel()):
-        rc = lib.scflow_chan_stats_nhwc(_ptr(x), _ptr(sums), n, H * W, C, _stream())
-    _lib.check(rc, "scflow_chan_stats_nhwc")
-    return sums
-
-
-def norm_act(x: torch.Tensor, sums=None, affine=None, res=None, res_sums=None, res_affine=None,
-             relu: bool = True, eps: float = 1e-5, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """out = act(N(x) [+ N_r(res)]) on channels-last (N,H,W,C) tensors; see scflow_norm_act_nhwc.
-    `affine` / `res_affine` are (scale, shift) per-channel fp32 tensors."""
-    lib = _lib.load()
-    x = _chk(x, "x")
-    n, H, W, C = x.shape
-    if res is not None:
-        res = _chk(res, "res")
-        assert res.shape == x.shape
-    if out is None:
-        out = x
-    sc, sh = affine if affine is not None else (None, None)
-    rsc, rsh = res_affine if res_affine is not None else (None, None)
-    if sums is not None:
-        sums = _chk(sums, "sums", torch.float64)
-    if res_sums is not None:
-        res_sums = _chk(res_sums, "res_sums", torch.float64)
-    with _timed("scflow_norm_act_nhwc", 1, 4 * x.numel() * (3 if res is not None else 2)):
-        rc = lib.scflow_norm_act_nhwc(_ptr(x), _ptr(sums), _ptr(sc), _ptr(sh), _ptr(res), _ptr(res_sums),
-                                      _ptr(rsc), _ptr(rsh), _ptr(out), n, H * W, C, float(eps),
-                                      1 if relu else 0, _stream())
-    _lib.check(rc, "scflow_norm_act_nhwc")
-    return out
-
-
-def instnorm_act(x: torch.Tensor, res: Optional[torch.Tensor] = None, res_affine=None, relu: bool = True,
-                 eps: float = 1e-5, out: Optional[torch.Tensor] = None, want_sums: bool = False):
-    """InstanceNorm (+ residual) (+ ReLU) of a channels-last (N,H,W,C) tensor in one launch, in place
-    unless `out` is given (scflow_instnorm_act_nhwc)."""
-    lib = _lib.load()
-    x = _chk(x, "x")
-    n, H, W, C = x.shape
-    if res is not None:
-        res = _chk(res, "res")
-        assert res.shape == x.shape
-    if out is None:
-        out = x
-    rsc, rsh = res_affine if res_affine is not None else (None, None)
-    sums = torch.empty((n, C, 2), device=x.device, dtype=torch.float64) if want_sums else None
-    with _timed("scflow_instnorm_act_nhwc", 1, 4 * x.numel() * (3 if res is not None else 2)):
-        rc = lib.scflow_instnorm_act_nhwc(_ptr(x), _ptr(res), _ptr(rsc), _ptr(rsh), _ptr(out), _ptr(sums), n, H * W, C,
-                                          float(eps), 1 if relu else 0, _stream())
-    _lib.check(rc, "scflow_instnorm_act_nhwc")
-    return (out, sums) if want_sums else out
 
 
 def lift_points(depth, K, R0, t0):
@@ -345,19 +289,6 @@ def conv_small_cin(x: torch.Tensor, conv: torch.nn.Conv2d, relu: bool) -> torch.
                                            _ptr(conv.bias.detach() if conv.bias is not None else None),
                                            _ptr(out), n, cin, h, w, cout, k, 1 if relu else 0, _stream())
     _lib.check(rc, "scflow_conv_small_cin_fwd")
-    return out.permute(0, 3, 1, 2)
-
-
-def stem_s2d(x: torch.Tensor) -> torch.Tensor:
-    """Planar (N,C<=4,H,W) image -> the 2x2 space-to-depth input of the stride-1 form of the encoder
-    stem: an (N,16,H/2+3,W/2+3)-shaped channels-last tensor (see scflow_stem_s2d_fwd)."""
-    lib = _lib.load()
-    x = _chk(x, "x")
-    n, c, h, w = x.shape
-    out = torch.empty((n, h // 2 + 3, w // 2 + 3, 16), device=x.device, dtype=torch.float32)
-    with _timed("scflow_stem_s2d_fwd", 1, 4 * (x.numel() + out.numel())):
-        rc = lib.scflow_stem_s2d_fwd(_ptr(x), _ptr(out), n, c, h, w, _stream())
-    _lib.check(rc, "scflow_stem_s2d_fwd")
     return out.permute(0, 3, 1, 2)
 
 

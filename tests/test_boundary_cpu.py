@@ -41,8 +41,7 @@ def test_abi_version_and_strerror(lib):
 def test_null_and_shape_rejected_without_gpu(lib):
     # argument validation happens before any CUDA call, so it is checkable on the CPU box
     assert lib.scflow_corr_lookup_fwd(None, 4, None, None, None, 1, 32, 32, 4, 0, 1, None) == -4
-    assert lib.scflow_norm_act_nhwc(*([None] * 9), 1, 16, 64, 1e-5, 1, None) == -4
-    assert lib.scflow_chan_stats_nhwc(None, None, 1, 16, 64, None) == -4
+    assert lib.scflow_norm_apply_split(*([None] * 3), 0, 0, None, None, None, 0, 0, None, 1, 16, 64, 1e-5, 1, None) == -4
     assert lib.scflow_nhwc_to_nchw(None, None, 1, 16, 64, 1, None) == -4
     assert lib.scflow_corr_pyramid_fwd(None, None, None, 4, 1, 256, 32, 32, 1, None, 0, None) == -4
     assert lib.scflow_upsample_fwd(None, None, None, 1, 1, 4, 4, 8, 1.0, None) == -4

@@ -134,11 +134,11 @@ def test_lookup_layouts_agree_full_size():
     assert float(a[1].abs().max()) == 0.0
 
 
-def test_lookup_generations_identical(monkeypatch):
+def test_lookup_generations_identical():
     """The second-generation NHWC kernel (16x12 TMA box at every level, immediate-offset taps,
     w0 = 1 - w1) replays the first generation's arithmetic: identical windows AND identical
-    values, on random, zero (round-trip edge case -> slow taps), far-out and mixed flows, for
-    every occupancy variant and both division modes; 512^2-crop shape included."""
+    values, on random, zero (round-trip edge case -> slow taps), far-out and mixed flows, for both
+    division modes; 512^2-crop shape included.  (gen1=True: SCFLOW_LAYOUT_NHWC_GEN1.)"""
     g = torch.Generator(device=DEV).manual_seed(5)
     for n, h, w in ((8, 32, 32), (2, 64, 64), (2, 24, 32)):
         pyr = [torch.randn(n * h * w, 1, h >> l, w >> l, device=DEV, generator=g) for l in range(4)]
@@ -147,16 +147,12 @@ def test_lookup_generations_identical(monkeypatch):
         flow[1, :, : h // 2] = 300.0
         flow[1, :, h // 2:] = torch.round(flow[1, :, h // 2:])       # integer coordinates, non-zero
         for div in (ops.DIV_IEEE, ops.DIV_RCP):
-            monkeypatch.setenv("SCFLOW_LK", "v1")
-            a, wa = ops.corr_lookup(pyr, flow, 4, div, return_windows=True)
-            a2 = ops.corr_lookup(pyr, flow, 4, div)
-            monkeypatch.setenv("SCFLOW_LK", "v2")
-            for cfg in ("0", "1", "2"):
-                monkeypatch.setenv("SCFLOW_LK2_CFG", cfg)
-                b, wb = ops.corr_lookup(pyr, flow, 4, div, return_windows=True)
-                b2 = ops.corr_lookup(pyr, flow, 4, div)
-                assert torch.equal(wa, wb), (n, h, w, div, cfg)
-                assert torch.equal(a, b) and torch.equal(a2, b2) and torch.equal(a, a2), (n, h, w, div, cfg)
+            a, wa = ops.corr_lookup(pyr, flow, 4, div, return_windows=True, gen1=True)
+            a2 = ops.corr_lookup(pyr, flow, 4, div, gen1=True)
+            b, wb = ops.corr_lookup(pyr, flow, 4, div, return_windows=True)
+            b2 = ops.corr_lookup(pyr, flow, 4, div)
+            assert torch.equal(wa, wb), (n, h, w, div)
+            assert torch.equal(a, b) and torch.equal(a2, b2) and torch.equal(a, a2), (n, h, w, div)
 
 
 def test_lookup_impulse_and_zero_flow():
@@ -323,50 +319,26 @@ def test_batch64_matches_per_crop_runs():
     assert float(O.rotation_geodesic(Ra.cpu(), Rb.cpu()).max()) < 1e-4
 
 
-# ------------------------------------------------------------------ f3 InstanceNorm in one launch
-@pytest.mark.parametrize("n,h,w,c", [(3, 128, 128, 64), (2, 64, 64, 96), (5, 32, 32, 128), (1, 8, 12, 64), (2, 24, 40, 96)])
-@pytest.mark.parametrize("with_res", [False, True])
-def test_instnorm_cluster_kernel_equals_two_launches(n, h, w, c, with_res):
-    """scflow_instnorm_act_nhwc (statistics + normalise in one cluster launch) against the
-    chan_stats + norm_act pair: statistics equal to fp64 rounding, outputs identical up to one
-    fp32 ulp of the coefficients, and against torch's instance_norm."""
-    g = torch.Generator(device=DEV).manual_seed(41)
-    x = torch.randn(n, h, w, c, device=DEV, generator=g) * 3.0 + 0.7
-    res = torch.randn(n, h, w, c, device=DEV, generator=g) if with_res else None
-    sums = ops.chan_stats(x)
-    want = ops.norm_act(x.clone(), sums=sums, res=res, relu=True)
-    got, gs = ops.instnorm_act(x.clone(), res=res, relu=True, want_sums=True)
-    assert float(((gs - sums).abs() / sums.abs().clamp_min(1.0)).max()) < 1e-13
-    assert float((got - want).abs().max()) <= 2e-6 * float(want.abs().max())
-    ref = torch.nn.functional.instance_norm(x.permute(0, 3, 1, 2)).permute(0, 2, 3, 1)
-    ref = torch.relu(ref + res) if with_res else torch.relu(ref)
-    assert float((got - ref).abs().max()) < 2e-5
-    # out-of-place and no activation
-    out = torch.empty_like(x)
-    ops.instnorm_act(x, relu=False, out=out)
-    assert float((out - torch.nn.functional.instance_norm(x.permute(0, 3, 1, 2)).permute(0, 2, 3, 1)).abs().max()) < 2e-5
-
-
 # ------------------------------------------------------------------ f3 encoder stem (space-to-depth form)
 @pytest.mark.parametrize("n,c,h,w", [(2, 3, 256, 256), (1, 3, 64, 96), (3, 1, 16, 8)])
 def test_stem_space_to_depth_input(n, c, h, w):
-    """scflow_stem_s2d_fwd == pixel_unshuffle + channel / border padding, bit for bit, and the 4x4
-    stride-1 filter over it == the shipped 7x7 stride-2 convolution (raft_encoder.py:286-288)."""
+    """scflow_stem_s2d_split_fwd == pixel_unshuffle + channel / border padding as hi + lo bf16 planes (16
+    significand bits), and the 4x4 stride-1 filter over it == the shipped 7x7 stride-2 convolution
+    (raft_encoder.py:286-288), evaluated in fp64."""
     from scflow_b200 import encoder as E
     g = torch.Generator(device=DEV).manual_seed(31)
     x = torch.rand(n, c, h, w, device=DEV, generator=g)
-    got = ops.stem_s2d(x)
+    planes = ops.stem_s2d_split(x)
+    got = planes[0].float() + planes[1].float()                       # (n, h/2+3, w/2+3, 16)
     want = torch.nn.functional.pad(torch.nn.functional.pixel_unshuffle(x, 2), (2, 1, 2, 1, 0, 16 - 4 * c))
-    assert got.shape == want.shape and torch.equal(got, want)
+    want = want.permute(0, 2, 3, 1)
+    assert got.shape == want.shape
+    assert float((got - want).abs().max()) <= 2.0 ** -17 * float(want.abs().max())
+    assert bool(((want == 0) <= (got == 0)).all())                     # padding and unused channels are exact zeros
     wgt = torch.randn(64, c, 7, 7, device=DEV, generator=g)
-    old = torch.backends.cudnn.allow_tf32
-    torch.backends.cudnn.allow_tf32 = False
-    try:
-        ref = torch.nn.functional.conv2d(x, wgt, None, 2, 3)
-        out = torch.nn.functional.conv2d(got, E._s2d_filter(wgt))
-    finally:
-        torch.backends.cudnn.allow_tf32 = old
-    assert rel(out, ref) < 1e-5
+    ref = torch.nn.functional.conv2d(x.double(), wgt.double(), None, 2, 3)
+    out = torch.nn.functional.conv2d(want.permute(0, 3, 1, 2).double(), E._s2d_filter(wgt).double())
+    assert rel(out, ref) < 1e-12
 
 
 # ------------------------------------------------------------------ a3 ConvGRU (tcgen05)
@@ -432,27 +404,7 @@ def test_decoder_with_tcgen05_gru(golden_dir):
     assert er < 1e-4 and et < 0.1
 
 
-# ------------------------------------------------------------------ f3 glue: norm + act kernels
-@pytest.mark.parametrize("n,h,w,c", [(2, 16, 24, 64), (3, 8, 8, 96), (1, 32, 32, 128), (2, 5, 7, 256)])
-def test_instance_norm_relu_residual_vs_torch(n, h, w, c):
-    g = torch.Generator().manual_seed(c)
-    x = (torch.randn(n, c, h, w, generator=g) * 3 + 1.5)
-    r = torch.randn(n, c, h, w, generator=g)
-    want = torch.relu(torch.nn.functional.instance_norm(x.double()) + torch.nn.functional.instance_norm(r.double()))
-    xn = x.to(DEV).permute(0, 2, 3, 1).contiguous()
-    rn = r.to(DEV).permute(0, 2, 3, 1).contiguous()
-    sums = ops.chan_stats(xn)
-    ref_s = torch.stack([x.double().sum((2, 3)), (x.double() ** 2).sum((2, 3))], dim=-1)
-    assert float((sums.cpu() - ref_s).abs().max() / ref_s.abs().max()) < 1e-6
-    out = ops.norm_act(xn.clone(), sums=sums, res=rn, res_sums=ops.chan_stats(rn), relu=True)
-    assert rel(out.permute(0, 3, 1, 2), want) < 2e-6
-    # plain norm + relu in place, and identity residual
-    y = xn.clone()
-    ops.norm_act(y, sums=sums, res=rn, relu=False)
-    want2 = torch.nn.functional.instance_norm(x.double()) + r.double()
-    assert rel(y.permute(0, 3, 1, 2), want2) < 2e-6
-
-
+# ------------------------------------------------------------------ f3 encoders: tensor-core path vs nn.Module path
 @pytest.mark.parametrize("norm", ["IN", "BN"])
 def test_encoder_fused_path_matches_module_path(norm):
     """The tensor-core inference path of RAFTEncoder (split-bf16 convolutions) equals the plain nn.Module

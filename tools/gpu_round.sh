@@ -21,7 +21,7 @@ SCFLOW_PROFILE=1 timeout 600 $CMD > gpurun_out/${TAG}_plain.log 2>&1 &&
 SCFLOW_PROFILE=1 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off \
   --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
-for K in corr_lookup_v2_kernel:2:2 convgru_fused_kernel:2:1 corr_tf32_kernel:1:0 instnorm_act_cluster_kernel:3:2 stem_s2d_kernel:1:0 norm_act_kernel:2:1 chan_stats_kernel:2:1 pose_flow_kernel:1:2 conv_small_cin_kernel:2:3 conv_small_cout_kernel:2:2 linear_splitk_kernel:2:2 group_norm4_act_kernel:1:3; do
+for K in corr_lookup_v2_kernel:2:2 corr_tf32_kernel:1:0 conv_patch_kernel:6:40 norm_apply_split_kernel:2:4 pose_flow_kernel:1:2 conv_small_cin_kernel:2:3 conv_small_cout:2:2 linear_splitk_kernel:2:2 group_norm4_act_kernel:1:3 split_bf16_kernel:2:4; do
   RE=${K%%:*}; R=${K#*:}; CNT=${R%%:*}; SKIP=${R#*:}
   SCFLOW_PROFILE=1 timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off \
     -k regex:"$RE" -s $SKIP -c $CNT -o /tmp/${TAG}_${RE} -f $CMD > gpurun_out/${TAG}_ncu_${RE}.log 2>&1

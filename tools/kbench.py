@@ -1,13 +1,13 @@
 """Per-kernel micro-benchmark at cfg2 shapes (N=64, 256x256 crops -> 32x32 features).
-    python tools/kbench.py [lookup] [gru] [corr] [pose] [--n 64] [--s 256]
+    python tools/kbench.py [lookup] [corr] [pose] [small] [posefc] [--n 64] [--s 256]   (convolutions: tools/convbench.py)
 Each kernel is timed with CUDA events over `reps` launches on rotating buffers larger than L2."""
 import os, sys, argparse
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from scflow_b200 import ops, gru_tc, modules
+from scflow_b200 import ops, modules
 
 ap = argparse.ArgumentParser()
-ap.add_argument("which", nargs="*", default=["lookup", "gru", "corr", "pose", "small"])   # also: norm
+ap.add_argument("which", nargs="*", default=["lookup", "corr", "pose", "small"])
 ap.add_argument("--n", type=int, default=64)
 ap.add_argument("--s", type=int, default=256)
 ap.add_argument("--reps", type=int, default=20)
@@ -56,15 +56,8 @@ if "lookup" in a.which:
     pyrs = [[torch.randn(N * P, 1, h >> l, w >> l, device=dev, generator=g) for l in range(4)] for _ in range(sets)]
     flow = [2.0 * torch.randn(N, 2, h, w, device=dev, generator=g) for _ in range(sets)]
     by = N * (P * 324 * 4 + P * 4 * 100 * 4 + 8 * P)
-    for tag, env in (("v1", {"SCFLOW_LK": "v1"}), ("v2 8x3", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "0"}),
-                     ("v2 6x5", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "1"}),
-                     ("v2 7x4", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "2"}),
-                     ("v2 8x2", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "3"}),
-                     ("v2 6x3", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "4"}),
-                     ("v2 12x2", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "5"}),
-                     ("v2 4x6", {"SCFLOW_LK": "v2", "SCFLOW_LK2_CFG": "6"})):
-        os.environ.update(env)
-        us = timeit(lambda i: ops.corr_lookup(pyrs[i % sets], flow[i % sets], 4, channels_last=True))
+    for tag, g1 in (("gen 1", True), ("gen 2", False)):
+        us = timeit(lambda i: ops.corr_lookup(pyrs[i % sets], flow[i % sets], 4, channels_last=True, gen1=g1))
         print(f"corr_lookup nhwc {tag:7s} {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)")
     zero = torch.zeros_like(flow[0])
     us = timeit(lambda i: ops.corr_lookup(pyrs[i % sets], zero, 4, channels_last=True))
@@ -72,21 +65,8 @@ if "lookup" in a.which:
     half = [f * (torch.rand(N, 1, h, w, device=dev, generator=g) > 0.57) for f in flow]     # 57 % background as in the bench crops
     us = timeit(lambda i: ops.corr_lookup(pyrs[i % sets], half[i % sets], 4, channels_last=True))
     print(f"corr_lookup nhwc 57 % zero-flow queries {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)")
-    os.environ.pop("SCFLOW_LK2_CFG", None); os.environ.pop("SCFLOW_LK", None)
     us = timeit(lambda i: ops.corr_lookup(pyrs[i % sets], flow[i % sets], 4, channels_last=False))
     print(f"corr_lookup nchw    {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)")
-if "gru" in a.which:
-    mod = modules.ConvGRU(128, 256).to(dev)
-    hs = [torch.randn(N, h, w, 128, device=dev, generator=g) for _ in range(3)]
-    xs = [gru_tc.round_tf32(torch.randn(N, h, w, 256, device=dev, generator=g)) for _ in range(3)]
-    hr = [gru_tc.round_tf32(t) for t in hs]
-    rh = torch.empty_like(hs[0])
-    fl = 3 * 2.0 * N * P * 128 * 1920
-    for tag, env in (("two launches", "0"), ("one launch", "1")):
-        os.environ["SCFLOW_GRU_FUSED"] = env
-        us = timeit(lambda i: gru_tc.update_inplace(mod, hs[i % 3], hr[i % 3], xs[i % 3], rh)) / 2
-        print(f"convgru pass ({tag:12s}) {us:8.1f} us  {fl/us/1e6:6.1f} TFLOP/s tf32")
-    os.environ.pop("SCFLOW_GRU_FUSED", None)
 if "pose" in a.which:
     from scflow_b200 import synthetic as syn
     cr = {k: v.to(dev) for k, v in syn.make_crops(4, S, seed=1).items()}
@@ -99,33 +79,21 @@ if "pose" in a.which:
     print(f"pose_flow           {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)  (includes 4 output allocations)")
 
 if "small" in a.which:
-    import torch.nn.functional as F
     from scflow_b200.modules import ConvModule, XHead
-    torch.backends.cudnn.allow_tf32 = True
-    torch.backends.cudnn.benchmark = True
     for cin, k, cout in ((2, 7, 128), (1, 3, 64)):
         m = ConvModule(cin, cout, k, padding=k // 2).to(dev)
         xs = [torch.randn(N, cin, h, w, device=dev, generator=g) for _ in range(4)]
         with torch.no_grad():
-            os.environ["SCFLOW_CIN_SEG"] = "8"
-            us8 = timeit(lambda i: m(xs[i % 4]))
-            os.environ.pop("SCFLOW_CIN_SEG")
-            print(f"conv_small_cin {cin}->{cout} {k}x{k}, 8 px per lane {us8:8.1f} us")
             us = timeit(lambda i: m(xs[i % 4]))
-            ref = timeit(lambda i: torch.relu_(F.conv2d(xs[i % 4].contiguous(memory_format=torch.channels_last), m.conv.weight, m.conv.bias, padding=k // 2)))
         by = N * P * (cin + cout) * 4
-        print(f"conv_small_cin {cin}->{cout} {k}x{k}  {us:8.1f} us  {by/us/1e3:7.1f} GB/s  (cuDNN+relu {ref:.1f} us)")
+        print(f"conv_small_cin {cin}->{cout} {k}x{k}  {us:8.1f} us  {by/us/1e3:7.1f} GB/s")
     for k, cout in ((3, 2), (1, 1)):
         hd = XHead(128, [256], cout, x="flow" if k == 3 else "mask").to(dev)
         ys = [torch.randn(N, 256, h, w, device=dev, generator=g).contiguous(memory_format=torch.channels_last) for _ in range(4)]
         by = N * P * (256 + cout) * 4
         with torch.no_grad():
-            ref = timeit(lambda i: hd.predict_layer(ys[i % 4]))
-            for tag, env in (("plain loads", "0"), ("TMA-staged", "1")):
-                os.environ["SCFLOW_COUT_TMA"] = env
-                us = timeit(lambda i: ops.conv_small_cout(ys[i % 4], hd.predict_layer))
-                print(f"conv_small_cout 256->{cout} {k}x{k} {tag:11s} {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)  (cuDNN {ref:.1f} us)")
-            os.environ.pop("SCFLOW_COUT_TMA")
+            us = timeit(lambda i: ops.conv_small_cout(ys[i % 4], hd.predict_layer))
+        print(f"conv_small_cout 256->{cout} {k}x{k} {us:8.1f} us  {by/us/1e3:7.1f} GB/s ({by/us/1e3/HBM*100:4.1f}% HBM)")
 if "posefc" in a.which:
     from scflow_b200.pose_head import MultiClassPoseHead
     head = MultiClassPoseHead(21, 224, "Basic", dict(type="GN", num_groups=32), dict(type="ReLU"),
@@ -140,17 +108,3 @@ if "posefc" in a.which:
             y = head.fc_layers(xs[i % 4]); return head.rotation_pred(y), head.translation_pred(y)
         r = timeit(ref)
     print(f"pose_fc (3 launches) {us:8.1f} us   (cuBLAS fp32 chain {r:.1f} us)")
-
-if "norm" in a.which:
-    # InstanceNorm + ReLU of the IN encoder's three activation shapes: statistics + normalise pair vs the
-    # one-launch cluster kernel (cluster size / CTAs per SM knobs)
-    for (hh, ww, cc) in ((128, 128, 64), (64, 64, 96), (32, 32, 128)):
-        xs_ = [torch.randn(N, hh, ww, cc, device=dev, generator=g) for _ in range(3)]
-        by = N * hh * ww * cc * 4
-        def pair(i):
-            x = xs_[i % 3]
-            ops.norm_act(x, sums=ops.chan_stats(x), relu=True)
-        us = timeit(pair)
-        print(f"IN {hh}x{ww}x{cc}: stats + normalise pair        {us:8.1f} us  ({3*by/us/1e3:7.1f} GB/s moved)")
-        us = timeit(lambda i: ops.instnorm_act(xs_[i % 3], relu=True))
-        print(f"IN {hh}x{ww}x{cc}: one cluster launch               {us:8.1f} us  ({2*by/us/1e3:7.1f} GB/s of HBM traffic)")
