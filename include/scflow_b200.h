@@ -89,6 +89,9 @@ int scflow_corr_pyramid_fwd(const float* feat1, const float* feat2, float* const
 #define SCFLOW_LAYOUT_NCHW 0
 #define SCFLOW_LAYOUT_NHWC 1
 #define SCFLOW_LAYOUT_NHWC_GEN1 2   /* NHWC through the first-generation kernel: the cross-check of the tests */
+#define SCFLOW_LAYOUT_NHWC_SPLIT 3  /* `out` = split-bf16 planes (n, h, w, [328 hi | 328 lo]) bf16, value = hi + lo,
+                                       channels 324..327 zero: the operand of the 1x1 convolution that consumes the
+                                       lookup (scflow_conv_tc_fwd); w % 32 == 0, else SCFLOW_E_UNSUPPORTED */
 int scflow_corr_lookup_fwd(const float* const* levels, int num_levels, const float* flow,
                            float* out, short* windows, int n, int h, int w, int radius,
                            int div_mode, int out_layout, void* stream);
@@ -168,9 +171,12 @@ int scflow_nhwc_to_nchw(const float* in, float* out, int n, int P, int C, int ro
 
 /* GroupNorm with 4 channels per group (+ ReLU) on channels-last (n, P, C), one launch: the conv -> GN ->
  * ReLU layers of MultiClassPoseHead (models/head/pose_head.py:128-137; norm_cfg GN num_groups=32 on 128
- * channels).  gamma/beta: [C].  x == out allowed.  C/4 must divide 512. */
-int scflow_group_norm4_act_nhwc(const float* x, const float* gamma, const float* beta, float* out, int n,
-                                int P, int C, float eps, int relu, void* stream);
+ * channels).  gamma/beta: [C].  x == out allowed.  C/4 must divide 512.  Outputs (either or both): out fp32
+ * (n, P, C); out_split = the result as split planes (out_pitch bf16 per pixel, lo plane out_lo further), the
+ * operand of the next scflow_conv_tc_fwd. */
+int scflow_group_norm4_act_nhwc(const float* x, const float* gamma, const float* beta, float* out, void* out_split,
+                                long long out_pitch, int out_lo, int n, int P, int C, float eps, int relu,
+                                void* stream);
 
 /* Fully connected tail of MultiClassPoseHead (models/head/pose_head.py:139-147, 201-211): fc0 + ReLU, fc1 +
  * ReLU, rotation_pred / translation_pred restricted to the class of label[0] (index_select(...)[:, 0, :],
@@ -207,10 +213,13 @@ int scflow_pose_fc_fwd_static(const float* x, const float* w0, const float* b0, 
 /* out (n, h, w, cout) channels-last = act(conv(in) + bias).  in: element (n, ci, y, x) at
  * n*stride_n + ci*stride_c + (y*w + x)*stride_px floats (planar or channels-last callers);
  * wpack: [cin][k][k][cout] (Conv2d weight (cout,cin,k,k) permuted 1,2,3,0); cin in {1,2},
- * ksize in {3,7}, cout % 32 == 0, w % 8 == 0. */
+ * ksize in {3,7}, cout % 32 == 0, w % 8 == 0.  Outputs (either or both): out fp32, out_split = the same
+ * values as split-bf16 planes (out_pitch bf16 per pixel, lo plane out_lo further): the operand of the
+ * tensor-core convolution that follows in flow_net / delta_flow_encoder / mask_encoder. */
 int scflow_conv_small_cin_fwd(const float* in, long long stride_n, long long stride_c, long long stride_px,
-                              const float* wpack, const float* bias, float* out, int n, int cin, int h,
-                              int w, int cout, int ksize, int relu, void* stream);
+                              const float* wpack, const float* bias, float* out, void* out_split,
+                              long long out_pitch, int out_lo, int n, int cin, int h, int w, int cout, int ksize,
+                              int relu, void* stream);
 
 /* Stem input of the RAFT encoders (raft_encoder.py:286-288: conv1 7x7 stride 2 on 3 channels) as the 2x2
  * space-to-depth image of the equivalent 4x4 stride-1 convolution: x planar (n, c <= 4, h, w), h and w even

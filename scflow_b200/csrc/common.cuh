@@ -39,4 +39,17 @@ __device__ __forceinline__ void inverse3x3(const float* __restrict__ m, float* _
   o[8] = (float)((a * e - b * d) * r);
 }
 
+// SPLIT-BF16 operand format of the tensor-core convolutions (conv_tc.cu): v -> hi = rn_bf16(v), lo = rn_bf16(v - hi),
+// two values per 32-bit word (low half = first value).  Packed conversion (cvt.rn.bf16x2.f32 = one F2FP in the
+// ALU pipe; the scalar __float2bfloat16_rn is a quarter-rate F2F.BF16.F32).
+__device__ __forceinline__ uint32_t cvt_bf16x2(float lo_half, float hi_half) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_half), "f"(lo_half));
+  return r;
+}
+__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+  hi = cvt_bf16x2(a, b);
+  lo = cvt_bf16x2(a - __uint_as_float(hi << 16), b - __uint_as_float(hi & 0xFFFF0000u));
+}
+
 }  // namespace scflow

@@ -133,18 +133,6 @@ __device__ __forceinline__ float tanhf_(float v) {
   return copysignf(__fdividef(1.0f - e, 1.0f + e), v);
 }
 
-// v -> (hi, lo) bf16 pair; two values packed per 32-bit word (low half = first value).  The PACKED conversion
-// (cvt.rn.bf16x2.f32 = one F2FP in the ALU pipe): the scalar __float2bfloat16_rn compiles to F2F.BF16.F32, a
-// quarter-rate conversion-pipe instruction that headed the epilogue's stall samples (four per pair of values).
-__device__ __forceinline__ uint32_t cvt_bf16x2(float lo_half, float hi_half) {
-  uint32_t r;
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_half), "f"(lo_half));
-  return r;
-}
-__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
-  hi = cvt_bf16x2(a, b);
-  lo = cvt_bf16x2(a - __uint_as_float(hi << 16), b - __uint_as_float(hi & 0xFFFF0000u));
-}
 __device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
 

@@ -163,7 +163,7 @@ corr_lookup_kernel(const LookupParams p) {
 
 namespace scflow {
 int launch_corr_lookup_nhwc(const float* const* levels, const float* flow, float* out, short* windows,
-                            int n, int h, int w, int div_mode, bool gen1, cudaStream_t stream);
+                            int n, int h, int w, int div_mode, bool gen1, bool split, cudaStream_t stream);
 }
 
 extern "C" int scflow_corr_lookup_fwd(const float* const* levels, int num_levels,
@@ -174,14 +174,16 @@ extern "C" int scflow_corr_lookup_fwd(const float* const* levels, int num_levels
   if (!levels || !flow || !out) return SCFLOW_E_NULL;
   if (radius != kR || num_levels != kLevels) return SCFLOW_E_UNSUPPORTED;
   if (div_mode != SCFLOW_DIV_IEEE && div_mode != SCFLOW_DIV_RCP) return SCFLOW_E_UNSUPPORTED;
-  if (out_layout != SCFLOW_LAYOUT_NCHW && out_layout != SCFLOW_LAYOUT_NHWC && out_layout != SCFLOW_LAYOUT_NHWC_GEN1)
+  if (out_layout != SCFLOW_LAYOUT_NCHW && out_layout != SCFLOW_LAYOUT_NHWC && out_layout != SCFLOW_LAYOUT_NHWC_GEN1 &&
+      out_layout != SCFLOW_LAYOUT_NHWC_SPLIT)
     return SCFLOW_E_UNSUPPORTED;
   if (out_layout != SCFLOW_LAYOUT_NCHW) {
     if (n <= 0 || h < 8 || w < 8) return SCFLOW_E_BAD_SHAPE;
     for (int l = 0; l < kLevels; ++l)
       if (!levels[l]) return SCFLOW_E_NULL;
     return launch_corr_lookup_nhwc(levels, flow, out, windows, n, h, w, div_mode,
-                                   out_layout == SCFLOW_LAYOUT_NHWC_GEN1, (cudaStream_t)stream);
+                                   out_layout == SCFLOW_LAYOUT_NHWC_GEN1, out_layout == SCFLOW_LAYOUT_NHWC_SPLIT,
+                                   (cudaStream_t)stream);
   }
   if (n <= 0 || h < 8 || w < 8 || ((h * w) % kQB) != 0) return SCFLOW_E_BAD_SHAPE;
   LookupParams p;

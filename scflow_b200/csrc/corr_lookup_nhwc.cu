@@ -323,18 +323,19 @@ corr_lookup_nhwc_kernel(const __grid_constant__ CUtensorMap map0, const __grid_c
 namespace scflow {
 
 int launch_corr_lookup_v2(const float* const* levels, const float* flow, float* out, short* windows,
-                          int n, int h, int w, int div_mode, cudaStream_t stream);
+                          int n, int h, int w, int div_mode, bool split, cudaStream_t stream);
 
 int launch_corr_lookup_nhwc(const float* const* levels, const float* flow, float* out, short* windows,
-                            int n, int h, int w, int div_mode, bool gen1, cudaStream_t stream) {
+                            int n, int h, int w, int div_mode, bool gen1, bool split, cudaStream_t stream) {
   using namespace lk;
   // second-generation kernel (corr_lookup_v2.cu) wherever every level row is a 16-byte multiple; this file's
   // kernel takes the other shapes, and any shape when the caller asks for it (SCFLOW_LAYOUT_NHWC_GEN1: the
   // tests hold the two independently written kernels to identical windows and values)
   if (!gen1) {
-    const int rc = launch_corr_lookup_v2(levels, flow, out, windows, n, h, w, div_mode, stream);
+    const int rc = launch_corr_lookup_v2(levels, flow, out, windows, n, h, w, div_mode, split, stream);
     if (rc != SCFLOW_E_UNSUPPORTED) return rc;
   }
+  if (split) return SCFLOW_E_UNSUPPORTED;      // split planes come from the second-generation kernel only
   if (((h >> (kLevels - 1)) < 1) || ((w >> (kLevels - 1)) < 1)) return SCFLOW_E_BAD_SHAPE;
   const long long total_q = (long long)n * h * w;
   if (total_q >= (1ll << 31)) return SCFLOW_E_BAD_SHAPE;

@@ -45,6 +45,7 @@ constexpr int kYRecBytes = kLevels * 3 * 16;         // 192
 constexpr int kRecBytes = kXRecBytes + kYRecBytes;   // 480
 constexpr int kWarpBytes = ((2 * kBufBytes + 2 * kRecBytes + 16 + 127) / 128) * 128;   // 7168
 constexpr int kOutFloats = kLevels * kD * kD;        // 324
+constexpr int kSplitC = (kOutFloats + 7) / 8 * 8;    // 328: channels per plane of the split-bf16 output
 
 struct Maps {
   CUtensorMap m[kLevels];
@@ -91,7 +92,7 @@ struct Cursor {
   int q, n, qi;
 };
 
-template <int DIV, int WARPS, int MINB, bool WIN>
+template <int DIV, int WARPS, int MINB, bool WIN, bool SPLIT>
 __global__ void __launch_bounds__(WARPS * 32, MINB)
 corr_lookup_v2_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p) {
   // no static shared memory in this kernel: the dynamic window starts 1 KiB-aligned, which the
@@ -286,7 +287,28 @@ corr_lookup_v2_kernel(const __grid_constant__ Maps maps, const __grid_constant__
       }
     }
     __syncwarp();          // every lane is done reading tile buffer b: it becomes the staging line
-    if (lane < 27) {
+    if (SPLIT) {
+      // split planes for the tensor-core 1x1 convolution that consumes the lookup (raft_decoder.py:152-155):
+      // 328 bf16 hi, then 328 bf16 lo (324 values + 4 zero channels each), two 656-byte bulk copies
+      uint16_t* so = reinterpret_cast<uint16_t*>(smem_raw + tb);
+      if (lane < 27) {
+#pragma unroll
+        for (int l = 0; l < kLevels; ++l) {
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            const float v = res[l][j];
+            const uint32_t hi = cvt_bf16x2(v, 0.f) & 0xffffu;
+            const uint32_t lo = cvt_bf16x2(v - __uint_as_float(hi << 16), 0.f) & 0xffffu;
+            const int idx = l * (kD * kD) + kD * k + 3 * g + j;
+            so[idx] = (uint16_t)hi;
+            so[kSplitC + idx] = (uint16_t)lo;
+          }
+        }
+      } else if (lane == 27) {
+#pragma unroll
+        for (int j = kOutFloats; j < kSplitC; ++j) { so[j] = 0; so[kSplitC + j] = 0; }
+      }
+    } else if (lane < 27) {
       float* so = reinterpret_cast<float*>(smem_raw + tb) + kD * k + 3 * g;
 #pragma unroll
       for (int l = 0; l < kLevels; ++l) {
@@ -298,10 +320,18 @@ corr_lookup_v2_kernel(const __grid_constant__ Maps maps, const __grid_constant__
     tc::fence_proxy_async();        // written by the generic proxy, read by the bulk copy
     __syncwarp();
     if (lane == 0) {
-      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
-                       p.out + (size_t)c0.q * kOutFloats),
-                   "r"(sbase + tb), "n"(kOutFloats * 4)
-                   : "memory");
+      if (SPLIT) {
+        const uint8_t* o = reinterpret_cast<const uint8_t*>(p.out) + (size_t)c0.q * (4 * kSplitC);
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(o), "r"(sbase + tb),
+                     "n"(2 * kSplitC) : "memory");
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(o + 2 * kSplitC),
+                     "r"(sbase + tb + 2 * kSplitC), "n"(2 * kSplitC) : "memory");
+      } else {
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
+                         p.out + (size_t)c0.q * kOutFloats),
+                     "r"(sbase + tb), "n"(kOutFloats * 4)
+                     : "memory");
+      }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     }
     c0 = c1; c1 = c2; c2 = advance(c2);
@@ -319,7 +349,7 @@ namespace scflow {
 // Returns SCFLOW_E_UNSUPPORTED when the shape / alignment is outside what this kernel takes (the
 // caller then uses the first-generation kernel), otherwise the launch status.
 int launch_corr_lookup_v2(const float* const* levels, const float* flow, float* out, short* windows,
-                          int n, int h, int w, int div_mode, cudaStream_t stream) {
+                          int n, int h, int w, int div_mode, bool split, cudaStream_t stream) {
   using namespace lk2;
   if ((w % 32) != 0 || (h >> (kLevels - 1)) < 1) return SCFLOW_E_UNSUPPORTED;
   const long long total_q = (long long)n * h * w;
@@ -349,10 +379,11 @@ int launch_corr_lookup_v2(const float* const* levels, const float* flow, float* 
   constexpr int warps = 8, minb = 3;
   typedef void (*Kern)(const Maps, const Params);
   const bool ieee = div_mode == SCFLOW_DIV_IEEE, win = windows != nullptr;
-  Kern kern = ieee ? (win ? (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_IEEE, warps, minb, true>
-                          : (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_IEEE, warps, minb, false>)
-                   : (win ? (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_RCP, warps, minb, true>
-                          : (Kern)corr_lookup_v2_kernel<SCFLOW_DIV_RCP, warps, minb, false>);
+#define SCFLOW_LK2(D, W_) (split ? (Kern)corr_lookup_v2_kernel<D, warps, minb, W_, true> \
+                                : (Kern)corr_lookup_v2_kernel<D, warps, minb, W_, false>)
+  Kern kern = ieee ? (win ? SCFLOW_LK2(SCFLOW_DIV_IEEE, true) : SCFLOW_LK2(SCFLOW_DIV_IEEE, false))
+                   : (win ? SCFLOW_LK2(SCFLOW_DIV_RCP, true) : SCFLOW_LK2(SCFLOW_DIV_RCP, false));
+#undef SCFLOW_LK2
   const int smem_bytes = warps * kWarpBytes;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);   // per device: every launch
   int sms = 0, dev = 0;

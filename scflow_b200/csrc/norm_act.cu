@@ -65,15 +65,17 @@ constexpr int kGNThreads = 512;
 
 __global__ void __launch_bounds__(kGNThreads)
 group_norm4_act_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
-                       const float* __restrict__ beta, float* __restrict__ out, int P, int C, float eps,
-                       int relu) {
+                       const float* __restrict__ beta, float* __restrict__ out, uint2* __restrict__ out_split,
+                       long long out_pitch, int out_lo, int P, int C, float eps, int relu) {
   __shared__ double red[kGNThreads][2];
   __shared__ float stat[256][2];                     // per group: mean, rstd
   const int G = C >> 2;                              // groups == float4 columns
   const int lanes = kGNThreads / G;
   const int g = threadIdx.x % G, pl = threadIdx.x / G;
   const float4* src = reinterpret_cast<const float4*>(x + (size_t)blockIdx.x * P * C) + g;
-  float4* dst = reinterpret_cast<float4*>(out + (size_t)blockIdx.x * P * C) + g;
+  float4* dst = out ? reinterpret_cast<float4*>(out + (size_t)blockIdx.x * P * C) + g : nullptr;
+  // split planes of the next convolution's operand: pixel pitch out_pitch bf16, lo plane out_lo further
+  uint2* dsp = out_split ? out_split + ((size_t)blockIdx.x * P * out_pitch) / 4 + g : nullptr;
   float s = 0.f, q = 0.f;
   if (pl < lanes) {
     int p = pl;
@@ -116,19 +118,30 @@ group_norm4_act_kernel(const float* __restrict__ x, const float* __restrict__ ga
     const float4 v = src[(size_t)p * G];
     float4 y = make_float4(fmaf(v.x, sc.x, sh.x), fmaf(v.y, sc.y, sh.y), fmaf(v.z, sc.z, sh.z), fmaf(v.w, sc.w, sh.w));
     if (relu) { y.x = fmaxf(y.x, 0.f); y.y = fmaxf(y.y, 0.f); y.z = fmaxf(y.z, 0.f); y.w = fmaxf(y.w, 0.f); }
-    dst[(size_t)p * G] = y;
+    if (dst) dst[(size_t)p * G] = y;
+    if (dsp) {
+      uint2 h, l;
+      split2(y.x, y.y, h.x, l.x);
+      split2(y.z, y.w, h.y, l.y);
+      dsp[((size_t)p * out_pitch) / 4] = h;
+      dsp[((size_t)p * out_pitch + out_lo) / 4] = l;
+    }
   }
 }
 }  // namespace na
 }  // namespace scflow
 
 extern "C" int scflow_group_norm4_act_nhwc(const float* x, const float* gamma, const float* beta, float* out,
-                                           int n, int P, int C, float eps, int relu, void* stream) {
+                                           void* out_split, long long out_pitch, int out_lo, int n, int P, int C,
+                                           float eps, int relu, void* stream) {
   using namespace scflow;
-  if (!x || !gamma || !beta || !out) return SCFLOW_E_NULL;
+  if (!x || !gamma || !beta || (!out && !out_split)) return SCFLOW_E_NULL;
+  if (out_split && ((out_pitch % 4) || (out_lo % 4) || (reinterpret_cast<uintptr_t>(out_split) & 7u)))
+    return SCFLOW_E_MISALIGNED;
   if (n <= 0 || P <= 0 || C < 4 || (C & 3) != 0 || (C >> 2) > 256 || na::kGNThreads % (C >> 2) != 0)
     return SCFLOW_E_BAD_SHAPE;
   if (!aligned16(x) || !aligned16(out) || !aligned16(gamma) || !aligned16(beta)) return SCFLOW_E_MISALIGNED;
-  na::group_norm4_act_kernel<<<n, na::kGNThreads, 0, (cudaStream_t)stream>>>(x, gamma, beta, out, P, C, eps, relu);
+  na::group_norm4_act_kernel<<<n, na::kGNThreads, 0, (cudaStream_t)stream>>>(
+      x, gamma, beta, out, static_cast<uint2*>(out_split), out_pitch, out_lo, P, C, eps, relu);
   return check_launch();
 }

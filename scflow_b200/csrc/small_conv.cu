@@ -27,9 +27,12 @@ struct CinParams {
   const float* in;        // element (n, ci, y, x) at n*sn + ci*sc + (y*w + x)*sp
   const float* wpack;     // [CIN][KS][KS][Cout]
   const float* bias;      // [Cout] or nullptr
-  float* out;             // (n, h, w, Cout) channels-last
+  float* out;             // (n, h, w, Cout) channels-last fp32, or nullptr
   long long sn, sc, sp;
   int n, h, w, cout, relu;
+  uint16_t* out_split;    // or/and split-bf16 planes: pixel pitch out_pitch bf16, lo plane out_lo further
+  long long out_pitch;
+  int out_lo;
 };
 
 // SEG pixels of a row per lane: the inputs are broadcast LDS.128, the filter taps one LDS.32 per
@@ -130,9 +133,28 @@ conv_small_cin_kernel(const CinParams p) {
           }
         }
       }
-      float* o = p.out + (((long long)n * p.h + y) * p.w + x0 + seg * SEG) * p.cout + c;
+      const long long pix0 = ((long long)n * p.h + y) * p.w + x0 + seg * SEG;
+      if (p.relu) {
 #pragma unroll
-      for (int i = 0; i < SEG; ++i) o[(long long)i * p.cout] = p.relu ? fmaxf(acc[i], 0.0f) : acc[i];
+        for (int i = 0; i < SEG; ++i) acc[i] = fmaxf(acc[i], 0.0f);
+      }
+      if (p.out) {
+        float* o = p.out + pix0 * p.cout + c;
+#pragma unroll
+        for (int i = 0; i < SEG; ++i) o[(long long)i * p.cout] = acc[i];
+      }
+      if (p.out_split) {        // the next layer is a tensor-core convolution: its operand, no fp32 round trip
+        uint16_t* o = p.out_split + pix0 * p.out_pitch + c;
+#pragma unroll
+        for (int i = 0; i < SEG; i += 2) {
+          uint32_t hi, lo;
+          split2(acc[i], acc[i + 1], hi, lo);
+          o[(long long)i * p.out_pitch] = (uint16_t)hi;
+          o[(long long)i * p.out_pitch + p.out_lo] = (uint16_t)lo;
+          o[(long long)(i + 1) * p.out_pitch] = (uint16_t)(hi >> 16);
+          o[(long long)(i + 1) * p.out_pitch + p.out_lo] = (uint16_t)(lo >> 16);
+        }
+      }
     }
     if (more) stash(patch0 + (buf ^ 1) * PATCH);
     __syncthreads();                                 // next patch visible; this one free for reuse
@@ -161,13 +183,14 @@ static int launch_cin(const CinParams& p, cudaStream_t st) {
 
 extern "C" int scflow_conv_small_cin_fwd(const float* in, long long stride_n, long long stride_c,
                                          long long stride_px, const float* wpack, const float* bias,
-                                         float* out, int n, int cin, int h, int w, int cout, int ksize,
-                                         int relu, void* stream) {
+                                         float* out, void* out_split, long long out_pitch, int out_lo, int n,
+                                         int cin, int h, int w, int cout, int ksize, int relu, void* stream) {
   using namespace scflow;
-  if (!in || !wpack || !out) return SCFLOW_E_NULL;
+  if (!in || !wpack || (!out && !out_split)) return SCFLOW_E_NULL;
   if (n <= 0 || h <= 0 || w <= 0 || (w % sc::kSegPx) != 0 || cout <= 0 || (cout & 31) != 0 || cout > 256)
     return SCFLOW_E_BAD_SHAPE;
-  sc::CinParams p{in, wpack, bias, out, stride_n, stride_c, stride_px, n, h, w, cout, relu};
+  sc::CinParams p{in, wpack, bias, out, stride_n, stride_c, stride_px, n, h, w, cout, relu,
+                  static_cast<uint16_t*>(out_split), out_pitch, out_lo};
   cudaStream_t st = (cudaStream_t)stream;
   if (cin == 2 && ksize == 7) return sc::launch_cin<2, 7>(p, st);
   if (cin == 1 && ksize == 3) return sc::launch_cin<1, 3>(p, st);

@@ -120,15 +120,15 @@ class SCFlowDecoder(nn.Module):
         pose_in = S.slice(cx + mo, hc + c_df + c_m)
         scratch = gru_tc.Scratch(n_, hh, ww, hc, dev)
         for _ in range(self.iters):
-            corr = self.corr_lookup(corr_pyramid, flow)
+            corr = self.corr_lookup.forward_split(corr_pyramid, flow)
             self.encoder.features_into(corr, flow, motion)
             gru_tc.update_inplace(self.gru, xh, h_state, scratch)
             delta_flow_pred = self.flow_pred.forward_split(h_split)
             mask = torch.sigmoid(self.mask_pred.forward_split(h_split))
-            d0 = dfe[0](delta_flow_pred)                               # 7x7 on 2 channels: FMA kernel
-            dfe[1].forward_split(C.to_split(d0.permute(0, 2, 3, 1)), out=pose_in.slice(hc, c_df))
-            m0 = me[0](mask)                                           # 3x3 on 1 channel
-            me[1].forward_split(C.to_split(m0.permute(0, 2, 3, 1)), out=pose_in.slice(hc + c_df, c_m))
+            d0 = dfe[0].forward_small_cin_split(delta_flow_pred)       # 7x7 on 2 channels: FMA kernel, split planes out
+            dfe[1].forward_split(d0, out=pose_in.slice(hc, c_df))
+            m0 = me[0].forward_small_cin_split(mask)                   # 3x3 on 1 channel
+            me[1].forward_split(m0, out=pose_in.slice(hc + c_df, c_m))
             delta_rotation, delta_translation = self.pose_pred.forward_split(pose_in, label)
             flow_pred = ops.upsample(flow, delta_flow_pred, scale, float(scale))
             upsample_mask_pred = ops.upsample(mask, None, scale, 1.0)

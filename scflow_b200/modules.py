@@ -80,7 +80,17 @@ class ConvModule(nn.Module):
         if self.norm_name != "gn" or not (self.gn.affine and self.gn.num_channels == 4 * self.gn.num_groups):
             raise NotImplementedError(f"ConvModule norm {self.norm_name} on the tensor-core path")
         raw = C.conv(x, C.packed_conv(self.conv, with_bias=False), want="f32")
+        if kw.get("want") == "split":           # the next layer is a tensor-core convolution: split planes only
+            n, h, w, c = raw.shape
+            return ops.group_norm4_act(raw, self.gn, relu=relu, split_out=C.alloc_split(n, h, w, c, raw.device))
         return ops.group_norm4_act(raw, self.gn, relu=relu)
+
+    def forward_small_cin_split(self, x: torch.Tensor) -> "C.Split":
+        """1-2 input channels (FMA kernel, csrc/small_conv.cu) with the result written as split-bf16 planes: the
+        operand of the tensor-core convolution that follows it in flow_net / delta_flow_encoder / mask_encoder."""
+        if not self._small_cin_ok(x):
+            return C.to_split(self.forward(x).permute(0, 2, 3, 1))
+        return ops.conv_small_cin(x, self.conv, relu=self.with_activation, split_out=True)
 
     def forward(self, x):
         if _needs_grad(x, *self.parameters()):
@@ -141,6 +151,10 @@ class CorrLookup(nn.Module):
             return autograd.corr_lookup(corr_pyramid, flow, self.r, self.div_mode)
         return ops.corr_lookup(corr_pyramid, flow, self.r, self.div_mode)
 
+    def forward_split(self, corr_pyramid: Sequence[torch.Tensor], flow: torch.Tensor) -> "C.Split":
+        """Inference: the lookup written as split-bf16 planes, the operand format of MotionEncoder.corr_net[0]."""
+        return ops.corr_lookup(corr_pyramid, flow, self.r, self.div_mode, split=True)
+
 
 class ConvGRU(nn.Module):
     """SeqConv GRU (a3).  Parameters keep the reference names conv_{z,r,q}.{0,1}.conv.*"""
@@ -194,14 +208,19 @@ class MotionEncoder(nn.Module):
         corr: (N,324,h,w)-shaped channels-last lookup result; flow: planar (N,2,h,w).
         Tensor-core / FMA launches only; what the reference concatenates is written in place: corr_net and
         flow_net store into the two channel slices of one split buffer that out_net reads."""
-        n, _, h, w = corr.shape
-        cs = C.to_split(corr.permute(0, 2, 3, 1))
+        if isinstance(corr, C.Split):
+            cs = corr
+            (n, h, w), dev = cs.shape, cs.buf.device
+        else:
+            n, _, h, w = corr.shape
+            dev = corr.device
+            cs = C.to_split(corr.permute(0, 2, 3, 1))
         a = self.corr_net[0].forward_split(cs)
-        cat = C.alloc_split(n, h, w, 256, corr.device)
+        cat = C.alloc_split(n, h, w, 256, dev)
         c1 = self.corr_net[1].conv.out_channels
         self.corr_net[1].forward_split(a, out=cat.slice(0, c1))
-        f0 = self.flow_net[0](flow)                                     # 7x7 on 2 channels: FMA kernel
-        self.flow_net[1].forward_split(C.to_split(f0.permute(0, 2, 3, 1)), out=cat.slice(c1, 256 - c1))
+        f0 = self.flow_net[0].forward_small_cin_split(flow)             # 7x7 on 2 channels: FMA kernel, split planes out
+        self.flow_net[1].forward_split(f0, out=cat.slice(c1, 256 - c1))
         co = self.out_net[0].conv.out_channels
         self.out_net[0].forward_split(cat, out=out.slice(0, co))        # writes co rounded up to 8 (zeros)
         C.split_planar(flow, C.Split(out.buf, 2, out.off + co))        # the flow pair over those zeros

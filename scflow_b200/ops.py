@@ -123,18 +123,19 @@ def corr_pyramid(feat1: torch.Tensor, feat2: torch.Tensor, num_levels: int = 4,
     return levels
 
 
-LAYOUT_NCHW, LAYOUT_NHWC, LAYOUT_NHWC_GEN1 = 0, 1, 2
+LAYOUT_NCHW, LAYOUT_NHWC, LAYOUT_NHWC_GEN1, LAYOUT_NHWC_SPLIT = 0, 1, 2, 3
 
 
 def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int = 4,
                 div_mode: int = DIV_IEEE, return_windows: bool = False, channels_last: bool = True,
-                gen1: bool = False):
+                gen1: bool = False, split: bool = False):
     """CorrLookup.forward (corr_lookup.py:102-136): (N, L*(2r+1)^2, H, W).
 
     With `channels_last` (default) the result has the reference's shape but channels-last
     strides (memory (N, H, W, 324)): what the warp-per-query kernel writes and what the
     downstream convolutions consume without a layout pass.  `gen1`: the first-generation kernel on any
-    shape (the tests' cross-check; the second generation runs wherever it applies otherwise)."""
+    shape (the tests' cross-check; the second generation runs wherever it applies otherwise).
+    `split`: return the result as a convtc.Split (split-bf16 planes) instead of an fp32 tensor."""
     lib = _lib.load()
     fl = _chk(flow, "flow")
     n, two, h, w = fl.shape
@@ -145,6 +146,19 @@ def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int
             raise _lib.ScflowError(f"pyramid[{l}] has shape {tuple(p.shape)}")
     L = len(lv)
     d = 2 * radius + 1
+    if split:
+        # straight into the split-bf16 planes the 1x1 convolution behind the lookup reads (convtc.Split);
+        # shapes the second-generation kernel does not take go through fp32 + one split pass
+        from . import convtc as C
+        sp = C.alloc_split(n, h, w, L * d * d, fl.device)
+        arr = (ctypes.c_void_p * L)(*[p.data_ptr() for p in lv])
+        with _timed("scflow_corr_lookup_fwd", 1):
+            rc = lib.scflow_corr_lookup_fwd(arr, L, _ptr(fl), _ptr(sp.buf), None, n, h, w, radius, div_mode,
+                                            LAYOUT_NHWC_SPLIT, _stream())
+        if rc == -2:                                   # SCFLOW_E_UNSUPPORTED
+            return C.to_split(corr_lookup(pyramid, flow, radius, div_mode).permute(0, 2, 3, 1), out=sp)
+        _lib.check(rc, "scflow_corr_lookup_fwd")
+        return sp
     if channels_last:
         out = torch.empty((n, h, w, L * d * d), device=fl.device, dtype=torch.float32).permute(0, 3, 1, 2)
     else:
@@ -268,9 +282,10 @@ def _packed_conv_weight(conv: torch.nn.Conv2d) -> torch.Tensor:
     return hit[1]
 
 
-def conv_small_cin(x: torch.Tensor, conv: torch.nn.Conv2d, relu: bool) -> torch.Tensor:
-    """act(conv(x) + bias) for cin in {1,2}: returns an NCHW-shaped channels-last tensor.  x may be
-    planar or channels-last (strides are passed through)."""
+def conv_small_cin(x: torch.Tensor, conv: torch.nn.Conv2d, relu: bool, split_out: bool = False):
+    """act(conv(x) + bias) for cin in {1,2}: returns an NCHW-shaped channels-last tensor, or, with
+    `split_out`, a convtc.Split (split-bf16 planes: the operand of the tensor-core convolution that follows).
+    x may be planar or channels-last (strides are passed through)."""
     lib = _lib.load()
     if not x.is_cuda or x.dtype != torch.float32:
         _chk(x, "x")
@@ -283,13 +298,21 @@ def conv_small_cin(x: torch.Tensor, conv: torch.nn.Conv2d, relu: bool) -> torch.
         x = x.contiguous()
         sn, sc, sp = cin * h * w, h * w, 1
     cout, k = conv.out_channels, conv.kernel_size[0]
-    out = torch.empty((n, h, w, cout), device=x.device, dtype=torch.float32)
-    with _timed("scflow_conv_small_cin_fwd", 1, 4 * (x.numel() + out.numel())):
+    out = sp_ = None
+    spl = (None, 0, 0)
+    if split_out:
+        from . import convtc as C
+        sp_ = C.alloc_split(n, h, w, cout, x.device)
+        spl = (ctypes.c_void_p(sp_.hi_ptr()), sp_.pitch, sp_.cp)
+    else:
+        out = torch.empty((n, h, w, cout), device=x.device, dtype=torch.float32)
+    with _timed("scflow_conv_small_cin_fwd", 1, 4 * (x.numel() + n * h * w * cout)):
         rc = lib.scflow_conv_small_cin_fwd(_ptr(x), sn, sc, sp, _ptr(_packed_conv_weight(conv)),
                                            _ptr(conv.bias.detach() if conv.bias is not None else None),
-                                           _ptr(out), n, cin, h, w, cout, k, 1 if relu else 0, _stream())
+                                           _ptr(out), spl[0], spl[1], spl[2], n, cin, h, w, cout, k,
+                                           1 if relu else 0, _stream())
     _lib.check(rc, "scflow_conv_small_cin_fwd")
-    return out.permute(0, 3, 1, 2)
+    return sp_ if split_out else out.permute(0, 3, 1, 2)
 
 
 def stem_s2d_split(x: torch.Tensor) -> torch.Tensor:
@@ -320,16 +343,22 @@ def conv_small_cout(x: torch.Tensor, conv: torch.nn.Conv2d) -> torch.Tensor:
     return out
 
 
-def group_norm4_act(x: torch.Tensor, gn: torch.nn.GroupNorm, relu: bool) -> torch.Tensor:
-    """In-place GroupNorm (4 channels per group) + ReLU on a channels-last (N,H,W,C) tensor."""
+def group_norm4_act(x: torch.Tensor, gn: torch.nn.GroupNorm, relu: bool, split_out=None):
+    """GroupNorm (4 channels per group) + ReLU on a channels-last (N,H,W,C) tensor: in place (returns x), or,
+    with `split_out` (a convtc.Split of the same pixels), written as split planes only -- the operand of the
+    next tensor-core convolution, without an fp32 round trip (returns split_out)."""
     lib = _lib.load()
     x = _chk(x, "x")
     n, H, W, C = x.shape
+    sp = (None, 0, 0) if split_out is None else (ctypes.c_void_p(split_out.hi_ptr()), split_out.pitch, split_out.cp)
+    if split_out is not None:
+        assert tuple(split_out.shape) == (n, H, W) and split_out.c == C
     with _timed("scflow_group_norm4_act_nhwc", 1, 8 * x.numel()):
-        rc = lib.scflow_group_norm4_act_nhwc(_ptr(x), _ptr(gn.weight.detach()), _ptr(gn.bias.detach()), _ptr(x),
+        rc = lib.scflow_group_norm4_act_nhwc(_ptr(x), _ptr(gn.weight.detach()), _ptr(gn.bias.detach()),
+                                             None if split_out is not None else _ptr(x), sp[0], sp[1], sp[2],
                                              n, H * W, C, float(gn.eps), 1 if relu else 0, _stream())
     _lib.check(rc, "scflow_group_norm4_act_nhwc")
-    return x
+    return x if split_out is None else split_out
 
 
 def pose_fc(x2d: torch.Tensor, w0: torch.Tensor, head, label: torch.Tensor, splitk: int = 4):

@@ -71,8 +71,8 @@ class MultiClassPoseHead(nn.Module):
             raise NotImplementedError("pose head FC widths beyond the split-K kernel's workspace")
         y = xs
         for i, layer in enumerate(self.conv_layers):
-            raw = layer.forward_split(y)                               # fp32 channels-last, GN+ReLU applied
-            y = C.to_split(raw) if i + 1 < len(self.conv_layers) else raw
+            # GN+ReLU applied; split planes between the convolutions, fp32 channels-last into the FC tail
+            y = layer.forward_split(y, want="split") if i + 1 < len(self.conv_layers) else layer.forward_split(y)
         n, hs, ws, c = y.shape
         return ops.pose_fc(y.reshape(n, hs * ws * c), self._fc0_permuted(hs * ws), self, label)
 

@@ -155,6 +155,25 @@ def test_lookup_generations_identical():
             assert torch.equal(a, b) and torch.equal(a2, b2) and torch.equal(a, a2), (n, h, w, div)
 
 
+def test_lookup_split_planes_equal_fp32_result():
+    """SCFLOW_LAYOUT_NHWC_SPLIT: the lookup written as split-bf16 planes (328 hi | 328 lo per query) carries the
+    fp32 result to 16 significand bits, with zeros in the four padding channels; shapes the second-generation
+    kernel does not take go through fp32 + one split pass and give the same planes."""
+    g = torch.Generator(device=DEV).manual_seed(9)
+    for n, h, w in ((4, 32, 32), (1, 64, 64), (2, 8, 16)):
+        pyr = [torch.randn(n * h * w, 1, h >> l, w >> l, device=DEV, generator=g) for l in range(4)]
+        flow = 5.0 * torch.randn(n, 2, h, w, device=DEV, generator=g)
+        flow[0, :, : h // 2] = 0.0
+        want = ops.corr_lookup(pyr, flow, 4).permute(0, 2, 3, 1)
+        sp = ops.corr_lookup(pyr, flow, 4, split=True)
+        assert sp.c == 324 and sp.cp == 328 and tuple(sp.shape) == (n, h, w)
+        got = sp.float()
+        assert float((got - want).abs().max()) <= 2.0 ** -16 * float(want.abs().max())
+        assert float(sp.buf[..., 324:328].float().abs().max()) == 0 and float(sp.buf[..., 652:656].float().abs().max()) == 0
+        from scflow_b200 import convtc as C
+        assert torch.equal(sp.buf[..., :324], C.to_split(want).buf[..., :324])          # same hi plane
+
+
 def test_lookup_impulse_and_zero_flow():
     h = w = 32
     qy, qx = 5, 6
@@ -443,6 +462,11 @@ def test_conv_small_cin_vs_torch(cin, k, cout, n, h, w, channels_last):
         got = m(x)
     assert ops.STATS.count == 1 and got.shape == want.shape
     assert rel(got, want) < 1e-5
+    # the same launch writing split-bf16 planes (the operand of the tensor-core convolution that follows):
+    # hi + lo carries 16 significand bits of the fp32 result
+    with torch.no_grad():
+        sp = m.forward_small_cin_split(x)
+    assert rel(sp.float().permute(0, 3, 1, 2), got) < 2.0 ** -16
 
 
 @pytest.mark.parametrize("k,cout,n,h,w", [(3, 2, 3, 32, 32), (1, 1, 2, 32, 32), (3, 2, 2, 8, 8), (3, 2, 1, 64, 64),
@@ -486,6 +510,10 @@ def test_group_norm_relu_vs_torch():
             got = m(x.contiguous(memory_format=torch.channels_last))
         assert ops.STATS.count == 3              # split pass, tensor-core convolution, GN+ReLU
         assert rel(got, want) < 2e-5
+        with torch.no_grad():                    # GN+ReLU written as split planes only (between two convolutions)
+            from scflow_b200 import convtc as C
+            sp = m.forward_split(C.to_split(x.permute(0, 2, 3, 1)), want="split")
+        assert rel(sp.float().permute(0, 3, 1, 2), want) < 3e-5
 
 
 @pytest.mark.parametrize("n,feat", [(64, 32), (3, 32), (2, 64), (5, 8)])
@@ -505,7 +533,7 @@ def test_pose_head_fused_vs_module_path(n, feat):
         head(x.contiguous(memory_format=torch.channels_last), label)       # packs the filters
         ops.STATS.reset()
         dr, dt = head(x.contiguous(memory_format=torch.channels_last), label)
-    assert ops.STATS.count == 12               # 3 x (split pass, tensor-core conv, GN+ReLU) + 3 FC launches
+    assert ops.STATS.count == 10               # split pass + 3 x (tensor-core conv, GN+ReLU -> split planes) + 3 FC launches
     assert dr.shape == dr_w.shape and dt.shape == dt_w.shape
     assert rel(dr, dr_w) < 1e-4 and rel(dt, dt_w) < 1e-4
 
