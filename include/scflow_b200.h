@@ -188,6 +188,14 @@ int scflow_pose_fc_fwd(const float* x, const float* w0, const float* b0, const f
                        const float* wr, const float* br, const float* wt, const float* bt,
                        const long long* label, float* workspace, float* dr, float* dt, int M, int K, int n0,
                        int n1, int num_class, int splitk, void* stream);
+/* The last stage alone (pose_head.py:144-147, 201-211): a1 = ReLU(b1 + sum over `splitk` blocks of part1
+ * (splitk, M, n1)), then rotation_pred / translation_pred restricted to the class of label[0].  With splitk = 1,
+ * part1 is fc1's pre-activation without bias: the hand-over from the tensor-core form of fc0 / fc1
+ * (scflow_conv_tc_fwd: fc0 is the hs x ws convolution that flatten + Linear amounts to, fc1 a 1x1 one). */
+int scflow_pose_tail_fwd(const float* part1, const float* b1, const float* wr, const float* br, const float* wt,
+                         const float* bt, const long long* label, float* dr, float* dt, int M, int splitk, int n1,
+                         int num_class, void* stream);
+
 
 /* scflow_pose_fc_fwd without a workspace argument and without any allocation: the split-K partial sums live
  * in a file-scope `static __device__` array of the library (SCFLOW_POSE_FC_STATIC_MAX_FLOATS floats = 4 MiB,
@@ -291,6 +299,12 @@ typedef struct scflow_conv_tc_desc {
    *               small filters stay resident in shared memory
    *   PATCH_PAIR  the same on CTA pairs (tcgen05 cta_group::2, M = 256): each CTA loads half the filter rows */
   int algo;
+  /* optional second input tensor of the same n, h, w: its cin2 channels continue the filter's input channels
+   * after the first tensor's cin (which must then be a multiple of bk).  What the reference concatenates in
+   * front of a convolution (raft_decoder.py:250: cat([r*h, x])) is read from where it lies. */
+  const void* x2;
+  int cin2;
+  long long x2_lo_off, x2_stride_w, x2_stride_h, x2_stride_n;
 } scflow_conv_tc_desc;
 
 /* Output spatial size: OH = (h + 2 pad_h - kh) / stride + 1, likewise OW.  Supported: OW a multiple of

@@ -35,7 +35,9 @@ class _Desc(ctypes.Structure):
         ("out_f32", ctypes.c_void_p), ("outf_pitch", ctypes.c_longlong), ("f32_tf32", ctypes.c_int),
         ("out_planar", ctypes.c_void_p), ("planar_tf32", ctypes.c_int),
         ("stats", ctypes.c_void_p), ("bn", ctypes.c_int), ("epi", ctypes.c_int), ("gru_c", ctypes.c_int),
-        ("gru_h", ctypes.c_void_p), ("gru_z", ctypes.c_void_p), ("algo", ctypes.c_int)]
+        ("gru_h", ctypes.c_void_p), ("gru_z", ctypes.c_void_p), ("algo", ctypes.c_int),
+        ("x2", ctypes.c_void_p), ("cin2", ctypes.c_int), ("x2_lo_off", ctypes.c_longlong),
+        ("x2_stride_w", ctypes.c_longlong), ("x2_stride_h", ctypes.c_longlong), ("x2_stride_n", ctypes.c_longlong)]
 
 
 EPI_PLAIN, EPI_GRU_ZR, EPI_GRU_GATE = 0, 1, 2
@@ -200,20 +202,25 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
          out_f32: Optional[torch.Tensor] = None, out_planar: Optional[torch.Tensor] = None,
          planar_tf32: bool = False, f32_tf32: bool = False, stats: Optional[torch.Tensor] = None, want: str = "split",
          view=None, bn: int = 0, epi: int = EPI_PLAIN, gru_h: Optional[torch.Tensor] = None,
-         gru_z: Optional[torch.Tensor] = None, algo: int = ALGO_AUTO):
+         gru_z: Optional[torch.Tensor] = None, algo: int = ALGO_AUTO, x2: Optional[Split] = None):
     """One convolution launch.  x: Split (n, h, w, cin).  Outputs: `out` (Split), `out_f32` (n, OH, OW, >=cout)
     fp32 channels-last (may be a channel slice of a wider buffer), `out_planar` (n, cout, OH, OW); when none is
     given one is allocated according to `want` ("split" | "f32" | "planar").  `view` = (n, h, w, cin, lo_off,
     stride_w, stride_h, stride_n) overrides how the input buffer is addressed (the stem's overlapped window
-    view).  Returns the output object(s) in the order split, f32, planar (only those produced)."""
+    view).  `x2`: a second Split of the same pixels whose channels continue x's as the filter's input channels
+    (x.c a multiple of 64): the operand the reference builds with torch.cat, read from where it lies.
+    Returns the output object(s) in the order split, f32, planar (only those produced)."""
     lib = _lib.load()
     n, h, w = x.shape
     cin = x.c
     lo_off, sw, sh, sn = x.cp, x.pitch, w * x.pitch, h * w * x.pitch
     if view is not None:
         n, h, w, cin, lo_off, sw, sh, sn = view
-    if cin != pk.cin:
-        raise _lib.ScflowError(f"conv_tc: input has {cin} channels, the filter takes {pk.cin}")
+    cin2 = 0 if x2 is None else x2.c
+    if x2 is not None and (tuple(x2.shape) != (n, h, w) or cin % 64 or view is not None):
+        raise _lib.ScflowError("conv_tc: the second input must cover the same pixels and follow a multiple of 64 channels")
+    if cin + cin2 != pk.cin:
+        raise _lib.ScflowError(f"conv_tc: input has {cin + cin2} channels, the filter takes {pk.cin}")
     oh, ow = out_hw(pk, h, w)
     dev = x.buf.device
     if out is None and out_f32 is None and out_planar is None:
@@ -228,6 +235,9 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
     d.kh, d.kw, d.stride, d.pad_h, d.pad_w, d.bk = pk.kh, pk.kw, pk.stride, pk.pad_h, pk.pad_w, pk.bk
     d.x = x.hi_ptr()
     d.x_lo_off, d.x_stride_w, d.x_stride_h, d.x_stride_n = lo_off, sw, sh, sn
+    if x2 is not None:
+        d.x2, d.cin2, d.x2_lo_off = x2.hi_ptr(), cin2, x2.cp
+        d.x2_stride_w, d.x2_stride_h, d.x2_stride_n = x2.pitch, w * x2.pitch, h * w * x2.pitch
     d.wpack = pk.w.data_ptr()
     d.bias = pk.bias.data_ptr() if pk.bias is not None else None
     d.relu = int(relu)
@@ -257,6 +267,7 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
     if stats is not None:
         assert stats.dtype == torch.float64 and stats.shape == (n, c8, 2) and stats.is_contiguous()
         d.stats = stats.data_ptr()
+    cin = cin + cin2
     flops = 2 * n * oh * ow * pk.cout * pk.cin * pk.kh * pk.kw
     # algorithmic bytes: split-plane input once, packed filter once, every output written once
     nbytes = (4 * n * h * w * cin + pk.w.numel() * 2

@@ -42,12 +42,14 @@ constexpr int SMEM_LIMIT = 227 * 1024;
 
 struct Maps {
   CUtensorMap a_hi, a_lo, w;
+  CUtensorMap b_hi, b_lo;                      // second input tensor (k-blocks kb_split ..): cat-free operands
 };
 
 struct Params {
   int n, OH, OW;
   int kh, kw, stride, pad_y, pad_x;
   int kblocks, ksteps_last;                    // k-blocks per tap; k-steps (16 channels) in the last one
+  int kb_split;                                // k-blocks [kb_split, kblocks) read the second input (= kblocks: none)
   int TW, TH, NI, tiles_x, tiles_y;            // tile rectangle, images per tile, tiles per image
   int m_tiles, n_tiles, bn;                    // bn = output channels per tile (multiple of 16, <= 256)
   int cout_pad;                                // n_tiles * bn = packed weight rows per (tap, k-block, part)
@@ -502,8 +504,10 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
             tc::mbar_wait(&empty[stage], phase ^ 1);
             uint8_t* st = smem + (size_t)stage * p.stage_bytes;
             tc::mbar_expect_tx(&full[stage], (uint32_t)p.stage_bytes);
-            tc::tma_load_4d(&maps.a_hi, &full[stage], st, kb * BK, ix, iy, tl.n0);
-            tc::tma_load_4d(&maps.a_lo, &full[stage], st + p.a_bytes, kb * BK, ix, iy, tl.n0);
+            const bool second = kb >= p.kb_split;
+            const int ch = (second ? kb - p.kb_split : kb) * BK;
+            tc::tma_load_4d(second ? &maps.b_hi : &maps.a_hi, &full[stage], st, ch, ix, iy, tl.n0);
+            tc::tma_load_4d(second ? &maps.b_lo : &maps.a_lo, &full[stage], st + p.a_bytes, ch, ix, iy, tl.n0);
             const int wrow = ((tap * p.kblocks + kb) * 2) * p.cout_pad + wrow0;
             tc::tma_load_2d(&maps.w, &full[stage], st + 2 * p.a_bytes, 0, wrow);
             tc::tma_load_2d(&maps.w, &full[stage], st + 2 * p.a_bytes + p.b_bytes, 0, wrow + p.cout_pad);
@@ -657,6 +661,7 @@ conv_patch_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Par
 
   if (warp == 0 && lane == 0) {
     tc::tma_prefetch_desc(&maps.a_hi); tc::tma_prefetch_desc(&maps.a_lo); tc::tma_prefetch_desc(&maps.w);
+    if (p.kb_split < p.kblocks) { tc::tma_prefetch_desc(&maps.b_hi); tc::tma_prefetch_desc(&maps.b_lo); }
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -696,17 +701,21 @@ conv_patch_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Par
         const int ix = tl.ox0 - p.pad_x, iy = tl.oy0 - p.pad_y;
         for (int kb = 0; kb < p.kblocks; ++kb) {
           uint8_t* st = a_ring + (size_t)as * p.a_stage_bytes;
+          const bool second = kb >= p.kb_split;
+          const int ch = (second ? kb - p.kb_split : kb) * 64;
+          const CUtensorMap* mh = second ? &maps.b_hi : &maps.a_hi;
+          const CUtensorMap* ml = second ? &maps.b_lo : &maps.a_lo;
           if (PAIR) {
             tc::mbar_wait(&a_empty[as], aph ^ 1);
             const uint32_t fb = map_to_rank(tc::smem_u32(&a_full[as]), 0);
             if (rank == 0) tc::mbar_expect_tx(&a_full[as], 4u * (uint32_t)p.patch_tx);
-            tc::tma_load_4d_2cta(&maps.a_hi, fb, st, kb * 64, ix, iy, tl.n0);
-            tc::tma_load_4d_2cta(&maps.a_lo, fb, st + p.patch_bytes, kb * 64, ix, iy, tl.n0);
+            tc::tma_load_4d_2cta(mh, fb, st, ch, ix, iy, tl.n0);
+            tc::tma_load_4d_2cta(ml, fb, st + p.patch_bytes, ch, ix, iy, tl.n0);
           } else {
             tc::mbar_wait(&a_empty[as], aph ^ 1);
             tc::mbar_expect_tx(&a_full[as], 2u * (uint32_t)p.patch_tx);
-            tc::tma_load_4d(&maps.a_hi, &a_full[as], st, kb * 64, ix, iy, tl.n0);
-            tc::tma_load_4d(&maps.a_lo, &a_full[as], st + p.patch_bytes, kb * 64, ix, iy, tl.n0);
+            tc::tma_load_4d(mh, &a_full[as], st, ch, ix, iy, tl.n0);
+            tc::tma_load_4d(ml, &a_full[as], st + p.patch_bytes, ch, ix, iy, tl.n0);
           }
           if (++as == p.a_stages) { as = 0; aph ^= 1; }
         }
@@ -923,7 +932,7 @@ __device__ __forceinline__ void in_coeffs(const double* sums, int n, int C, int 
   }
 }
 
-__global__ void __launch_bounds__(kApplyThreads)
+__global__ void __launch_bounds__(kApplyThreads, 2)
 norm_apply_split_kernel(const ApplyParams p) {
   const int groups = p.C >> 3;
   const int lanes = kApplyThreads / groups;
@@ -935,43 +944,64 @@ norm_apply_split_kernel(const ApplyParams p) {
   float sc[8], sh[8], rsc[8], rsh[8];
   in_coeffs(p.sums, n, p.C, c, p.P, p.eps, sc, sh);
   if (p.res_raw) in_coeffs(p.res_sums, n, p.C, c, p.P, p.eps, rsc, rsh);
-  for (int px = p0 + pl; px < p1; px += lanes) {
-    const size_t pix = (size_t)n * p.P + px;
-    const float4 a = *reinterpret_cast<const float4*>(p.x + pix * p.C + c);
-    const float4 b = *reinterpret_cast<const float4*>(p.x + pix * p.C + c + 4);
-    float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  // two pixels per thread and iteration, every load issued before the first use (two CTAs per SM): with one
+  // pixel a thread had 32-64 bytes in flight and the pass sat at 0.65 of the HBM peak
+  constexpr int U = 2;
+  for (int px0 = p0 + pl; px0 < p1; px0 += U * lanes) {
+    float v[U][8], r[U][8];
+    uint32_t hw[U][4], lw[U][4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], sc[j], sh[j]);
-    if (p.res_raw) {
-      const float4 ra = *reinterpret_cast<const float4*>(p.res_raw + pix * p.C + c);
-      const float4 rb = *reinterpret_cast<const float4*>(p.res_raw + pix * p.C + c + 4);
-      const float r[8] = {ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] += fmaf(r[j], rsc[j], rsh[j]);
-    } else if (p.res_split) {
-      const uint4 h = *reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + c);
-      const uint4 l = *reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + p.res_lo + c);
-      const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        v[2 * e] += bf_lo(hw[e]) + bf_lo(lw[e]);
-        v[2 * e + 1] += bf_hi(hw[e]) + bf_hi(lw[e]);
+    for (int u = 0; u < U; ++u) {
+      const int px = px0 + u * lanes;
+      if (px < p1) {
+        const size_t pix = (size_t)n * p.P + px;
+        const float4 a = __ldcs(reinterpret_cast<const float4*>(p.x + pix * p.C + c));
+        const float4 b = __ldcs(reinterpret_cast<const float4*>(p.x + pix * p.C + c + 4));
+        v[u][0] = a.x; v[u][1] = a.y; v[u][2] = a.z; v[u][3] = a.w; v[u][4] = b.x; v[u][5] = b.y; v[u][6] = b.z; v[u][7] = b.w;
+        if (p.res_raw) {
+          const float4 ra = __ldcs(reinterpret_cast<const float4*>(p.res_raw + pix * p.C + c));
+          const float4 rb = __ldcs(reinterpret_cast<const float4*>(p.res_raw + pix * p.C + c + 4));
+          r[u][0] = ra.x; r[u][1] = ra.y; r[u][2] = ra.z; r[u][3] = ra.w; r[u][4] = rb.x; r[u][5] = rb.y; r[u][6] = rb.z; r[u][7] = rb.w;
+        } else if (p.res_split) {
+          const uint4 h = __ldg(reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + c));
+          const uint4 l = __ldg(reinterpret_cast<const uint4*>(p.res_split + pix * p.res_pitch + p.res_lo + c));
+          hw[u][0] = h.x; hw[u][1] = h.y; hw[u][2] = h.z; hw[u][3] = h.w;
+          lw[u][0] = l.x; lw[u][1] = l.y; lw[u][2] = l.z; lw[u][3] = l.w;
+        }
       }
     }
-    if (p.relu) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
-    }
-    uint4 h, l;
-    split2(v[0], v[1], h.x, l.x);
-    split2(v[2], v[3], h.y, l.y);
-    split2(v[4], v[5], h.z, l.z);
-    split2(v[6], v[7], h.w, l.w);
-    *reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + c) = h;
-    *reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + p.out_lo + c) = l;
-    if (p.out_f32) {
-      *reinterpret_cast<float4*>(p.out_f32 + pix * p.C + c) = make_float4(v[0], v[1], v[2], v[3]);
-      *reinterpret_cast<float4*>(p.out_f32 + pix * p.C + c + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    for (int u = 0; u < U; ++u) {
+      const int px = px0 + u * lanes;
+      if (px >= p1) break;
+      const size_t pix = (size_t)n * p.P + px;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[u][j] = fmaf(v[u][j], sc[j], sh[j]);
+      if (p.res_raw) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[u][j] += fmaf(r[u][j], rsc[j], rsh[j]);
+      } else if (p.res_split) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          v[u][2 * e] += bf_lo(hw[u][e]) + bf_lo(lw[u][e]);
+          v[u][2 * e + 1] += bf_hi(hw[u][e]) + bf_hi(lw[u][e]);
+        }
+      }
+      if (p.relu) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[u][j] = fmaxf(v[u][j], 0.f);
+      }
+      uint4 h, l;
+      split2(v[u][0], v[u][1], h.x, l.x);
+      split2(v[u][2], v[u][3], h.y, l.y);
+      split2(v[u][4], v[u][5], h.z, l.z);
+      split2(v[u][6], v[u][7], h.w, l.w);
+      *reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + c) = h;
+      *reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + p.out_lo + c) = l;
+      if (p.out_f32) {
+        *reinterpret_cast<float4*>(p.out_f32 + pix * p.C + c) = make_float4(v[u][0], v[u][1], v[u][2], v[u][3]);
+        *reinterpret_cast<float4*>(p.out_f32 + pix * p.C + c + 4) = make_float4(v[u][4], v[u][5], v[u][6], v[u][7]);
+      }
     }
   }
 }
@@ -1171,8 +1201,14 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
   }
   p.cout_store = (d->cout + 7) / 8 * 8;
   const int bk = d->bk;
-  p.kblocks = (d->cin + bk - 1) / bk;
-  p.ksteps_last = ((d->cin - (p.kblocks - 1) * bk) + 15) / 16;
+  // a second input tensor (d->x2, cin2 channels) continues the filter's input channels after the first one's:
+  // what the reference builds with torch.cat before a convolution is read from where it lies
+  const int cin2 = d->x2 ? d->cin2 : 0;
+  if (cin2 < 0 || (d->x2 && (cin2 == 0 || (d->cin % bk) != 0))) return SCFLOW_E_BAD_SHAPE;
+  const int cin_all = d->cin + cin2;
+  p.kblocks = (cin_all + bk - 1) / bk;
+  p.kb_split = d->x2 ? d->cin / bk : p.kblocks;
+  p.ksteps_last = ((cin_all - (p.kblocks - 1) * bk) + 15) / 16;
   const int algo = d->algo & 0xff;
   if (algo > SCFLOW_CONV_PATCH_PAIR) return SCFLOW_E_BAD_SHAPE;
   int sms = 0, dev = 0;
@@ -1255,7 +1291,7 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
     // the gate epilogues work on whole 32-channel chunks of a 32-aligned hidden width
     if (p.epi != SCFLOW_EPI_GRU_ZR && p.epi != SCFLOW_EPI_GRU_GATE) return SCFLOW_E_UNSUPPORTED;
     if (!p.gru_h || !p.gru_z || !p.out_split || p.gru_c <= 0 || (p.gru_c % 32) || (p.bn % 32) || p.stats ||
-        d->cout != (p.epi == SCFLOW_EPI_GRU_ZR ? 2 : 1) * p.gru_c || (p.epi == SCFLOW_EPI_GRU_GATE && !p.res_f32))
+        d->cout != (p.epi == SCFLOW_EPI_GRU_ZR ? 2 : 1) * p.gru_c)
       return SCFLOW_E_BAD_SHAPE;
     if (!aligned16(p.gru_h) || !aligned16(p.gru_z)) return SCFLOW_E_MISALIGNED;
   }
@@ -1271,7 +1307,9 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
       (p.out_f32 && (!aligned16(p.out_f32) || (p.outf_pitch % 4))) ||
       (p.res_split && (!aligned16(p.res_split) || (p.res_pitch % 8) || (p.res_lo % 8))) ||
       (p.res_f32 && (!aligned16(p.res_f32) || (p.resf_pitch % 4))) || !aligned16(d->x) || !aligned16(d->wpack) ||
-      (d->x_lo_off % 8) || (d->x_stride_w % 8) || (d->x_stride_h % 8) || (d->x_stride_n % 8))
+      (d->x_lo_off % 8) || (d->x_stride_w % 8) || (d->x_stride_h % 8) || (d->x_stride_n % 8) ||
+      (d->x2 && (!aligned16(d->x2) || (d->x2_lo_off % 8) || (d->x2_stride_w % 8) || (d->x2_stride_h % 8) ||
+                 (d->x2_stride_n % 8))))
     return SCFLOW_E_MISALIGNED;
 
   Maps maps;
@@ -1288,6 +1326,16 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
     if (!encode_bf16_map(&maps.a_hi, xb, 4, dims, strides, box, es, bk) ||
         !encode_bf16_map(&maps.a_lo, xb + d->x_lo_off, 4, dims, strides, box, es, bk))
       return SCFLOW_E_DRIVER;
+    maps.b_hi = maps.a_hi; maps.b_lo = maps.a_lo;
+    if (d->x2) {
+      const uint64_t dims2[4] = {(uint64_t)cin2, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
+      const uint64_t strides2[3] = {(uint64_t)d->x2_stride_w * 2, (uint64_t)d->x2_stride_h * 2,
+                                    (uint64_t)d->x2_stride_n * 2};
+      const __nv_bfloat16* xb2 = static_cast<const __nv_bfloat16*>(d->x2);
+      if (!encode_bf16_map(&maps.b_hi, xb2, 4, dims2, strides2, box, es, bk) ||
+          !encode_bf16_map(&maps.b_lo, xb2 + d->x2_lo_off, 4, dims2, strides2, box, es, bk))
+        return SCFLOW_E_DRIVER;
+    }
     const uint64_t wd[2] = {(uint64_t)bk, (uint64_t)d->kh * d->kw * p.kblocks * 2 * p.cout_pad};
     const uint64_t ws[1] = {(uint64_t)bk * 2};
     const uint32_t wb[2] = {(uint32_t)bk, (uint32_t)(pair ? p.bn / 2 : p.bn)};

@@ -158,6 +158,20 @@ extern "C" int scflow_pose_fc_fwd(const float* x, const float* w0, const float* 
   return check_launch();
 }
 
+// The tail alone: a1 = ReLU(b1 + sum of `splitk` partial-sum blocks of fc1) and the 9 predictor rows of the class of
+// label[0].  With splitk = 1 `part1` is simply fc1's pre-activation without bias (M, n1): what the tensor-core
+// path of the pose head (fc0 as an hs x ws convolution, fc1 as a 1x1 convolution on scflow_conv_tc_fwd) hands over.
+extern "C" int scflow_pose_tail_fwd(const float* part1, const float* b1, const float* wr, const float* br,
+                                    const float* wt, const float* bt, const long long* label, float* dr, float* dt,
+                                    int M, int splitk, int n1, int num_class, void* stream) {
+  using namespace scflow;
+  if (!part1 || !b1 || !wr || !br || !wt || !bt || !label || !dr || !dt) return SCFLOW_E_NULL;
+  if (M <= 0 || n1 <= 0 || n1 > 8192 || num_class <= 0 || splitk <= 0 || splitk > 64) return SCFLOW_E_BAD_SHAPE;
+  ph::TailParams p{part1, b1, wr, br, wt, bt, label, dr, dt, M, splitk, n1, num_class};
+  ph::pose_tail_kernel<<<M, 320, (size_t)n1 * sizeof(float), (cudaStream_t)stream>>>(p);
+  return check_launch();
+}
+
 // ---------------------------------------------------------------------------------------------
 // scflow_pose_fc_fwd_static: the same three launches with the split-K partials in a file-scope device array
 // instead of a caller-supplied workspace, for callers that cannot allocate device memory (CUDA graph capture,

@@ -1,15 +1,14 @@
 """ConvGRU (SeqConv, models/decoder/raft_decoder.py:235-253) on the split-bf16 tensor-core convolution family.
 
 Round 1 ran the gates in TF32 (one tcgen05 MMA per product): 5.7e-5 / 8.9e-5 rad of the 1e-4 rad pose budget
-went to this module alone.  Here every product is three bf16 MMAs (csrc/conv_tc.cu), and a pass is three
+went to this module alone.  Here every product is three bf16 MMAs (csrc/conv_tc.cu), and a pass is two
 launches of the same implicit-GEMM kernel with gate epilogues:
 
-    zr    conv over [x | h] (384 ch)  -> z = sigmoid(.) kept in fp32, r = sigmoid(.), r*h as split planes
-    qx    conv over x (256 ch) + bq    -> the x part of the q pre-activation, fp32
-    gate  conv over r*h (128 ch) + qx  -> q = tanh(.), h = (1-z) h + z q, in place (fp32) + split planes
+    zr    conv over [x | h] (384 ch)        -> z = sigmoid(.) kept in fp32, r = sigmoid(.), r*h as split planes
+    gate  conv over [r*h | x] (two tensors)  -> q = tanh(.), h = (1-z) h + z q, in place (fp32) + split planes
 
 The exact fp32 hidden state lives beside its split copy (the MMA operand of the next pass and of the heads).
-Weights stay fp32 nn.Parameters under the reference names; the three packs per pass are derived caches keyed on
+Weights stay fp32 nn.Parameters under the reference names; the two packs per pass are derived caches keyed on
 the parameters' version counters and storage.  Operand channel order is [x | h] (the decoder keeps x, h and the
 pose head's extra features in ONE split buffer so that every consumer reads a contiguous channel range); the
 filters' input channels are permuted accordingly when packed.
@@ -28,7 +27,7 @@ def _key(mod, p):
 
 
 def packs(mod, p: int):
-    """(zr, qx, qh) packed filters of pass p (0: (1,5), 1: (5,1))."""
+    """(zr, q) packed filters of pass p (0: (1,5), 1: (5,1))."""
     cache = mod.__dict__.setdefault("_scflow_gru_packs", {})
     key = _key(mod, p)
     hit = cache.get(p)
@@ -42,21 +41,19 @@ def packs(mod, p: int):
         perm = torch.cat([torch.arange(ch, ch + cx), torch.arange(0, ch)]).to(cz.weight.device)
         w_zr = torch.cat([cz.weight, cr.weight], 0).float()[:, perm].contiguous()
         b_zr = torch.cat([cz.bias, cr.bias], 0)
-        w_qx = cq.weight.float()[:, ch:].contiguous()
-        w_qh = cq.weight.float()[:, :ch].contiguous()
+        # q reads cat([r*h, x]) (raft_decoder.py:250) from where the two lie: r*h in the scratch planes, x in the
+        # state buffer (two tensor maps, no concatenation): the filter keeps the reference's input-channel order
         val = (C.pack_weights(w_zr, b_zr, cz.stride, cz.padding),
-               C.pack_weights(w_qx, cq.bias, cq.stride, cq.padding),
-               C.pack_weights(w_qh, None, cq.stride, cq.padding))
+               C.pack_weights(cq.weight.float().contiguous(), cq.bias, cq.stride, cq.padding))
     cache[p] = (key, val)
     return val
 
 
 class Scratch:
-    """Per-shape work buffers of the update: z (fp32), the x part of q (fp32), r*h (split planes)."""
+    """Per-shape work buffers of the update: z (fp32), r*h (split planes)."""
 
     def __init__(self, n, h, w, ch, device):
         self.z = torch.empty((n, h, w, ch), device=device, dtype=torch.float32)
-        self.qx = torch.empty((n, h, w, ch), device=device, dtype=torch.float32)
         self.rh = C.alloc_split(n, h, w, ch, device)
 
 
@@ -71,10 +68,9 @@ def update_inplace(mod, xh: "C.Split", h_state: torch.Tensor, scratch: Scratch =
     sc = scratch or Scratch(n, H, W, ch, h_state.device)
     x_part, h_part = xh.slice(0, cx), xh.slice(cx, ch)
     for p in (0, 1):
-        zr, qx, qh = packs(mod, p)
+        zr, q = packs(mod, p)
         C.conv(xh, zr, out=sc.rh, epi=C.EPI_GRU_ZR, gru_h=h_state, gru_z=sc.z)
-        C.conv(x_part, qx, out_f32=sc.qx)
-        C.conv(sc.rh, qh, res_f32=sc.qx, out=h_part, epi=C.EPI_GRU_GATE, gru_h=h_state, gru_z=sc.z)
+        C.conv(sc.rh, q, x2=x_part, out=h_part, epi=C.EPI_GRU_GATE, gru_h=h_state, gru_z=sc.z)
 
 
 def forward(mod, h: torch.Tensor, x: torch.Tensor) -> torch.Tensor:

@@ -361,6 +361,25 @@ def group_norm4_act(x: torch.Tensor, gn: torch.nn.GroupNorm, relu: bool, split_o
     return x if split_out is None else split_out
 
 
+def pose_tail(part1: torch.Tensor, head, label: torch.Tensor):
+    """ReLU(fc1 pre-activation (M, n1) + bias) -> (dr (M,6), dt (M,3)) of the class of label[0]
+    (scflow_pose_tail_fwd)."""
+    lib = _lib.load()
+    part1 = _chk(part1, "part1")
+    M, n1 = part1.shape
+    label = _chk(label, "label", torch.int64)
+    dr = torch.empty((M, 6), device=part1.device, dtype=torch.float32)
+    dt = torch.empty((M, 3), device=part1.device, dtype=torch.float32)
+    d = lambda t: _ptr(t.detach())
+    with _timed("scflow_pose_tail_fwd", 1):
+        rc = lib.scflow_pose_tail_fwd(_ptr(part1), d(head.fc_layers[1][0].bias), d(head.rotation_pred.weight),
+                                      d(head.rotation_pred.bias), d(head.translation_pred.weight),
+                                      d(head.translation_pred.bias), _ptr(label), _ptr(dr), _ptr(dt), M, 1, n1,
+                                      head.num_class, _stream())
+    _lib.check(rc, "scflow_pose_tail_fwd")
+    return dr, dt
+
+
 def pose_fc(x2d: torch.Tensor, w0: torch.Tensor, head, label: torch.Tensor, splitk: int = 4):
     """FC tail of MultiClassPoseHead on x2d (M, K) with the (possibly column-permuted) fc0 weight w0:
     returns (dr (M,6), dt (M,3)) of the class of label[0]."""

@@ -50,31 +50,37 @@ class MultiClassPoseHead(nn.Module):
         with torch.no_grad():
             self.rotation_pred.bias.copy_(torch.tensor([1., 0., 0., 0., 1., 0.] * self.num_class))
 
-    def _fc0_permuted(self, P: int) -> torch.Tensor:
-        """fc0 weight with its columns re-ordered from flatten(NCHW) = c*P + p to the channels-last memory
-        order p*C + c of the conv stack's output (so no flatten copy is needed); cached per version."""
-        w = self.fc_layers[0][0].weight
-        key = (w._version, w.data_ptr(), P)
-        hit = self.__dict__.get("_scflow_fc0")
+    def _fc_packs(self, hs: int, ws: int):
+        """fc0 / fc1 as convolution filters for the tensor-core family: flatten(NCHW) + Linear(C*hs*ws -> n0) IS the
+        hs x ws convolution (no padding) with the weight viewed as (n0, C, hs, ws); fc1 a 1x1 one (its bias and
+        ReLU are applied by the tail kernel).  Cached on the parameters' version counters."""
+        from . import convtc as C
+        fc0, fc1 = self.fc_layers[0][0], self.fc_layers[1][0]
+        key = (C._key(fc0.weight, fc0.bias, fc1.weight), hs, ws)
+        hit = self.__dict__.get("_scflow_fc_packs")
         if hit is None or hit[0] != key:
-            C = w.shape[1] // P
-            hit = (key, w.detach().view(w.shape[0], C, P).permute(0, 2, 1).reshape(w.shape[0], P * C).contiguous())
-            self.__dict__["_scflow_fc0"] = hit
+            c = fc0.in_features // (hs * ws)
+            with torch.no_grad():
+                pk0 = C.pack_weights(fc0.weight.view(fc0.out_features, c, hs, ws), fc0.bias, 1, 0)
+                pk1 = C.pack_weights(fc1.weight.view(fc1.out_features, fc1.in_features, 1, 1), None, 1, 0)
+            hit = (key, (pk0, pk1))
+            self.__dict__["_scflow_fc_packs"] = hit
         return hit[1]
 
     def forward_split(self, xs, label: torch.Tensor):
         """Inference on a split-plane input (convtc.Split of cat[h | delta-flow feat | mask feat]): three
-        stride-2 tensor-core convolutions, each followed by the one-launch GN+ReLU kernel, then the whole FC
-        tail in three launches (csrc/pose_head.cu)."""
+        stride-2 tensor-core convolutions, each followed by the one-launch GN+ReLU kernel (split planes out), fc0
+        and fc1 on the same convolution family (narrow 32-filter tiles so that 32 SMs share the 8 MB fc0 weight),
+        and the tail kernel (bias + ReLU of fc1, the selected class's 9 predictor rows)."""
         from . import convtc as C, ops
-        if self.fc_layers[1][0].out_features + self.fc_layers[0][0].out_features > 12288:
-            raise NotImplementedError("pose head FC widths beyond the split-K kernel's workspace")
         y = xs
-        for i, layer in enumerate(self.conv_layers):
-            # GN+ReLU applied; split planes between the convolutions, fp32 channels-last into the FC tail
-            y = layer.forward_split(y, want="split") if i + 1 < len(self.conv_layers) else layer.forward_split(y)
-        n, hs, ws, c = y.shape
-        return ops.pose_fc(y.reshape(n, hs * ws * c), self._fc0_permuted(hs * ws), self, label)
+        for layer in self.conv_layers:
+            y = layer.forward_split(y, want="split")                     # conv -> GN+ReLU -> split planes
+        n, hs, ws = y.shape
+        pk0, pk1 = self._fc_packs(hs, ws)
+        a0 = C.conv(y, pk0, relu=True, bn=32)                            # (n, 1, 1, n0) split planes
+        a1 = C.conv(a0, pk1, want="f32", bn=32)                          # (n, 1, 1, n1) fp32, pre-activation
+        return ops.pose_tail(a1.view(n, -1)[:, :pk1.cout], self, label)
 
     def forward(self, x: torch.Tensor, label: torch.Tensor):
         if not (torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters()))):

@@ -110,6 +110,27 @@ def test_conv_tc_algorithms_vs_fp64(n, h, w, cin, cout, kh, kw, ph, pw, algo):
     assert e < TOL + 3 * (cin * kh * kw / 16) * 2.0 ** -24, e
 
 
+@pytest.mark.parametrize("algo", [C.ALGO_TAP_BOXES, C.ALGO_PATCH, C.ALGO_PATCH_PAIR])
+def test_conv_tc_two_input_tensors_equal_concatenation(algo):
+    """x2: the filter's input channels continue in a second tensor (raft_decoder.py:250, cat([r*h, x]) read from
+    where the two lie): identical to the convolution of the concatenated operand."""
+    g = torch.Generator().manual_seed(21)
+    n, h, w, c1, c2, cout = 2, 32, 32, 128, 256, 128
+    a = torch.randn(n, h, w, c1, generator=g)
+    b = torch.randn(n, h, w, c2, generator=g)
+    wt = torch.randn(cout, c1 + c2, 1, 5, generator=g) / (5 * (c1 + c2)) ** 0.5
+    bias = torch.randn(cout, generator=g)
+    pk = C.pack_weights(wt.to(DEV), bias.to(DEV), 1, (0, 2))
+    wide = C.alloc_split(n, h, w, 512, DEV, zero=True)              # b lives in a channel slice of a wider buffer
+    bs = C.to_split(b.to(DEV), out=wide.slice(64, c2))
+    got = C.conv(C.to_split(a.to(DEV)), pk, x2=bs, relu=True, algo=algo)
+    one = C.conv(C.to_split(torch.cat([a, b], -1).to(DEV)), pk, relu=True, algo=algo)
+    torch.cuda.synchronize()
+    assert torch.equal(got.buf, one.buf)
+    want = _ref(torch.cat([a, b], -1), wt, bias, 1, (0, 2), relu=True)
+    assert _err(got.float(), want) < TOL + 3 * (5 * (c1 + c2) / 16) * 2.0 ** -24
+
+
 def test_conv_tc_outputs_residuals_stats():
     g = torch.Generator().manual_seed(7)
     n, h, w, cin, cout = 3, 16, 16, 64, 96

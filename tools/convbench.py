@@ -50,7 +50,7 @@ SHAPES = [
     ("pose 3x3/2 224->128 @32->16", 32, 32, 224, 128, 3, 3, 2, 1, 1, "f32", 8),
     ("pose 3x3/2 128->128 @16->8", 16, 16, 128, 128, 3, 3, 2, 1, 1, "f32", 8),
     ("GRU zr epilogue 1x5 384->256 @32", 32, 32, 384, 256, 1, 5, 1, 0, 2, "gru_zr", 16),
-    ("GRU gate epilogue 1x5 128->128 @32", 32, 32, 128, 128, 1, 5, 1, 0, 2, "gru_gate", 16),
+    ("GRU gate epilogue 1x5 128+256->128 @32", 32, 32, 384, 128, 1, 5, 1, 0, 2, "gru_gate", 16),
 ]
 
 
@@ -94,7 +94,6 @@ for name, h, w, cin, cout, kh, kw, s, ph, pw, out, calls in SHAPES:
                             gru_h=torch.randn(N, oh, ow, 128, device=dev), gru_z=torch.empty(N, oh, ow, 128, device=dev)))
         elif out == "gru_gate":
             kw_.append(dict(out=C.alloc_split(N, oh, ow, 128, dev), epi=C.EPI_GRU_GATE,
-                            res_f32=torch.randn(N, oh, ow, 128, device=dev),
                             gru_h=torch.randn(N, oh, ow, 128, device=dev), gru_z=torch.rand(N, oh, ow, 128, device=dev)))
         else:
             kw_.append(dict(out_f32=torch.empty(N, oh, ow, c8, device=dev),
