@@ -518,10 +518,11 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    // The whole warp walks the loops (warp-uniform control flow keeps descriptors and addresses in uniform
-    // registers); one elected lane issues the MMAs and commits.  Issued from a single diverged lane the same
-    // loop cost ~55 SASS instructions per MMA (broadcast + elect sequences) and bound the narrow tiles.
-    {
+    // ONE ELECTED lane (elect.sync, so the compiler knows exactly one thread runs the region and keeps
+    // descriptors and addresses in uniform registers) walks the loops, issues the MMAs and commits.  Written as
+    // `if (lane == 0)` the same loop compiled to ~55 SASS instructions per MMA (R2UR.BROADCAST + ELECT + BRA.U.ANY
+    // sequences around every tcgen05.mma) and the issuing thread bound the narrow tiles (tensor pipe 24-33 %).
+    if (tc::elect_one()) {
       const uint32_t idesc = make_idesc_bf16(BM, p.bn);
       const uint32_t idesc2 = make_idesc_bf16(BM, 2 * p.bn);
       const uint32_t smem0 = tc::smem_u32(smem);
@@ -548,34 +549,31 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
             const uint64_t dal = tc::make_smem_desc(a_lo, 16, kSbo, kLayout);
             const uint64_t dbh = tc::make_smem_desc(b_hi, 16, kSbo, kLayout);
             const uint64_t dbl = tc::make_smem_desc(b_lo, 16, kSbo, kLayout);
-            if (tc::elect_one()) {
 #pragma unroll
-              for (int ks = 0; ks < BK / 16; ++ks) {
-                if (ks < nks) {
-                  if (fold) {
-                    // narrow tiles fold two of the three products into one instruction: [B_hi;B_lo] are
-                    // adjacent in the stage = one 2 bn-row operand; columns [0,bn) get a_hi.b_hi, [bn,2bn)
-                    // a_hi.b_lo, the epilogue adds the halves
-                    mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc2, acc | (uint32_t)ks);
-                    mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, 1u);
-                  } else {
-                    mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);   // small terms first
-                    mma_bf16_ss(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
-                    mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
-                  }
+            for (int ks = 0; ks < BK / 16; ++ks) {
+              if (ks < nks) {
+                if (fold) {
+                  // narrow tiles fold two of the three products into one instruction: [B_hi;B_lo] are
+                  // adjacent in the stage = one 2 bn-row operand; columns [0,bn) get a_hi.b_hi, [bn,2bn)
+                  // a_hi.b_lo, the epilogue adds the halves
+                  mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc2, acc | (uint32_t)ks);
+                  mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                } else {
+                  mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);   // small terms first
+                  mma_bf16_ss(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
+                  mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
                 }
               }
-              tc::tc_commit(&empty[stage]);
             }
-            __syncwarp();
+            tc::tc_commit(&empty[stage]);
             acc = 1u;
             if (++stage == p.stages) { stage = 0; phase ^= 1; }
           }
         }
-        if (tc::elect_one()) tc::tc_commit(&acc_full[buf]);
-        __syncwarp();
+        tc::tc_commit(&acc_full[buf]);
       }
     }
+    __syncwarp();
   } else {
     // ------------------------------------------------------------------ epilogue (8 warps)
     const int quarter = warp & 3;                           // TMEM lanes this warp may read
@@ -629,7 +627,8 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
 // Barrier waits are plain CTA-scope try_waits also in PAIR mode: what they guard is written by the async
 // proxy (TMA, tcgen05.commit) and read by the async proxy; the cluster-scope acquire form costs an L1
 // invalidate (CCTL.IVALL) per wait.
-// warp 0: patch producer, warp 1: MMA issuer (PAIR: rank 0's), warps 2..9: epilogue, warp 10: filter producer.
+// warp 0: patch producer, warp 1: MMA issuer (one elected lane; PAIR: rank 0's), warps 2..9: epilogue,
+// warp 10: filter producer.
 constexpr int P_THREADS = THREADS + 32;
 constexpr int MAX_A_STAGES = 4, MAX_W_STAGES = 32;
 constexpr int P_BAR_BYTES = 1024;
@@ -752,13 +751,14 @@ conv_patch_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Par
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer (warp-uniform; see above)
-    if (rank == 0) {
+    // ------------------------------------------------------------------ MMA issuer (one elected lane; see above)
+    if (rank == 0 && tc::elect_one()) {
       const uint32_t idesc = make_idesc_bf16(PAIR ? 2 * BM : BM, p.bn);
       const uint32_t idesc2 = make_idesc_bf16(BM, 2 * p.bn);
       const uint32_t a0 = tc::smem_u32(a_ring), w0 = tc::smem_u32(w_ring);
       const uint32_t sbo = (uint32_t)p.pitch * 128u;          // one output row of the tile = one swizzle atom
       const bool fold = p.fold != 0, resident = p.w_resident != 0;
+      const uint64_t lo_off = (uint64_t)(p.wb_bytes >> 4);    // B_lo behind B_hi, in descriptor address units
       int as = 0, ws = 0; uint32_t aph = 0, wph = 0, it = 0;
       for (int u = unit0; u < total; u += units_grid, ++it) {
         const uint32_t buf = it & 1;
@@ -766,61 +766,57 @@ conv_patch_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Par
         tc::tc_fence_after();
         const uint32_t d = tmem_base + buf * 256u;
         uint32_t acc = 0;
+        // a resident filter is in place after the first tile: nothing to wait for inside a k-block then (the
+        // wait + fence per tap is most of the issue cost of the 64-filter encoder layers, whose 12 MMAs per tap
+        // are 32 cycles each)
+        const bool wait_w = !(resident && it > 0);
         for (int kb = 0; kb < p.kblocks; ++kb) {
           tc::mbar_wait(&a_full[as], aph);
           tc::tc_fence_after();
-          const uint32_t a_hi = a0 + as * p.a_stage_bytes, a_lo = a_hi + p.patch_bytes;
+          const uint32_t a_hi = a0 + as * p.a_stage_bytes;
+          const uint64_t dah0 = tc::make_smem_desc(a_hi, 16, sbo, kLayout);
+          const uint64_t dal0 = tc::make_smem_desc(a_hi + p.patch_bytes, 16, sbo, kLayout);
           const int nks = kb == p.kblocks - 1 ? p.ksteps_last : 4;
           int ky = 0, kx = 0;
           for (int tap = 0; tap < taps; ++tap) {
-            // a resident slab's barrier completes its phase 0 once and is waited on with parity 0 ever after
-            tc::mbar_wait(&w_full[ws], wph);
-            tc::tc_fence_after();
-            const uint32_t shift = (uint32_t)(ky * p.pitch + kx) * 128u;
-            const uint32_t b_hi = w0 + ws * p.w_stage_bytes, b_lo = b_hi + p.wb_bytes;
-            const uint64_t dah = tc::make_smem_desc(a_hi + shift, 16, sbo, kLayout);
-            const uint64_t dal = tc::make_smem_desc(a_lo + shift, 16, sbo, kLayout);
-            const uint64_t dbh = tc::make_smem_desc(b_hi, 16, 1024, kLayout);
-            const uint64_t dbl = tc::make_smem_desc(b_lo, 16, 1024, kLayout);
-            if (tc::elect_one()) {
+            if (wait_w) {
+              tc::mbar_wait(&w_full[ws], wph);                // a resident slab: parity 0 of a barrier that completes once
+              tc::tc_fence_after();
+            }
+            const uint64_t sh = (uint64_t)((ky * p.pitch + kx) * 8);            // rows of 128 bytes, >> 4
+            const uint64_t dah = dah0 + sh, dal = dal0 + sh;
+            const uint64_t dbh = tc::make_smem_desc(w0 + ws * p.w_stage_bytes, 16, 1024, kLayout), dbl = dbh + lo_off;
 #pragma unroll
-              for (int ks = 0; ks < 4; ++ks) {
-                if (ks < nks) {
-                  if (PAIR) {
-                    mma_bf16_ss_2cta(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
-                    mma_bf16_ss_2cta(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
-                    mma_bf16_ss_2cta(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
-                  } else if (fold) {
-                    mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc2, acc | (uint32_t)ks);   // [B_hi;B_lo]: 2 bn rows
-                    mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, 1u);
-                  } else {
-                    mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
-                    mma_bf16_ss(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
-                    mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
-                  }
+            for (int ks = 0; ks < 4; ++ks) {
+              if (ks < nks) {
+                if (PAIR) {
+                  mma_bf16_ss_2cta(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
+                  mma_bf16_ss_2cta(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
+                  mma_bf16_ss_2cta(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                } else if (fold) {
+                  mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc2, acc | (uint32_t)ks);   // [B_hi;B_lo]: 2 bn rows
+                  mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                } else {
+                  mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
+                  mma_bf16_ss(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
+                  mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
                 }
               }
-              if (!resident) {
-                if (PAIR) tc::tc_commit_2cta(&w_empty[ws]); else tc::tc_commit(&w_empty[ws]);
-              }
             }
-            __syncwarp();
+            if (!resident) {
+              if (PAIR) tc::tc_commit_2cta(&w_empty[ws]); else tc::tc_commit(&w_empty[ws]);
+            }
             acc = 1u;
             if (++kx == p.kw) { kx = 0; ++ky; }
             if (++ws == p.w_stages) { ws = 0; if (!resident) wph ^= 1; }
           }
-          if (tc::elect_one()) {
-            if (PAIR) tc::tc_commit_2cta(&a_empty[as]); else tc::tc_commit(&a_empty[as]);
-          }
-          __syncwarp();
+          if (PAIR) tc::tc_commit_2cta(&a_empty[as]); else tc::tc_commit(&a_empty[as]);
           if (++as == p.a_stages) { as = 0; aph ^= 1; }
         }
-        if (tc::elect_one()) {
-          if (PAIR) tc::tc_commit_2cta(&acc_full[buf]); else tc::tc_commit(&acc_full[buf]);
-        }
-        __syncwarp();
+        if (PAIR) tc::tc_commit_2cta(&acc_full[buf]); else tc::tc_commit(&acc_full[buf]);
       }
     }
+    __syncwarp();
   } else if (warp >= 2 && warp < 2 + NEPI) {
     // ------------------------------------------------------------------ epilogue (8 warps, own TMEM)
     const int quarter = warp & 3;
