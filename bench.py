@@ -156,11 +156,14 @@ def seeded_weights(core):
 
 
 # --------------------------------------------------------------------------- CPU / reference arm
-def cpu_refiner_state():
+def cpu_refiner_state(S=256):
     from scflow_b200 import synthetic as syn
     gd = os.path.join(ROOT, "tests", "golden")
     es = json.load(open(os.path.join(gd, "encoder_state_shapes.json")))
     ds = {k: tuple(v) for k, v in json.load(open(os.path.join(gd, "decoder_state_shapes.json"))).items()}
+    # the fixture holds the 256x256 head: fc0 reads 128 channels of the (S/64)^2 map the three stride-2 layers leave
+    k0 = "pose_pred.fc_layers.0.0.weight"
+    ds[k0] = (ds[k0][0], 128 * (S // 64) ** 2)
     return (syn.fill_state_dict(es["IN"], seed=61, gain=1.7), syn.fill_state_dict(es["BN"], seed=62, gain=1.7),
             syn.fill_state_dict(ds, seed=64))
 
@@ -171,7 +174,7 @@ def reference_model(S=256):
     try:
         from oracle import _ref_shims as RS
         if RS.reference_available():
-            return RS.ReferenceRefiner(S, cpu_refiner_state()), "reference"
+            return RS.ReferenceRefiner(S, cpu_refiner_state(S)), "reference"
     except Exception as e:                                  # pragma: no cover - reported in the line
         sys.stderr.write(f"reference files unavailable ({e}); timing the oracle port\n")
     return None, "port"
@@ -214,7 +217,7 @@ def reference_arm(args):
     B, S = args.batch, args.image
     batch = tile_batch(make_batch(4, 1234, S), B)
     model, kind = reference_model(S)
-    n, ts = cpu_run(batch, cpu_refiner_state(), max(1, args.steps), max(0, args.warmup), model)
+    n, ts = cpu_run(batch, cpu_refiner_state(S), max(1, args.steps), max(0, args.warmup), model)
     ms = 1e3 * sum(ts) / len(ts)
     val = n / (ms / 1e3)
     sample = f"the full step: {n} crops per timed step (same refiner, weights and input generator as our arm)"
@@ -353,8 +356,17 @@ def ours(args):
             ready[j % 2].record(copy_stream)
         state["prefetched"] = j
 
+    gather_events = []
+
     def step_resident(i):
         poses = graphs[i % 2]() if graphs else core.refine(resident[i % 2])
+        if world > 1:                 # the collective's own device time
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            out = gather_poses(poses, B * world)
+            b.record()
+            gather_events.append((a, b))
+            return out
         return gather_poses(poses, B * world)
 
     def step_e2e(i):
@@ -406,9 +418,13 @@ def ours(args):
         barrier()
         ms = torch.tensor([a.elapsed_time(b)], device=dev)
         if world > 1:
+            every = [torch.zeros_like(ms) for _ in range(world)]
+            dist.all_gather(every, ms)
+            timed.per_rank = sorted(float(t.item()) for t in every)
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    timed.per_rank = None
     for i in range(W):
         step_resident(i)
     for i in range(2):
@@ -418,7 +434,16 @@ def ours(args):
         sampler.start()
     if os.environ.get("SCFLOW_PROFILE") == "1":      # ncu --profile-from-start off
         torch.cuda.profiler.start()
+    gather_events.clear()
     ms_total = timed(step_resident, args.steps, False)
+    ranks = None
+    if world > 1 and timed.per_rank:
+        pr = [t / args.steps for t in timed.per_rank]
+        ag = sum(a.elapsed_time(b) for a, b in gather_events) / max(1, len(gather_events))
+        ranks = {"ms_per_step_min": pr[0], "ms_per_step_median": pr[len(pr) // 2], "ms_per_step_max": pr[-1],
+                 "allgather_ms_per_step_rank0": ag,
+                 "note": "value uses the MAX over ranks of the barrier-bracketed region; the pose all-gather is "
+                         "48 B per crop, its time here includes waiting for the slowest rank"}
     if os.environ.get("SCFLOW_PROFILE") == "1":
         torch.cuda.profiler.stop()
     launches = ops.STATS.count
@@ -524,10 +549,10 @@ def ours(args):
         from scflow_b200.refiner import unpack_pose
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
-        ns = 16
+        ns = 16 if S <= 256 else 8
         sample = tile_batch(make_batch(4, 1234, S), ns)
         model, kind = reference_model(S)
-        n, ts = cpu_run(sample, cpu_refiner_state(), 2, 1, model)
+        n, ts = cpu_run(sample, cpu_refiner_state(S), 2, 1, model)
         cpu = {"value": n / (sum(ts) / len(ts)), "unit": UNIT, "cores": torch.get_num_threads(), "kind": kind,
                "sample": f"{n} of the step's {B} crops per run, 1 warm-up + 2 timed runs of "
                          + ("the unmodified reference modules (baseline/_ref + shims)" if kind == "reference"
@@ -554,7 +579,7 @@ def ours(args):
         "tf32_peak_note": "cuBLAS TF32 8192^3 back to back, builder-measured in this run (MEASURED_PEAKS.json has "
                           "no TF32 entry)",
         "eager_ms_per_step": ms_eager / args.steps, "event_pair_overhead_us": ev_ms * 1e3, "kernels": kern,
-        "cpu_baseline": cpu, "clocks": clocks,
+        "cpu_baseline": cpu, "clocks": clocks, "ranks": ranks,
         "precision": {"ours": PRECISION_TEXT, "library_calls_on_the_path": "none (no cuDNN / cuBLAS)",
                       "deviation_from_oracle": parity},
     }))
