@@ -63,6 +63,30 @@ const char* scflow_strerror(int rc);
 int scflow_last_cuda_error(void);
 
 /* ---------------------------------------------------------------------------------------------
+ * f4  Around the hot path: the renderer call and the pose-error evaluator (csrc/render.cu).
+ *
+ * scflow_render_fwd: what Renderer.forward (models/utils/rendering.py:185-248) asks of pytorch3d with the shipped
+ * configuration (configs/refine_models/scflow_ycbv_real.py:261-274: HardPhongShader, one face per pixel, blur radius
+ * 0, seperate_lights) and what the refiner reads back (models/refiner/base_refiner.py:106-112).  Meshes are packed:
+ * verts / normals / colors (sum V, 3), faces (sum F, 3) with vertex indices LOCAL to their mesh, voff / foff
+ * [classes + 1] offsets, vmax / fmax the largest mesh; per image: labels (int64), R (n,3,3), t (n,3), K (n,3,3)
+ * (OpenCV).  Outputs: image (n, 3, h, w) planar, zbuf (n, h, w) view-space z (-1 = background), mask (n, h, w) or
+ * NULL.  workspace: scflow_render_workspace_bytes(n, vmax, h, w) bytes.  No host synchronisation.
+ *
+ * scflow_add_error_fwd: ADD / ADD-S (symmetric[class] != 0: nearest predicted vertex) mean 3-D error and mean 2-D
+ * projection error per object, ADD.eval_pose_error (metrics/add.py:354-394) + project_3d_point
+ * (datasets/pose.py:18-70).  err3d / err2d: (n) doubles.
+ * ------------------------------------------------------------------------------------------- */
+size_t scflow_render_workspace_bytes(int n, int vmax, int h, int w);
+int scflow_render_fwd(const float* verts, const float* normals, const float* colors, const int* faces, const int* voff,
+                      const int* foff, int vmax, int fmax, const long long* labels, const float* R, const float* t,
+                      const float* K, int n, int h, int w, float bg_r, float bg_g, float bg_b, float* image,
+                      float* zbuf, float* mask, void* workspace, void* stream);
+int scflow_add_error_fwd(const float* verts, const int* voff, int vmax, const long long* labels, const int* symmetric,
+                         const float* gt_r, const float* gt_t, const float* pred_r, const float* pred_t,
+                         const float* K, double* err3d, double* err2d, int n, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * a1  CorrelationPyramid.forward   models/decoder/raft_decoder.py:35-58
  *     replaces torch.matmul (:48-50), the /sqrt(C) pass (:51-52) and 3x nn.AvgPool2d (:54-56).
  * feat1, feat2: (n, c, h, w).  levels[l]: (n*h*w, 1, h>>l, w>>l), l < num_levels (host array of

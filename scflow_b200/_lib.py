@@ -33,6 +33,10 @@ SIGNATURES = {
     "scflow_downsample_fwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, c_float, _P]),
     "scflow_group_norm4_act_nhwc": (c_int, [_P, _P, _P, _P, _P, ctypes.c_longlong, c_int, c_int, c_int, c_int, c_float,
                                             c_int, _P]),
+    "scflow_render_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "scflow_render_fwd": (c_int, [_P] * 6 + [c_int, c_int] + [_P] * 4 + [c_int, c_int, c_int, c_float, c_float, c_float]
+                          + [_P] * 5),
+    "scflow_add_error_fwd": (c_int, [_P, _P, c_int] + [_P] * 9 + [c_int, _P]),
     "scflow_pose_tail_fwd": (c_int, [_P] * 9 + [c_int, c_int, c_int, c_int, _P]),
     "scflow_pose_fc_workspace_floats": (c_size_t, [c_int, c_int, c_int, c_int]),
     "scflow_pose_fc_fwd": (c_int, [_P] * 13 + [c_int] * 6 + [_P]),

@@ -208,3 +208,33 @@ def test_decoder_gradients_s64(golden_dir):
     for k, want in norms.items():
         got = 0.0 if sd[k].grad is None else float(sd[k].grad.double().norm())
         assert abs(got - want) <= 2e-3 * max(want, 1e-6), (k, got, want)
+
+
+def test_add_oracle_equals_reference_golden(golden_dir):
+    """oracle/render_oracle.add_errors (restatement of metrics/add.py:354-394 + datasets/pose.py:18-70) against the
+    outputs of the UNMODIFIED reference method (oracle/gen_golden_add.py): identical in float64."""
+    import numpy as np
+    from oracle import render_oracle as RO
+    g = np.load(os.path.join(golden_dir, "add_eval.npz"))
+    vl = [g[f"verts{i}"].astype(np.float64) for i in range(3)]
+    f = lambda k: g[k].astype(np.float64)
+    e3n, e2, e3 = RO.add_errors(vl, f("gt_t"), f("gt_r"), f("pred_t"), f("pred_r"), g["labels"], f("k"),
+                                {"cls_2": True}, list(g["diam"]))
+    assert np.abs(e3 - g["e3"]).max() < 1e-12 and np.abs(e2 - g["e2"]).max() < 1e-12
+    assert np.abs(e3n - g["e3n"]).max() < 1e-12
+
+
+def test_render_oracle_known_answers():
+    """A fronto-parallel square at depth 500: constant z-buffer, coverage equal to the projected area, ambient-only
+    colour where the light (placed by rendering.py:203-206 behind the surface) adds nothing."""
+    import numpy as np
+    from oracle import render_oracle as RO
+    verts = np.array([[-50, -50, 0], [50, -50, 0], [50, 50, 0], [-50, 50, 0]], np.float32)
+    faces = np.array([[0, 1, 2], [0, 2, 3]], np.int32)
+    colors = np.full((4, 3), 0.8, np.float32)
+    K = np.array([[320.0, 0, 32], [0, 320.0, 32], [0, 0, 1]])
+    img, z, fi = RO.render(verts, faces, colors, np.eye(3), np.array([0, 0, 500.0]), K, 64, 64)
+    hit = z > 0
+    assert abs(hit.sum() - 64 * 64) <= 2 * 64 + 4          # the square projects to exactly 64 x 64 image units
+    assert np.allclose(z[hit], 500.0)
+    assert np.allclose(img[:, ~hit], 0.5)
