@@ -347,6 +347,12 @@ int scflow_conv_tc_pack_weights(const float* w, const float* scale, void* packed
 int scflow_split_bf16(const float* in, long long in_pitch, void* out, long long out_pitch, int out_lo,
                       int channels, long long pixels, void* stream);
 
+/* planar fp32 (n, c, h, w), c * kw <= 16, kw odd -> split planes (n, h, w, [16 hi | 16 lo]) holding per pixel its kw
+ * x-neighbours of every channel (index dx * c + ci; zero outside the image and in unused slots): the input side of the
+ * 1-2 channel convolutions (flow_net[0], delta_flow_encoder[0], mask_encoder[0]; raft_decoder.py:152-160,
+ * scflow_decoder.py:96-106) in their tensor-core form, a kh x 1 convolution on 16 channels (scflow_conv_tc_fwd). */
+int scflow_expand_taps_fwd(const float* in, void* out, int n, int c, int kw, int h, int w, void* stream);
+
 /* planar fp32 (n, cf, pixels) -> channels [0, cf) of a split-plane slice starting at `out` (hi plane; lo plane
  * out_lo elements further; out_pitch elements per pixel): the flow pair appended to the motion features
  * (raft_decoder.py:165). */

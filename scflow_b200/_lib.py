@@ -37,6 +37,7 @@ SIGNATURES = {
     "scflow_render_fwd": (c_int, [_P] * 6 + [c_int, c_int] + [_P] * 4 + [c_int, c_int, c_int, c_float, c_float, c_float]
                           + [_P] * 5),
     "scflow_add_error_fwd": (c_int, [_P, _P, c_int] + [_P] * 9 + [c_int, _P]),
+    "scflow_expand_taps_fwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_pose_tail_fwd": (c_int, [_P] * 9 + [c_int, c_int, c_int, c_int, _P]),
     "scflow_pose_fc_workspace_floats": (c_size_t, [c_int, c_int, c_int, c_int]),
     "scflow_pose_fc_fwd": (c_int, [_P] * 13 + [c_int] * 6 + [_P]),

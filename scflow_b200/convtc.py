@@ -281,6 +281,37 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
     return res_[0] if len(res_) == 1 else res_
 
 
+def expand_taps(x: torch.Tensor, kw: int) -> Split:
+    """planar fp32 (n, c, h, w), c * kw <= 16 -> Split (n, h, w, 16): per pixel its kw x-neighbours of every channel
+    (scflow_expand_taps_fwd)."""
+    lib = _lib.load()
+    n, c, h, w = x.shape
+    if not x.is_cuda or x.dtype != torch.float32:
+        raise _lib.ScflowError("expand_taps: expected a CUDA fp32 tensor")
+    x = x.contiguous()
+    out = alloc_split(n, h, w, 16, x.device)
+    with _timed("scflow_expand_taps_fwd", 1, 4 * x.numel() + 64 * n * h * w):
+        rc = lib.scflow_expand_taps_fwd(_ptr(x), _ptr(out.buf), n, c, kw, h, w, _stream())
+    _lib.check(rc, "scflow_expand_taps_fwd")
+    return out
+
+
+def packed_small_cin(conv: nn.Conv2d) -> Packed:
+    """A kh x kw filter on 1-2 input channels as the kh x 1 filter on the 16 expanded channels of expand_taps
+    (input channel dx * c + ci), cached like packed_conv."""
+    key = _key(conv.weight, conv.bias)
+    hit = conv.__dict__.get("_scflow_cin")
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    cout, c, kh, kw = conv.weight.shape
+    with torch.no_grad():
+        w = conv.weight.detach().float().permute(0, 3, 1, 2).reshape(cout, kw * c, kh)     # [co][dx*c + ci][ky]
+        w = torch.nn.functional.pad(w, (0, 0, 0, 16 - kw * c)).unsqueeze(-1).contiguous()    # (cout, 16, kh, 1)
+        pk = pack_weights(w, conv.bias, 1, (conv.padding[0], 0))
+    conv.__dict__["_scflow_cin"] = (key, pk)
+    return pk
+
+
 def split_planar(x: torch.Tensor, out: Split) -> None:
     """planar fp32 (n, cf, h, w) -> the cf channels of the split slice `out` (scflow_split_planar)."""
     lib = _lib.load()

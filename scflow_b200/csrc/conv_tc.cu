@@ -1020,6 +1020,35 @@ __global__ void split_planar_kernel(const float* __restrict__ in, __nv_bfloat16*
   }
 }
 
+// planar fp32 (n, c <= 2, h, w) -> split planes (n, h, w, [16 | 16]) holding, per pixel, its kw <= 8 x-neighbours
+// x - kw/2 .. x + kw/2 of every channel (channel index dx * c + ci, zero outside the image and in the unused slots):
+// a kh x kw convolution on 1-2 channels becomes a kh x 1 convolution on 16 channels, i.e. kh taps of one 16-wide
+// k-step on the tensor cores, instead of kh * kw * c FMAs per output on the FP32 pipe.
+__global__ void expand_taps_kernel(const float* __restrict__ in, uint4* __restrict__ out, int c, int kw, int H, int W,
+                                   long long total) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int x = (int)(i % W);
+    const long long r = i / W;
+    const int y = (int)(r % H);
+    const long long n = r / H;
+    float v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = 0.f;
+    for (int dx = 0; dx < kw; ++dx) {
+      const int xx = x + dx - kw / 2;
+      if (xx < 0 || xx >= W) continue;
+      for (int ci = 0; ci < c; ++ci) v[dx * c + ci] = __ldg(in + ((n * c + ci) * H + y) * W + xx);
+    }
+    uint32_t hi[8], lo[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) split2(v[2 * k], v[2 * k + 1], hi[k], lo[k]);
+    uint4* o = out + i * 4;                                   // 64 bytes per pixel: 16 hi, 16 lo
+    o[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]); o[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+    o[2] = make_uint4(lo[0], lo[1], lo[2], lo[3]); o[3] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+  }
+}
+
 static bool encode_bf16_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
                             const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr, int bk) {
   tc::EncodeTiledFn fn = tc::get_encode_tiled();
@@ -1143,6 +1172,16 @@ extern "C" int scflow_split_bf16(const float* in, long long in_pitch, void* out,
   const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
   ctc::split_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
       in, in_pitch, static_cast<__nv_bfloat16*>(out), out_pitch, out_lo, c8, vec ? channels : 0, pixels);
+  return check_launch();
+}
+
+extern "C" int scflow_expand_taps_fwd(const float* in, void* out, int n, int c, int kw, int h, int w, void* stream) {
+  if (!in || !out) return SCFLOW_E_NULL;
+  if (n <= 0 || h <= 0 || w <= 0 || c <= 0 || kw <= 0 || !(kw & 1) || c * kw > 16) return SCFLOW_E_BAD_SHAPE;
+  if (!aligned16(out)) return SCFLOW_E_MISALIGNED;
+  const long long total = (long long)n * h * w;
+  const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  ctc::expand_taps_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(in, static_cast<uint4*>(out), c, kw, h, w, total);
   return check_launch();
 }
 

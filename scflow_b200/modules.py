@@ -90,7 +90,12 @@ class ConvModule(nn.Module):
         operand of the tensor-core convolution that follows it in flow_net / delta_flow_encoder / mask_encoder."""
         if not self._small_cin_ok(x):
             return C.to_split(self.forward(x).permute(0, 2, 3, 1))
-        return ops.conv_small_cin(x, self.conv, relu=self.with_activation, split_out=True)
+        c = self.conv
+        if x.shape[-2] % 16 == 0 and c.in_channels * c.kernel_size[1] <= 16:
+            # tensor-core form: the kw x-neighbours of the 1-2 channels expanded to 16 channels, then a kh x 1
+            # convolution (kh taps of one k-step) instead of kh * kw * c FMAs per output on the FP32 pipe
+            return C.conv(C.expand_taps(x, c.kernel_size[1]), C.packed_small_cin(c), relu=self.with_activation)
+        return ops.conv_small_cin(x, c, relu=self.with_activation, split_out=True)
 
     def forward(self, x):
         if _needs_grad(x, *self.parameters()):
