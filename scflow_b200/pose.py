@@ -2,7 +2,8 @@
 
 The reference keeps ragged per-crop point lists built with ``nonzero`` (a host sync per crop).
 Here ``cal_3d_2d_corr`` accepts a whole batch and returns a dense ``PointSet``; the two
-``*_list`` arguments of ``get_flow_from_delta_pose_and_points`` accept that PointSet."""
+``*_list`` arguments of ``get_flow_from_delta_pose_and_points`` accept that PointSet, or the reference's ragged
+lists (scattered into a PointSet on the device)."""
 from __future__ import annotations
 
 from dataclasses import dataclass
@@ -40,7 +41,20 @@ def get_flow_from_delta_pose_and_points(rotation_dst, translation_dst, k, points
     """pose.py:66-88 -> (n, 2, height, width)."""
     ps = points_3d_list
     if not isinstance(ps, PointSet):
-        raise TypeError("pass the PointSet returned by scflow_b200.pose.cal_3d_2d_corr")
+        # the reference's ragged form (what a RAFTDecoder-style caller built with the reference's own
+        # cal_3d_2d_corr): per image (Ni, 2) pixel coordinates (x, y) and (Ni, 3) object-frame points, scattered
+        # into the dense PointSet the kernel reads (device-side indexing, no host synchronisation)
+        n = len(points_3d_list)
+        if len(points_2d_list) != n or n != rotation_dst.shape[0]:
+            raise ValueError("points_2d_list / points_3d_list must hold one entry per image")
+        dev = rotation_dst.device
+        pts = torch.zeros((n, 3, height, width), device=dev, dtype=torch.float32)
+        msk = torch.zeros((n, height, width), device=dev, dtype=torch.uint8)
+        for i, (p2, p3) in enumerate(zip(points_2d_list, points_3d_list)):
+            x, y = p2[:, 0].to(torch.int64), p2[:, 1].to(torch.int64)
+            pts[i, :, y, x] = p3.t().float()
+            msk[i, y, x] = 1
+        ps = PointSet(pts, msk)
     if torch.is_grad_enabled() and (rotation_dst.requires_grad or translation_dst.requires_grad):
         raise NotImplementedError("differentiable pose-induced flow: use scflow_b200.autograd.pose_flow "
                                   "(depth path), as SCFlowDecoder does when training")

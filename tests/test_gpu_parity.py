@@ -225,6 +225,29 @@ def test_lift_and_pose_flow_vs_oracle_and_golden(golden_dir):
     assert torch.equal(R3, R) and torch.equal(t3, t)
 
 
+def test_pose_flow_accepts_the_reference_list_form():
+    """get_flow_from_delta_pose_and_points with the reference's ragged arguments (pose.py:66-88: per image (Ni, 2)
+    pixel coordinates and (Ni, 3) points, as the reference's own cal_3d_2d_corr builds them) equals the dense
+    PointSet form and the oracle."""
+    from scflow_b200 import pose as P
+    cr = syn.make_crops(3, 64, seed=7)
+    c = _cuda(cr)
+    ps, _ = P.cal_3d_2d_corr(c["depth"], c["K"], c["R0"], c["t0"])
+    R1 = c["R0"] @ torch.tensor([[0.995, -0.0998, 0.0], [0.0998, 0.995, 0.0], [0.0, 0.0, 1.0]], device=DEV)
+    t1 = c["t0"] + torch.tensor([2.0, -1.0, 6.0], device=DEV)
+    dense = P.get_flow_from_delta_pose_and_points(R1, t1, c["K"], ps, ps, 64, 64, invalid_num=400.)
+    p2l, p3l = [], []
+    for i in range(3):
+        ys, xs = torch.nonzero(ps.mask[i], as_tuple=True)
+        p2l.append(torch.stack([xs, ys], -1).float())
+        p3l.append(ps.points3d[i][:, ys, xs].t().contiguous())
+    ragged = P.get_flow_from_delta_pose_and_points(R1, t1, c["K"], p2l, p3l, 64, 64, invalid_num=400.)
+    assert torch.equal(dense, ragged)
+    pts, mask = O.lift_points_dense(cr["depth"], cr["K"], cr["R0"], cr["t0"])
+    want = O.pose_flow_dense(R1.cpu(), t1.cpu(), cr["K"], pts, mask, 400.)
+    assert float((ragged.cpu() - want).abs().max()) < 1e-3
+
+
 def test_identity_delta_pose_keeps_pose_and_zero_flow():
     """KAT from the zero-initialised pose head (pose_head.py:187-198): dR6 = [1,0,0,0,1,0], dt = 0
     => R_k = R_0, t_k = t_0 and the pose-induced flow vanishes on the foreground."""
@@ -319,6 +342,28 @@ def test_refiner_vs_golden(golden_dir, tag, s, seed):
     et = float((out[3][-1].cpu() - tg[-1]).abs().max())
     print(f"refiner {tag}: pose err {er:.3e} rad, {et:.3e} mm")
     assert er < 1e-4 and et < 0.1
+
+
+def test_refiner_batch64_vs_oracle():
+    """Whole-refiner parity at the bench's size (BASELINE.json configs[1]: 64 crops of 256 x 256, 8 iterations):
+    every one of the 64 final poses against the fp32 CPU oracle, within the north_star budget."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    from scflow_b200.refiner import unpack_pose
+    torch.set_num_threads(os.cpu_count() or 1)
+    host = bench.tile_batch(bench.make_batch(4, 1234, 256), 64)
+    core = bench.seeded_weights(SCFlowRefinerCore(256)).eval().to(DEV)
+    with torch.no_grad():
+        Rg, tg = unpack_pose(core.refine({k: v.to(DEV) for k, v in host.items()}).cpu())
+        se, sc, sd = bench.cpu_refiner_state(256)
+        o = O.refiner_forward(se, sc, sd, host["rendered_images"], host["real_images"], host["R0"], host["t0"],
+                              host["depth"], host["K"], host["labels"])
+    er = float(O.rotation_geodesic(Rg, o["rotations"][-1]).max())
+    et = float((tg - o["translations"][-1]).abs().max())
+    moved = float(O.rotation_geodesic(o["rotations"][-1], host["R0"]).max())
+    print(f"64 crops: pose err {er:.3e} rad, {et:.3e} mm (the poses moved by up to {moved:.3f} rad)")
+    assert moved > 1e-2 and er < 1e-4 and et < 0.1
 
 
 def test_batch64_matches_per_crop_runs():
