@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define SCFLOW_ABI_VERSION 6
+#define SCFLOW_ABI_VERSION 7
 
 enum {
   SCFLOW_OK = 0,
@@ -386,10 +386,18 @@ int scflow_corr_lookup_bwd(const float* grad_out, int grad_layout, const float* 
 
 /* First half of the backward of scflow_corr_pyramid_fwd (raft_decoder.py:48-56): folds the level
  * gradients (NULL entries = no gradient) into grad_corr (n*h*w, h, w) = d loss / d (f1^T f2), i.e.
- * including the 1/sqrt(c) scale and the 2x2-mean adjoints.  The caller finishes with two plain
- * batched GEMMs: d f1 = f2 . grad_corr^T, d f2 = f1 . grad_corr (per crop). */
+ * including the 1/sqrt(c) scale and the 2x2-mean adjoints.  scflow_corr_pyramid_bwd finishes the job. */
 int scflow_corr_fold_bwd(const float* const* grad_levels, int num_levels, float* grad_corr, int n,
                          int c, int h, int w, void* stream);
+
+/* Second half: the two batched GEMMs autograd runs behind `torch.matmul(feat1^T, feat2)`
+ * (raft_decoder.py:53), d f1[c][q] = sum_t f2[c][t] G[q][t] and d f2[c][t] = sum_q f1[c][q] G[q][t], as one
+ * tcgen05 kind::tf32 launch.  grad_corr (n, P, P) from scflow_corr_fold_bwd; feat1/feat2/grad_f1/grad_f2
+ * (n, c, h, w) fp32 planar; either gradient pointer may be NULL (not wanted).  precision as in the forward:
+ * SCFLOW_PREC_TF32 runs on the tensor cores when c % 128 == 0, h*w % 256 == 0 and all pointers are 32-byte
+ * aligned (the shipped shapes); SCFLOW_PREC_FP32 and every other shape run the fp32 FMA kernel. */
+int scflow_corr_pyramid_bwd(const float* grad_corr, const float* feat1, const float* feat2, float* grad_f1,
+                            float* grad_f2, int n, int c, int h, int w, int precision, void* stream);
 
 /* Adjoint of scflow_upsample_fwd: grad_in (n, c, h, w) = mul * resize^T(grad_out (n, c, h*scale,
  * w*scale)); the gradient is the same for `in` and `add`. */

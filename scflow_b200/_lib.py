@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libscflow_b200.so")
 
 _P = c_void_p
-ABI_VERSION = 6
+ABI_VERSION = 7
 # name -> (restype, argtypes); mirrors include/scflow_b200.h one to one
 SIGNATURES = {
     "scflow_abi_version": (c_int, []),
@@ -56,6 +56,7 @@ SIGNATURES = {
     "scflow_split_bf16": (c_int, [_P, ctypes.c_longlong, _P, ctypes.c_longlong, c_int, c_int, ctypes.c_longlong, _P]),
     "scflow_corr_lookup_bwd": (c_int, [_P, c_int, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_corr_fold_bwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, _P]),
+    "scflow_corr_pyramid_bwd": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_upsample_bwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, c_float, _P]),
     "scflow_pose_flow_bwd": (c_int, [_P] * 8 + [c_int, c_int, c_int, _P]),
 }

@@ -33,6 +33,7 @@ class CorrPyramidFn(torch.autograd.Function):
         levels = ops.corr_pyramid(feat1, feat2, num_levels, precision)
         ctx.save_for_backward(feat1, feat2)
         ctx.num_levels = num_levels
+        ctx.precision = precision
         return tuple(levels)
 
     @staticmethod
@@ -48,13 +49,8 @@ class CorrPyramidFn(torch.autograd.Function):
         with _timed("scflow_corr_fold_bwd", 1, 4 * n * P * P * 2):
             rc = lib.scflow_corr_fold_bwd(_ptr_array(gs), ctx.num_levels, _ptr(gcorr), n, c, h, w, _stream())
         _lib.check(rc, "scflow_corr_fold_bwd")
-        f1 = feat1.reshape(n, c, P).float()
-        f2 = feat2.reshape(n, c, P).float()
-        g1 = g2 = None
-        if ctx.needs_input_grad[0]:      # corr[q,t] = sum_c f1[c,q] f2[c,t]  ->  d f1 = f2 . G^T
-            g1 = torch.bmm(f2, gcorr.transpose(1, 2)).reshape(feat1.shape)
-        if ctx.needs_input_grad[1]:      #                                        d f2 = f1 . G
-            g2 = torch.bmm(f1, gcorr).reshape(feat2.shape)
+        g1, g2 = ops.corr_pyramid_bwd(gcorr, feat1, feat2, ctx.needs_input_grad[0], ctx.needs_input_grad[1],
+                                      ctx.precision)
         return g1, g2, None, None
 
 

@@ -15,7 +15,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libscflow_b200.so")
 STAMP = os.path.join(HERE, "csrc", ".build_stamp")
-SOURCES = ["abi.cu", "corr_lookup.cu", "corr_lookup_nhwc.cu", "corr_lookup_v2.cu", "pose_flow.cu", "corr_pyramid.cu", "pack.cu", "norm_act.cu", "backward.cu", "small_conv.cu", "pose_head.cu", "conv_tc.cu", "render.cu"]
+SOURCES = ["abi.cu", "corr_lookup.cu", "corr_lookup_nhwc.cu", "corr_lookup_v2.cu", "pose_flow.cu", "corr_pyramid.cu", "pack.cu", "norm_act.cu", "backward.cu", "small_conv.cu", "pose_head.cu", "conv_tc.cu", "render.cu", "corr_bwd.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--cudart", "static"]
 

@@ -126,6 +126,30 @@ def corr_pyramid(feat1: torch.Tensor, feat2: torch.Tensor, num_levels: int = 4,
 LAYOUT_NCHW, LAYOUT_NHWC, LAYOUT_NHWC_GEN1, LAYOUT_NHWC_SPLIT = 0, 1, 2, 3
 
 
+def corr_pyramid_bwd(grad_corr: torch.Tensor, feat1: torch.Tensor, feat2: torch.Tensor, want1: bool = True,
+                     want2: bool = True, precision: int = PREC_TF32):
+    """The two GEMMs behind the backward of `torch.matmul(feat1^T, feat2)` (raft_decoder.py:53):
+    grad_corr (n, P, P) = d loss / d (f1^T f2) -> (d feat1, d feat2), one `scflow_corr_pyramid_bwd` launch
+    (tcgen05 kind::tf32 at the shipped shapes; fp32 FMA for PREC_FP32).  corr[q,t] = sum_c f1[c,q] f2[c,t], so
+    d f1 = f2 . G^T and d f2 = f1 . G."""
+    lib = _lib.load()
+    f1, f2, g = _chk(feat1, "feat1"), _chk(feat2, "feat2"), _chk(grad_corr, "grad_corr")
+    n, c, h, w = f1.shape
+    P = h * w
+    if tuple(g.shape) != (n, P, P) or f2.shape != f1.shape:
+        raise _lib.ScflowError(f"corr_pyramid_bwd: grad_corr {tuple(g.shape)} vs features {tuple(f1.shape)}")
+    g1 = torch.empty_like(f1) if want1 else None
+    g2 = torch.empty_like(f2) if want2 else None
+    if g1 is None and g2 is None:
+        return None, None
+    nprod = (g1 is not None) + (g2 is not None)
+    with _timed("scflow_corr_pyramid_bwd", 1, 4 * n * (P * P + 2 * c * P) * nprod):
+        rc = lib.scflow_corr_pyramid_bwd(_ptr(g), _ptr(f1), _ptr(f2), _ptr(g1), _ptr(g2), n, c, h, w, precision,
+                                         _stream())
+    _lib.check(rc, "scflow_corr_pyramid_bwd")
+    return g1, g2
+
+
 def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int = 4,
                 div_mode: int = DIV_IEEE, return_windows: bool = False, channels_last: bool = True,
                 gen1: bool = False, split: bool = False):

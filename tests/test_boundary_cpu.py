@@ -33,7 +33,7 @@ def test_header_symbols_exported(lib):
 
 
 def test_abi_version_and_strerror(lib):
-    assert lib.scflow_abi_version() == _lib.ABI_VERSION == 6
+    assert lib.scflow_abi_version() == _lib.ABI_VERSION == 7
     assert lib.scflow_strerror(0) == b"ok"
     assert b"not implemented" in lib.scflow_strerror(-2)
 

@@ -76,6 +76,26 @@ def test_corr_pyramid_backward_vs_oracle(prec, tol, n, c, h, w):
     assert rel(d2.grad, f2.grad) < tol
 
 
+@pytest.mark.parametrize("prec,tol", [(ops.PREC_FP32, 2e-6), (ops.PREC_TF32, 2e-3)])
+@pytest.mark.parametrize("n,c,h,w", [(3, 256, 32, 32), (2, 128, 16, 32), (2, 96, 8, 12)])
+def test_corr_pyramid_bwd_gemms_vs_fp64(prec, tol, n, c, h, w):
+    """scflow_corr_pyramid_bwd alone against the fp64 contraction; (3, 256, 32, 32) and (2, 128, 16, 32) are on the
+    tcgen05 tiling in TF32 mode, (2, 96, 8, 12) is a ragged shape on the fp32 kernel in both modes."""
+    g = torch.Generator().manual_seed(21)
+    P = h * w
+    f1 = torch.randn(n, c, h, w, generator=g)
+    f2 = torch.randn(n, c, h, w, generator=g)
+    G = torch.randn(n, P, P, generator=g)
+    e1 = torch.einsum("nct,nqt->ncq", f2.double().reshape(n, c, P), G.double()).reshape(n, c, h, w)
+    e2 = torch.einsum("ncq,nqt->nct", f1.double().reshape(n, c, P), G.double()).reshape(n, c, h, w)
+    g1, g2 = ops.corr_pyramid_bwd(G.to(DEV), f1.to(DEV), f2.to(DEV), True, True, prec)
+    assert rel(g1, e1.float()) < tol and rel(g2, e2.float()) < tol
+    only1, none2 = ops.corr_pyramid_bwd(G.to(DEV), f1.to(DEV), f2.to(DEV), True, False, prec)
+    assert none2 is None and torch.equal(only1, g1)
+    none1, only2 = ops.corr_pyramid_bwd(G.to(DEV), f1.to(DEV), f2.to(DEV), False, True, prec)
+    assert none1 is None and torch.equal(only2, g2)
+
+
 def test_corr_pyramid_backward_partial_levels():
     """Levels that received no gradient (None) are skipped, as autograd would."""
     ft = syn.make_features(1, 8, 32, seed=4, c=32, hc=4)
