@@ -12,6 +12,7 @@
 // All HBM-bound.  Every query / crop owns its output exclusively, so no kernel here needs global
 // atomics except the 12-value-per-crop reduction of pose_flow_bwd.
 #include "common.cuh"
+#include <cstddef>
 
 namespace scflow {
 namespace bw {
@@ -114,6 +115,187 @@ corr_lookup_bwd_kernel(const LookupBwdParams p) {
   }
 }
 
+
+// ---- shipped shapes (w % 32 == 0, h % 8 == 0): no atomics, no whole-plane staging ------------------------------
+// fp32 shared-memory atomicAdd compiles to a compare-and-swap loop (ATOMS.CAST.SPIN), and that loop was the
+// kernel above.  The gradient of a query on a level is nonzero only inside the window the forward read, and it is
+// separable there: tap (a, b) adds g[a][b] wx(a, X) wy(b, Y) to its 2 x 2 cells, so
+//     T[a][Y] = sum_b g[a][b] wy(b, Y)       G[Y][X] = sum_a T[a][Y] wx(a, X)
+// with every output owned by one lane.  x0(a) and the weights come from the forward's exact op sequence per tap;
+// relative to tap 0, x0(a) = x0(0) + a + e with e in {-1, 0, 1} (floors next to integer coordinates, e.g. at
+// flow = 0, are irregular by an ulp), so tap a can only reach the cells x0(0) + a - 1 .. x0(0) + a + 2 and a cell
+// only the taps a - 2 .. a + 1: four products per output, whatever the floors did.  The 1-D weights are stored
+// skewed (us[k][cell] = weight of tap cell + 1 - k) in plane-aligned columns, the window (12 rows x 16 columns)
+// starts on a 16-byte chunk of the plane and is written straight to global memory over a zero fill of the four
+// planes (the overwrite contract; __syncwarp orders the two stores of a warp).  A warp stages the gradients of four
+// consecutive queries through shared memory (16 bytes per channel row of a planar gradient) on its own.
+constexpr int kWQ = 4, kGP = kLevels * kTaps + 5, kGuard = 4, kWinWarps = 8;   // 5 zero pads per query, 4 in front:
+                                                                                 // phase B reads up to 3 taps outside a row
+struct WinScratch {
+  float usx[kLevels][4][16];    // x weights, skewed: [k][column of the window]
+  float usy[kLevels][4][12];    // y weights: [k][row of the window]
+  float t[kLevels][kD][12];     // T[a][row]
+  int xb[kLevels], yb[kLevels], xoff[kLevels], pad[4];
+};
+static_assert(sizeof(WinScratch) % 16 == 0 && offsetof(WinScratch, usy) % 16 == 0 && offsetof(WinScratch, t) % 16 == 0,
+              "scratch rows are read as float4");
+struct WinWarp {
+  float guard[kGuard];
+  float g[kWQ * kGP];           // the gradients of the warp's queries, [query][324 + 5 zero pads]
+  WinScratch sc;
+};
+static_assert(sizeof(WinWarp) % 16 == 0 && offsetof(WinWarp, sc) % 16 == 0, "scratch alignment");
+constexpr size_t kWinSmem = kWinWarps * sizeof(WinWarp);
+
+struct WinParams {
+  const float* grad_out;
+  const float* flow;
+  float* grad_lvl[kLevels];
+  int n, h, w, div_mode, nhwc;
+  int chunks[kLevels];          // float4 chunks per level plane
+  float rcp[2][kLevels];        // 1 / max(size - 1, 1) per axis and level (SCFLOW_DIV_RCP)
+  int ctask[kLevels + 1];       // phase C: prefix sums of min(48 window chunks, plane chunks)
+  float inv_wl4[kLevels];       // 1 / (chunks per plane row)
+};
+
+__device__ __forceinline__ float pick4(const float4& v, int t) { return t == 0 ? v.x : t == 1 ? v.y : t == 2 ? v.z : v.w; }
+
+__global__ void __launch_bounds__(kWinWarps * 32, 3)
+corr_lookup_bwd_win_kernel(const WinParams p) {
+  extern __shared__ float4 smem4[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  WinWarp& ws = reinterpret_cast<WinWarp*>(smem4)[warp];
+  WinScratch& sc = ws.sc;
+  float* gt = ws.g;
+  constexpr int C = kLevels * kTaps;
+  if (lane < 4) ws.guard[lane] = 0.f;
+  for (int i = lane; i < kWQ * (kGP - C); i += 32) gt[(i / (kGP - C)) * kGP + C + i % (kGP - C)] = 0.f;
+  const int P = p.h * p.w;
+  const long long wtiles = ((long long)p.n * P) / kWQ;
+  // a warp owns kWQ consecutive queries at a time: it stages their gradients itself (no block-wide barrier, so
+  // the warps of an SM drift apart and one warp's loads overlap another's arithmetic)
+  for (long long wt = (long long)blockIdx.x * kWinWarps + warp; wt < wtiles; wt += (long long)gridDim.x * kWinWarps) {
+    const long long q0 = wt * kWQ;
+    const int n = (int)(q0 / P), qin0 = (int)(q0 - (long long)n * P);
+    __syncwarp();
+    float fl = 0.f;                                 // lanes 0..3: fx of the four queries, 4..7: fy
+    if (lane < 2 * kWQ) fl = __ldg(p.flow + ((long long)n * 2 + (lane >> 2)) * P + qin0 + (lane & 3));
+    if (p.nhwc) {                                   // 4 x 324 contiguous floats
+      const float4* src = reinterpret_cast<const float4*>(p.grad_out + q0 * C);
+#pragma unroll 4
+      for (int i = lane; i < kWQ * C / 4; i += 32) {
+        const float4 v = __ldg(src + i);
+        const int q = (4 * i) / C, ch = 4 * i - q * C;       // 324 % 4 == 0: a chunk never straddles two queries
+        float* d = gt + q * kGP + ch;
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+      }
+    } else {                                        // 324 rows, 4 consecutive queries (16 bytes) of each
+      const float* src = p.grad_out + (long long)n * C * P + qin0;
+#pragma unroll 4
+      for (int ch = lane; ch < C; ch += 32) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(src + (long long)ch * P));
+        gt[ch] = v.x; gt[kGP + ch] = v.y; gt[2 * kGP + ch] = v.z; gt[3 * kGP + ch] = v.w;
+      }
+    }
+    __syncwarp();
+#pragma unroll 1
+    for (int qi = 0; qi < kWQ; ++qi) {
+      const int qin = qin0 + qi;
+      const long long q = q0 + qi;
+      const int y = qin / p.w, x = qin - y * p.w;
+      const float fx = __shfl_sync(0xffffffffu, fl, qi), fy = __shfl_sync(0xffffffffu, fl, kWQ + qi);
+      const float* g = gt + qi * kGP;
+      // zeros: the weight tables of this query and the four planes
+      {
+        float4* z = reinterpret_cast<float4*>(sc.usx);
+        for (int i = lane; i < (int)(offsetof(WinScratch, t) / 16); i += 32) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int l = 0; l < kLevels; ++l) {
+        float4* dst = reinterpret_cast<float4*>(p.grad_lvl[l] + q * (long long)((p.h >> l) * (p.w >> l)));
+        for (int c = lane; c < p.chunks[l]; c += 32) dst[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      __syncwarp();
+      // A: one (level, axis, tap) per lane, three 9-lane groups per round: the tap's cell and weights by the forward's
+      //    op sequence, placed into the skewed tables; tap 0 (shuffled across its group) fixes the window origin
+#pragma unroll
+      for (int rnd = 0; rnd < 3; ++rnd) {
+        const int sub = lane / kD, idx = lane - sub * kD;
+        const int grp = min(rnd * 3 + sub, kLevels * 2 - 1), l = grp >> 1, dir = grp & 1;
+        const bool live = lane < 3 * kD && rnd * 3 + sub < kLevels * 2;
+        const float scl = 1.0f / (float)(1 << l);
+        const int size = (dir ? p.h : p.w) >> l;
+        const float centre = __fmul_rn(__fadd_rn(dir ? (float)y : (float)x, dir ? fy : fx), scl);
+        const float ic = unnorm_coord(centre, idx - kR, (float)max(size - 1, 1), p.rcp[dir][l], (float)(size - 1), p.div_mode);
+        const float c0f = floorf(ic);
+        const int c0 = floor_clamped(ic, -32, size + 32);
+        const int d0 = __shfl_sync(0xffffffffu, c0, lane - idx);
+        const float w1 = __fsub_rn(ic, c0f), w0 = __fsub_rn(__fadd_rn(c0f, 1.0f), ic);
+        const int base = dir ? d0 - 1 : ((d0 - 1) >> 2) << 2;   // first row / first (chunk-aligned) column
+        const int off = d0 - base;                              // 1 (rows), 1..4 (columns)
+        const int e = c0 - d0 - idx;                            // -1, 0, 1 for every tap that can touch the plane
+        const int k0 = e + 1, pos = idx - 1 + off;              // us[k][pos + k] belongs to tap idx
+        float* tab = dir ? &sc.usy[l][0][0] : &sc.usx[l][0][0];
+        const int pitch = dir ? 12 : 16;
+        if (live && k0 >= 0 && k0 <= 3) tab[k0 * pitch + pos + k0] = w0;
+        if (live && k0 + 1 >= 0 && k0 + 1 <= 3) tab[(k0 + 1) * pitch + pos + k0 + 1] = w1;
+        if (live && idx == 0) {
+          if (dir) sc.yb[l] = base; else { sc.xb[l] = base; sc.xoff[l] = off; }
+        }
+      }
+      __syncwarp();
+      // B: T[l][a][r] = sum_k g[l][a][r - k] usy[l][k][r]     (r = window row; 108 tasks of 4 rows)
+#pragma unroll
+      for (int task = lane; task < kLevels * kD * 3; task += 32) {
+        const int l = task / (kD * 3), r = task - l * kD * 3, a = r / 3, rg = r - a * 3;
+        const float* gp = g + l * kTaps + a * kD;
+        float gv[7];
+#pragma unroll
+        for (int m = 0; m < 7; ++m) gv[m] = gp[4 * rg - 3 + m];    // taps outside 0..8: a neighbour or a zero pad, weight 0
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float4 u = reinterpret_cast<const float4*>(sc.usy[l][k])[rg];
+          acc.x = fmaf(gv[3 - k], u.x, acc.x); acc.y = fmaf(gv[4 - k], u.y, acc.y);
+          acc.z = fmaf(gv[5 - k], u.z, acc.z); acc.w = fmaf(gv[6 - k], u.w, acc.w);
+        }
+        reinterpret_cast<float4*>(sc.t[l][a])[rg] = acc;
+      }
+      __syncwarp();
+      // C: G[l][r][col] = sum_k T[l][col - xoff + 1 - k][r] usx[l][k][col], one 16-byte chunk of the plane per task:
+      //    the 48 chunks of the window, or the chunks of the plane where the plane is the smaller of the two
+      for (int task = lane; task < p.ctask[kLevels]; task += 32) {
+        const int l = (task >= p.ctask[1]) + (task >= p.ctask[2]) + (task >= p.ctask[3]);
+        const int ci = task - p.ctask[l];
+        const int wl = p.w >> l, hl = p.h >> l;
+        int j, ch;
+        if (p.ctask[l + 1] - p.ctask[l] == 48) { j = ci >> 2; ch = ci & 3; }
+        else {
+          const int Yp = __float2int_rz(((float)ci + 0.5f) * p.inv_wl4[l]), Xp = (ci - Yp * (wl >> 2)) * 4;
+          j = Yp - sc.yb[l];
+          ch = (Xp - sc.xb[l]) >> 2;
+          if (j < 0 || j >= 12 || ch < 0 || ch >= 4) continue;
+        }
+        const int Y = sc.yb[l] + j, X4 = sc.xb[l] + 4 * ch;
+        if (Y < 0 || Y >= hl || X4 < 0 || X4 >= wl) continue;
+        const int a0 = 4 * ch - sc.xoff[l] - 2;                 // tap of (cell 0, k = 3)
+        float tv[7];
+#pragma unroll
+        for (int m = 0; m < 7; ++m) tv[m] = sc.t[l][min(max(a0 + m, 0), kD - 1)][j];
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float4 u = reinterpret_cast<const float4*>(sc.usx[l][k])[ch];
+          acc.x = fmaf(tv[3 - k], u.x, acc.x); acc.y = fmaf(tv[4 - k], u.y, acc.y);
+          acc.z = fmaf(tv[5 - k], u.z, acc.z); acc.w = fmaf(tv[6 - k], u.w, acc.w);
+        }
+        *reinterpret_cast<float4*>(p.grad_lvl[l] + q * (long long)(hl * wl) + Y * wl + X4) = acc;
+      }
+      __syncwarp();
+    }
+  }
+}
+
 }  // namespace bw
 }  // namespace scflow
 
@@ -126,6 +308,31 @@ extern "C" int scflow_corr_lookup_bwd(const float* grad_out, int grad_layout, co
   if (div_mode != SCFLOW_DIV_IEEE && div_mode != SCFLOW_DIV_RCP) return SCFLOW_E_UNSUPPORTED;
   if (grad_layout != SCFLOW_LAYOUT_NCHW && grad_layout != SCFLOW_LAYOUT_NHWC) return SCFLOW_E_UNSUPPORTED;
   if (n <= 0 || h < 8 || w < 8) return SCFLOW_E_BAD_SHAPE;
+  for (int l = 0; l < bw::kLevels; ++l) {
+    if (!grad_levels[l]) return SCFLOW_E_NULL;
+    if (!aligned16(grad_levels[l])) return SCFLOW_E_MISALIGNED;
+  }
+  if ((w % 32) == 0 && (h % 8) == 0 && aligned16(grad_out)) {
+    bw::WinParams wp;
+    wp.grad_out = grad_out; wp.flow = flow;
+    wp.n = n; wp.h = h; wp.w = w; wp.div_mode = div_mode;
+    wp.nhwc = grad_layout == SCFLOW_LAYOUT_NHWC;
+    wp.ctask[0] = 0;
+    for (int l = 0; l < bw::kLevels; ++l) {
+      wp.grad_lvl[l] = grad_levels[l];
+      wp.chunks[l] = ((h >> l) * (w >> l)) / 4;
+      wp.rcp[0][l] = 1.0f / (float)((w >> l) - 1 > 1 ? (w >> l) - 1 : 1);
+      wp.rcp[1][l] = 1.0f / (float)((h >> l) - 1 > 1 ? (h >> l) - 1 : 1);
+      wp.ctask[l + 1] = wp.ctask[l] + (wp.chunks[l] < 48 ? wp.chunks[l] : 48);
+      wp.inv_wl4[l] = 1.0f / (float)((w >> l) >> 2);
+    }
+    cudaFuncSetAttribute(bw::corr_lookup_bwd_win_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)bw::kWinSmem);
+    const long long tiles = ((long long)n * h * w / bw::kWQ + bw::kWinWarps - 1) / bw::kWinWarps;
+    const long long blocks = tiles < 3 * 148 ? tiles : 3 * 148;
+    bw::corr_lookup_bwd_win_kernel<<<(unsigned)blocks, bw::kWinWarps * 32, bw::kWinSmem, (cudaStream_t)stream>>>(wp);
+    return check_launch();
+  }
   bw::LookupBwdParams p;
   p.grad_out = grad_out; p.flow = flow;
   p.n = n; p.h = h; p.w = w; p.div_mode = div_mode;
@@ -134,8 +341,6 @@ extern "C" int scflow_corr_lookup_bwd(const float* grad_out, int grad_layout, co
   p.gs_c = grad_layout == SCFLOW_LAYOUT_NHWC ? 1 : P;
   int off = 0;
   for (int l = 0; l < bw::kLevels; ++l) {
-    if (!grad_levels[l]) return SCFLOW_E_NULL;
-    if (!aligned16(grad_levels[l])) return SCFLOW_E_MISALIGNED;
     p.grad_lvl[l] = grad_levels[l];
     p.plane_off[l] = off;
     off += (((h >> l) * (w >> l)) + 3) & ~3;      // 16-byte aligned planes in the staging area

@@ -36,7 +36,7 @@ def _strict_fp32():
 
 
 @pytest.mark.parametrize("channels_last_grad", [False, True])
-@pytest.mark.parametrize("n,h,w", [(2, 8, 16), (1, 32, 32), (3, 8, 8), (1, 64, 64)])
+@pytest.mark.parametrize("n,h,w", [(2, 8, 16), (1, 32, 32), (3, 8, 8), (1, 64, 64), (3, 16, 32)])
 def test_lookup_backward_vs_oracle(n, h, w, channels_last_grad):
     ft = syn.make_features(n, h, w, seed=11, c=16, hc=4)
     flow = lookup_flow(n, h, w, 12)
