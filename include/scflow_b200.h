@@ -50,6 +50,7 @@ enum {
 #define SCFLOW_CONV_PATCH_PAIR 3
 
 /* correlation arithmetic */
+#define SCFLOW_STATS_REPLICAS 8 /* accumulators per (image, channel) of scflow_conv_tc_desc.stats */
 #define SCFLOW_PREC_FP32 0      /* CUDA-core fp32 FMA (exact-mode parity anchor)          */
 #define SCFLOW_PREC_TF32 1      /* tcgen05 kind::tf32, fp32 accumulate in TMEM (default)  */
 
@@ -302,7 +303,9 @@ typedef struct scflow_conv_tc_desc {
   float* out_f32; long long outf_pitch; int f32_tf32;      /* f32_tf32: round to the nearest TF32 */
   float* out_planar; int planar_tf32;
   /* optional: per-(image, channel) sum and sum of squares of the value BEFORE residual/ReLU
-   * (after bias), added into stats[n][cout8][2] (zeroed by the caller) -- InstanceNorm statistics */
+   * (after bias), added into stats[n][SCFLOW_STATS_REPLICAS][cout8][2] (zeroed by the caller) -- InstanceNorm
+   * statistics; the replicas (picked per warp and tile) keep the fp64 atomics of one image from serialising
+   * on a handful of L2 lines, their sum is the statistic */
   double* stats;
   /* tile width override: output channels per tile (multiple of 16 that divides the padded cout), 0 = the
    * widest tile (<= 256).  Narrower tiles trade operand re-reads for fuller waves. */
@@ -360,7 +363,7 @@ int scflow_split_planar(const float* in, void* out, long long out_pitch, int out
                         long long pixels, void* stream);
 
 /* InstanceNorm2d (+ residual) + ReLU of a raw convolution output (n, P, C) fp32 from the statistics
- * scflow_conv_tc_fwd accumulated (sums[n][C][2]), written as split planes for the next convolution
+ * scflow_conv_tc_fwd accumulated (sums[n][SCFLOW_STATS_REPLICAS][C][2], C <= 256), written as split planes for the next convolution
  * (models/backbone/resnet.py:64-92): y = act((x - mean) rstd + r), r = nothing | res_split (split planes,
  * final values) | (res_raw - rmean) rrstd (the down-sampling branch: raw fp32 + its own statistics).
  * Biased variance, as F.instance_norm.  out_f32 (n, P, C), optional: the same values in fp32. */

@@ -42,6 +42,7 @@ class _Desc(ctypes.Structure):
 
 EPI_PLAIN, EPI_GRU_ZR, EPI_GRU_GATE = 0, 1, 2
 # scflow_conv_tc_desc.algo: operand movement (include/scflow_b200.h)
+STATS_REPLICAS = 8          # SCFLOW_STATS_REPLICAS: accumulators per (image, channel) of the conv epilogue statistics
 ALGO_AUTO, ALGO_TAP_BOXES, ALGO_PATCH, ALGO_PATCH_PAIR = 0, 1, 2, 3
 
 
@@ -265,7 +266,7 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
         assert out_planar.shape == (n, c8, oh, ow) and out_planar.is_contiguous()
         d.out_planar, d.planar_tf32 = out_planar.data_ptr(), int(planar_tf32)
     if stats is not None:
-        assert stats.dtype == torch.float64 and stats.shape == (n, c8, 2) and stats.is_contiguous()
+        assert stats.dtype == torch.float64 and stats.shape == (n, STATS_REPLICAS, c8, 2) and stats.is_contiguous()
         d.stats = stats.data_ptr()
     cin = cin + cin2
     flops = 2 * n * oh * ow * pk.cout * pk.cin * pk.kh * pk.kw
@@ -330,7 +331,7 @@ def norm_apply(x: torch.Tensor, sums: torch.Tensor, *, relu: bool = True, eps: f
     conv epilogue -> split planes (scflow_norm_apply_split)."""
     lib = _lib.load()
     n, h, w, c = x.shape
-    assert x.is_contiguous() and sums.shape == (n, c, 2) and sums.dtype == torch.float64
+    assert x.is_contiguous() and sums.shape == (n, STATS_REPLICAS, c, 2) and sums.dtype == torch.float64
     if out is None:
         out = alloc_split(n, h, w, c, x.device)
     with _timed("scflow_norm_apply_split", 1, (8 + (4 if res is not None or res_raw is not None else 0)) * x.numel()):

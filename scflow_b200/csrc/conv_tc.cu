@@ -284,7 +284,11 @@ __device__ __forceinline__ void epilogue_plain(const Params& p, const Tile& tl, 
       // lane i now holds channel bitrev-free index: after the halving steps element 0 of lane l is channel l
       const int nw = __shfl_sync(0xffffffffu, n, 0);
       if (lane < nv && nw < p.n) {
-        double* dst = p.stats + ((long long)nw * p.cout_store + c0 + lane) * 2;
+        // SCFLOW_STATS_REPLICAS accumulators per (image, channel): the CTAs of a wave work on one or two images, and
+        // 512 same-address fp64 atomics per tile serialise in L2 (E1 at 256x256: 476 -> 37x us); the replica is
+        // picked by the warp's TMEM quarter and the tile's parity, norm_apply adds them up
+        const int rep = ((threadIdx.x >> 5) & 3) + 4 * (((tl.ox0 >> 3) ^ (tl.oy0 >> 4)) & 1);
+        double* dst = p.stats + (((long long)nw * SCFLOW_STATS_REPLICAS + rep) * p.cout_store + c0 + lane) * 2;
         atomicAdd(dst, (double)s[0]);
         atomicAdd(dst + 1, (double)q[0]);
       }
@@ -914,17 +918,22 @@ struct ApplyParams {
 };
 constexpr int kApplyThreads = 256;
 constexpr int kApplyChunk = 256;     // pixels per CTA
+constexpr int kApplyMaxC = 256;
 
-__device__ __forceinline__ void in_coeffs(const double* sums, int n, int C, int c, int P, float eps, float* sc,
-                                          float* sh) {
+// scale / shift of InstanceNorm for the channels of image n, once per CTA: thread c adds the replicas up
+__device__ __forceinline__ void in_coeffs(const double* sums, int n, int C, int P, float eps, float* sc, float* sh) {
+  for (int c = threadIdx.x; c < C; c += kApplyThreads) {
+    double su = 0.0, sq = 0.0;
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const double su = sums[((size_t)n * C + c + j) * 2], sq = sums[((size_t)n * C + c + j) * 2 + 1];
+    for (int r = 0; r < SCFLOW_STATS_REPLICAS; ++r) {
+      const double2 v = *reinterpret_cast<const double2*>(sums + (((size_t)n * SCFLOW_STATS_REPLICAS + r) * C + c) * 2);
+      su += v.x; sq += v.y;
+    }
     const double mean = su / P;
     const double var = fmax(sq / P - mean * mean, 0.0);       // biased, as F.instance_norm
     const float rstd = 1.0f / sqrtf((float)var + eps);
-    sc[j] = rstd;
-    sh[j] = -(float)mean * rstd;
+    sc[c] = rstd;
+    sh[c] = -(float)mean * rstd;
   }
 }
 
@@ -933,13 +942,20 @@ norm_apply_split_kernel(const ApplyParams p) {
   const int groups = p.C >> 3;
   const int lanes = kApplyThreads / groups;
   const int cg = threadIdx.x % groups, pl = threadIdx.x / groups;
-  if (pl >= lanes) return;
   const int n = blockIdx.y;
+  __shared__ float coef[4][kApplyMaxC];
+  in_coeffs(p.sums, n, p.C, p.P, p.eps, coef[0], coef[1]);
+  if (p.res_raw) in_coeffs(p.res_sums, n, p.C, p.P, p.eps, coef[2], coef[3]);
+  __syncthreads();
+  if (pl >= lanes) return;
   const int p0 = blockIdx.x * kApplyChunk, p1 = min(p0 + kApplyChunk, p.P);
   const int c = 8 * cg;
   float sc[8], sh[8], rsc[8], rsh[8];
-  in_coeffs(p.sums, n, p.C, c, p.P, p.eps, sc, sh);
-  if (p.res_raw) in_coeffs(p.res_sums, n, p.C, c, p.P, p.eps, rsc, rsh);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = coef[0][c + j]; sh[j] = coef[1][c + j];
+    if (p.res_raw) { rsc[j] = coef[2][c + j]; rsh[j] = coef[3][c + j]; }
+  }
   // two pixels per thread and iteration, every load issued before the first use (two CTAs per SM): with one
   // pixel a thread had 32-64 bytes in flight and the pass sat at 0.65 of the HBM peak
   constexpr int U = 2;
@@ -1203,8 +1219,8 @@ extern "C" int scflow_norm_apply_split(const float* x, const double* sums, const
   using namespace scflow::ctc;
   if (!x || !sums || !out) return SCFLOW_E_NULL;
   if ((res_raw == nullptr) != (res_sums == nullptr)) return SCFLOW_E_NULL;
-  if (n <= 0 || P <= 0 || C < 8 || (C & 7) || (C >> 3) > kApplyThreads || n > 65535) return SCFLOW_E_BAD_SHAPE;
-  if (!aligned16(x) || !aligned16(out) || !aligned16(res_split) || !aligned16(res_raw) || !aligned16(out_f32) ||
+  if (n <= 0 || P <= 0 || C < 8 || (C & 7) || C > kApplyMaxC || n > 65535) return SCFLOW_E_BAD_SHAPE;
+  if (!aligned16(x) || !aligned16(out) || !aligned16(sums) || !aligned16(res_sums) || !aligned16(res_split) || !aligned16(res_raw) || !aligned16(out_f32) ||
       (out_pitch % 8) || (out_lo % 8) || (res_split && ((res_pitch % 8) || (res_lo % 8))))
     return SCFLOW_E_MISALIGNED;
   ApplyParams p{x, sums, static_cast<const __nv_bfloat16*>(res_split), res_pitch, res_lo, res_raw, res_sums,

@@ -98,9 +98,11 @@ pose_tail_kernel(const TailParams p) {
     a1[k] = fmaxf(s, 0.0f);
   }
   __syncthreads();
+  // An out-of-range class makes the reference's index_select raise (a device assert on CUDA).  No host
+  // synchronisation here: the pose of such a batch comes back as NaN instead of a silently clamped class.
   long long cls = p.label[0];
-  if (cls < 0) cls = 0;
-  if (cls >= p.num_class) cls = p.num_class - 1;
+  const bool bad_class = cls < 0 || cls >= p.num_class;
+  if (bad_class) cls = 0;
   if (warp < 9) {
     const int o = warp;
     const bool rot = o < 6;
@@ -110,6 +112,7 @@ pose_tail_kernel(const TailParams p) {
     for (int k = lane; k < p.n1; k += 32) s = fmaf(__ldg(wrow + k), a1[k], s);
     s = warp_sum(s);
     if (lane == 0) {
+      if (bad_class) s = __int_as_float(0x7fc00000);
       if (rot) p.dr[m * 6 + o] = s + __ldg(p.br + row);
       else p.dt[m * 3 + (o - 6)] = s + __ldg(p.bt + row);
     }

@@ -83,8 +83,8 @@ class _Stats:
         self.n, self.used = n, 0
 
     def take(self, c: int) -> torch.Tensor:
-        k = self.n * c * 2
-        out = self.buf[self.used:self.used + k].view(self.n, c, 2)
+        k = self.n * C.STATS_REPLICAS * c * 2
+        out = self.buf[self.used:self.used + k].view(self.n, C.STATS_REPLICAS, c, 2)
         self.used += k
         assert self.used <= self.buf.numel()
         return out
@@ -211,7 +211,7 @@ class RAFTEncoder(nn.Module):
             y = C.conv(xs, _stem_pack(self.conv1, n1), relu=True, view=view)
         else:
             _plain_in(n1)
-            st = _Stats(n, x.device, n * 2 * (64 * 5 + 96 * 5 + 128 * 5))
+            st = _Stats(n, x.device, n * C.STATS_REPLICAS * 2 * (64 * 5 + 96 * 5 + 128 * 5))
             raw, sums = _conv_raw(xs, self.conv1, st, view=view, pk=_stem_pack(self.conv1))
             y = C.norm_apply(raw, sums, relu=True, eps=n1.eps)
         if taps is not None:

@@ -1,6 +1,6 @@
-"""Registry seam (reference registry.py:17): when the reference tree (and mmengine) is importable
-the modules register into ITS ``MODELS`` so ``MODELS.build(cfg.model)`` picks them up unchanged;
-otherwise a dict-backed stand-in with the same two calls is used."""
+"""Registry seam (reference registry.py:17).  The package keeps its own dict-backed registry with the same two calls
+(`register_module`, `build`); `install()` is the explicit, opt-in step that overrides the reference's classes in the
+reference's own ``MODELS``."""
 from __future__ import annotations
 
 
@@ -28,18 +28,29 @@ class _LocalRegistry:
         return cls(**cfg)
 
 
-try:  # pragma: no cover - only inside the reference's environment
-    from registry import MODELS as _REF_MODELS  # type: ignore
-    MODELS = _REF_MODELS
-    USING_REFERENCE_REGISTRY = True
-except Exception:
-    MODELS = _LocalRegistry("model")
-    USING_REFERENCE_REGISTRY = False
+MODELS = _LocalRegistry("model")
+_CLASSES = []
 
 
 def register(cls):
-    """Register under the reference's class name, replacing the reference class if present."""
-    try:
-        return MODELS.register_module(force=True)(cls)
-    except TypeError:
-        return MODELS.register_module()(cls)
+    """Register into scflow_b200's own registry (used by `MODELS.build(pose_head_cfg)` inside the decoder).
+    Nothing outside this package is touched at import time; see `install`."""
+    _CLASSES.append(cls)
+    return MODELS.register_module(force=True)(cls)
+
+
+def install(models_registry=None):
+    """Opt-in override inside the reference's environment: put SCFlowDecoder / MultiClassPoseHead / RAFTEncoder
+    into the reference's `registry.MODELS` (registry.py:17) under the reference's class names (force=True), so
+    `MODELS.build(cfg.model)` builds these instead.  Call it AFTER the reference's `models` package has been
+    imported and only for configs on the supported path (net_type='Basic', 6-D rotation, mask_corr=False ...):
+    the replaced classes raise on anything else, which is why importing scflow_b200 alone does not do this.
+    Returns the names it replaced."""
+    if models_registry is None:
+        from registry import MODELS as models_registry  # type: ignore  # the reference tree must be importable
+    for cls in _CLASSES:
+        try:
+            models_registry.register_module(force=True, module=cls)
+        except TypeError:                       # a registry without `module=`: decorator form
+            models_registry.register_module(force=True)(cls)
+    return [c.__name__ for c in _CLASSES]

@@ -74,6 +74,24 @@ def test_registry_builds_from_config_dict():
     assert dec2.pose_pred.fc_layers[0][0].in_features == 128 * 8 * 8
 
 
+def test_install_is_opt_in_and_overrides_a_foreign_registry():
+    """Importing the package registers nothing outside it; `install(registry)` replaces the three reference class
+    names in the registry it is given (the reference's `registry.MODELS`), force=True."""
+    class Foreign:
+        def __init__(self):
+            self.mods = {"SCFlowDecoder": object, "Other": int}
+        def register_module(self, name=None, force=False, module=None):
+            key = name or module.__name__
+            if key in self.mods and not force:
+                raise KeyError(key)
+            self.mods[key] = module
+            return module
+    reg = Foreign()
+    names = sb.install(reg)
+    assert set(names) >= {"SCFlowDecoder", "MultiClassPoseHead", "RAFTEncoder"}
+    assert reg.mods["SCFlowDecoder"] is sb.SCFlowDecoder and reg.mods["Other"] is int
+
+
 @pytest.mark.parametrize("over", [dict(net_type="Small"), dict(mask_corr=True), dict(mask_flow=True),
                                   dict(depth_transform="linear"), dict(gru_type="Conv"),
                                   dict(detach_flow=False)])

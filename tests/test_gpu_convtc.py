@@ -155,11 +155,13 @@ def test_conv_tc_outputs_residuals_stats():
     assert float(wide_f[..., :32].abs().max()) == 0 and float(wide_f[..., 32 + cout:].abs().max()) == 0
     assert _err(planar.permute(0, 2, 3, 1), want) < TOL
     # fp32 residual + InstanceNorm statistics of the pre-residual value
-    stats = torch.zeros(n, cout, 2, device=DEV, dtype=torch.float64)
+    stats = torch.zeros(n, C.STATS_REPLICAS, cout, 2, device=DEV, dtype=torch.float64)
     got = C.conv(xs, pk, relu=True, res_f32=r.to(DEV), stats=stats, want="f32")
     torch.cuda.synchronize()
     assert _err(got[..., :cout], want) < TOL
     pre = _ref(x, wt, b, 1, 1)
+    assert int((stats.abs().sum((0, 2, 3)) > 0).sum()) > 1          # the atomics are spread over the replicas
+    stats = stats.sum(1)
     assert _err(stats[:, :, 0], pre.sum((1, 2))) < 1e-5
     assert _err(stats[:, :, 1], (pre * pre).sum((1, 2))) < 1e-5
     # planar output rounded to TF32: low 13 mantissa bits are zero
@@ -224,7 +226,9 @@ def test_norm_apply_split_vs_torch():
     xd, rd = x.to(DEV), r.to(DEV)
     def sums(t):
         d = t.double()
-        return torch.stack([d.sum((1, 2)), (d * d).sum((1, 2))], -1).contiguous()
+        full = torch.stack([d.sum((1, 2)), (d * d).sum((1, 2))], -1)              # (n, c, 2)
+        part = torch.rand(C.STATS_REPLICAS, 1, 1, 1, device=t.device, dtype=torch.float64)
+        return (full[None] * part / part.sum()).permute(1, 0, 2, 3).contiguous()    # replicas that add up to it
     inorm = lambda t: F.instance_norm(t.double().permute(0, 3, 1, 2)).permute(0, 2, 3, 1)
     got = C.norm_apply(xd, sums(xd), relu=True).float()
     assert _err(got, torch.relu(inorm(x))) < 2e-5

@@ -583,6 +583,21 @@ def test_pose_head_fused_vs_module_path(n, feat):
     assert rel(dr, dr_w) < 1e-4 and rel(dt, dt_w) < 1e-4
 
 
+def test_pose_head_out_of_range_class_is_loud():
+    """pose_head.py:209-210: index_select raises on a class outside [0, num_class).  The kernel path cannot raise
+    without a host synchronisation; it returns NaN poses instead of silently clamping the class."""
+    from scflow_b200.pose_head import MultiClassPoseHead
+    head = MultiClassPoseHead(21, 224, "Basic", dict(type="GN", num_groups=32), dict(type="ReLU"),
+                              feat_size=(32, 32), rotation_mode="ortho6d").to(DEV).eval()
+    x = torch.randn(2, 224, 32, 32, device=DEV).contiguous(memory_format=torch.channels_last)
+    with torch.no_grad():
+        dr, dt = head(x, torch.tensor([3, 3], device=DEV))
+        assert torch.isfinite(dr).all() and torch.isfinite(dt).all()
+        for bad in (21, -1):
+            dr, dt = head(x, torch.tensor([bad, 3], device=DEV))
+            assert torch.isnan(dr).all() and torch.isnan(dt).all()
+
+
 @pytest.mark.parametrize("tag,s,seed", [("cfg1", 256, 63)])
 def test_refiner_has_one_precision_mode(golden_dir, tag, s, seed):
     """No cuDNN / cuBLAS call is left on the inference path: torch's TF32 switches (which moved round 1's

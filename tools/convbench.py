@@ -19,6 +19,7 @@ ap.add_argument("--only", default="")
 ap.add_argument("--once", action="store_true")
 ap.add_argument("--bn", type=int, default=0, help="output-channel tile width override (0: widest)")
 ap.add_argument("--algo", type=int, default=0, help="0 auto, 1 per-tap boxes, 2 patch, 3 patch on CTA pairs")
+ap.add_argument("--hw-scale", type=int, default=1, help="k: the same pixels as k x k larger images (cfg4 = 2), n / k^2 of them")
 a = ap.parse_args()
 dev = "cuda"
 N = a.n
@@ -30,6 +31,7 @@ if os.path.exists(p):
 # name, h, w, cin, cout, kh, kw, stride, pad_h, pad_w, out ("split" | "f32+stats" | "f32" | "planar"), calls per step
 SHAPES = [
     ("enc 3x3 64->64 @128 (IN raw+stats)", 128, 128, 64, 64, 3, 3, 1, 1, 1, "f32+stats", 8),
+    ("enc 3x3 64->64 @128 (no stats, f32)", 128, 128, 64, 64, 3, 3, 1, 1, 1, "f32", 0),
     ("enc 3x3 64->64 @128 (BN split)", 128, 128, 64, 64, 3, 3, 1, 1, 1, "split", 4),
     ("enc 3x3/2 64->96 @128->64", 128, 128, 64, 96, 3, 3, 2, 1, 1, "f32+stats", 3),
     ("enc 1x1/2 64->96 @128->64", 128, 128, 64, 96, 1, 1, 2, 0, 0, "f32+stats", 3),
@@ -72,6 +74,7 @@ total_us = 0.0
 for name, h, w, cin, cout, kh, kw, s, ph, pw, out, calls in SHAPES:
     if a.only and a.only not in name:
         continue
+    h, w, N = h * a.hw_scale, w * a.hw_scale, a.n // (a.hw_scale * a.hw_scale)
     wt = torch.randn(cout, cin, kh, kw, device=dev, generator=g) / (cin * kh * kw) ** 0.5
     b = torch.randn(cout, device=dev, generator=g)
     pk = C.pack_weights(wt, None if "stats" in out else b, s, (ph, pw))
@@ -97,7 +100,7 @@ for name, h, w, cin, cout, kh, kw, s, ph, pw, out, calls in SHAPES:
                             gru_h=torch.randn(N, oh, ow, 128, device=dev), gru_z=torch.rand(N, oh, ow, 128, device=dev)))
         else:
             kw_.append(dict(out_f32=torch.empty(N, oh, ow, c8, device=dev),
-                            stats=torch.zeros(N, c8, 2, device=dev, dtype=torch.float64)))
+                            stats=torch.zeros(N, C.STATS_REPLICAS, c8, 2, device=dev, dtype=torch.float64)))
     algo = a.algo if (s == 1 or a.algo <= 1) else 1
     if a.bn and cout % a.bn == 0 and cout > a.bn and "bn" not in kw_[0]:
         for k_ in kw_:
