@@ -50,6 +50,7 @@ enum {
 #define SCFLOW_CONV_PATCH_PAIR 3
 
 /* correlation arithmetic */
+#define SCFLOW_CONV_DOT_PITCH 20  /* floats per channel row of scflow_conv_tc_desc.dot_w: 3 x 3 taps x 2 outputs, padded */
 #define SCFLOW_STATS_REPLICAS 8 /* accumulators per (image, channel) of scflow_conv_tc_desc.stats */
 #define SCFLOW_PREC_FP32 0      /* CUDA-core fp32 FMA (exact-mode parity anchor)          */
 #define SCFLOW_PREC_TF32 1      /* tcgen05 kind::tf32, fp32 accumulate in TMEM (default)  */
@@ -332,12 +333,30 @@ typedef struct scflow_conv_tc_desc {
   const void* x2;
   int cin2;
   long long x2_lo_off, x2_stride_w, x2_stride_h, x2_stride_n;
+  /* optional projection output (ABI v7): dot_out[pixel][slot][k] = sum over the slot's channels c of
+   * y[pixel][c] dot_w[c][k], k < dot_n <= dot_pitch <= SCFLOW_CONV_DOT_PITCH (dot_pitch % 4 == 0), y the finished
+   * output (after bias / residual / ReLU); dot_w is [cout padded as the pack][SCFLOW_CONV_DOT_PITCH] fp32 (zero
+   * rows past cout).  A slot is one (output-channel tile, epilogue warp half): dot_slots = 2 * cout_pad / bn with
+   * bn given explicitly; every slot of every pixel is written (plain stores, no initialisation, run-to-run
+   * identical bits) and their sum is the projection.  With dot_n = kh' kw' cout' and dot_w[c][tap cout' + co] =
+   * W'[co][c][tap] these are the per-pixel tap products of a following small convolution W' (the 1-2 channel
+   * predictors of the flow / mask heads, raft_decoder.py:256-294); scflow_tap_sum_fwd adds slots and taps up,
+   * and the head's (n, 256, h, w) feature map is never written.  No other output is required with dot_out. */
+  const float* dot_w;
+  float* dot_out;
+  int dot_n, dot_pitch, dot_slots;
 } scflow_conv_tc_desc;
 
 /* Output spatial size: OH = (h + 2 pad_h - kh) / stride + 1, likewise OW.  Supported: OW a multiple of
  * 128, or 128 % OW == 0 with OH a multiple of 128/OW or 128/OW a multiple of OH (whole small images per
  * tile); cout <= 256 or split evenly into <= 256-channel tiles; cin any (zero-filled to k-steps of 16). */
 int scflow_conv_tc_fwd(const scflow_conv_tc_desc* desc, void* stream);
+
+/* out (n, cout, h, w) planar = bias[co] + sum over slots and the ks x ks taps of dot[(n, y + ky - ks/2, x + kx -
+ * ks/2)][slot][(ky ks + kx) cout + co] (zero outside the image): finishes a small convolution whose per-pixel tap
+ * products scflow_conv_tc_fwd left in dot_out (slots x pitch floats per pixel).  ks 1 or 3, ks ks cout <= pitch. */
+int scflow_tap_sum_fwd(const float* dot, int slots, int pitch, const float* bias, float* out, int n, int h, int w,
+                       int ks, int cout, void* stream);
 
 /* Weight pack: fp32 (cout, cin, kh, kw) [times scale[cout], e.g. a folded eval BatchNorm] ->
  * [tap][k-block][hi|lo][cout_pad][bk] bf16.  cout_pad = cout rounded up to 16 (<= 256) per tile. */

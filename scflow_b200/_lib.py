@@ -55,6 +55,7 @@ SIGNATURES = {
                                         _P, c_int, c_int, c_int, c_float, c_int, _P]),
     "scflow_split_bf16": (c_int, [_P, ctypes.c_longlong, _P, ctypes.c_longlong, c_int, c_int, ctypes.c_longlong, _P]),
     "scflow_corr_lookup_bwd": (c_int, [_P, c_int, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
+    "scflow_tap_sum_fwd": (c_int, [_P, c_int, c_int, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_corr_fold_bwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, _P]),
     "scflow_corr_pyramid_bwd": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_upsample_bwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, c_float, _P]),

@@ -37,11 +37,14 @@ class _Desc(ctypes.Structure):
         ("stats", ctypes.c_void_p), ("bn", ctypes.c_int), ("epi", ctypes.c_int), ("gru_c", ctypes.c_int),
         ("gru_h", ctypes.c_void_p), ("gru_z", ctypes.c_void_p), ("algo", ctypes.c_int),
         ("x2", ctypes.c_void_p), ("cin2", ctypes.c_int), ("x2_lo_off", ctypes.c_longlong),
-        ("x2_stride_w", ctypes.c_longlong), ("x2_stride_h", ctypes.c_longlong), ("x2_stride_n", ctypes.c_longlong)]
+        ("x2_stride_w", ctypes.c_longlong), ("x2_stride_h", ctypes.c_longlong), ("x2_stride_n", ctypes.c_longlong),
+        ("dot_w", ctypes.c_void_p), ("dot_out", ctypes.c_void_p), ("dot_n", ctypes.c_int), ("dot_pitch", ctypes.c_int),
+        ("dot_slots", ctypes.c_int)]
 
 
 EPI_PLAIN, EPI_GRU_ZR, EPI_GRU_GATE = 0, 1, 2
 # scflow_conv_tc_desc.algo: operand movement (include/scflow_b200.h)
+DOT_PITCH = 20              # SCFLOW_CONV_DOT_PITCH
 STATS_REPLICAS = 8          # SCFLOW_STATS_REPLICAS: accumulators per (image, channel) of the conv epilogue statistics
 ALGO_AUTO, ALGO_TAP_BOXES, ALGO_PATCH, ALGO_PATCH_PAIR = 0, 1, 2, 3
 
@@ -203,13 +206,17 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
          out_f32: Optional[torch.Tensor] = None, out_planar: Optional[torch.Tensor] = None,
          planar_tf32: bool = False, f32_tf32: bool = False, stats: Optional[torch.Tensor] = None, want: str = "split",
          view=None, bn: int = 0, epi: int = EPI_PLAIN, gru_h: Optional[torch.Tensor] = None,
-         gru_z: Optional[torch.Tensor] = None, algo: int = ALGO_AUTO, x2: Optional[Split] = None):
+         gru_z: Optional[torch.Tensor] = None, algo: int = ALGO_AUTO, x2: Optional[Split] = None,
+         dot: Optional[tuple] = None):
     """One convolution launch.  x: Split (n, h, w, cin).  Outputs: `out` (Split), `out_f32` (n, OH, OW, >=cout)
     fp32 channels-last (may be a channel slice of a wider buffer), `out_planar` (n, cout, OH, OW); when none is
     given one is allocated according to `want` ("split" | "f32" | "planar").  `view` = (n, h, w, cin, lo_off,
     stride_w, stride_h, stride_n) overrides how the input buffer is addressed (the stem's overlapped window
     view).  `x2`: a second Split of the same pixels whose channels continue x's as the filter's input channels
     (x.c a multiple of 64): the operand the reference builds with torch.cat, read from where it lies.
+    `dot` = (dot_w [cout_pad, DOT_PITCH] fp32, dot_out [n, OH, OW, slots, pitch] fp32, dot_n) with `bn` given and
+    slots = 2 * cout_pad / bn: the projections of every finished output pixel, one partial sum per slot (see
+    `head_predict`); with `dot` and no explicit output nothing else is written.
     Returns the output object(s) in the order split, f32, planar (only those produced)."""
     lib = _lib.load()
     n, h, w = x.shape
@@ -224,7 +231,7 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
         raise _lib.ScflowError(f"conv_tc: input has {cin + cin2} channels, the filter takes {pk.cin}")
     oh, ow = out_hw(pk, h, w)
     dev = x.buf.device
-    if out is None and out_f32 is None and out_planar is None:
+    if out is None and out_f32 is None and out_planar is None and dot is None:
         if want == "split":
             out = alloc_split(n, oh, ow, pk.cout, dev)
         elif want == "f32":
@@ -268,6 +275,12 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
     if stats is not None:
         assert stats.dtype == torch.float64 and stats.shape == (n, STATS_REPLICAS, c8, 2) and stats.is_contiguous()
         d.stats = stats.data_ptr()
+    if dot is not None:
+        dw, dout, dn = dot
+        assert dw.dtype == torch.float32 and dw.is_contiguous() and dw.shape[1] == DOT_PITCH and dw.shape[0] >= _rup(pk.cout, 16)
+        assert dout.dtype == torch.float32 and dout.is_contiguous() and dout.shape[:3] == (n, oh, ow) and dout.shape[4] >= dn
+        d.dot_w, d.dot_out, d.dot_n = dw.data_ptr(), dout.data_ptr(), dn
+        d.dot_slots, d.dot_pitch = dout.shape[3], dout.shape[4]
     cin = cin + cin2
     flops = 2 * n * oh * ow * pk.cout * pk.cin * pk.kh * pk.kw
     # algorithmic bytes: split-plane input once, packed filter once, every output written once
@@ -279,7 +292,50 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
         rc = lib.scflow_conv_tc_fwd(ctypes.byref(d), _stream())
     _lib.check(rc, f"scflow_conv_tc_fwd({n}x{h}x{w}x{cin} -> {pk.cout}, {pk.kh}x{pk.kw}/{pk.stride})")
     res_ = tuple(o for o in (out, out_f32, out_planar) if o is not None)
+    if not res_:
+        return None
     return res_[0] if len(res_) == 1 else res_
+
+
+def packed_dot(pred: nn.Conv2d, cout_pad: int) -> torch.Tensor:
+    """The 1-2 channel predictor W' (cout', c, ks, ks) behind a head's last layer as projection vectors of that
+    layer's output pixel: dot_w[c][(ky ks + kx) cout' + co] = W'[co][c][ky][kx], rows padded to cout_pad."""
+    key = _key(pred.weight, pred.bias)
+    hit = pred.__dict__.get("_scflow_dot")
+    if hit is not None and hit[0] == (key, cout_pad):
+        return hit[1]
+    co, c, kh, kw = pred.weight.shape
+    if kh != kw or kh * kw * co > DOT_PITCH:
+        raise _lib.ScflowError(f"head predictor {tuple(pred.weight.shape)}: more than {DOT_PITCH} tap products per pixel")
+    with torch.no_grad():
+        w = pred.weight.detach().float().permute(1, 2, 3, 0).reshape(c, kh * kw * co)
+        dw = torch.zeros(cout_pad, DOT_PITCH, device=w.device, dtype=torch.float32)
+        dw[:c, :kh * kw * co] = w
+    pred.__dict__["_scflow_dot"] = ((key, cout_pad), dw)
+    return dw
+
+
+def head_predict(x: Split, pk: Packed, pred: nn.Conv2d, *, relu: bool = True) -> torch.Tensor:
+    """last 3x3 layer of a head (ReLU) + its 1-2 channel predictor (raft_decoder.py:256-294) without the
+    (n, 256, h, w) feature map in between: the layer's epilogue accumulates the predictor's per-pixel tap products
+    (scflow_conv_tc_desc.dot_out), scflow_tap_sum_fwd adds the taps and the bias -> planar (n, cout', h, w)."""
+    lib = _lib.load()
+    n, h, w = x.shape
+    oh, ow = out_hw(pk, h, w)
+    co, _, ks, _ = pred.weight.shape
+    dn = ks * ks * co
+    dw = packed_dot(pred, _rup(pk.cout, 16))
+    cp = _rup(pk.cout, 16)
+    bn = cp // 2 if cp % 32 == 0 and cp // 2 >= 64 else cp            # the fuller-wave tile width conv_tc picks itself
+    slots = 2 * (cp // bn)
+    dout = torch.empty((n, oh, ow, slots, _rup(dn, 4)), device=x.buf.device, dtype=torch.float32)
+    conv(x, pk, relu=relu, dot=(dw, dout, dn), bn=bn)
+    out = torch.empty((n, co, oh, ow), device=x.buf.device, dtype=torch.float32)
+    with _timed("scflow_tap_sum_fwd", 1, 4 * (dout.numel() + out.numel())):
+        rc = lib.scflow_tap_sum_fwd(_ptr(dout), slots, dout.shape[4], _ptr(pred.bias), _ptr(out), n, oh, ow, ks, co,
+                                    _stream())
+    _lib.check(rc, "scflow_tap_sum_fwd")
+    return out
 
 
 def expand_taps(x: torch.Tensor, kw: int) -> Split:

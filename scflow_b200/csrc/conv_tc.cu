@@ -77,6 +77,9 @@ struct Params {
   int w_stages, w_stage_bytes, wb_bytes;       // ring of filter slabs: one entry = one (k-block, tap), hi + lo
   int w_resident;                              // the whole filter stays in shared memory (w_stages = all entries)
   int wide;                                    // epilogue pointers / pitches are 32-byte aligned: 256-bit accesses
+  const float* dot_w;                          // [cout_pad][SCFLOW_CONV_DOT_PITCH]: projections of the output pixel
+  float* dot_out;                              // [pixels][dot_slots][dot_pitch]
+  int dot_n, dot_pitch, dot_slots;
 };
 
 __device__ __forceinline__ uint32_t make_idesc_bf16(int m, int n) {
@@ -228,8 +231,11 @@ __device__ __forceinline__ void add_split16(const __nv_bfloat16* src_hi, const _
   }
 }
 
+constexpr int kEpiPlain = 0, kEpiGru = 1, kEpiDot = 2;   // epilogue a kernel instance is compiled with
+
 // One accumulator tile (128 pixels x bn channels in TMEM at taddr) through the epilogue of this warp:
 // chunks of 32 columns j = half, half + 2, ...; lane = pixel (n, oy, ox).  `live`: the pixel exists.
+template <bool DOT>
 __device__ __forceinline__ void epilogue_plain(const Params& p, const Tile& tl, uint32_t taddr, int half, int lane,
                                               int n, int oy, int ox, bool live, uint64_t* acc_full, uint32_t parity) {
   const int chunks = (p.bn + 31) >> 5;
@@ -237,6 +243,9 @@ __device__ __forceinline__ void epilogue_plain(const Params& p, const Tile& tl, 
   const long long pix = ((long long)n * p.OH + oy) * p.OW + ox;
   const bool wide = p.wide != 0;
   bool waited = false;
+  float dacc[DOT ? SCFLOW_CONV_DOT_PITCH : 1];
+#pragma unroll
+  for (int k = 0; k < (DOT ? SCFLOW_CONV_DOT_PITCH : 1); ++k) dacc[k] = 0.f;
   for (int j = half; j < chunks; j += 2) {
     const int c0 = tl.nt * p.bn + j * 32;               // first output channel of the chunk
     if (!waited) {
@@ -326,6 +335,24 @@ __device__ __forceinline__ void epilogue_plain(const Params& p, const Tile& tl, 
 #pragma unroll
       for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
     }
+    if (DOT) {
+      // projections of the finished pixel onto dot_n vectors (the 1-2 channel predictor behind a head's last
+      // 3x3 layer, raft_decoder.py:256-294): every lane reads the same weights (one L1 wavefront per load);
+      // channels past cout carry zero weights and zero activations.  (fma.rn.f32x2 was measured: slower.)
+      const int n4 = (p.dot_n + 3) >> 2;
+      const float4* wr = reinterpret_cast<const float4*>(p.dot_w) + (size_t)c0 * (SCFLOW_CONV_DOT_PITCH / 4);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+#pragma unroll
+        for (int k4 = 0; k4 < SCFLOW_CONV_DOT_PITCH / 4; ++k4) {
+          if (k4 < n4) {
+            const float4 w4 = __ldg(wr + i * (SCFLOW_CONV_DOT_PITCH / 4) + k4);
+            dacc[4 * k4] = fmaf(v[i], w4.x, dacc[4 * k4]); dacc[4 * k4 + 1] = fmaf(v[i], w4.y, dacc[4 * k4 + 1]);
+            dacc[4 * k4 + 2] = fmaf(v[i], w4.z, dacc[4 * k4 + 2]); dacc[4 * k4 + 3] = fmaf(v[i], w4.w, dacc[4 * k4 + 3]);
+          }
+        }
+      }
+    }
     if (p.out_split) {
       __nv_bfloat16* oh = p.out_split + pix * p.out_pitch + c0;
 #pragma unroll
@@ -360,6 +387,14 @@ __device__ __forceinline__ void epilogue_plain(const Params& p, const Tile& tl, 
   if (!waited) {                                       // a warp without a chunk of this tile still hands it back
     tc::mbar_wait(acc_full, parity);
     tc::tc_fence_after();
+  }
+  if (DOT && live) {
+    // one slot per (output-channel tile, warp half): plain stores, summed in a fixed order by tap_sum_kernel --
+    // no initialisation, and the same bits on every run (atomics would add the partial sums in arrival order)
+    float4* dp = reinterpret_cast<float4*>(p.dot_out + (pix * p.dot_slots + tl.nt * 2 + half) * p.dot_pitch);
+#pragma unroll
+    for (int k4 = 0; k4 < SCFLOW_CONV_DOT_PITCH / 4; ++k4)
+      if (4 * k4 < p.dot_pitch) dp[k4] = make_float4(dacc[4 * k4], dacc[4 * k4 + 1], dacc[4 * k4 + 2], dacc[4 * k4 + 3]);
   }
 }
 
@@ -458,7 +493,7 @@ __device__ __forceinline__ void epilogue_gru(const Params& p, const Tile& tl, ui
   }
 }
 
-template <int BK, bool GRU>   // channels per k-block: 64 (128-byte swizzle) or 32 (64-byte swizzle); ConvGRU epilogues
+template <int BK, int EPI>    // channels per k-block: 64 (128-byte swizzle) or 32 (64-byte swizzle); ConvGRU epilogues
 __global__ void __launch_bounds__(THREADS, 1)
 conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p) {
   constexpr uint32_t kLayout = BK == 64 ? 2u : 4u;          // SWIZZLE_128B : SWIZZLE_64B
@@ -593,8 +628,8 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
       const int n = tl.n0 + mi, oy = tl.oy0 + my, ox = tl.ox0 + mx;
       const bool live = n < p.n;
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * 256u;
-      if (GRU) epilogue_gru(p, tl, taddr, half, lane, n, oy, ox, live, &acc_full[buf], (it >> 1) & 1);
-      else epilogue_plain(p, tl, taddr, half, lane, n, oy, ox, live, &acc_full[buf], (it >> 1) & 1);
+      if (EPI == kEpiGru) epilogue_gru(p, tl, taddr, half, lane, n, oy, ox, live, &acc_full[buf], (it >> 1) & 1);
+      else epilogue_plain<EPI == kEpiDot>(p, tl, taddr, half, lane, n, oy, ox, live, &acc_full[buf], (it >> 1) & 1);
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&acc_empty[buf]);
@@ -637,7 +672,7 @@ constexpr int P_THREADS = THREADS + 32;
 constexpr int MAX_A_STAGES = 4, MAX_W_STAGES = 32;
 constexpr int P_BAR_BYTES = 1024;
 
-template <bool PAIR, bool GRU>
+template <bool PAIR, int EPI>
 __global__ void __launch_bounds__(P_THREADS, 1)
 conv_patch_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params p) {
   constexpr uint32_t kLayout = 2u;                          // SWIZZLE_128B
@@ -835,8 +870,8 @@ conv_patch_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Par
       const uint32_t buf = it & 1;
       const int n = alive ? tl.n0 : p.n, oy = tl.oy0 + my, ox = tl.ox0 + mx;
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * 256u;
-      if (GRU) epilogue_gru(p, tl, taddr, half, lane, n, oy, ox, alive, &acc_full[buf], (it >> 1) & 1);
-      else epilogue_plain(p, tl, taddr, half, lane, n, oy, ox, alive, &acc_full[buf], (it >> 1) & 1);
+      if (EPI == kEpiGru) epilogue_gru(p, tl, taddr, half, lane, n, oy, ox, alive, &acc_full[buf], (it >> 1) & 1);
+      else epilogue_plain<EPI == kEpiDot>(p, tl, taddr, half, lane, n, oy, ox, alive, &acc_full[buf], (it >> 1) & 1);
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) {
@@ -1191,6 +1226,66 @@ extern "C" int scflow_split_bf16(const float* in, long long in_pitch, void* out,
   return check_launch();
 }
 
+namespace scflow {
+namespace ctc {
+// A CTA finishes a band of kTapRows image rows: the slot sums of the band and its halo rows go to shared memory
+// (coalesced: the pitch floats of a pixel are contiguous), then one thread per (row, x, channel) adds the taps.
+constexpr int kTapRows = 4;
+__global__ void __launch_bounds__(256) tap_sum_kernel(const float* __restrict__ dot, int slots, int pitch,
+                                                      const float* __restrict__ bias, float* __restrict__ out,
+                                                      int h, int w, int ks, int cout) {
+  extern __shared__ float tsm[];                       // [kTapRows + 2 pad][w][pitch]
+  const int pad = ks >> 1, rows = kTapRows + 2 * pad;
+  const int bands = (h + kTapRows - 1) / kTapRows;
+  const int n = blockIdx.x / bands, y0 = (blockIdx.x % bands) * kTapRows - pad;
+  const int p4 = pitch >> 2, per_row4 = w * p4;         // pitch % 4 == 0: 16-byte loads, four slots in flight each
+  float4* tsm4 = reinterpret_cast<float4*>(tsm);
+#pragma unroll 4
+  for (int i = threadIdx.x; i < rows * per_row4; i += blockDim.x) {
+    const int r = i / per_row4, j = i - r * per_row4, y = y0 + r;
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (y >= 0 && y < h) {
+      const int px = j / p4, k4 = j - px * p4;
+      const float4* d = reinterpret_cast<const float4*>(dot + (((long long)n * h + y) * w + px) * slots * pitch) + k4;
+      for (int sl = 0; sl < slots; ++sl) {
+        const float4 a = __ldg(d + sl * p4);
+        t.x += a.x; t.y += a.y; t.z += a.z; t.w += a.w;
+      }
+    }
+    tsm4[i] = t;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < kTapRows * w * cout; i += blockDim.x) {
+    const int x = i % w, r = (i / w) % kTapRows, co = i / (w * kTapRows), y = y0 + pad + r;
+    if (y >= h) continue;
+    float s = bias ? __ldg(bias + co) : 0.f;
+    for (int ky = 0; ky < ks; ++ky)
+      for (int kx = 0; kx < ks; ++kx) {
+        const int xx = x + kx - pad;
+        if (xx >= 0 && xx < w) s += tsm[((r + ky) * w + xx) * pitch + (ky * ks + kx) * cout + co];
+      }
+    out[(((long long)n * cout + co) * h + y) * w + x] = s;
+  }
+}
+}  // namespace ctc
+}  // namespace scflow
+
+extern "C" int scflow_tap_sum_fwd(const float* dot, int slots, int pitch, const float* bias, float* out, int n, int h,
+                                  int w, int ks, int cout, void* stream) {
+  using namespace scflow::ctc;
+  if (!dot || !out) return SCFLOW_E_NULL;
+  if (n <= 0 || h <= 0 || w <= 0 || cout <= 0 || slots <= 0 || (ks != 1 && ks != 3) || ks * ks * cout > pitch ||
+      (pitch % 4))
+    return SCFLOW_E_BAD_SHAPE;
+  if (!aligned16(dot)) return SCFLOW_E_MISALIGNED;
+  const size_t smem = (size_t)(kTapRows + 2 * (ks >> 1)) * w * pitch * sizeof(float);
+  if (smem > 200 * 1024) return SCFLOW_E_BAD_SHAPE;
+  cudaFuncSetAttribute(tap_sum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const int bands = (h + kTapRows - 1) / kTapRows;
+  tap_sum_kernel<<<(unsigned)(n * bands), 256, smem, (cudaStream_t)stream>>>(dot, slots, pitch, bias, out, h, w, ks, cout);
+  return check_launch();
+}
+
 extern "C" int scflow_expand_taps_fwd(const float* in, void* out, int n, int c, int kw, int h, int w, void* stream) {
   if (!in || !out) return SCFLOW_E_NULL;
   if (n <= 0 || h <= 0 || w <= 0 || c <= 0 || kw <= 0 || !(kw & 1) || c * kw > 16) return SCFLOW_E_BAD_SHAPE;
@@ -1346,7 +1441,16 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
       return SCFLOW_E_BAD_SHAPE;
     if (!aligned16(p.gru_h) || !aligned16(p.gru_z)) return SCFLOW_E_MISALIGNED;
   }
-  if (!p.out_split && !p.out_f32 && !p.out_planar) return SCFLOW_E_NULL;
+  p.dot_w = d->dot_w; p.dot_out = d->dot_out; p.dot_n = d->dot_n; p.dot_pitch = d->dot_pitch; p.dot_slots = d->dot_slots;
+  if (p.dot_out) {
+    if (!p.dot_w) return SCFLOW_E_NULL;
+    // the slot count is part of the buffer's layout: the caller fixes the tile width (bn) and with it n_tiles
+    if (p.epi != SCFLOW_EPI_PLAIN || p.dot_n < 1 || p.dot_n > SCFLOW_CONV_DOT_PITCH || p.dot_pitch < p.dot_n ||
+        (p.dot_pitch % 4) || p.dot_pitch > SCFLOW_CONV_DOT_PITCH || d->bn == 0 || p.dot_slots != 2 * p.n_tiles)
+      return SCFLOW_E_BAD_SHAPE;
+    if (!aligned16(p.dot_w) || !aligned16(p.dot_out)) return SCFLOW_E_MISALIGNED;
+  }
+  if (!p.out_split && !p.out_f32 && !p.out_planar && !p.dot_out) return SCFLOW_E_NULL;
   {
     auto a32 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 31u) == 0; };
     p.wide = a32(p.out_split) && (p.out_pitch % 16) == 0 && (p.out_lo % 16) == 0 && a32(p.out_f32) &&
@@ -1422,8 +1526,10 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
       cudaLaunchKernelEx(&cfg, kern, maps, p);
       return check_launch();
     };
-    if (pair) return gru ? launch(conv_patch_kernel<true, true>) : launch(conv_patch_kernel<true, false>);
-    return gru ? launch(conv_patch_kernel<false, true>) : launch(conv_patch_kernel<false, false>);
+    if (pair) return gru ? launch(conv_patch_kernel<true, kEpiGru>)
+                         : p.dot_out ? launch(conv_patch_kernel<true, kEpiDot>) : launch(conv_patch_kernel<true, kEpiPlain>);
+    return gru ? launch(conv_patch_kernel<false, kEpiGru>)
+               : p.dot_out ? launch(conv_patch_kernel<false, kEpiDot>) : launch(conv_patch_kernel<false, kEpiPlain>);
   }
   const int total = p.m_tiles * p.n_tiles;
   const int grid = total < sms ? total : sms;
@@ -1432,7 +1538,14 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
     kern<<<grid, THREADS, smem_bytes, st>>>(maps, p);
   };
   const bool gru = p.epi != SCFLOW_EPI_PLAIN;
-  if (bk == 64) { if (gru) launch1(conv_tc_kernel<64, true>); else launch1(conv_tc_kernel<64, false>); }
-  else { if (gru) launch1(conv_tc_kernel<32, true>); else launch1(conv_tc_kernel<32, false>); }
+  if (bk == 64) {
+    if (gru) launch1(conv_tc_kernel<64, kEpiGru>);
+    else if (p.dot_out) launch1(conv_tc_kernel<64, kEpiDot>);
+    else launch1(conv_tc_kernel<64, kEpiPlain>);
+  } else {
+    if (gru) launch1(conv_tc_kernel<32, kEpiGru>);
+    else if (p.dot_out) launch1(conv_tc_kernel<32, kEpiDot>);
+    else launch1(conv_tc_kernel<32, kEpiPlain>);
+  }
   return check_launch();
 }

@@ -256,12 +256,15 @@ class XHead(nn.Module):
             raise ValueError(f"x must be 'flow' or 'mask', but got {x}")
 
     def forward_split(self, hs: "C.Split") -> torch.Tensor:
-        """Inference on the split-plane hidden state: 3x3 convs on the tensor cores, the 1-2 channel
-        predictor as one pass over the fp32 feature map (csrc/small_conv.cu); planar (N, x_channels, h, w)."""
+        """Inference on the split-plane hidden state: 3x3 convs on the tensor cores, the 1-2 channel predictor
+        folded into the last layer's epilogue (convtc.head_predict); planar (N, x_channels, h, w)."""
         y = hs
-        for i, layer in enumerate(self.layers):
-            y = layer.forward_split(y, want="f32" if i == len(self.layers) - 1 else "split")
-        return ops.conv_small_cout(y.permute(0, 3, 1, 2), self.predict_layer)
+        for layer in self.layers[:-1]:
+            y = layer.forward_split(y, want="split")
+        last = self.layers[-1]
+        if last.with_norm or not (last.with_activation and isinstance(last.activate, nn.ReLU)):
+            raise NotImplementedError("XHead: the last feature layer must be conv + ReLU on the tensor-core path")
+        return C.head_predict(y, C.packed_conv(last.conv), self.predict_layer, relu=True)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if _needs_grad(x, *self.parameters()):

@@ -238,3 +238,27 @@ def test_norm_apply_split_vs_torch():
     got = C.norm_apply(xd, sums(xd), relu=False, res_raw=rd, res_sums=sums(rd), out_f32=f32).float()
     assert _err(got, inorm(x) + inorm(r)) < 2e-5
     assert _err(f32, inorm(x) + inorm(r)) < 2e-6
+
+
+@pytest.mark.parametrize("ks,co,n,hw,cmid", [(3, 2, 3, 32, 256), (1, 1, 3, 32, 256), (3, 2, 2, 64, 256), (3, 1, 5, 16, 96)])
+def test_head_predict_vs_fp64(ks, co, n, hw, cmid):
+    """A head's last 3x3 layer + ReLU + its 1-2 channel predictor (raft_decoder.py:256-294) with the predictor's tap
+    products accumulated in the layer's epilogue (dot_out) and summed by scflow_tap_sum_fwd, against the two
+    convolutions in fp64.  The (n, cmid, h, w) feature map is never written."""
+    g = torch.Generator().manual_seed(100 * ks + co + n)
+    cin = 128
+    x = torch.randn(n, hw, hw, cin, generator=g)
+    w1 = torch.randn(cmid, cin, 3, 3, generator=g) / (cin * 9) ** 0.5
+    b1 = torch.randn(cmid, generator=g) * 0.1
+    pred = torch.nn.Conv2d(cmid, co, ks, padding=ks // 2)
+    with torch.no_grad():
+        pred.weight.copy_(torch.randn(pred.weight.shape, generator=g) / (cmid * ks * ks) ** 0.5)
+        pred.bias.copy_(torch.randn(co, generator=g))
+    mid = _ref(x, w1, b1, 1, 1, relu=True)                                   # (n, h, w, cmid) fp64
+    want = F.conv2d(mid.permute(0, 3, 1, 2), pred.weight.double(), pred.bias.double(), 1, ks // 2)
+    pk = C.pack_weights(w1.to(DEV), b1.to(DEV), 1, (1, 1))
+    got = C.head_predict(C.to_split(x.to(DEV)), pk, pred.to(DEV))
+    assert got.shape == want.shape
+    assert _err(got, want) < 3e-5
+    got2 = C.head_predict(C.to_split(x.to(DEV)), pk, pred)                   # cached projection vectors, fresh scratch
+    assert _err(got2, want) < 3e-5

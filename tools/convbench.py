@@ -48,6 +48,8 @@ SHAPES = [
     ("gru 1x5 256->128 @32", 32, 32, 256, 128, 1, 5, 1, 0, 2, "f32", 8),
     ("gru 1x5 128->128 @32", 32, 32, 128, 128, 1, 5, 1, 0, 2, "split", 8),
     ("head 3x3 128->256 @32", 32, 32, 128, 256, 3, 3, 1, 1, 1, "f32", 16),
+    ("head 3x3 128->256 @32 + 3x3 ->2 predictor", 32, 32, 128, 256, 3, 3, 1, 1, 1, "dot18", 8),
+    ("head 3x3 128->256 @32 + 1x1 ->1 predictor", 32, 32, 128, 256, 3, 3, 1, 1, 1, "dot1", 8),
     ("head 3x3 64->32 @32", 32, 32, 64, 32, 3, 3, 1, 1, 1, "split", 8),
     ("pose 3x3/2 224->128 @32->16", 32, 32, 224, 128, 3, 3, 2, 1, 1, "f32", 8),
     ("pose 3x3/2 128->128 @16->8", 16, 16, 128, 128, 3, 3, 2, 1, 1, "f32", 8),
@@ -92,6 +94,10 @@ for name, h, w, cin, cout, kh, kw, s, ph, pw, out, calls in SHAPES:
             kw_.append(dict(out_f32=torch.empty(N, oh, ow, c8, device=dev), relu=True))
         elif out == "planar":
             kw_.append(dict(out_planar=torch.empty(N, c8, oh, ow, device=dev), planar_tf32=True))
+        elif out.startswith("dot"):
+            dn = int(out[3:])
+            kw_.append(dict(relu=True, bn=128, dot=(torch.randn(256, C.DOT_PITCH, device=dev),
+                                                    torch.empty(N, oh, ow, 4, (dn + 3) // 4 * 4, device=dev), dn)))
         elif out == "gru_zr":
             kw_.append(dict(out=C.alloc_split(N, oh, ow, 128, dev), epi=C.EPI_GRU_ZR, bn=128,
                             gru_h=torch.randn(N, oh, ow, 128, device=dev), gru_z=torch.empty(N, oh, ow, 128, device=dev)))
