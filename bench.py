@@ -50,14 +50,26 @@ NCU_KERNEL = {
 }
 
 
+def _latest_profile(suffix):
+    d = os.path.join(ROOT, "profiles")
+    files = sorted(f for f in os.listdir(d) if f.endswith(suffix)) if os.path.isdir(d) else []
+    return os.path.join(d, files[-1]) if files else None
+
+
 def ncu_traffic(launcher):
+    """DRAM bytes (read + write) per launch from the committed `ncu --set full` captures: convolution shapes from
+    profiles/*_conv_traffic.json (single launches of tools/convbench.py at the bench's sizes, keyed by shape), the
+    other kernels from profiles/*_ncu_full_summary.txt (launches of the bench's own timed region)."""
+    if launcher.startswith("scflow_conv_tc_fwd["):
+        f = _latest_profile("_conv_traffic.json")
+        ent = json.load(open(f)).get(launcher[len("scflow_conv_tc_fwd["):-1]) if f else None
+        return ent["traffic_bytes"] if ent else None
     frag = NCU_KERNEL.get(launcher.split("[")[0])
-    files = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if f.endswith("_ncu_full_summary.txt")) \
-        if os.path.isdir(os.path.join(ROOT, "profiles")) else []
-    if not frag or not files:
+    f = _latest_profile("_ncu_full_summary.txt")
+    if not frag or not f:
         return None
     vals, take = [], False
-    for line in open(os.path.join(ROOT, "profiles", files[-1])):
+    for line in open(f):
         if line.startswith("=="):
             take = frag in line
         elif take and line.strip().startswith("traffic (DRAM read + write)"):

@@ -50,6 +50,8 @@ SHAPES = [
     ("head 3x3 128->256 @32", 32, 32, 128, 256, 3, 3, 1, 1, 1, "f32", 16),
     ("head 3x3 128->256 @32 + 3x3 ->2 predictor", 32, 32, 128, 256, 3, 3, 1, 1, 1, "dot18", 8),
     ("head 3x3 128->256 @32 + 1x1 ->1 predictor", 32, 32, 128, 256, 3, 3, 1, 1, 1, "dot1", 8),
+    ("small-cin 7x1 16->128 @32 (flow / mask encoders)", 32, 32, 16, 128, 7, 1, 1, 3, 0, "split", 16),
+    ("small-cin 3x1 16->64 @32", 32, 32, 16, 64, 3, 1, 1, 1, 0, "split", 8),
     ("head 3x3 64->32 @32", 32, 32, 64, 32, 3, 3, 1, 1, 1, "split", 8),
     ("pose 3x3/2 224->128 @32->16", 32, 32, 224, 128, 3, 3, 2, 1, 1, "f32", 8),
     ("pose 3x3/2 128->128 @16->8", 16, 16, 128, 128, 3, 3, 2, 1, 1, "f32", 8),

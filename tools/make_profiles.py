@@ -11,7 +11,10 @@ go, pr = os.path.join(root, "gpurun_out"), os.path.join(root, "profiles")
 os.makedirs(pr, exist_ok=True)
 for src, dst in ((f"{tag}_bench.json", f"{rnd}_bench.json"), (f"{tag}_bench_ref.json", f"{rnd}_bench_reference.json"),
                  (f"{tag}_launches.csv", f"{rnd}_launches.csv"), (f"{tag}_bench_cfg4.json", f"{rnd}_bench_cfg4_512.json"),
-                 (f"{tag}_bench_train.json", f"{rnd}_bench_train.json")):
+                 (f"{tag}_bench_train.json", f"{rnd}_bench_train.json"),
+                 (f"{tag}_bench_torch_gpu.json", f"{rnd}_bench_torch_gpu.json"),
+                 (f"{tag}_convbench.txt", f"{rnd}_convbench.txt"), (f"{tag}_corrbwd.json", f"{rnd}_corr_bwd_gemm.json"),
+                 (f"{tag}_lookupbwd.json", f"{rnd}_lookup_bwd.json")):
     if os.path.exists(os.path.join(go, src)):
         shutil.copy(os.path.join(go, src), os.path.join(pr, dst))
 out = subprocess.run([sys.executable, os.path.join(root, "tools", "launch_summary.py"),
