@@ -324,7 +324,7 @@ def algorithmic_bytes(name, B, S=256, C=256):
 
 def ours(args):
     from scflow_b200 import ops
-    from scflow_b200.refiner import GraphedRefiner, SCFlowRefinerCore, gather_poses
+    from scflow_b200.refiner import GraphedRefiner, PoseGatherer, SCFlowRefinerCore, gather_poses
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -384,16 +384,15 @@ def ours(args):
             outs.append(p.clone())
         return torch.cat(outs, 0)
 
+    gatherer = PoseGatherer(B * micro * world, dev)
+    if world > 1:                     # the collective's own device time on its stream
+        gatherer.events = gather_events
+    gatherer_e2e = PoseGatherer(B * world, dev)
+
     def step_resident(i):
-        poses = run_micro(i)
-        if world > 1:                 # the collective's own device time
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            out = gather_poses(poses, B * micro * world)
-            b.record()
-            gather_events.append((a, b))
-            return out
-        return gather_poses(poses, B * micro * world)
+        # the poses of step i are gathered on a side stream while step i + 1 computes (PoseGatherer): the ranks do
+        # not meet every step; the timed region closes with a device-wide synchronise that includes the last gather
+        return gatherer.submit(run_micro(i))
 
     def step_e2e(i):
         if g_e2e:
@@ -409,16 +408,15 @@ def ours(args):
         # D2H read of the step's result: an asynchronous copy into pinned memory on the compute stream;
         # the host picks up step i-1's poses while step i runs (as a serving loop would), the last one
         # at the barrier that closes the timed region
-        out = gather_poses(poses, B * world)
-        slot = i % 2
+        slot = gatherer_e2e.submit(poses)                     # gather + D2H read on the side stream
         if state.get("host") is None:
-            state["host"] = [torch.empty(out.shape, dtype=out.dtype, pin_memory=True) for _ in range(2)]
-            state["done"] = [torch.cuda.Event() for _ in range(2)]
+            shp = gatherer_e2e.out[0].shape
+            state["host"] = [torch.empty(shp, dtype=torch.float32, pin_memory=True) for _ in range(2)]
+            state["done"] = [None, None]
             state["pending"] = [False, False]
-        state["host"][slot].copy_(out, non_blocking=True)
-        state["done"][slot].record(torch.cuda.current_stream(dev))
+        state["done"][slot] = gatherer_e2e.to_host(slot, state["host"][slot])
         state["pending"][slot] = True
-        prev = (i + 1) % 2
+        prev = 1 - slot
         if state["pending"][prev]:
             state["done"][prev].synchronize()
             state["pending"][prev] = False
@@ -468,8 +466,9 @@ def ours(args):
         ag = sum(a.elapsed_time(b) for a, b in gather_events) / max(1, len(gather_events))
         ranks = {"ms_per_step_min": pr[0], "ms_per_step_median": pr[len(pr) // 2], "ms_per_step_max": pr[-1],
                  "allgather_ms_per_step_rank0": ag,
-                 "note": "value uses the MAX over ranks of the barrier-bracketed region; the pose all-gather is "
-                         "48 B per crop, its time here includes waiting for the slowest rank"}
+                 "note": "value uses the MAX over ranks of the barrier-bracketed region; the pose all-gather (48 B per "
+                         "crop) runs on a side stream under the next step's compute, its time here includes waiting "
+                         "for the slowest rank"}
     if os.environ.get("SCFLOW_PROFILE") == "1":
         torch.cuda.profiler.stop()
     launches = ops.STATS.count

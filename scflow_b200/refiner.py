@@ -159,6 +159,86 @@ def gather_poses(local: torch.Tensor, total: int) -> torch.Tensor:
     return torch.cat([out[r * mx: r * mx + (hi - lo)] for r, (lo, hi) in enumerate(sizes)], dim=0)
 
 
+class PoseGatherer:
+    """The pose all-gather of a serving loop, off the compute stream.  `gather_poses` on the compute stream makes
+    every rank wait for the slowest one EVERY step (measured at N = 8: 0.98 ms of a 17.5 ms step, efficiency
+    0.969); here step i's poses are staged (one small copy on the compute stream) and gathered on a side stream
+    while step i + 1 computes, two slots deep, so the ranks only meet when a result is read.  `submit` returns the
+    slot; `result(slot)` makes the current stream wait for that gather and returns the (total, 12) poses in crop
+    order; `to_host(slot, pinned)` enqueues the device-to-host read behind the gather on the side stream and
+    returns an event to synchronise on.  On CPU tensors (gloo tests) everything is synchronous."""
+
+    def __init__(self, total: int, device, width: int = 12, slots: int = 2):
+        self.total, self.width = total, width
+        self.world = dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+        self.rank = dist.get_rank() if self.world > 1 else 0
+        self.sizes = [shard_range(total, r, self.world) for r in range(self.world)]
+        self.mx = max(hi - lo for lo, hi in self.sizes)
+        self.even = all(hi - lo == self.mx for lo, hi in self.sizes)
+        self.cuda = torch.device(device).type == "cuda"
+        self.stage = [torch.zeros((self.mx, width), device=device) for _ in range(slots)]
+        self.out = [torch.empty((self.world * self.mx, width), device=device) for _ in range(slots)]
+        self.comm = torch.cuda.Stream(device=device) if self.cuda else None
+        self.done = [torch.cuda.Event() if self.cuda else None for _ in range(slots)]
+        self.used = [False] * slots
+        self.i = 0
+        self.events = None            # set to a list to collect (start, end) timing events of every gather
+
+    def submit(self, local: torch.Tensor) -> int:
+        slot = self.i % len(self.stage)
+        self.i += 1
+        n = local.shape[0]
+        if self.cuda:
+            cur = torch.cuda.current_stream(local.device)
+            if self.used[slot]:
+                cur.wait_event(self.done[slot])          # the gather that last read this staging slot (long done)
+            self.stage[slot][:n].copy_(local)
+            ready = torch.cuda.Event()
+            ready.record(cur)
+            with torch.cuda.stream(self.comm):
+                self.comm.wait_event(ready)
+                if self.events is not None:
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record(self.comm)
+                self._gather(slot)
+                if self.events is not None:
+                    b.record(self.comm)
+                    self.events.append((a, b))
+                self.done[slot].record(self.comm)
+        else:
+            self.stage[slot][:n].copy_(local)
+            self._gather(slot)
+        self.used[slot] = True
+        return slot
+
+    def _gather(self, slot: int) -> None:
+        if self.world == 1:
+            self.out[slot].copy_(self.stage[slot])
+        else:
+            dist.all_gather_into_tensor(self.out[slot], self.stage[slot])
+
+    def result(self, slot: int) -> torch.Tensor:
+        if self.cuda:
+            torch.cuda.current_stream(self.out[slot].device).wait_event(self.done[slot])
+        o = self.out[slot]
+        if self.even:
+            return o[: self.total]
+        return torch.cat([o[r * self.mx: r * self.mx + (hi - lo)] for r, (lo, hi) in enumerate(self.sizes)], dim=0)
+
+    def to_host(self, slot: int, pinned: torch.Tensor):
+        """Device-to-host read of the gathered (padded) poses of `slot` behind its gather; returns the event (or
+        None on CPU) after which `pinned` holds them."""
+        if not self.cuda:
+            pinned.copy_(self.out[slot])
+            return None
+        with torch.cuda.stream(self.comm):
+            pinned.copy_(self.out[slot], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self.comm)
+        self.done[slot].record(self.comm)                # the slot is free again only after the read
+        return ev
+
+
 @torch.no_grad()
 def refine_sharded(core: SCFlowRefinerCore, batch: Dict[str, torch.Tensor], micro_batch: int = 64):
     """Refine this rank's shard of `batch` (already sliced by the caller with shard_range) in

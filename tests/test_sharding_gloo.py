@@ -8,7 +8,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from scflow_b200.refiner import gather_poses, pack_pose, shard_range, unpack_pose
+from scflow_b200.refiner import PoseGatherer, gather_poses, pack_pose, shard_range, unpack_pose
 
 
 def test_shard_range_covers_everything():
@@ -42,7 +42,12 @@ def _worker(rank, world, port, total, q):
     lo, hi = shard_range(total, rank, world)
     full = torch.arange(total * 12, dtype=torch.float32).reshape(total, 12)
     got = gather_poses(full[lo:hi].clone(), total)
-    q.put((rank, torch.equal(got, full)))
+    ok = torch.equal(got, full)
+    pg = PoseGatherer(total, "cpu")                    # the pipelined form: three steps through two slots
+    for step in range(3):
+        slot = pg.submit(full[lo:hi] + step)
+        ok = ok and torch.equal(pg.result(slot), full + step)
+    q.put((rank, ok))
     dist.destroy_process_group()
 
 
