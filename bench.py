@@ -796,12 +796,16 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch-gpu"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-fork", action="store_true", help="A/B: the up-sampling branch on the compute stream")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--image", type=int, default=256, help="crop side (256 = configs[1]; 512 = configs[3])")
     ap.add_argument("--strong", type=int, default=0, metavar="TOTAL",
                     help="configs[2] as written: TOTAL crops (512) split over the ranks, micro-batches of --batch (extra line)")
     ap.add_argument("--train", action="store_true", help="configs[4]: forward+backward+optimizer step, batch 32/GPU")
     args = ap.parse_args()
+    if args.no_fork:
+        import scflow_b200.decoder as _dec
+        _dec.FORK_UPSAMPLE = False
     # libraries (NCCL's version banner, cuDNN warnings) write to fd 1: keep the real stdout for the
     # one JSON line and send everything else to stderr
     global _OUT

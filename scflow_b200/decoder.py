@@ -27,6 +27,17 @@ from .modules import (ConvGRU, ConvModule, CorrelationPyramid, CorrLookup, Motio
 from .registry import MODELS, register
 
 
+FORK_UPSAMPLE = True          # the up-sampling branch of the inference loop on a side stream (see _forward_inference)
+_SIDE = {}
+
+
+def _side_stream(dev) -> "torch.cuda.Stream":
+    key = torch.device(dev).index if torch.device(dev).index is not None else torch.cuda.current_device()
+    if key not in _SIDE:
+        _SIDE[key] = torch.cuda.Stream(device=dev)
+    return _SIDE[key]
+
+
 @register
 class SCFlowDecoder(nn.Module):
     _h_channels = {'Basic': 128, 'Small': 96}
@@ -129,9 +140,22 @@ class SCFlowDecoder(nn.Module):
             dfe[1].forward_split(d0, out=pose_in.slice(hc, c_df))
             m0 = me[0].forward_small_cin_split(mask)                   # 3x3 on 1 channel
             me[1].forward_split(m0, out=pose_in.slice(hc + c_df, c_m))
+            # The two 8x up-samplings (returned lists only) depend on nothing after the heads; the pose head is
+            # a chain of nine small launches (16x16 ... 1x1 maps: 8-128 CTAs) that leaves most SMs idle.  Fork:
+            # the up-samplings run on a side stream under it (a second branch of the captured graph).
+            if FORK_UPSAMPLE:
+                main = torch.cuda.current_stream(dev)
+                side = _side_stream(dev)
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    flow_pred = ops.upsample(flow, delta_flow_pred, scale, float(scale))
+                    upsample_mask_pred = ops.upsample(mask, None, scale, 1.0)
             delta_rotation, delta_translation = self.pose_pred.forward_split(pose_in, label)
-            flow_pred = ops.upsample(flow, delta_flow_pred, scale, float(scale))
-            upsample_mask_pred = ops.upsample(mask, None, scale, 1.0)
+            if FORK_UPSAMPLE:
+                main.wait_stream(side)      # join before pose_flow replaces `flow`
+            else:
+                flow_pred = ops.upsample(flow, delta_flow_pred, scale, float(scale))
+                upsample_mask_pred = ops.upsample(mask, None, scale, 1.0)
             # pose compose + pose-induced flow + next iteration's 1/8 flow: one launch
             update_rotation, update_translation, flow_full, flow = ops.pose_flow(
                 update_rotation, update_translation, K, dR6=delta_rotation.float(),
