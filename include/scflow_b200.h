@@ -117,7 +117,10 @@ int scflow_corr_pyramid_fwd(const float* feat1, const float* feat2, float* const
 #define SCFLOW_LAYOUT_NHWC_GEN1 2   /* NHWC through the first-generation kernel: the cross-check of the tests */
 #define SCFLOW_LAYOUT_NHWC_SPLIT 3  /* `out` = split-bf16 planes (n, h, w, [328 hi | 328 lo]) bf16, value = hi + lo,
                                        channels 324..327 zero: the operand of the 1x1 convolution that consumes the
-                                       lookup (scflow_conv_tc_fwd); w % 32 == 0, else SCFLOW_E_UNSUPPORTED */
+                                       lookup (scflow_conv_tc_fwd); w % 32 == 0, else SCFLOW_E_UNSUPPORTED.
+                                       Plane channel order is LANE-MAJOR: plane channel 12 (9 g + a) + 3 level + j
+                                       holds the reference's channel 81 level + 9 a + 3 g + j (a, g*3 + j = x, y tap);
+                                       pack the consumer's filter with its input channels in that order */
 int scflow_corr_lookup_fwd(const float* const* levels, int num_levels, const float* flow,
                            float* out, short* windows, int n, int h, int w, int radius,
                            int div_mode, int out_layout, void* stream);

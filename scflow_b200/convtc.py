@@ -173,8 +173,10 @@ def _key(*tensors):
 
 
 def packed_conv(conv: nn.Conv2d, bn: Optional[nn.BatchNorm2d] = None, with_bias: bool = True,
-                tag: str = "") -> Packed:
-    """Cached pack of an nn.Conv2d, optionally with an eval BatchNorm folded in (y = conv*scale + shift)."""
+                tag: str = "", in_order: Optional[torch.Tensor] = None) -> Packed:
+    """Cached pack of an nn.Conv2d, optionally with an eval BatchNorm folded in (y = conv*scale + shift).
+    `in_order` (needs its own `tag`): input channel c' of the packed filter is the module's channel in_order[c']
+    (an operand whose producer wrote its channels in another order, e.g. the lookup's split planes)."""
     ts = [conv.weight, conv.bias]
     if bn is not None:
         ts += [bn.weight, bn.bias, bn.running_mean, bn.running_var]
@@ -192,7 +194,8 @@ def packed_conv(conv: nn.Conv2d, bn: Optional[nn.BatchNorm2d] = None, with_bias:
             shift = bn.bias.float() + (b0 - bn.running_mean.float()) * scale
             pk = pack_weights(conv.weight, shift, conv.stride, conv.padding, scale=scale)
         else:
-            pk = pack_weights(conv.weight, conv.bias if with_bias else None, conv.stride, conv.padding)
+            wt = conv.weight if in_order is None else conv.weight[:, in_order.to(conv.weight.device)]
+            pk = pack_weights(wt, conv.bias if with_bias else None, conv.stride, conv.padding)
     cache[tag] = (key, pk)
     return pk
 

@@ -290,23 +290,27 @@ corr_lookup_v2_kernel(const __grid_constant__ Maps maps, const __grid_constant__
     if (SPLIT) {
       // split planes for the tensor-core 1x1 convolution that consumes the lookup (raft_decoder.py:152-155):
       // 328 bf16 hi, then 328 bf16 lo (324 values + 4 zero channels each), two 656-byte bulk copies
-      uint16_t* so = reinterpret_cast<uint16_t*>(smem_raw + tb);
+      // Channel order of the planes: LANE-MAJOR, c' = 12 * lane + 3 * level + j for the value of channel
+      // 81 * level + 9 * a + 3 * g + j (lane = 9 g + a).  The consumer is a 1x1 convolution whose input channels
+      // are permuted to match when its filter is packed (ops.LOOKUP_SPLIT_ORDER), so a lane's twelve values leave
+      // as three 8-byte stores per plane with packed conversions instead of 24 two-byte stores (the natural order
+      // cost 7 us of the 55).
+      uint8_t* so = smem_raw + tb;
       if (lane < 27) {
+        uint32_t hi[6], lo[6];
 #pragma unroll
-        for (int l = 0; l < kLevels; ++l) {
-#pragma unroll
-          for (int j = 0; j < 3; ++j) {
-            const float v = res[l][j];
-            const uint32_t hi = cvt_bf16x2(v, 0.f) & 0xffffu;
-            const uint32_t lo = cvt_bf16x2(v - __uint_as_float(hi << 16), 0.f) & 0xffffu;
-            const int idx = l * (kD * kD) + kD * k + 3 * g + j;
-            so[idx] = (uint16_t)hi;
-            so[kSplitC + idx] = (uint16_t)lo;
-          }
+        for (int t = 0; t < 6; ++t) {
+          const float v0 = res[(2 * t) / 3][(2 * t) % 3], v1 = res[(2 * t + 1) / 3][(2 * t + 1) % 3];
+          hi[t] = cvt_bf16x2(v0, v1);
+          lo[t] = cvt_bf16x2(v0 - __uint_as_float(hi[t] << 16), v1 - __uint_as_float(hi[t] & 0xffff0000u));
         }
+        uint2* ph = reinterpret_cast<uint2*>(so + 24 * lane);
+        uint2* pl = reinterpret_cast<uint2*>(so + 2 * kSplitC + 24 * lane);
+        ph[0] = make_uint2(hi[0], hi[1]); ph[1] = make_uint2(hi[2], hi[3]); ph[2] = make_uint2(hi[4], hi[5]);
+        pl[0] = make_uint2(lo[0], lo[1]); pl[1] = make_uint2(lo[2], lo[3]); pl[2] = make_uint2(lo[4], lo[5]);
       } else if (lane == 27) {
-#pragma unroll
-        for (int j = kOutFloats; j < kSplitC; ++j) { so[j] = 0; so[kSplitC + j] = 0; }
+        *reinterpret_cast<uint2*>(so + 2 * kOutFloats) = make_uint2(0u, 0u);               // 4 zero channels
+        *reinterpret_cast<uint2*>(so + 2 * kSplitC + 2 * kOutFloats) = make_uint2(0u, 0u);
       }
     } else if (lane < 27) {
       float* so = reinterpret_cast<float*>(smem_raw + tb) + kD * k + 3 * g;

@@ -213,14 +213,17 @@ class MotionEncoder(nn.Module):
         corr: (N,324,h,w)-shaped channels-last lookup result; flow: planar (N,2,h,w).
         Tensor-core / FMA launches only; what the reference concatenates is written in place: corr_net and
         flow_net store into the two channel slices of one split buffer that out_net reads."""
-        if isinstance(corr, C.Split):
+        if isinstance(corr, C.Split):          # CorrLookup.forward_split: channels in the kernel's lane-major order
             cs = corr
             (n, h, w), dev = cs.shape, cs.buf.device
+            c0 = self.corr_net[0]
+            if c0.with_norm or not (c0.with_activation and isinstance(c0.activate, nn.ReLU)):
+                raise NotImplementedError("MotionEncoder.corr_net[0] must be conv + ReLU on the tensor-core path")
+            a = C.conv(cs, C.packed_conv(c0.conv, tag="lookup_order", in_order=ops.lookup_split_order()), relu=True)
         else:
             n, _, h, w = corr.shape
             dev = corr.device
-            cs = C.to_split(corr.permute(0, 2, 3, 1))
-        a = self.corr_net[0].forward_split(cs)
+            a = self.corr_net[0].forward_split(C.to_split(corr.permute(0, 2, 3, 1)))
         cat = C.alloc_split(n, h, w, 256, dev)
         c1 = self.corr_net[1].conv.out_channels
         self.corr_net[1].forward_split(a, out=cat.slice(0, c1))

@@ -150,6 +150,22 @@ def corr_pyramid_bwd(grad_corr: torch.Tensor, feat1: torch.Tensor, feat2: torch.
     return g1, g2
 
 
+def lookup_split_order(num_levels: int = 4, radius: int = 4) -> torch.Tensor:
+    """Channel order of the lookup's split-plane output (SCFLOW_LAYOUT_NHWC_SPLIT): plane channel c' holds the
+    reference's channel order[c'] (corr_lookup.py:134: channel = 81 level + 9 a + b).  Lane-major: lane = 9 g + a of
+    the kernel owns taps (a, b = 3 g + j) of every level and writes its twelve values side by side, c' = 12 lane +
+    3 level + j.  The 1x1 convolution behind the lookup is packed with its input channels in this order."""
+    d = 2 * radius + 1
+    assert num_levels == 4 and d == 9, "the split layout exists for the shipped lookup (4 levels, radius 4)"
+    order = torch.empty(num_levels * d * d, dtype=torch.long)
+    for lane in range(27):
+        g, a = divmod(lane, 9)
+        for l in range(num_levels):
+            for j in range(3):
+                order[12 * lane + 3 * l + j] = d * d * l + d * a + 3 * g + j
+    return order
+
+
 def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int = 4,
                 div_mode: int = DIV_IEEE, return_windows: bool = False, channels_last: bool = True,
                 gen1: bool = False, split: bool = False):
@@ -159,7 +175,8 @@ def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int
     strides (memory (N, H, W, 324)): what the warp-per-query kernel writes and what the
     downstream convolutions consume without a layout pass.  `gen1`: the first-generation kernel on any
     shape (the tests' cross-check; the second generation runs wherever it applies otherwise).
-    `split`: return the result as a convtc.Split (split-bf16 planes) instead of an fp32 tensor."""
+    `split`: return the result as a convtc.Split (split-bf16 planes) instead of an fp32 tensor, its channels in
+    the kernel's lane-major order (`lookup_split_order`)."""
     lib = _lib.load()
     fl = _chk(flow, "flow")
     n, two, h, w = fl.shape
@@ -180,7 +197,8 @@ def corr_lookup(pyramid: Sequence[torch.Tensor], flow: torch.Tensor, radius: int
             rc = lib.scflow_corr_lookup_fwd(arr, L, _ptr(fl), _ptr(sp.buf), None, n, h, w, radius, div_mode,
                                             LAYOUT_NHWC_SPLIT, _stream())
         if rc == -2:                                   # SCFLOW_E_UNSUPPORTED
-            return C.to_split(corr_lookup(pyramid, flow, radius, div_mode).permute(0, 2, 3, 1), out=sp)
+            nat = corr_lookup(pyramid, flow, radius, div_mode).permute(0, 2, 3, 1)
+            return C.to_split(nat[..., lookup_split_order(L, radius).to(nat.device)].contiguous(), out=sp)
         _lib.check(rc, "scflow_corr_lookup_fwd")
         return sp
     if channels_last:

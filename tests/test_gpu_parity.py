@@ -156,15 +156,18 @@ def test_lookup_generations_identical():
 
 
 def test_lookup_split_planes_equal_fp32_result():
-    """SCFLOW_LAYOUT_NHWC_SPLIT: the lookup written as split-bf16 planes (328 hi | 328 lo per query) carries the
-    fp32 result to 16 significand bits, with zeros in the four padding channels; shapes the second-generation
+    """SCFLOW_LAYOUT_NHWC_SPLIT: the lookup written as split-bf16 planes (328 hi | 328 lo per query, channels in
+    the kernel's lane-major order `ops.lookup_split_order`) carries the fp32 result to 16 significand bits, with
+    zeros in the four padding channels; shapes the second-generation
     kernel does not take go through fp32 + one split pass and give the same planes."""
     g = torch.Generator(device=DEV).manual_seed(9)
     for n, h, w in ((4, 32, 32), (1, 64, 64), (2, 8, 16)):
         pyr = [torch.randn(n * h * w, 1, h >> l, w >> l, device=DEV, generator=g) for l in range(4)]
         flow = 5.0 * torch.randn(n, 2, h, w, device=DEV, generator=g)
         flow[0, :, : h // 2] = 0.0
-        want = ops.corr_lookup(pyr, flow, 4).permute(0, 2, 3, 1)
+        order = ops.lookup_split_order().to(DEV)
+        assert sorted(order.tolist()) == list(range(324))
+        want = ops.corr_lookup(pyr, flow, 4).permute(0, 2, 3, 1)[..., order]      # the planes' lane-major channel order
         sp = ops.corr_lookup(pyr, flow, 4, split=True)
         assert sp.c == 324 and sp.cp == 328 and tuple(sp.shape) == (n, h, w)
         got = sp.float()
