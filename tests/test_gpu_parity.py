@@ -369,6 +369,46 @@ def test_refiner_batch64_vs_oracle():
     assert moved > 1e-2 and er < 1e-4 and et < 0.1
 
 
+def test_forked_upsampling_changes_nothing_and_pose_gatherer_cuda():
+    """The side-stream branch of the inference loop (decoder.FORK_UPSAMPLE) produces bit-identical outputs, eagerly
+    and through the captured graph; PoseGatherer on CUDA (world 1: staging + side stream + host read) returns the
+    poses it was given."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    import scflow_b200.decoder as dec_mod
+    from scflow_b200.refiner import GraphedRefiner, PoseGatherer
+    host = bench.tile_batch(bench.make_batch(4, 1234, 256), 8)
+    dev_batch = {k: v.to(DEV) for k, v in host.items()}
+    core = bench.seeded_weights(SCFlowRefinerCore(256)).eval().to(DEV)
+    outs = {}
+    old = dec_mod.FORK_UPSAMPLE
+    try:
+        for flag in (False, True):
+            dec_mod.FORK_UPSAMPLE = flag
+            with torch.no_grad():
+                full = core.get_pose(dev_batch["rendered_images"], dev_batch["real_images"], dev_batch["R0"],
+                                     dev_batch["t0"], dev_batch["depth"], dev_batch["K"], dev_batch["labels"])
+                torch.cuda.synchronize()
+                outs[flag] = [t.clone() for lst in full for t in lst]
+        graphed = GraphedRefiner(core, dev_batch)                       # captured with the fork on
+        poses_g = graphed().clone()
+        with torch.no_grad():
+            poses_e = core.refine(dev_batch)
+    finally:
+        dec_mod.FORK_UPSAMPLE = old
+    assert len(outs[False]) == len(outs[True]) and all(torch.equal(a, b) for a, b in zip(outs[False], outs[True]))
+    assert torch.equal(poses_g, poses_e)
+    pg = PoseGatherer(8, DEV)
+    pinned = torch.empty(pg.out[0].shape, pin_memory=True)
+    for step in range(3):
+        slot = pg.submit(poses_e + step)
+        ev = pg.to_host(slot, pinned)
+        assert torch.equal(pg.result(slot), poses_e + step)
+        ev.synchronize()
+        assert torch.equal(pinned[:8], (poses_e + step).cpu())
+
+
 def test_batch64_matches_per_crop_runs():
     """Crops are independent: refining 64 crops at once equals refining them 8 at a time."""
     dec, _ = _build_decoder(256, 77, None)
