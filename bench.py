@@ -541,7 +541,8 @@ def ours(args):
     # flops / peak is printed beside it.  The TF32 kernels (correlation, ConvGRU) execute one TF32 MMA per
     # product: ceiling 1/2 of the bf16 peak; the TF32 cuBLAS figure measured in this run is printed too.
     def mma_per_product(k):
-        return 3.0 if k.startswith("scflow_conv_tc_fwd") else 2.0
+        from scflow_b200 import convtc as _C
+        return float(_C.MMA_TERMS) if k.startswith("scflow_conv_tc_fwd") else 2.0
     single = [k for k in kern if kern[k]["flops_per_launch"] or algorithmic_bytes(k, B, S)]
     share = lambda k: kern[k]["avg_ms"] * kern[k]["calls_per_step"]
     top = max(single, key=share)
@@ -558,7 +559,7 @@ def ours(args):
         return {"kernel": k, "bound": "tensor", "achieved": t, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
                 "frac": t / pk["bf16_sustained"], "traffic": ncu_traffic(k) if (B, S) == (64, 256) else None,
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (%s)" % pk["src"],
-                "mma_per_product": mma_per_product(k) if mma_per_product(k) == 3.0 else 1.0,
+                "mma_per_product": mma_per_product(k) if k.startswith("scflow_conv_tc_fwd") else 1.0,
                 "tensor_pipe_frac": t * mma_per_product(k) / pk["bf16_sustained"],
                 "note": "frac counts algorithmic flops; tensor_pipe_frac = executed MMA work in bf16-equivalents "
                         "(3 bf16 MMAs per product for the split-bf16 kernels, 1 TF32 MMA = 2 bf16-equivalents)",
@@ -810,6 +811,9 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch-gpu"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "bf16x2", "bf16"],
+                    help="bf16x3 = the refiner's parity mode (default); bf16x2 / bf16 = the opt-in reduced modes, an EXTRA "
+                         "line with its own deviation, never the headline")
     ap.add_argument("--no-fork", action="store_true", help="A/B: the up-sampling branch on the compute stream")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--image", type=int, default=256, help="crop side (256 = configs[1]; 512 = configs[3])")
@@ -820,6 +824,16 @@ def main():
     if args.no_fork:
         import scflow_b200.decoder as _dec
         _dec.FORK_UPSAMPLE = False
+    if args.precision != "bf16x3":
+        import scflow_b200.convtc as _C
+        _C.set_precision(args.precision)
+        global PRECISION_DTYPE, PRECISION_TEXT, METRIC
+        terms = {"bf16x2": 2, "bf16": 1}[args.precision]
+        PRECISION_DTYPE = f"{args.precision} (OPT-IN reduced mode: {terms} bf16 MMA per product); tf32 correlation"
+        PRECISION_TEXT = (f"OPT-IN reduced mode {args.precision}: " + ("activations rounded to bf16, filters exact (2 MMAs per "
+                          "product)" if terms == 2 else "plain bf16 operands (1 MMA per product)") + "; NOT the parity mode: "
+                          "tolerance stated separately (DESIGN 2), see deviation_from_oracle")
+        METRIC = METRIC + f" [reduced precision {args.precision}]"
     # libraries (NCCL's version banner, cuDNN warnings) write to fd 1: keep the real stdout for the
     # one JSON line and send everything else to stderr
     global _OUT

@@ -348,6 +348,10 @@ typedef struct scflow_conv_tc_desc {
   const float* dot_w;
   float* dot_out;
   int dot_n, dot_pitch, dot_slots;
+  /* bf16 MMAs per product: 0 or 3 = a_lo.b_hi + a_hi.b_lo + a_hi.b_hi (fp32-grade: THE mode of the refiner, the
+   * one the parity claims are made in).  Opt-in reduced modes, tolerance stated separately: 2 =
+   * a_hi.(b_hi + b_lo): activations rounded to bf16, filters exact; 1 = a_hi.b_hi: plain bf16 operands. */
+  int mma_terms;
 } scflow_conv_tc_desc;
 
 /* Output spatial size: OH = (h + 2 pad_h - kh) / stride + 1, likewise OW.  Supported: OW a multiple of

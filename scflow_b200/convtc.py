@@ -39,11 +39,13 @@ class _Desc(ctypes.Structure):
         ("x2", ctypes.c_void_p), ("cin2", ctypes.c_int), ("x2_lo_off", ctypes.c_longlong),
         ("x2_stride_w", ctypes.c_longlong), ("x2_stride_h", ctypes.c_longlong), ("x2_stride_n", ctypes.c_longlong),
         ("dot_w", ctypes.c_void_p), ("dot_out", ctypes.c_void_p), ("dot_n", ctypes.c_int), ("dot_pitch", ctypes.c_int),
-        ("dot_slots", ctypes.c_int)]
+        ("dot_slots", ctypes.c_int), ("mma_terms", ctypes.c_int)]
 
 
 EPI_PLAIN, EPI_GRU_ZR, EPI_GRU_GATE = 0, 1, 2
 # scflow_conv_tc_desc.algo: operand movement (include/scflow_b200.h)
+MMA_TERMS = 3               # bf16 MMAs per product of every conv() launch: 3 = fp32-grade (the refiner's one parity
+                            # mode); 2 / 1 = the opt-in reduced modes of scflow_conv_tc_desc.mma_terms (set_precision)
 DOT_PITCH = 20              # SCFLOW_CONV_DOT_PITCH
 STATS_REPLICAS = 8          # SCFLOW_STATS_REPLICAS: accumulators per (image, channel) of the conv epilogue statistics
 ALGO_AUTO, ALGO_TAP_BOXES, ALGO_PATCH, ALGO_PATCH_PAIR = 0, 1, 2, 3
@@ -254,6 +256,7 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
     d.relu = int(relu)
     c8 = _rup(pk.cout, 8)
     d.bn, d.epi, d.algo = bn, epi, algo
+    d.mma_terms = MMA_TERMS
     if epi != EPI_PLAIN:
         # ConvGRU epilogues: exact fp32 state + update gate, (n, oh, ow, C) contiguous; out = a C-channel slice
         assert gru_h.is_contiguous() and gru_z.is_contiguous() and gru_h.shape == gru_z.shape
@@ -298,6 +301,14 @@ def conv(x: Split, pk: Packed, *, relu: bool = False, res: Optional[Split] = Non
     if not res_:
         return None
     return res_[0] if len(res_) == 1 else res_
+
+
+def set_precision(mode: str) -> None:
+    """"bf16x3" (default, fp32-grade products: the mode every parity claim is made in), or the opt-in reduced modes
+    "bf16x2" (activations rounded to bf16, filters exact: 2 MMAs per product) and "bf16" (1 MMA).  Applies to every
+    later conv() launch; a captured graph keeps the mode it was captured in."""
+    global MMA_TERMS
+    MMA_TERMS = {"bf16x3": 3, "bf16x2": 2, "bf16": 1}[mode]
 
 
 def packed_dot(pred: nn.Conv2d, cout_pad: int) -> torch.Tensor:

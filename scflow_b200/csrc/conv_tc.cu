@@ -77,6 +77,7 @@ struct Params {
   int w_stages, w_stage_bytes, wb_bytes;       // ring of filter slabs: one entry = one (k-block, tap), hi + lo
   int w_resident;                              // the whole filter stays in shared memory (w_stages = all entries)
   int wide;                                    // epilogue pointers / pitches are 32-byte aligned: 256-bit accesses
+  int terms;                                   // bf16 MMAs per product: 3 (fp32-grade, default), 2 (activations as bf16), 1 (bf16)
   const float* dot_w;                          // [cout_pad][SCFLOW_CONV_DOT_PITCH]: projections of the output pixel
   float* dot_out;                              // [pixels][dot_slots][dot_pitch]
   int dot_n, dot_pitch, dot_slots;
@@ -566,6 +567,7 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
       const uint32_t idesc2 = make_idesc_bf16(BM, 2 * p.bn);
       const uint32_t smem0 = tc::smem_u32(smem);
       const bool fold = p.fold != 0;
+      const int terms = p.terms;
       int stage = 0; uint32_t phase = 0; uint32_t it = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
         const uint32_t buf = it & 1;
@@ -596,11 +598,16 @@ conv_tc_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Params
                   // adjacent in the stage = one 2 bn-row operand; columns [0,bn) get a_hi.b_hi, [bn,2bn)
                   // a_hi.b_lo, the epilogue adds the halves
                   mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc2, acc | (uint32_t)ks);
-                  mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, 1u);
-                } else {
+                  if (terms == 3) mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                } else if (terms == 3) {
                   mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);   // small terms first
                   mma_bf16_ss(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
                   mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                } else if (terms == 2) {                                                   // opt-in reduced modes
+                  mma_bf16_ss(d, dah + 2 * ks, dbl + 2 * ks, idesc, acc | (uint32_t)ks);
+                  mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                } else {
+                  mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
                 }
               }
             }
@@ -797,6 +804,7 @@ conv_patch_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Par
       const uint32_t a0 = tc::smem_u32(a_ring), w0 = tc::smem_u32(w_ring);
       const uint32_t sbo = (uint32_t)p.pitch * 128u;          // one output row of the tile = one swizzle atom
       const bool fold = p.fold != 0, resident = p.w_resident != 0;
+      const int terms = p.terms;
       const uint64_t lo_off = (uint64_t)(p.wb_bytes >> 4);    // B_lo behind B_hi, in descriptor address units
       int as = 0, ws = 0; uint32_t aph = 0, wph = 0, it = 0;
       for (int u = unit0; u < total; u += units_grid, ++it) {
@@ -829,16 +837,28 @@ conv_patch_kernel(const __grid_constant__ Maps maps, const __grid_constant__ Par
             for (int ks = 0; ks < 4; ++ks) {
               if (ks < nks) {
                 if (PAIR) {
-                  mma_bf16_ss_2cta(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
-                  mma_bf16_ss_2cta(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
-                  mma_bf16_ss_2cta(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                  if (terms == 3) {
+                    mma_bf16_ss_2cta(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
+                    mma_bf16_ss_2cta(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
+                    mma_bf16_ss_2cta(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                  } else if (terms == 2) {                                                 // opt-in reduced modes
+                    mma_bf16_ss_2cta(d, dah + 2 * ks, dbl + 2 * ks, idesc, acc | (uint32_t)ks);
+                    mma_bf16_ss_2cta(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                  } else {
+                    mma_bf16_ss_2cta(d, dah + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
+                  }
                 } else if (fold) {
                   mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc2, acc | (uint32_t)ks);   // [B_hi;B_lo]: 2 bn rows
-                  mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, 1u);
-                } else {
+                  if (terms == 3) mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                } else if (terms == 3) {
                   mma_bf16_ss(d, dal + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
                   mma_bf16_ss(d, dah + 2 * ks, dbl + 2 * ks, idesc, 1u);
                   mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                } else if (terms == 2) {
+                  mma_bf16_ss(d, dah + 2 * ks, dbl + 2 * ks, idesc, acc | (uint32_t)ks);
+                  mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, 1u);
+                } else {
+                  mma_bf16_ss(d, dah + 2 * ks, dbh + 2 * ks, idesc, acc | (uint32_t)ks);
                 }
               }
             }
@@ -1173,7 +1193,7 @@ static bool plan_patch(const scflow_conv_tc_desc* d, Params& p, int algo, bool* 
       p.TW = 8; p.TH = 16; p.NI = 1;
       p.tiles_x = p.OW / 8; p.tiles_y = p.OH / 16;
       p.m_tiles = tiles;
-      p.fold = (!pr && p.bn <= 128) ? 1 : 0;
+      p.fold = (!pr && p.bn <= 128 && p.terms != 1) ? 1 : 0;
       *smem_bytes = 1024 + (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.w_stages * p.w_stage_bytes + P_BAR_BYTES;
       return true;
     }
@@ -1339,6 +1359,8 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
   p.OW = (d->w + 2 * d->pad_w - d->kw) / d->stride + 1;
   if (p.OH <= 0 || p.OW <= 0) return SCFLOW_E_BAD_SHAPE;
   p.kh = d->kh; p.kw = d->kw; p.stride = d->stride; p.pad_y = d->pad_h; p.pad_x = d->pad_w;
+  if (d->mma_terms < 0 || d->mma_terms > 3) return SCFLOW_E_UNSUPPORTED;
+  p.terms = d->mma_terms == 0 ? 3 : d->mma_terms;
   p.cout_pad = cout_pad_of(d->cout, &p.bn, &p.n_tiles);
   if (d->bn > 0) {                             // caller-chosen tile width: must tile the pack
     if ((d->bn % 16) || d->bn > 256 || (p.cout_pad % d->bn)) return SCFLOW_E_BAD_SHAPE;
@@ -1392,7 +1414,7 @@ extern "C" int scflow_conv_tc_fwd(const scflow_conv_tc_desc* d, void* stream) {
       q.tiles_x = q.OW / q.TW; q.tiles_y = q.OH / q.TH;
       const int groups = (q.n + q.NI - 1) / q.NI;
       q.m_tiles = groups * q.tiles_x * q.tiles_y;
-      q.fold = q.bn <= 128 ? 1 : 0;
+      q.fold = (q.bn <= 128 && q.terms != 1) ? 1 : 0;
       q.a_bytes = BM * bk * 2;
       q.b_bytes = q.bn * bk * 2;
       q.stage_bytes = 2 * (q.a_bytes + q.b_bytes);

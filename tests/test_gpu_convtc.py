@@ -262,3 +262,27 @@ def test_head_predict_vs_fp64(ks, co, n, hw, cmid):
     assert _err(got, want) < 3e-5
     got2 = C.head_predict(C.to_split(x.to(DEV)), pk, pred)                   # cached projection vectors, fresh scratch
     assert _err(got2, want) < 3e-5
+
+
+@pytest.mark.parametrize("mode,tol", [("bf16x2", 3e-3), ("bf16", 6e-3)])
+def test_reduced_precision_modes_are_opt_in_and_bounded(mode, tol):
+    """scflow_conv_tc_desc.mma_terms: the default is three MMAs per product (2e-5); the opt-in modes drop the
+    activation's low part (bf16x2) or both low parts (bf16) and stay within the tolerance DESIGN 2 states for them.
+    Covers the pair, fold and plain issue paths (cout 256 / 64 / 192) and the per-tap kernel (1x1)."""
+    assert C.MMA_TERMS == 3
+    g = torch.Generator().manual_seed(5)
+    try:
+        for cin, cout, k in ((128, 256, 3), (64, 64, 3), (256, 192, 3), (128, 256, 1)):
+            x = torch.randn(2, 32, 32, cin, generator=g)
+            wt = torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5
+            b = torch.randn(cout, generator=g)
+            want = _ref(x, wt, b, 1, k // 2)
+            pk = C.pack_weights(wt.to(DEV), b.to(DEV), 1, (k // 2, k // 2))
+            xs = C.to_split(x.to(DEV))
+            C.set_precision("bf16x3")
+            e3 = _err(C.conv(xs, pk, want="f32")[..., :cout], want)
+            C.set_precision(mode)
+            er = _err(C.conv(xs, pk, want="f32")[..., :cout], want)
+            assert e3 < TOL and TOL < er < tol, (cin, cout, k, e3, er)
+    finally:
+        C.set_precision("bf16x3")

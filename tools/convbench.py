@@ -20,7 +20,9 @@ ap.add_argument("--once", action="store_true")
 ap.add_argument("--bn", type=int, default=0, help="output-channel tile width override (0: widest)")
 ap.add_argument("--algo", type=int, default=0, help="0 auto, 1 per-tap boxes, 2 patch, 3 patch on CTA pairs")
 ap.add_argument("--hw-scale", type=int, default=1, help="k: the same pixels as k x k larger images (cfg4 = 2), n / k^2 of them")
+ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "bf16x2", "bf16"])
 a = ap.parse_args()
+C.set_precision(a.precision)
 dev = "cuda"
 N = a.n
 PEAK = 1400.0
