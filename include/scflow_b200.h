@@ -433,6 +433,18 @@ int scflow_corr_pyramid_bwd(const float* grad_corr, const float* feat1, const fl
 int scflow_upsample_bwd(const float* grad_out, float* grad_in, int n, int c, int h, int w, int scale,
                         float mul, void* stream);
 
+/* get_pose_from_delta_pose (models/utils/pose.py:124-149, ortho6d rotation delta, depth_transform = 'exp') for the
+ * training path and its adjoint, one launch each (under autograd the same algebra is ~60 element-wise launches per
+ * iteration).  dR6 (n, 6), dt (n, 3), R_src (n, 3, 3) row-major, t_src (n, 3) -> R_dst = dR R_src, t_dst.
+ * Backward: grad_R (n, 3, 3) and / or grad_t (n, 3) (either may be NULL = zero) -> grad_dR6, grad_dt, and, where
+ * the pointers are not NULL, grad_R_src / grad_t_src (the shipped config detaches the pose: NULL).
+ * detach_depth_for_xy as the reference's flag (tz' does not carry the gradient of tx', ty'). */
+int scflow_pose_compose_fwd(const float* dR6, const float* dt, const float* R_src, const float* t_src, float* R_dst,
+                            float* t_dst, int n, float weight, void* stream);
+int scflow_pose_compose_bwd(const float* grad_R, const float* grad_t, const float* dR6, const float* dt,
+                            const float* R_src, const float* t_src, float* grad_dR6, float* grad_dt, float* grad_R_src,
+                            float* grad_t_src, int n, float weight, int detach_depth_for_xy, void* stream);
+
 /* Gradient of the pose-induced flow (scflow_pose_flow_fwd's flow_full, depth path) wrt the pose it
  * was rendered with: grad_pose (n, 12) = [dL/dR row-major | dL/dt], overwritten.  R, t are the
  * (n,3,3)/(n,3) pose of the forward call; depth/K/R0/t0 as in the forward. */

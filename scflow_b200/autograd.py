@@ -9,7 +9,7 @@ hand-written adjoint (scflow_b200/csrc/backward.cu):
                                            detached on the SCFlow path, scflow_decoder.py:193-194)
   upsample       scflow_decoder.py:223-228 one gather kernel
   pose_flow      pose.py:66-88             one per-crop reduction kernel (wrt R_k, t_k)
-  compose_pose   pose.py:124-169           a dozen 3x3 torch ops (differentiable as written)
+  compose_pose   pose.py:124-169           scflow_pose_compose_fwd / _bwd (one launch each)
 """
 from __future__ import annotations
 
@@ -148,10 +148,58 @@ def pose_flow(R, t, K, depth, R0, t0, scale=8, invalid_num=0.0):
     return PoseFlowFn.apply(R, t, K, depth, R0, t0, scale, invalid_num)
 
 
+class PoseComposeFn(torch.autograd.Function):
+    """get_pose_from_delta_pose (pose.py:124-149, ortho6d + 'exp'): scflow_pose_compose_fwd / _bwd, one launch each."""
+
+    @staticmethod
+    def forward(ctx, rotation_delta, translation_delta, rotation_src, translation_src, weight, detach_depth_for_xy):
+        lib = _lib.load()
+        r6, dt = _chk(rotation_delta, "rotation_delta"), _chk(translation_delta, "translation_delta")
+        Rs, ts = _chk(rotation_src, "rotation_src"), _chk(translation_src, "translation_src")
+        n = r6.shape[0]
+        if r6.shape != (n, 6) or dt.shape != (n, 3) or Rs.shape != (n, 3, 3) or ts.shape != (n, 3):
+            raise _lib.ScflowError("compose_pose: expected (n,6) ortho6d, (n,3), (n,3,3), (n,3)")
+        R, t = torch.empty_like(Rs), torch.empty_like(ts)
+        with _timed("scflow_pose_compose_fwd", 1, 4 * n * 33):
+            rc = lib.scflow_pose_compose_fwd(_ptr(r6), _ptr(dt), _ptr(Rs), _ptr(ts), _ptr(R), _ptr(t), n, float(weight),
+                                             _stream())
+        _lib.check(rc, "scflow_pose_compose_fwd")
+        ctx.save_for_backward(r6, dt, Rs, ts)
+        ctx.meta = (float(weight), bool(detach_depth_for_xy))
+        return R, t
+
+    @staticmethod
+    def backward(ctx, gR, gt):
+        r6, dt, Rs, ts = ctx.saved_tensors
+        weight, detach = ctx.meta
+        lib = _lib.load()
+        n = r6.shape[0]
+        if gR is None and gt is None:
+            return None, None, None, None, None, None
+        gR = None if gR is None else _chk(gR, "grad_R")
+        gt = None if gt is None else _chk(gt, "grad_t")
+        g6, gdt = torch.empty_like(r6), torch.empty_like(dt)
+        gRs = torch.empty_like(Rs) if ctx.needs_input_grad[2] else None
+        gts = torch.empty_like(ts) if ctx.needs_input_grad[3] else None
+        with _timed("scflow_pose_compose_bwd", 1, 4 * n * 54):
+            rc = lib.scflow_pose_compose_bwd(_ptr(gR), _ptr(gt), _ptr(r6), _ptr(dt), _ptr(Rs), _ptr(ts), _ptr(g6),
+                                             _ptr(gdt), _ptr(gRs), _ptr(gts), n, weight, int(detach), _stream())
+        _lib.check(rc, "scflow_pose_compose_bwd")
+        return g6, gdt, gRs, gts, None, None
+
+
 def compose_pose(rotation_delta, translation_delta, rotation_src, translation_src, weight=10.0,
                  detach_depth_for_xy=False):
-    """get_pose_from_delta_pose (pose.py:124-149, ortho6d + 'exp') with torch ops: N x 3 x 3 algebra,
-    differentiable as written.  Same formulas as the fused inference kernel (pose_flow.cu)."""
+    """get_pose_from_delta_pose (pose.py:124-149, ortho6d + 'exp') on the training path: one kernel forward, one
+    backward (`PoseComposeFn`)."""
+    return PoseComposeFn.apply(rotation_delta.float(), translation_delta.float(), rotation_src.float(),
+                               translation_src.float(), weight, detach_depth_for_xy)
+
+
+def compose_pose_torch(rotation_delta, translation_delta, rotation_src, translation_src, weight=10.0,
+                       detach_depth_for_xy=False):
+    """The same function with torch ops (differentiable as written): what `compose_pose` replaced; kept as the
+    tests' second implementation."""
     x_raw, y_raw = rotation_delta[:, 0:3], rotation_delta[:, 3:6]
     x = F.normalize(x_raw, p=2, dim=1)
     z = F.normalize(torch.cross(x, y_raw, dim=1), p=2, dim=1)

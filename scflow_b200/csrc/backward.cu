@@ -594,3 +594,129 @@ extern "C" int scflow_pose_flow_bwd(const float* grad_full, const float* depth, 
   bw::pose_flow_bwd_kernel<<<dim3(bx, n), 256, 0, st>>>(grad_full, depth, K, R0, t0, R, t, grad_pose, H, W);
   return check_launch();
 }
+
+// ---------------------------------------------------------------------------------------------
+// pose compose (get_pose_from_delta_pose, models/utils/pose.py:124-149, ortho6d + 'exp') forward and backward for the
+// training path: one thread per crop.  Under autograd the same algebra is ~20 element-wise launches forward and
+// ~40 backward per iteration; here it is one each.
+//   x = xr / |xr|, z = (x X yr) / |x X yr|, y = z X x, dR = [x y z] (columns), R' = dR R
+//   tz' = tz / exp(dz), tx' = tz'* (dx / w + tx / tz), ty' likewise  (tz'* = tz' detached if detach_depth_for_xy)
+namespace scflow {
+namespace bw {
+
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 cross3(V3 a, V3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+__device__ __forceinline__ float dot3(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ V3 add3(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ V3 scale3(V3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+// F.normalize(v, eps = 1e-12): v / max(|v|, eps)
+__device__ __forceinline__ V3 normalize3(V3 v, float* denom) {
+  const float d = fmaxf(sqrtf(dot3(v, v)), 1e-12f);
+  *denom = d;
+  return scale3(v, 1.0f / d);
+}
+// adjoint of u = v / max(|v|, eps)
+__device__ __forceinline__ V3 normalize3_bwd(V3 u, float denom, V3 gu) {
+  if (denom <= 1e-12f) return scale3(gu, 1.0f / denom);
+  return scale3(add3(gu, scale3(u, -dot3(u, gu))), 1.0f / denom);
+}
+
+__global__ void __launch_bounds__(128) pose_compose_fwd_kernel(const float* __restrict__ dR6, const float* __restrict__ dt,
+                                                               const float* __restrict__ Rs, const float* __restrict__ ts,
+                                                               float* __restrict__ Rd, float* __restrict__ td, int n,
+                                                               float weight) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* r6 = dR6 + 6 * i;
+  float dx, dz;
+  const V3 x = normalize3({r6[0], r6[1], r6[2]}, &dx);
+  const V3 yr = {r6[3], r6[4], r6[5]};
+  const V3 z = normalize3(cross3(x, yr), &dz);
+  const V3 y = cross3(z, x);
+  const float D[3][3] = {{x.x, y.x, z.x}, {x.y, y.y, z.y}, {x.z, y.z, z.z}};      // columns x, y, z
+  const float* R = Rs + 9 * i;
+  for (int a = 0; a < 3; ++a)
+    for (int b = 0; b < 3; ++b) Rd[9 * i + 3 * a + b] = D[a][0] * R[b] + D[a][1] * R[3 + b] + D[a][2] * R[6 + b];
+  const float tx = ts[3 * i], ty = ts[3 * i + 1], tz = ts[3 * i + 2];
+  const float vz = tz / expf(dt[3 * i + 2]);
+  td[3 * i] = vz * (dt[3 * i] / weight + tx / tz);
+  td[3 * i + 1] = vz * (dt[3 * i + 1] / weight + ty / tz);
+  td[3 * i + 2] = vz;
+}
+
+__global__ void __launch_bounds__(128) pose_compose_bwd_kernel(const float* __restrict__ gR, const float* __restrict__ gt,
+                                                               const float* __restrict__ dR6, const float* __restrict__ dt,
+                                                               const float* __restrict__ Rs, const float* __restrict__ ts,
+                                                               float* __restrict__ g6, float* __restrict__ gdt,
+                                                               float* __restrict__ gRs, float* __restrict__ gts, int n,
+                                                               float weight, int detach_depth_for_xy) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* r6 = dR6 + 6 * i;
+  float dnx, dnz;
+  const V3 x = normalize3({r6[0], r6[1], r6[2]}, &dnx);
+  const V3 yr = {r6[3], r6[4], r6[5]};
+  const V3 z = normalize3(cross3(x, yr), &dnz);
+  const V3 y = cross3(z, x);
+  const float* R = Rs + 9 * i;
+  float G[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+  if (gR) for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) G[a][b] = gR[9 * i + 3 * a + b];
+  // R' = D R:  dL/dD = G R^T,  dL/dR = D^T G
+  float gD[3][3];
+  for (int a = 0; a < 3; ++a)
+    for (int c = 0; c < 3; ++c) gD[a][c] = G[a][0] * R[3 * c] + G[a][1] * R[3 * c + 1] + G[a][2] * R[3 * c + 2];
+  if (gRs) {
+    const float D[3][3] = {{x.x, y.x, z.x}, {x.y, y.y, z.y}, {x.z, y.z, z.z}};
+    for (int c = 0; c < 3; ++c)
+      for (int b = 0; b < 3; ++b) gRs[9 * i + 3 * c + b] = D[0][c] * G[0][b] + D[1][c] * G[1][b] + D[2][c] * G[2][b];
+  }
+  const V3 gx0 = {gD[0][0], gD[1][0], gD[2][0]}, gy = {gD[0][1], gD[1][1], gD[2][1]}, gz0 = {gD[0][2], gD[1][2], gD[2][2]};
+  // y = z X x
+  const V3 gz = add3(gz0, cross3(x, gy));
+  V3 gx = add3(gx0, cross3(gy, z));
+  // z = normalize(zp), zp = x X yr
+  const V3 gzp = normalize3_bwd(z, dnz, gz);
+  gx = add3(gx, cross3(yr, gzp));
+  const V3 gyr = cross3(gzp, x);
+  const V3 gxr = normalize3_bwd(x, dnx, gx);
+  g6[6 * i] = gxr.x; g6[6 * i + 1] = gxr.y; g6[6 * i + 2] = gxr.z;
+  g6[6 * i + 3] = gyr.x; g6[6 * i + 4] = gyr.y; g6[6 * i + 5] = gyr.z;
+  // translation
+  const float tx = ts[3 * i], ty = ts[3 * i + 1], tz = ts[3 * i + 2];
+  const float e = 1.0f / expf(dt[3 * i + 2]);
+  const float vz = tz * e;
+  const float ax = dt[3 * i] / weight + tx / tz, ay = dt[3 * i + 1] / weight + ty / tz;
+  const float g0 = gt ? gt[3 * i] : 0.f, g1 = gt ? gt[3 * i + 1] : 0.f, g2 = gt ? gt[3 * i + 2] : 0.f;
+  const float gvz = g2 + (detach_depth_for_xy ? 0.f : g0 * ax + g1 * ay);
+  gdt[3 * i] = g0 * vz / weight;
+  gdt[3 * i + 1] = g1 * vz / weight;
+  gdt[3 * i + 2] = -vz * gvz;
+  if (gts) {
+    gts[3 * i] = g0 * vz / tz;
+    gts[3 * i + 1] = g1 * vz / tz;
+    gts[3 * i + 2] = gvz * e - vz * (g0 * tx + g1 * ty) / (tz * tz);
+  }
+}
+
+}  // namespace bw
+}  // namespace scflow
+
+extern "C" int scflow_pose_compose_fwd(const float* dR6, const float* dt, const float* R_src, const float* t_src,
+                                       float* R_dst, float* t_dst, int n, float weight, void* stream) {
+  if (!dR6 || !dt || !R_src || !t_src || !R_dst || !t_dst) return SCFLOW_E_NULL;
+  if (n <= 0 || weight == 0.0f) return SCFLOW_E_BAD_SHAPE;
+  scflow::bw::pose_compose_fwd_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(dR6, dt, R_src, t_src, R_dst, t_dst, n,
+                                                                                      weight);
+  return scflow::check_launch();
+}
+
+extern "C" int scflow_pose_compose_bwd(const float* grad_R, const float* grad_t, const float* dR6, const float* dt,
+                                       const float* R_src, const float* t_src, float* grad_dR6, float* grad_dt,
+                                       float* grad_R_src, float* grad_t_src, int n, float weight,
+                                       int detach_depth_for_xy, void* stream) {
+  if (!dR6 || !dt || !R_src || !t_src || !grad_dR6 || !grad_dt || (!grad_R && !grad_t)) return SCFLOW_E_NULL;
+  if (n <= 0 || weight == 0.0f) return SCFLOW_E_BAD_SHAPE;
+  scflow::bw::pose_compose_bwd_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      grad_R, grad_t, dR6, dt, R_src, t_src, grad_dR6, grad_dt, grad_R_src, grad_t_src, n, weight, detach_depth_for_xy);
+  return scflow::check_launch();
+}

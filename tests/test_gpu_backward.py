@@ -146,6 +146,36 @@ def test_pose_flow_backward_vs_oracle():
     assert rel(td.grad, t.grad) < 1e-4
 
 
+@pytest.mark.parametrize("detach", [False, True])
+def test_pose_compose_kernels_all_gradients_vs_fp64(detach):
+    """scflow_pose_compose_fwd / _bwd against autograd through the same algebra in fp64 (the torch form the kernels
+    replaced), gradients wrt all four inputs, both detach_depth_for_xy settings, one-sided output gradients."""
+    rs = np.random.RandomState(41)
+    n = 37
+    cr = syn.make_crops(4, 64, seed=42)
+    R0 = cr["R0"].repeat(10, 1, 1)[:n]; t0 = cr["t0"].repeat(10, 1)[:n] * torch.from_numpy(1 + 0.1 * rs.rand(n, 1)).float()
+    dR6 = torch.from_numpy((np.array([[1, 0, 0, 0, 1, 0]]) + 0.3 * rs.standard_normal((n, 6))).astype(np.float32))
+    dt = torch.from_numpy((0.2 * rs.standard_normal((n, 3))).astype(np.float32))
+    gR = torch.from_numpy(rs.standard_normal((n, 3, 3)).astype(np.float32))
+    gt = torch.from_numpy(rs.standard_normal((n, 3)).astype(np.float32))
+    ins64 = [v.double().requires_grad_(True) for v in (dR6, dt, R0, t0)]
+    R, t = ag.compose_pose_torch(*ins64, detach_depth_for_xy=detach)
+    torch.autograd.backward([R, t], [gR.double(), gt.double()])
+    insd = [v.to(DEV).requires_grad_(True) for v in (dR6, dt, R0, t0)]
+    Rd, td = ag.compose_pose(*insd, detach_depth_for_xy=detach)
+    assert rel(Rd, R) < 1e-6 and rel(td, t) < 1e-6
+    torch.autograd.backward([Rd, td], [gR.to(DEV), gt.to(DEV)])
+    for a, b in zip(insd, ins64):
+        assert rel(a.grad, b.grad) < 2e-6
+    only = [v.to(DEV).requires_grad_(True) for v in (dR6, dt)]
+    Rd, td = ag.compose_pose(only[0], only[1], R0.to(DEV), t0.to(DEV), detach_depth_for_xy=detach)
+    (td * gt.to(DEV)).sum().backward()                                  # no gradient reaches R'
+    ref = [v.double().requires_grad_(True) for v in (dR6, dt)]
+    _, t2 = ag.compose_pose_torch(ref[0], ref[1], R0.double(), t0.double(), detach_depth_for_xy=detach)
+    (t2 * gt.double()).sum().backward()
+    assert float(only[0].grad.abs().max()) == 0 and rel(only[1].grad, ref[1].grad) < 2e-6
+
+
 def test_compose_pose_matches_oracle_and_kernel():
     rs = np.random.RandomState(31)
     cr = syn.make_crops(4, 64, seed=32)
