@@ -433,6 +433,17 @@ int scflow_corr_pyramid_bwd(const float* grad_corr, const float* feat1, const fl
 int scflow_upsample_bwd(const float* grad_out, float* grad_in, int n, int c, int h, int w, int scale,
                         float mul, void* stream);
 
+/* ConvGRU gate arithmetic of the training path (models/decoder/raft_decoder.py:245-252) around the gate
+ * convolutions (which stay nn.Conv2d under autograd): rh = sigmoid(a_r) h and h' = (1 - z) h + z q with
+ * z = sigmoid(a_z), q = tanh(a_q), forward and adjoint, one launch each.  Contiguous fp32 tensors of `total`
+ * elements. */
+int scflow_gru_reset_fwd(const float* a_r, const float* h, float* rh, long long total, void* stream);
+int scflow_gru_reset_bwd(const float* grad_rh, const float* a_r, const float* h, float* grad_a_r, float* grad_h,
+                         long long total, void* stream);
+int scflow_gru_blend_fwd(const float* a_z, const float* a_q, const float* h, float* h_new, long long total, void* stream);
+int scflow_gru_blend_bwd(const float* grad_h_new, const float* a_z, const float* a_q, const float* h, float* grad_a_z,
+                         float* grad_a_q, float* grad_h, long long total, void* stream);
+
 /* get_pose_from_delta_pose (models/utils/pose.py:124-149, ortho6d rotation delta, depth_transform = 'exp') for the
  * training path and its adjoint, one launch each (under autograd the same algebra is ~60 element-wise launches per
  * iteration).  dR6 (n, 6), dt (n, 3), R_src (n, 3, 3) row-major, t_src (n, 3) -> R_dst = dR R_src, t_dst.

@@ -59,6 +59,10 @@ SIGNATURES = {
     "scflow_corr_fold_bwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, _P]),
     "scflow_corr_pyramid_bwd": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "scflow_upsample_bwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, c_float, _P]),
+    "scflow_gru_reset_fwd": (c_int, [_P, _P, _P, ctypes.c_longlong, _P]),
+    "scflow_gru_reset_bwd": (c_int, [_P, _P, _P, _P, _P, ctypes.c_longlong, _P]),
+    "scflow_gru_blend_fwd": (c_int, [_P, _P, _P, _P, ctypes.c_longlong, _P]),
+    "scflow_gru_blend_bwd": (c_int, [_P, _P, _P, _P, _P, _P, _P, ctypes.c_longlong, _P]),
     "scflow_pose_compose_fwd": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_float, _P]),
     "scflow_pose_compose_bwd": (c_int, [_P] * 10 + [c_int, c_float, c_int, _P]),
     "scflow_pose_flow_bwd": (c_int, [_P] * 8 + [c_int, c_int, c_int, _P]),

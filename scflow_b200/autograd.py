@@ -148,6 +148,71 @@ def pose_flow(R, t, K, depth, R0, t0, scale=8, invalid_num=0.0):
     return PoseFlowFn.apply(R, t, K, depth, R0, t0, scale, invalid_num)
 
 
+class GruResetFn(torch.autograd.Function):
+    """rh = sigmoid(a_r) * h (raft_decoder.py:249-250): scflow_gru_reset_fwd / _bwd."""
+
+    @staticmethod
+    def forward(ctx, a_r, h):
+        lib = _lib.load()
+        a, hh = _chk(a_r, "a_r"), _chk(h, "h")
+        if a.shape != hh.shape:
+            raise _lib.ScflowError("gru_reset: a_r and h differ in shape")
+        out = torch.empty_like(hh)
+        with _timed("scflow_gru_reset_fwd", 1, 12 * hh.numel()):
+            rc = lib.scflow_gru_reset_fwd(_ptr(a), _ptr(hh), _ptr(out), hh.numel(), _stream())
+        _lib.check(rc, "scflow_gru_reset_fwd")
+        ctx.save_for_backward(a, hh)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        a, hh = ctx.saved_tensors
+        lib = _lib.load()
+        g = _chk(g, "grad_rh")
+        ga, gh = torch.empty_like(a), torch.empty_like(hh)
+        with _timed("scflow_gru_reset_bwd", 1, 20 * hh.numel()):
+            rc = lib.scflow_gru_reset_bwd(_ptr(g), _ptr(a), _ptr(hh), _ptr(ga), _ptr(gh), hh.numel(), _stream())
+        _lib.check(rc, "scflow_gru_reset_bwd")
+        return ga, gh
+
+
+class GruBlendFn(torch.autograd.Function):
+    """h' = (1 - sigmoid(a_z)) h + sigmoid(a_z) tanh(a_q) (raft_decoder.py:248-252): scflow_gru_blend_fwd / _bwd."""
+
+    @staticmethod
+    def forward(ctx, a_z, a_q, h):
+        lib = _lib.load()
+        az, aq, hh = _chk(a_z, "a_z"), _chk(a_q, "a_q"), _chk(h, "h")
+        if az.shape != hh.shape or aq.shape != hh.shape:
+            raise _lib.ScflowError("gru_blend: a_z, a_q and h differ in shape")
+        out = torch.empty_like(hh)
+        with _timed("scflow_gru_blend_fwd", 1, 16 * hh.numel()):
+            rc = lib.scflow_gru_blend_fwd(_ptr(az), _ptr(aq), _ptr(hh), _ptr(out), hh.numel(), _stream())
+        _lib.check(rc, "scflow_gru_blend_fwd")
+        ctx.save_for_backward(az, aq, hh)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        az, aq, hh = ctx.saved_tensors
+        lib = _lib.load()
+        g = _chk(g, "grad_h")
+        gz, gq, gh = torch.empty_like(az), torch.empty_like(aq), torch.empty_like(hh)
+        with _timed("scflow_gru_blend_bwd", 1, 28 * hh.numel()):
+            rc = lib.scflow_gru_blend_bwd(_ptr(g), _ptr(az), _ptr(aq), _ptr(hh), _ptr(gz), _ptr(gq), _ptr(gh),
+                                          hh.numel(), _stream())
+        _lib.check(rc, "scflow_gru_blend_bwd")
+        return gz, gq, gh
+
+
+def gru_reset(a_r, h):
+    return GruResetFn.apply(a_r, h)
+
+
+def gru_blend(a_z, a_q, h):
+    return GruBlendFn.apply(a_z, a_q, h)
+
+
 class PoseComposeFn(torch.autograd.Function):
     """get_pose_from_delta_pose (pose.py:124-149, ortho6d + 'exp'): scflow_pose_compose_fwd / _bwd, one launch each."""
 

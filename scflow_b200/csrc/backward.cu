@@ -720,3 +720,79 @@ extern "C" int scflow_pose_compose_bwd(const float* grad_R, const float* grad_t,
       grad_R, grad_t, dR6, dt, R_src, t_src, grad_dR6, grad_dt, grad_R_src, grad_t_src, n, weight, detach_depth_for_xy);
   return scflow::check_launch();
 }
+
+// ---------------------------------------------------------------------------------------------
+// ConvGRU gate arithmetic of the training path (models/decoder/raft_decoder.py:245-252) around the three gate
+// convolutions, forward and adjoint, one launch each instead of the element-wise autograd chain (sigmoid, mul, tanh,
+// 1 - z, mul, mul, add and their ~14 backward launches per pass):
+//   reset:  rh = sigmoid(a_r) * h
+//   blend:  h' = (1 - z) h + z q,  z = sigmoid(a_z), q = tanh(a_q)
+// Contiguous fp32 tensors of one shape; four elements per thread where the count allows.
+namespace scflow {
+namespace bw {
+
+__device__ __forceinline__ float sigmoidf_(float a) { return 1.0f / (1.0f + expf(-a)); }
+
+template <int MODE>   // 0 reset fwd, 1 reset bwd, 2 blend fwd, 3 blend bwd
+__global__ void __launch_bounds__(256) gru_gates_kernel(const float* __restrict__ g, const float* __restrict__ a0,
+                                                        const float* __restrict__ a1, const float* __restrict__ h,
+                                                        float* __restrict__ o0, float* __restrict__ o1,
+                                                        float* __restrict__ o2, long long total) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const float hv = h[i];
+    if (MODE == 0) {
+      o0[i] = sigmoidf_(a0[i]) * hv;
+    } else if (MODE == 1) {
+      const float r = sigmoidf_(a0[i]), gv = g[i];
+      o0[i] = gv * hv * r * (1.0f - r);          // d a_r
+      o1[i] = gv * r;                            // d h
+    } else if (MODE == 2) {
+      const float z = sigmoidf_(a0[i]), q = tanhf(a1[i]);
+      o0[i] = (1.0f - z) * hv + z * q;
+    } else {
+      const float z = sigmoidf_(a0[i]), q = tanhf(a1[i]), gv = g[i];
+      o0[i] = gv * (q - hv) * z * (1.0f - z);    // d a_z
+      o1[i] = gv * z * (1.0f - q * q);           // d a_q
+      o2[i] = gv * (1.0f - z);                   // d h
+    }
+  }
+}
+
+}  // namespace bw
+}  // namespace scflow
+
+static int gru_gates_launch(int mode, const float* g, const float* a0, const float* a1, const float* h, float* o0,
+                            float* o1, float* o2, long long total, void* stream) {
+  using namespace scflow::bw;
+  if (total <= 0) return SCFLOW_E_BAD_SHAPE;
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148LL * 16) blocks = 148LL * 16;
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (mode) {
+    case 0: gru_gates_kernel<0><<<(unsigned)blocks, 256, 0, st>>>(g, a0, a1, h, o0, o1, o2, total); break;
+    case 1: gru_gates_kernel<1><<<(unsigned)blocks, 256, 0, st>>>(g, a0, a1, h, o0, o1, o2, total); break;
+    case 2: gru_gates_kernel<2><<<(unsigned)blocks, 256, 0, st>>>(g, a0, a1, h, o0, o1, o2, total); break;
+    default: gru_gates_kernel<3><<<(unsigned)blocks, 256, 0, st>>>(g, a0, a1, h, o0, o1, o2, total); break;
+  }
+  return scflow::check_launch();
+}
+
+extern "C" int scflow_gru_reset_fwd(const float* a_r, const float* h, float* rh, long long total, void* stream) {
+  if (!a_r || !h || !rh) return SCFLOW_E_NULL;
+  return gru_gates_launch(0, nullptr, a_r, nullptr, h, rh, nullptr, nullptr, total, stream);
+}
+extern "C" int scflow_gru_reset_bwd(const float* grad_rh, const float* a_r, const float* h, float* grad_a_r, float* grad_h,
+                                    long long total, void* stream) {
+  if (!grad_rh || !a_r || !h || !grad_a_r || !grad_h) return SCFLOW_E_NULL;
+  return gru_gates_launch(1, grad_rh, a_r, nullptr, h, grad_a_r, grad_h, nullptr, total, stream);
+}
+extern "C" int scflow_gru_blend_fwd(const float* a_z, const float* a_q, const float* h, float* h_new, long long total,
+                                    void* stream) {
+  if (!a_z || !a_q || !h || !h_new) return SCFLOW_E_NULL;
+  return gru_gates_launch(2, nullptr, a_z, a_q, h, h_new, nullptr, nullptr, total, stream);
+}
+extern "C" int scflow_gru_blend_bwd(const float* grad_h_new, const float* a_z, const float* a_q, const float* h,
+                                    float* grad_a_z, float* grad_a_q, float* grad_h, long long total, void* stream) {
+  if (!grad_h_new || !a_z || !a_q || !h || !grad_a_z || !grad_a_q || !grad_h) return SCFLOW_E_NULL;
+  return gru_gates_launch(3, grad_h_new, a_z, a_q, h, grad_a_z, grad_a_q, grad_h, total, stream);
+}

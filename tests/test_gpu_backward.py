@@ -176,6 +176,36 @@ def test_pose_compose_kernels_all_gradients_vs_fp64(detach):
     assert float(only[0].grad.abs().max()) == 0 and rel(only[1].grad, ref[1].grad) < 2e-6
 
 
+def test_convgru_training_path_vs_fp64_autograd():
+    """ConvGRU under autograd (raft_decoder.py:235-253): cuDNN gate convolutions + the fused gate kernels
+    (scflow_gru_reset / _blend fwd + bwd) against the plain torch chain in fp64: output and every gradient."""
+    import copy
+    g = torch.Generator().manual_seed(51)
+    gru = sb.ConvGRU(128, 256, "SeqConv")
+    ref = copy.deepcopy(gru).double()
+    h = torch.randn(3, 128, 16, 24, generator=g) * 0.5
+    x = torch.randn(3, 256, 16, 24, generator=g) * 0.5
+    go = torch.randn(3, 128, 16, 24, generator=g)
+    hr, xr = h.double().requires_grad_(True), x.double().requires_grad_(True)
+    y = hr
+    for cz, cr, cq in zip(ref.conv_z, ref.conv_r, ref.conv_q):
+        hx = torch.cat([y, xr], 1)
+        z, r = torch.sigmoid(cz.conv(hx)), torch.sigmoid(cr.conv(hx))
+        q = torch.tanh(cq.conv(torch.cat([r * y, xr], 1)))
+        y = (1 - z) * y + z * q
+    y.backward(go.double())
+    gru = gru.to(DEV)
+    hd, xd = h.to(DEV).requires_grad_(True), x.to(DEV).requires_grad_(True)
+    ops.STATS.reset()
+    yd = gru(hd, xd)
+    assert ops.STATS.count == 4                      # reset + blend, two passes
+    yd.backward(go.to(DEV))
+    assert rel(yd, y) < 2e-5
+    assert rel(hd.grad, hr.grad) < 2e-5 and rel(xd.grad, xr.grad) < 2e-5
+    for (k, p), (_, pr) in zip(gru.named_parameters(), ref.named_parameters()):
+        assert rel(p.grad, pr.grad) < 5e-5, k
+
+
 def test_compose_pose_matches_oracle_and_kernel():
     rs = np.random.RandomState(31)
     cr = syn.make_crops(4, 64, seed=32)
