@@ -814,6 +814,7 @@ def main():
     ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "bf16x2", "bf16"],
                     help="bf16x3 = the refiner's parity mode (default); bf16x2 / bf16 = the opt-in reduced modes, an EXTRA "
                          "line with its own deviation, never the headline")
+    ap.add_argument("--no-gru-pre", action="store_true", help="A/B: ConvGRU convolutions over all 384 input channels")
     ap.add_argument("--no-fork", action="store_true", help="A/B: the up-sampling branch on the compute stream")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--image", type=int, default=256, help="crop side (256 = configs[1]; 512 = configs[3])")
@@ -824,6 +825,9 @@ def main():
     if args.no_fork:
         import scflow_b200.decoder as _dec
         _dec.FORK_UPSAMPLE = False
+    if args.no_gru_pre:
+        import scflow_b200.decoder as _dec
+        _dec.GRU_PRECOMPUTE = False
     if args.precision != "bf16x3":
         import scflow_b200.convtc as _C
         _C.set_precision(args.precision)

@@ -316,8 +316,8 @@ typedef struct scflow_conv_tc_desc {
   int bn;
   /* epilogue: SCFLOW_EPI_PLAIN, or the two ConvGRU epilogues (models/decoder/raft_decoder.py:245-252) over
    * gru_h (n, OH, OW, gru_c) exact fp32 hidden state and gru_z (same shape) update gate:
-   *   GRU_ZR    cout = 2 gru_c = [z | r] pre-activations: z = sigmoid(.) -> gru_z; r = sigmoid(.),
-   *             r * gru_h -> out_split (gru_c channels)
+   *   GRU_ZR    cout = 2 gru_c = [z | r] pre-activations (+ res_f32, 2 gru_c channels, if given): z = sigmoid(.)
+   *             -> gru_z; r = sigmoid(.), r * gru_h -> out_split (gru_c channels)
    *   GRU_GATE  cout = gru_c, res_f32 = the x-part of the q convolution: q = tanh(acc + res + bias);
    *             gru_h = (1 - z) gru_h + z q in place, and as split planes -> out_split */
   int epi, gru_c;

@@ -420,10 +420,17 @@ __device__ __forceinline__ void epilogue_gru(const Params& p, const Tile& tl, ui
         const float* hp = p.gru_h + pix * p.gru_c + c0;
 #pragma unroll
         for (int k = 0; k < 4; ++k) { ld8(zp + 8 * k, ga + 8 * k, wide); ld8_rw(hp + 8 * k, gb + 8 * k, wide); }
-      } else if (!zhalf) {
-        const float* hp = p.gru_h + pix * p.gru_c + (c0 - p.gru_c);
+      } else {
+        if (p.res_f32) {                             // iteration-invariant part of the pre-activation (see below)
+          const float* rp = p.res_f32 + pix * p.resf_pitch + c0;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) ld8(hp + 8 * k, gb + 8 * k, wide);
+          for (int k = 0; k < 4; ++k) ld8(rp + 8 * k, ga + 8 * k, wide);
+        }
+        if (!zhalf) {
+          const float* hp = p.gru_h + pix * p.gru_c + (c0 - p.gru_c);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) ld8(hp + 8 * k, gb + 8 * k, wide);
+        }
       }
     };
     if (live && !fold) load_operands();
@@ -451,7 +458,13 @@ __device__ __forceinline__ void epilogue_gru(const Params& p, const Tile& tl, ui
     }
     if (!gate) {
       // raft_decoder.py:247-250, first half: channels [0,C) z = sigmoid(.) -> gru_z (fp32);
-      // channels [C,2C) r = sigmoid(.), r.h -> split planes (the operand of the q convolution)
+      // channels [C,2C) r = sigmoid(.), r.h -> split planes (the operand of the q convolution).
+      // res_f32 (2C channels): a part of the pre-activation computed elsewhere -- the context features are the same
+      // in all iterations, their share of the convolution (and the bias) is computed once per forward
+      if (p.res_f32) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += ga[i];
+      }
       if (zhalf) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = sigmoidf_(v[i]);

@@ -27,6 +27,7 @@ from .modules import (ConvGRU, ConvModule, CorrelationPyramid, CorrLookup, Motio
 from .registry import MODELS, register
 
 
+GRU_PRECOMPUTE = True         # the context features' share of the ConvGRU gate convolutions once per forward (gru_tc.precompute)
 FORK_UPSAMPLE = True          # the up-sampling branch of the inference loop on a side stream (see _forward_inference)
 _SIDE = {}
 
@@ -130,10 +131,12 @@ class SCFlowDecoder(nn.Module):
         xh, motion = S.slice(0, cx + mo + hc), S.slice(cx, mo)
         pose_in = S.slice(cx + mo, hc + c_df + c_m)
         scratch = gru_tc.Scratch(n_, hh, ww, hc, dev)
+        # the context features' share of the gate convolutions is the same in all iterations: once, here
+        gru_pre = gru_tc.precompute(self.gru, S.slice(0, cx)) if GRU_PRECOMPUTE and cx % 64 == 0 and hc % 64 == 0 else None
         for _ in range(self.iters):
             corr = self.corr_lookup.forward_split(corr_pyramid, flow)
             self.encoder.features_into(corr, flow, motion)
-            gru_tc.update_inplace(self.gru, xh, h_state, scratch)
+            gru_tc.update_inplace(self.gru, xh, h_state, scratch, pre=gru_pre)
             delta_flow_pred = self.flow_pred.forward_split(h_split)
             mask = torch.sigmoid(self.mask_pred.forward_split(h_split))
             d0 = dfe[0].forward_small_cin_split(delta_flow_pred)       # 7x7 on 2 channels: FMA kernel, split planes out

@@ -484,6 +484,39 @@ def test_convgru_tcgen05_vs_oracle(n, h, w):
     assert torch.equal(again, got)
 
 
+def test_convgru_context_precompute_equals_full_convolution():
+    """gru_tc.precompute: the context channels' share of the gate pre-activations (the same in every iteration) is
+    convolved once and added in the gate epilogues; the recurrent convolutions then cover [motion | h] only.  Same
+    result as the convolution over all 384 channels (fp32 accumulation split in two: 2e-5), over two successive updates, and
+    against the oracle."""
+    from scflow_b200 import gru_tc, convtc as C
+    sd = _gru_sd(23)
+    mod = sb.ConvGRU(128, 256)
+    mod.load_state_dict(sd)
+    mod.to(DEV)
+    rs = np.random.RandomState(24)
+    n, h, w = 3, 32, 32
+    hh = torch.from_numpy(np.tanh(rs.standard_normal((n, 128, h, w))).astype(np.float32))
+    xx = torch.from_numpy(rs.standard_normal((n, 256, h, w)).astype(np.float32))
+    outs = []
+    for use_pre in (False, True):
+        h_state = hh.to(DEV).permute(0, 2, 3, 1).contiguous().clone()
+        xh = C.alloc_split(n, h, w, 384, DEV)
+        C.to_split(xx.to(DEV).permute(0, 2, 3, 1), out=xh.slice(0, 256))
+        C.to_split(h_state, out=xh.slice(256, 128))
+        pre = gru_tc.precompute(mod, xh.slice(0, 128)) if use_pre else None
+        for p_ in (0, 1):                                   # filter packs are cached: build them before counting
+            gru_tc.packs_split(mod, p_, 128) if use_pre else gru_tc.packs(mod, p_)
+        ops.STATS.reset()
+        for _ in range(2):
+            gru_tc.update_inplace(mod, xh, h_state, pre=pre)
+        assert ops.STATS.count == 8
+        outs.append((h_state.clone(), xh.slice(256, 128).float().clone()))
+    assert rel(outs[1][0], outs[0][0]) < 2e-5 and rel(outs[1][1], outs[0][1]) < 2e-5
+    want = O.conv_gru(O.conv_gru(hh, xx, sd), xx, sd)
+    assert rel(outs[1][0].permute(0, 3, 1, 2), want) < 5e-5
+
+
 def test_convgru_weight_cache_tracks_parameter_updates():
     from scflow_b200 import gru_tc
     mod = sb.ConvGRU(128, 256).to(DEV)
