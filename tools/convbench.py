@@ -57,6 +57,8 @@ SHAPES = [
     ("head 3x3 64->32 @32", 32, 32, 64, 32, 3, 3, 1, 1, 1, "split", 8),
     ("pose 3x3/2 224->128 @32->16", 32, 32, 224, 128, 3, 3, 2, 1, 1, "f32", 8),
     ("pose 3x3/2 128->128 @16->8", 16, 16, 128, 128, 3, 3, 2, 1, 1, "f32", 8),
+    ("GRU zr epilogue 1x5 256->256 @32 (context precomputed)", 32, 32, 256, 256, 1, 5, 1, 0, 2, "gru_zr", 16),
+    ("GRU gate epilogue 1x5 128+128->128 @32 (context precomputed)", 32, 32, 256, 128, 1, 5, 1, 0, 2, "gru_gate", 16),
     ("GRU zr epilogue 1x5 384->256 @32", 32, 32, 384, 256, 1, 5, 1, 0, 2, "gru_zr", 16),
     ("GRU gate epilogue 1x5 128+256->128 @32", 32, 32, 384, 128, 1, 5, 1, 0, 2, "gru_gate", 16),
 ]

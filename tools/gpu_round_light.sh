@@ -10,7 +10,7 @@ timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/$
 echo "bench reference rc=$?"
 timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err
 echo "bench rc=$?"; cut -c1-300 gpurun_out/${TAG}_bench.json
-timeout 600 python bench.py --image 512 --batch 16 --steps 5 --no-cpu-baseline > gpurun_out/${TAG}_bench_cfg4.json 2> gpurun_out/${TAG}_bench_cfg4.err
+timeout 600 python bench.py --image 512 --batch 16 --steps 5 > gpurun_out/${TAG}_bench_cfg4.json 2> gpurun_out/${TAG}_bench_cfg4.err
 echo "bench cfg4 rc=$?"
 timeout 600 python bench.py --train --steps 5 > gpurun_out/${TAG}_bench_train.json 2> gpurun_out/${TAG}_bench_train.err
 echo "bench train rc=$?"
