@@ -45,6 +45,14 @@ def test_null_and_shape_rejected_without_gpu(lib):
     assert lib.scflow_nhwc_to_nchw(None, None, 1, 16, 64, 1, None) == -4
     assert lib.scflow_corr_pyramid_fwd(None, None, None, 4, 1, 256, 32, 32, 1, None, 0, None) == -4
     assert lib.scflow_upsample_fwd(None, None, None, 1, 1, 4, 4, 8, 1.0, None) == -4
+    # entry points added in round 2
+    assert lib.scflow_corr_pyramid_bwd(None, None, None, None, None, 1, 256, 32, 32, 1, None) == -4
+    assert lib.scflow_tap_sum_fwd(None, 4, 20, None, None, 1, 32, 32, 3, 2, None) == -4
+    assert lib.scflow_pose_compose_fwd(None, None, None, None, None, None, 4, 10.0, None) == -4
+    assert lib.scflow_pose_compose_bwd(*([None] * 10), 4, 10.0, 0, None) == -4
+    assert lib.scflow_gru_reset_fwd(None, None, None, 16, None) == -4
+    assert lib.scflow_gru_blend_bwd(*([None] * 7), 16, None) == -4
+    assert lib.scflow_expand_taps_fwd(None, None, 1, 2, 7, 32, 32, None) == -4
 
 
 def test_decoder_state_dict_matches_reference(golden_dir):
