@@ -18,7 +18,7 @@ done <<'LIST'
 3x3/1 96->96 @64x64|128|enc 3x3 96->96 @64
 3x3/1 128->256 @32x32|64|head 3x3 128->256 @32 + 3x3 ->2
 3x3/1 256->192 @32x32|64|mot 3x3 256->192 @32
-1x5/1 384->256 @32x32|64|GRU zr epilogue 1x5 384->256 @32
-5x1/1 384->256 @32x32|64|gru 5x1 384->256 @32
+1x5/1 256->256 @32x32|64|GRU zr epilogue 1x5 256->256 @32
+1x5/1 256->128 @32x32|64|GRU gate epilogue 1x5 128+128->128 @32
 LIST
 python tools/conv_traffic_json.py $TAG
