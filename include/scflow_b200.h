@@ -93,7 +93,8 @@ int scflow_add_error_fwd(const float* verts, const int* voff, int vmax, const lo
  *     replaces torch.matmul (:48-50), the /sqrt(C) pass (:51-52) and 3x nn.AvgPool2d (:54-56).
  * feat1, feat2: (n, c, h, w).  levels[l]: (n*h*w, 1, h>>l, w>>l), l < num_levels (host array of
  * device pointers).  corr[n*P+q][t] = sum_c feat1[n,c,q] feat2[n,c,t] / sqrt(c).
- * TF32 path needs c % 32 == 0, h % 8 == 0, w % 32 == 0, (h*w) % 128 == 0, num_levels <= 4.
+ * The tcgen05 TF32 kernel needs c % 32 == 0, h % 8 == 0, w % 32 == 0, (h*w) % 128 == 0; a SCFLOW_PREC_TF32 request on
+ * any other shape runs the fp32 FMA kernel (a stricter result, not a refusal).  num_levels <= 4.
  * ------------------------------------------------------------------------------------------- */
 size_t scflow_corr_pyramid_workspace_bytes(int n, int c, int h, int w, int precision);
 int scflow_corr_pyramid_fwd(const float* feat1, const float* feat2, float* const* levels,

@@ -423,6 +423,11 @@ extern "C" int scflow_corr_pyramid_fwd(const float* feat1, const float* feat2, f
     if (!levels[l]) return SCFLOW_E_NULL;
   if (n <= 0 || c <= 0 || h <= 0 || w <= 0) return SCFLOW_E_BAD_SHAPE;
   if (precision == SCFLOW_PREC_FP32) return corr_fp32(feat1, feat2, levels, num_levels, n, c, h, w, (cudaStream_t)stream);
-  if (precision == SCFLOW_PREC_TF32) return corr_tf32(feat1, feat2, levels, num_levels, n, c, h, w, (cudaStream_t)stream);
+  if (precision == SCFLOW_PREC_TF32) {
+    // shapes outside the tcgen05 tiling (w % 32, h % 8, c % 32, h*w % 128) take the fp32 FMA kernel: a stricter
+    // result than the one asked for, never a refusal (the same rule as scflow_corr_pyramid_bwd)
+    const int rc = corr_tf32(feat1, feat2, levels, num_levels, n, c, h, w, (cudaStream_t)stream);
+    return rc == SCFLOW_E_BAD_SHAPE ? corr_fp32(feat1, feat2, levels, num_levels, n, c, h, w, (cudaStream_t)stream) : rc;
+  }
   return SCFLOW_E_UNSUPPORTED;
 }
